@@ -1,0 +1,57 @@
+"""The CPU oracle (oracle/) against the reference-generated golden vectors: this is what pins it."""
+import numpy as np
+import pytest
+
+from oracle import ccsd_oracle as oc
+from oracle import triples_oracle as ot
+
+TOL = 1e-12
+
+
+@pytest.mark.parametrize("tag", ["sym", "gen"])
+def test_builders_and_residuals(golden, tag):
+    g = golden
+    blk = oc.Blocks(g.blocks)
+    t1, t2 = g[tag + "_t1"], g[tag + "_t2"]
+    r1, r2, im = oc.residuals(g.F, blk, t1, t2, want_intermediates=True)
+    for k in ("Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij"):
+        assert np.abs(im[k] - g[tag + "_" + k]).max() < TOL, k
+    assert np.abs(r1 - g[tag + "_r1"]).max() < TOL
+    assert np.abs(r2 - g[tag + "_r2"]).max() < TOL
+    assert np.abs(oc.tau(t1, t2, 1.0, 0.5) - g[tag + "_tau_1_h"]).max() < 1e-15
+    assert abs(oc.cc_energy(g.F, blk, t1, t2) - float(g[tag + "_energy"])) < TOL
+
+
+@pytest.mark.parametrize("tag", ["sym", "gen"])
+def test_triples_on_test_amplitudes(golden, tag):
+    g = golden
+    t1, t2 = g[tag + "_t1"], g[tag + "_t2"]
+    ref = float(g[tag + "_et_tjl"])
+    assert abs(ot.t_tjl(g.F, g.blocks, t1, t2) - ref) < TOL
+    if g.nv <= 13:
+        assert abs(ot.t_vikings(g.F, g.blocks, t1, t2) - float(g[tag + "_et_vikings"])) < TOL
+
+
+def test_solve_cc_matches_reference_iterations(golden):
+    g = golden
+    log = []
+    ecc, t1, t2, niter = oc.solve_cc(g.F, g.blocks, 1e-12, 1e-12, maxiter=100, log=log)
+    ref_log = g["solve_iter_log"]
+    assert niter == ref_log.shape[0]
+    assert abs(ecc - float(g["solve_eccsd"])) < 1e-12
+    assert np.abs(t1 - g["solve_t1"]).max() < 1e-11
+    assert np.abs(t2 - g["solve_t2"]).max() < 1e-11
+    for (it, e, de, rms), row in zip(log[1:], ref_log):
+        assert abs(e - row[0]) < 1e-12
+    et = ot.t_tjl(g.F, g.blocks, t1, t2)
+    assert abs(et - float(g["solve_et"])) < 1e-12
+    # t_tjl == t_vikings on symmetric ERIs (reference test_005:38-40)
+    assert abs(float(g["solve_et"]) - float(g["solve_et_vikings"])) < 1e-12
+
+
+@pytest.mark.parametrize("tag,kw", [("nodiis", dict(max_diis=0)), ("diis3s2", dict(max_diis=3, start_diis=2))])
+def test_diis_variants(golden, tag, kw):
+    g = golden
+    ecc, t1, t2, niter = oc.solve_cc(g.F, g.blocks, 1e-10, 1e-10, maxiter=200, **kw)
+    assert niter == int(g["solve_%s_niter" % tag])
+    assert abs(ecc - float(g["solve_%s_ecc" % tag])) < 1e-12
