@@ -1,0 +1,146 @@
+"""
+CudaBackend: the one execution back end of the engine - every call goes through the C ABI of
+libpyccb200.so (include/pyccb200.h) onto the current CUDA stream of PyTorch, which is used
+for device-memory ownership only.  Constructing it without the shared object or without a
+B200 raises EngineError; nothing here (or anywhere in pycc_b200) computes on the CPU.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import EngineError
+
+_DT = {torch.float64: _lib.F64, torch.float32: _lib.F32}
+
+
+def dtype_code(t):
+    try:
+        return _DT[t.dtype if isinstance(t, torch.Tensor) else t]
+    except KeyError:
+        raise EngineError("unsupported dtype %r (float64 / float32 only)" % (t,))
+
+
+class CudaBackend(object):
+    def __init__(self, device=None, workspace_bytes=256 << 20):
+        self.lib = _lib.load()
+        if not torch.cuda.is_available() or self.lib.pccb_device_count() <= 0:
+            raise EngineError("no CUDA device visible: the pycc_b200 engine has no CPU fallback")
+        self.device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+        if self.device.type != "cuda":
+            raise EngineError("pycc_b200 runs on CUDA devices only (got %s)" % self.device)
+        index = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", index)
+        h = C.c_void_p()
+        rc = self.lib.pccb_create(index, C.byref(h))
+        if rc != 0:
+            raise EngineError("pccb_create failed (%d): %s" % (rc, self.lib.pccb_last_error(None).decode()))
+        self.h = h
+        self._ws = torch.empty(workspace_bytes, dtype=torch.uint8, device=self.device)
+        self._check(self.lib.pccb_set_workspace(self.h, self._ws.data_ptr(), workspace_bytes))
+        self._stream = None
+        self.bind_stream()
+
+    # -- plumbing ------------------------------------------------------------------------------
+    def _check(self, rc):
+        if rc != 0:
+            raise EngineError("libpyccb200 error %d: %s" % (rc, self.lib.pccb_last_error(self.h).decode()))
+
+    def bind_stream(self):
+        """Launch on PyTorch's current stream for this device (so torch.cuda.Event timing and
+        tensor lifetimes see the kernels)."""
+        s = torch.cuda.current_stream(self.device).cuda_stream
+        if s != self._stream:
+            self._check(self.lib.pccb_set_stream(self.h, s))
+            self._stream = s
+
+    def close(self):
+        if getattr(self, "h", None) is not None and self.h:
+            self.lib.pccb_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def empty(self, shape, dtype=torch.float64):
+        return torch.empty(shape, dtype=dtype, device=self.device)
+
+    def zeros(self, shape, dtype=torch.float64):
+        return torch.zeros(shape, dtype=dtype, device=self.device)
+
+    def to_device(self, x, dtype=torch.float64):
+        if isinstance(x, torch.Tensor):
+            return x.to(device=self.device, dtype=dtype).contiguous()
+        return torch.as_tensor(x, dtype=dtype).to(self.device).contiguous()
+
+    def use_naive_contract(self, flag):
+        self._check(self.lib.pccb_set_contract_impl(self.h, _lib.IMPL_NAIVE if flag else _lib.IMPL_TENSOR))
+
+    def launch_count(self):
+        n = C.c_int64()
+        self._check(self.lib.pccb_launch_count(self.h, C.byref(n)))
+        return n.value
+
+    def synchronize(self):
+        self._check(self.lib.pccb_synchronize(self.h))
+
+    # -- operator seam ---------------------------------------------------------------------------
+    def contract(self, desc):
+        self._check(self.lib.pccb_contract(self.h, C.byref(desc)))
+
+    # -- solver seam -----------------------------------------------------------------------------
+    def pair_combine(self, out, X, c0, c1, u, w, c2, no, nv):
+        self._check(self.lib.pccb_pair_combine(self.h, dtype_code(out), out.data_ptr(), X.data_ptr(), c0, c1,
+                                               None if u is None else u.data_ptr(),
+                                               None if w is None else w.data_ptr(), c2, no, nv))
+
+    def pair_symmetrize(self, r2, no, nv):
+        self._check(self.lib.pccb_pair_symmetrize(self.h, dtype_code(r2), r2.data_ptr(), no, nv))
+
+    def permute4(self, out, src_view, alpha=1.0, beta=0.0):
+        """out (contiguous 4-D) = alpha * src_view (any strides) + beta * out"""
+        shape = (C.c_int64 * 4)(*out.shape)
+        strides = (C.c_int64 * 4)(*src_view.stride())
+        self._check(self.lib.pccb_permute4(self.h, dtype_code(out), out.data_ptr(), src_view.data_ptr(), shape,
+                                           strides, alpha, beta))
+
+    def update_amplitudes(self, t1, t2, r1, r2, eps, no, nv, symmetrize):
+        out = C.c_double()
+        self._check(self.lib.pccb_update_amplitudes(self.h, dtype_code(t2), t1.data_ptr(), t2.data_ptr(),
+                                                    r1.data_ptr(), r2.data_ptr(), eps.data_ptr(), no, nv,
+                                                    1 if symmetrize else 0, C.byref(out)))
+        return out.value
+
+    def cc_energy(self, fov, ld_fov, t1, t2, oovv, no, nv):
+        out = C.c_double()
+        self._check(self.lib.pccb_cc_energy(self.h, dtype_code(t2), fov.data_ptr(), ld_fov, t1.data_ptr(),
+                                            t2.data_ptr(), oovv.data_ptr(), no, nv, C.byref(out)))
+        return out.value
+
+    def dot(self, x, y):
+        out = C.c_double()
+        self._check(self.lib.pccb_dot(self.h, dtype_code(x), x.data_ptr(), y.data_ptr(), x.numel(), C.byref(out)))
+        return out.value
+
+    def axpby(self, out, a, x, b=0.0, y=None):
+        self._check(self.lib.pccb_axpby(self.h, dtype_code(out), out.data_ptr(), a, x.data_ptr(), b,
+                                        None if y is None else y.data_ptr(), out.numel()))
+
+    def lincomb(self, out, vecs, coefs):
+        n = len(vecs)
+        ptrs = (C.c_void_p * n)(*[v.data_ptr() for v in vecs])
+        cs = (C.c_double * n)(*[float(c) for c in coefs])
+        self._check(self.lib.pccb_lincomb(self.h, dtype_code(out), out.data_ptr(), ptrs, cs, n, out.numel()))
+
+    def triples_energy(self, W, ijk, t1, t2, oovv, fov, ld_fov, eps, no, nv):
+        """W: [ntrip, nv, nv, nv]; ijk: list of (i,j,k).  Returns a list of per-triplet energies."""
+        n = len(ijk)
+        flat = (C.c_int32 * (3 * n))(*[int(x) for t in ijk for x in t])
+        out = (C.c_double * n)()
+        self._check(self.lib.pccb_triples_energy(self.h, dtype_code(W), W.data_ptr(), flat, n, t1.data_ptr(),
+                                                 t2.data_ptr(), oovv.data_ptr(), fov.data_ptr(), ld_fov,
+                                                 eps.data_ptr(), no, nv, out))
+        return list(out)

@@ -1,0 +1,84 @@
+// Internal definitions shared by the translation units of libpyccb200.so (not part of the ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+#include <string>
+
+#include "../../include/pyccb200.h"
+
+struct pccb_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t stream = nullptr;
+    void* ws = nullptr;           // caller-owned split-K workspace
+    size_t ws_bytes = 0;
+    int impl = PCCB_IMPL_TENSOR;
+    long long launches = 0;
+    double* partial_dev = nullptr;   // small library-owned scratch for fixed-order reductions
+    double* result_host = nullptr;   // pinned
+    size_t partial_cap = 0;          // doubles
+    std::string err;
+};
+
+extern thread_local std::string g_create_error;
+
+#define PCCB_FAIL(ctx, code, ...)                                   \
+    do {                                                            \
+        char buf_[512];                                             \
+        snprintf(buf_, sizeof(buf_), __VA_ARGS__);                  \
+        (ctx)->err = buf_;                                          \
+        return (code);                                              \
+    } while (0)
+
+#define PCCB_CUDA(ctx, call)                                                                   \
+    do {                                                                                       \
+        cudaError_t e_ = (call);                                                               \
+        if (e_ != cudaSuccess)                                                                 \
+            PCCB_FAIL(ctx, PCCB_ERR_CUDA, "%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                      __FILE__, __LINE__);                                                     \
+    } while (0)
+
+#define PCCB_CHECK_LAUNCH(ctx, what)                                                            \
+    do {                                                                                        \
+        cudaError_t e_ = cudaGetLastError();                                                    \
+        if (e_ != cudaSuccess)                                                                  \
+            PCCB_FAIL(ctx, PCCB_ERR_CUDA, "launch of %s failed: %s", what, cudaGetErrorString(e_)); \
+        (ctx)->launches++;                                                                      \
+    } while (0)
+
+#define PCCB_REQUIRE(ctx, cond, ...)                          \
+    do {                                                      \
+        if (!(cond)) PCCB_FAIL(ctx, PCCB_ERR_ARG, __VA_ARGS__); \
+    } while (0)
+
+// device-side compound index (see pccb_cidx)
+struct DIdx {
+    long long s_hi, s_lo;
+    unsigned div;
+    unsigned pad_;
+};
+
+__host__ __device__ __forceinline__ long long didx_off(const DIdx& c, unsigned i) {
+    unsigned q = i / c.div;
+    unsigned r = i - q * c.div;
+    return (long long)q * c.s_hi + (long long)r * c.s_lo;
+}
+
+static inline DIdx to_didx(const pccb_cidx& c, long long extent) {
+    DIdx d;
+    long long div = c.div;
+    if (div <= 0 || div >= extent) {   // flat
+        d.div = 0x7fffffffu;
+        d.s_hi = 0;
+    } else {
+        d.div = (unsigned)div;
+        d.s_hi = c.s_hi;
+    }
+    d.s_lo = c.s_lo;
+    d.pad_ = 0;
+    return d;
+}
+
+// fixed-order two-stage sum reduction helpers (reduce.cu)
+int pccb_ensure_partials(pccb_ctx* ctx, size_t ndoubles);

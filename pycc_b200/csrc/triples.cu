@@ -1,0 +1,204 @@
+// (T) energy reduction: disconnected triples + Lee-Rendell closed-shell energy expression,
+// evaluated per occupied triplet from the connected W[a,b,c] that pccb_contract produced
+// (pycc/cctriples.py:68-83 t3d_ijk, :124-150 body of t_tjl).
+//
+// The expression needs W and V at all six permutations of (a,b,c).  A CTA owns the 8x8 (a,b)
+// brick pair (TA >= TB) and walks TC <= TB; for each canonical brick triple it stages the six
+// permuted 8x8x8 bricks of W in shared memory with coalesced 64-byte runs, so W is read from
+// HBM/L2 exactly once per triplet (8*v^3 bytes: HBM-roofline work, ~1 % of the W build).
+// Reductions are fixed-order: warp shuffle -> block -> one partial per CTA -> one block per
+// triplet.
+#include "common.cuh"
+
+namespace {
+
+constexpr int TB_ = 8;                 // brick edge
+constexpr int BRICK = TB_ * TB_ * (TB_ + 1);   // padded [8][8][9]
+
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    return v;
+}
+
+template <typename T>
+struct TriplesArgs {
+    const T* W;           // [ntrip][nv][nv][nv]
+    const int* ijk;       // device [3*ntrip]
+    const T* t1;          // [no][nv]
+    const T* t2;          // [no][no][nv][nv]
+    const T* g;           // oovv
+    const T* fov;         // F[o,v] with row stride ld_fov
+    const T* eps;         // Fock diagonal, occupied first
+    long long ld_fov;
+    int no, nv, nb, ntrip;
+    double* partials;     // [ntrip][nb*(nb+1)/2]
+};
+
+// brick(x0,y0,z0) of W -> s[x][y][z] (padded), zero beyond nv
+template <typename T>
+__device__ __forceinline__ void load_brick(double* s, const T* W, int nv, int x0, int y0, int z0, int tid) {
+    const int z = tid & 7, y = (tid >> 3) & 7, x = tid >> 6;
+    const int gx = x0 + x, gy = y0 + y, gz = z0 + z;
+    double v = 0.0;
+    if (gx < nv && gy < nv && gz < nv) v = (double)W[((long long)gx * nv + gy) * nv + gz];
+    s[(x * TB_ + y) * (TB_ + 1) + z] = v;
+}
+
+__device__ __forceinline__ double brick_at(const double* s, int x, int y, int z) {
+    return s[(x * TB_ + y) * (TB_ + 1) + z];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_constant__ TriplesArgs<T> p) {
+    __shared__ double sW[6][BRICK];
+    __shared__ double sred[16];
+    const int TBk = blockIdx.x, TAk = blockIdx.y, t = blockIdx.z;
+    if (TBk > TAk) return;
+    const int tid = threadIdx.x;
+    const int lc = tid & 7, lb = (tid >> 3) & 7, la = tid >> 6;
+    const int nv = p.nv, no = p.no;
+    const int i = p.ijk[3 * t], j = p.ijk[3 * t + 1], k = p.ijk[3 * t + 2];
+    const T* W = p.W + (long long)t * nv * nv * nv;
+    const long long nvv = (long long)nv * nv;
+    const T* g_ij = p.g + ((long long)i * no + j) * nvv;
+    const T* g_ik = p.g + ((long long)i * no + k) * nvv;
+    const T* g_jk = p.g + ((long long)j * no + k) * nvv;
+    const T* t_ij = p.t2 + ((long long)i * no + j) * nvv;
+    const T* t_ik = p.t2 + ((long long)i * no + k) * nvv;
+    const T* t_jk = p.t2 + ((long long)j * no + k) * nvv;
+    const T* t1i = p.t1 + (long long)i * nv;
+    const T* t1j = p.t1 + (long long)j * nv;
+    const T* t1k = p.t1 + (long long)k * nv;
+    const T* fi = p.fov + (long long)i * p.ld_fov;
+    const T* fj = p.fov + (long long)j * p.ld_fov;
+    const T* fk = p.fov + (long long)k * p.ld_fov;
+    const double eocc = (double)p.eps[i] + (double)p.eps[j] + (double)p.eps[k];
+    const double occ = 2.0 - (double)((i == j) + (i == k) + (j == k));
+
+    const int A0 = TAk * TB_, B0 = TBk * TB_;
+    const int a = A0 + la, b = B0 + lb;
+    double esum = 0.0;
+
+    for (int TCk = 0; TCk <= TBk; ++TCk) {
+        const int C0 = TCk * TB_;
+        const int c = C0 + lc;
+        __syncthreads();
+        load_brick(sW[0], W, nv, A0, B0, C0, tid);   // [a][b][c]
+        load_brick(sW[1], W, nv, A0, C0, B0, tid);   // [a][c][b]
+        load_brick(sW[2], W, nv, B0, A0, C0, tid);   // [b][a][c]
+        load_brick(sW[3], W, nv, B0, C0, A0, tid);   // [b][c][a]
+        load_brick(sW[4], W, nv, C0, A0, B0, tid);   // [c][a][b]
+        load_brick(sW[5], W, nv, C0, B0, A0, tid);   // [c][b][a]
+        __syncthreads();
+        if (a < nv && b < nv && c < nv && a >= b && b >= c) {
+            const double Wabc = brick_at(sW[0], la, lb, lc);
+            const double Wacb = brick_at(sW[1], la, lc, lb);
+            const double Wbac = brick_at(sW[2], lb, la, lc);
+            const double Wbca = brick_at(sW[3], lb, lc, la);
+            const double Wcab = brick_at(sW[4], lc, la, lb);
+            const double Wcba = brick_at(sW[5], lc, lb, la);
+            // disconnected part for an ordered triple (x,y,z) of virtual indices (cctriples.py:69-74)
+            auto dis = [&](int x, int y, int z) {
+                return (double)g_ij[(long long)x * nv + y] * (double)t1k[z] +
+                       (double)g_ik[(long long)x * nv + z] * (double)t1j[y] +
+                       (double)g_jk[(long long)y * nv + z] * (double)t1i[x] +
+                       (double)t_ij[(long long)x * nv + y] * (double)fk[z] +
+                       (double)t_ik[(long long)x * nv + z] * (double)fj[y] +
+                       (double)t_jk[(long long)y * nv + z] * (double)fi[x];
+            };
+            const double sinv = 1.0 / (1.0 + (double)((a == b) + (a == c) + (b == c)));
+            const double Vabc = (Wabc + dis(a, b, c)) * sinv;
+            const double Vacb = (Wacb + dis(a, c, b)) * sinv;
+            const double Vbac = (Wbac + dis(b, a, c)) * sinv;
+            const double Vbca = (Wbca + dis(b, c, a)) * sinv;
+            const double Vcab = (Wcab + dis(c, a, b)) * sinv;
+            const double Vcba = (Wcba + dis(c, b, a)) * sinv;
+            const double X = Wabc * Vabc + Wacb * Vacb + Wbac * Vbac + Wbca * Vbca + Wcab * Vcab + Wcba * Vcba;
+            const double Y = Vabc + Vbca + Vcab;
+            const double Z = Vacb + Vbac + Vcba;
+            const double Wc = Wabc + Wbca + Wcab;
+            const double Wa = Wacb + Wbac + Wcba;
+            const double denom = eocc - (double)p.eps[no + a] - (double)p.eps[no + b] - (double)p.eps[no + c];
+            esum += ((Y - 2.0 * Z) * Wc + (Z - 2.0 * Y) * Wa + 3.0 * X) * occ / denom;
+        }
+    }
+    esum = warp_sum(esum);
+    if ((tid & 31) == 0) sred[tid >> 5] = esum;
+    __syncthreads();
+    if (tid == 0) {
+        double r = 0.0;
+#pragma unroll
+        for (int w = 0; w < 16; ++w) r += sred[w];
+        const int npair = p.nb * (p.nb + 1) / 2;
+        p.partials[(long long)t * npair + TAk * (TAk + 1) / 2 + TBk] = r;
+    }
+}
+
+__global__ void sum_rows_kernel(const double* __restrict__ partials, int n, double* __restrict__ out) {
+    __shared__ double sh[8];
+    const double* row = partials + (long long)blockIdx.x * n;
+    double v = 0.0;
+    for (int q = threadIdx.x; q < n; q += blockDim.x) v += row[q];
+    v = warp_sum(v);
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double r = 0.0;
+        for (int w = 0; w < 8; ++w) r += sh[w];
+        out[blockIdx.x] = r;
+    }
+}
+
+template <typename T>
+int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_host, int ntrip, const void* t1,
+                     const void* t2, const void* g, const void* fov, int64_t ld_fov, const void* eps, int64_t no,
+                     int64_t nv, double* et_host) {
+    const int nb = (int)((nv + TB_ - 1) / TB_);
+    const int npair = nb * (nb + 1) / 2;
+    PCCB_REQUIRE(ctx, ntrip >= 1 && ntrip <= 65535, "pccb_triples_energy: ntrip=%d out of range", ntrip);
+    PCCB_REQUIRE(ctx, nb <= 65535, "pccb_triples_energy: nv too large");
+    // scratch: partials [ntrip*npair] | results [ntrip] | ijk (as ints) [3*ntrip]
+    const size_t need = (size_t)ntrip * npair + ntrip + (3 * (size_t)ntrip + 1) / 2 + 8;
+    int rc = pccb_ensure_partials(ctx, need);
+    if (rc) return rc;
+    double* partials = ctx->partial_dev;
+    double* results = partials + (size_t)ntrip * npair;
+    int* ijk_dev = reinterpret_cast<int*>(results + ntrip);
+    PCCB_CUDA(ctx, cudaMemcpyAsync(ijk_dev, ijk_host, sizeof(int) * 3 * ntrip, cudaMemcpyHostToDevice, ctx->stream));
+    TriplesArgs<T> a;
+    a.W = (const T*)w_dev; a.ijk = ijk_dev; a.t1 = (const T*)t1; a.t2 = (const T*)t2; a.g = (const T*)g;
+    a.fov = (const T*)fov; a.eps = (const T*)eps; a.ld_fov = ld_fov; a.no = (int)no; a.nv = (int)nv; a.nb = nb;
+    a.ntrip = ntrip; a.partials = partials;
+    // non-canonical CTAs (TB > TA) exit at once, so only their partial slots stay unused
+    dim3 grid(nb, nb, ntrip);
+    triples_energy_kernel<T><<<grid, 512, 0, ctx->stream>>>(a);
+    PCCB_CHECK_LAUNCH(ctx, "triples_energy_kernel");
+    sum_rows_kernel<<<ntrip, 256, 0, ctx->stream>>>(partials, npair, results);
+    PCCB_CHECK_LAUNCH(ctx, "sum_rows_kernel");
+    PCCB_CUDA(ctx, cudaMemcpyAsync(et_host, results, sizeof(double) * ntrip, cudaMemcpyDeviceToHost, ctx->stream));
+    PCCB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return PCCB_OK;
+}
+
+}  // namespace
+
+extern "C" int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, const int32_t* ijk_host, int ntrip,
+                                   const void* t1_dev, const void* t2_dev, const void* oovv_dev, const void* fov_dev,
+                                   int64_t ld_fov, const void* eps_dev, int64_t no, int64_t nv, double* et_host) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, w_dev && ijk_host && t1_dev && t2_dev && oovv_dev && fov_dev && eps_dev && et_host,
+                 "pccb_triples_energy: null argument");
+    PCCB_REQUIRE(ctx, no > 0 && nv > 0, "pccb_triples_energy: bad sizes");
+    for (int t = 0; t < ntrip; ++t)
+        for (int q = 0; q < 3; ++q)
+            PCCB_REQUIRE(ctx, ijk_host[3 * t + q] >= 0 && ijk_host[3 * t + q] < no,
+                         "pccb_triples_energy: triplet %d has an occupied index out of range", t);
+    if (dtype == PCCB_F64)
+        return triples_energy_t<double>(ctx, w_dev, ijk_host, ntrip, t1_dev, t2_dev, oovv_dev, fov_dev, ld_fov,
+                                        eps_dev, no, nv, et_host);
+    if (dtype == PCCB_F32)
+        return triples_energy_t<float>(ctx, w_dev, ijk_host, ntrip, t1_dev, t2_dev, oovv_dev, fov_dev, ld_fov,
+                                       eps_dev, no, nv, et_host);
+    PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
+}

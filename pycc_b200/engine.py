@@ -1,0 +1,212 @@
+"""
+CCSD residual engine: every builder of ``ccwfn.residuals`` (pycc/ccwfn.py:331-366) recast as
+fused strided FP64 tensor-core contractions (``pccb_contract``) plus a handful of memory-bound
+kernels, planned once per (o, v) and replayed every iteration.
+
+Data layout in HBM (all C-contiguous, FP64 unless precision='SP'):
+    constants   F (n,n), eps (n)                      Fock matrix and its diagonal
+                oooo[mnij] ooov[mnie] oovv[ijab] ovov[mbje] ovvv[mbef] vvvv[abef]
+                Loovv[mnef] = 2<mn|ef> - <mn|fe>      (pycc/hamiltonian.py:39, oovv block only)
+                Looov[mnie] = 2<mn|ie> - <nm|ie>
+    amplitudes  t1[ia], t2[ijab]
+    per iteration (never bigger than o^2 v^2):
+                tau = t2 + t1 t1, tauh = t2 + t1 t1/2, tauW = t2/2 + t1 t1, t2s = 2 t2 - t2^T
+                Fae Fmi Fme Wmnij, and in "ring layout" [j,b,m,e]:
+                Wr1[jbme] = Wmbej[mbej]   Wr2[jbme] = Wmbje[mbje]   Zr[mijb] = Zmbij[mbij]
+The ring layout makes the five o^3 v^3 contractions of r_T2 (ccwfn.py:609-614) plain
+(ov) x (ov) GEMMs whose K index (m,e) is contiguous in the W operand; the reference's other
+slices of ERI / L (oovo, ovvo, vvvo, ovoo, L_ovvv, L_ovvo, L_oovo) are *views* of the six stored
+blocks by the 8-fold symmetry and are never materialised.
+
+Differences from the reference's operation order (results agree to rounding):
+  * (t2 - t2^T) Wmbej + t2 (Wmbej + Wmbje^T)  is evaluated as  t2s Wmbej + t2 Wmbje^T;
+  * the two o^3 v^3 terms built from tmp = t1 t1 (ccwfn.py:612-614) are factorised through
+    o^3 v intermediates (2 o^3 v^2 flops each instead of 2 o^3 v^3);
+  * -1/2 t2 (t1 Fme) terms (ccwfn.py:601-605) are folded into dressed Fae / Fmi matrices.
+"""
+import torch
+
+from . import _lib
+from .dsl import TRef, plan
+
+
+class CCSDEngine(object):
+    def __init__(self, backend, F, blocks, no, nv, dtype=torch.float64):
+        self.be = be = backend
+        self.no, self.nv, self.dtype = int(no), int(nv), dtype
+        self.dcode = _lib.F64 if dtype == torch.float64 else _lib.F32
+        o, v = self.no, self.nv
+        n = o + v
+        self.F = be.to_device(F, dtype)
+        if tuple(self.F.shape) != (n, n):
+            raise ValueError("F must be (%d,%d)" % (n, n))
+        self.eps = torch.diagonal(self.F).contiguous()
+        shapes = dict(oooo=(o, o, o, o), ooov=(o, o, o, v), oovv=(o, o, v, v), ovov=(o, v, o, v),
+                      ovvv=(o, v, v, v), vvvv=(v, v, v, v))
+        self.blk = {}
+        for k, shp in shapes.items():
+            if k not in blocks:
+                raise ValueError("missing ERI block %r" % k)
+            t = be.to_device(blocks[k], dtype)
+            if tuple(t.shape) != shp:
+                raise ValueError("ERI block %s has shape %s, expected %s" % (k, tuple(t.shape), shp))
+            self.blk[k] = t
+        # spin-adapted constants
+        self.Loovv = be.empty((o, o, v, v), dtype)
+        be.pair_combine(self.Loovv, self.blk["oovv"], 2.0, -1.0, None, None, 0.0, o, v)
+        self.Looov = be.empty((o, o, o, v), dtype)
+        be.permute4(self.Looov, self.blk["ooov"], 2.0, 0.0)
+        be.permute4(self.Looov, self.blk["ooov"].permute(1, 0, 2, 3), -1.0, 1.0)
+        # amplitudes and per-iteration buffers
+        E = lambda *s: be.zeros(s, dtype)
+        self.t1, self.t2 = E(o, v), E(o, o, v, v)
+        self.tau, self.tauh, self.tauW, self.t2s = E(o, o, v, v), E(o, o, v, v), E(o, o, v, v), E(o, o, v, v)
+        self.Fae, self.Fmi, self.Fme = E(v, v), E(o, o), E(o, v)
+        self.Fae2, self.Fmi2 = E(v, v), E(o, o)
+        self.Wmnij = E(o, o, o, o)
+        self.Wr1, self.Wr2 = E(o, v, o, v), E(o, v, o, v)       # [j,b,m,e]
+        self.Zr = E(o, o, o, v)                                  # [m,i,j,b]
+        self.Y1, self.Y2 = E(o, o, o, v), E(o, o, v, o)          # [i,m,j,b], [i,m,a,j]
+        self.r1, self.r2 = E(o, v), E(o, o, v, v)
+        self._build_plans()
+
+    # ---------------------------------------------------------------------------------------
+    def _tensors(self):
+        o = self.no
+        F = self.F
+        d = dict(self.blk)
+        d.update(Foo=F[:o, :o], Fov=F[:o, o:], Fvv=F[o:, o:], Loovv=self.Loovv, Looov=self.Looov,
+                 t1=self.t1, t2=self.t2, tau=self.tau, tauh=self.tauh, tauW=self.tauW, t2s=self.t2s,
+                 Fae=self.Fae, Fmi=self.Fmi, Fme=self.Fme, Fae2=self.Fae2, Fmi2=self.Fmi2, Wmnij=self.Wmnij,
+                 Wr1=self.Wr1, Wr2=self.Wr2, Zr=self.Zr, Y1=self.Y1, Y2=self.Y2, r1=self.r1, r2=self.r2)
+        return {k: TRef.of(t, k) for k, t in d.items()}
+
+    # Statements, grouped per reference builder.  Index letters as in the reference.
+    STATEMENTS = {
+        # build_Fae (pycc/ccwfn.py:421-428); L[o,v,v,v] = 2<ma|fe> - <ma|ef>
+        "Fae": ["Fae[ae] = Fvv[ae] - 0.5*t1[ma]*Fov[me] - tauh[mnaf]*Loovv[mnef]",
+                "Fae[ae] += 2.0*t1[mf]*ovvv[mafe] - t1[mf]*ovvv[maef]"],
+        # build_Fmi (:441-447); L[o,o,o,v] = Looov
+        "Fmi": ["Fmi[mi] = Foo[mi] + 0.5*Fov[me]*t1[ie] + Loovv[mnef]*tauh[inef]",
+                "Fmi[mi] += t1[ne]*Looov[mnie]"],
+        # build_Fme (:456-460)
+        "Fme": ["Fme[me] = Fov[me] + Loovv[mnef]*t1[nf]"],
+        # build_Wmnij (:473-482); <mn|ej> = <nm|je>
+        "Wmnij": ["Wmnij[mnij] = oooo[mnij] + oovv[mnef]*tau[ijef]",
+                  "Wmnij[mnij] += ooov[mnie]*t1[je]",
+                  "Wmnij[mnij] += ooov[nmje]*t1[ie]"],
+        # build_Wmbej (:498-505) in ring layout Wr1[jbme]; <mb|ej> = <mj|eb>, <mn|ej> = <nm|je>
+        "Wmbej": ["Wr1[jbme] = oovv[mjeb] - tauW[jnfb]*oovv[mnef] + 0.5*t2[njfb]*Loovv[mnef]",
+                  "Wr1[jbme] += t1[jf]*ovvv[mbef]",
+                  "Wr1[jbme] -= t1[nb]*ooov[nmje]"],
+        # build_Wmbje (:520-526) in ring layout Wr2[jbme] = Wmbje[mbje]
+        "Wmbje": ["Wr2[jbme] = -1.0*ovov[mbje] + tauW[jnfb]*oovv[mnfe]",
+                  "Wr2[jbme] -= t1[jf]*ovvv[mbfe]",
+                  "Wr2[jbme] += t1[nb]*ooov[mnje]"],
+        # build_Zmbij (:537) as Zr[mijb]
+        "Zmbij": ["Zr[mijb] = ovvv[mbef]*tau[ijef]"],
+        # r_T1 (:548-557); L[o,v,v,o][nafi] = 2<ni|fa> - <na|if>; L[o,o,v,o][nmei] = Looov[mnie]
+        "r_T1": ["r1[ia] = Fov[ia] + t1[ie]*Fae[ae] - Fmi[mi]*t1[ma] + t2s[mief]*ovvv[maef] - Looov[mnie]*t2[mnae]",
+                 "r1[ia] += t2s[imae]*Fme[me]",
+                 "r1[ia] += 2.0*t1[nf]*oovv[nifa] - t1[nf]*ovov[naif]"],
+        # r_T2 (:596-616), unsymmetrised; <ab|ej> = <ja|be>, <mb|ij> = <ij|mb>
+        "r_T2": ["Fae2[be] = Fae[be] - 0.5*t1[mb]*Fme[me]",
+                 "Fmi2[mj] = Fmi[mj] + 0.5*Fme[me]*t1[je]",
+                 "r2[ijab] = 0.5*oovv[ijab] + 0.5*tau[ijef]*vvvv[abef]",
+                 "r2[ijab] += 0.5*Wmnij[mnij]*tau[mnab]",
+                 "r2[ijab] += t2s[imae]*Wr1[jbme] + t2[imae]*Wr2[jbme]",
+                 "r2[ijab] += t2[mjae]*Wr2[ibme]",
+                 "r2[ijab] += t2[ijae]*Fae2[be]",
+                 "r2[ijab] -= Fmi2[mj]*t2[imab]",
+                 "r2[ijab] -= t1[ma]*Zr[mijb]",
+                 "Y1[imjb] = t1[ie]*oovv[mjeb]",
+                 "r2[ijab] -= t1[ma]*Y1[imjb]",
+                 "Y2[imaj] = t1[ie]*ovov[maje]",
+                 "r2[ijab] -= Y2[imaj]*t1[mb]",
+                 "r2[ijab] += t1[ie]*ovvv[jabe]",
+                 "r2[ijab] -= t1[ma]*ooov[ijmb]"],
+    }
+
+    def _build_plans(self):
+        T = self._tensors()
+        self.plans = {}
+        for name, stmts in self.STATEMENTS.items():
+            launches = []
+            for s in stmts:
+                launches += plan(s, T, self.dcode)
+            self.plans[name] = launches
+
+    def _run(self, name):
+        for L in self.plans[name]:
+            self.be.contract(L.desc)
+
+    # ---- amplitude-dependent element-wise preparations ---------------------------------------
+    def prepare(self):
+        """tau variants and the spin-adapted t2 (build_tau, pycc/ccwfn.py:408-410; :554)."""
+        be, o, v = self.be, self.no, self.nv
+        be.pair_combine(self.tau, self.t2, 1.0, 0.0, self.t1, self.t1, 1.0, o, v)
+        be.pair_combine(self.tauh, self.t2, 1.0, 0.0, self.t1, self.t1, 0.5, o, v)
+        be.pair_combine(self.tauW, self.t2, 0.5, 0.0, self.t1, self.t1, 1.0, o, v)
+        be.pair_combine(self.t2s, self.t2, 2.0, -1.0, None, None, 0.0, o, v)
+
+    def set_amplitudes(self, t1, t2):
+        self.t1.copy_(torch.as_tensor(t1).to(self.t1.device, self.dtype))
+        self.t2.copy_(torch.as_tensor(t2).to(self.t2.device, self.dtype))
+
+    def set_fock(self, F):
+        """A different Fock operator for the next residuals() call (ccwfn.residuals takes F)."""
+        self.F.copy_(torch.as_tensor(F).to(self.F.device, self.dtype))
+        self.eps.copy_(torch.diagonal(self.F))
+
+    def residuals(self, symmetrize=True):
+        """r1, r2 for the amplitudes held in self.t1 / self.t2 (pycc/ccwfn.py:357-366)."""
+        self.be.bind_stream()
+        self.prepare()
+        for name in ("Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij", "r_T1", "r_T2"):
+            self._run(name)
+        if symmetrize:
+            self.be.pair_symmetrize(self.r2, self.no, self.nv)       # ccwfn.py:621
+        return self.r1, self.r2
+
+    def run_builder(self, name):
+        self.be.bind_stream()
+        self.prepare()
+        deps = {"Fae": [], "Fmi": [], "Fme": [], "Wmnij": [], "Wmbej": [], "Wmbje": [], "Zmbij": [],
+                "r_T1": ["Fae", "Fmi", "Fme"],
+                "r_T2": ["Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij"]}
+        for d in deps[name]:
+            self._run(d)
+        self._run(name)
+
+    # reference-ordered views of the ring-layout intermediates
+    def Wmbej_view(self):
+        return self.Wr1.permute(2, 1, 3, 0)      # [j,b,m,e] -> [m,b,e,j]
+
+    def Wmbje_view(self):
+        return self.Wr2.permute(2, 1, 0, 3)      # [j,b,m,e] -> [m,b,j,e]
+
+    def Zmbij_view(self):
+        return self.Zr.permute(0, 3, 1, 2)       # [m,i,j,b] -> [m,b,i,j]
+
+    def energy(self):
+        """cc_energy (pycc/ccwfn.py:717-718)."""
+        self.be.bind_stream()
+        o = self.no
+        fov = self.F[:o, o:]
+        return self.be.cc_energy(fov, self.F.stride(0), self.t1, self.t2, self.blk["oovv"], self.no, self.nv)
+
+    def update(self, symmetrize_on_the_fly):
+        """t += r/D; returns the squared increment norm (pycc/ccwfn.py:287-290)."""
+        self.be.bind_stream()
+        return self.be.update_amplitudes(self.t1, self.t2, self.r1, self.r2, self.eps, self.no, self.nv,
+                                         symmetrize_on_the_fly)
+
+    def flops_issued(self):
+        """Flops the planned launches actually issue per residuals() call (2*M*N*K summed)."""
+        tot = 0
+        for launches in self.plans.values():
+            for L in launches:
+                d = L.desc
+                for q in range(d.nseg):
+                    tot += 2 * d.M * d.N * d.batch * d.seg[q].K
+        return tot
