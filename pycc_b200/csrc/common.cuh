@@ -52,31 +52,47 @@ extern thread_local std::string g_create_error;
         if (!(cond)) PCCB_FAIL(ctx, PCCB_ERR_ARG, __VA_ARGS__); \
     } while (0)
 
-// device-side compound index (see pccb_cidx)
+// device-side compound index (see pccb_cidx): offset(i) = (i / div) * s_hi + (i % div) * s_lo.
+// The division is a multiply-high + shift with a host-computed magic number (exact for
+// i < 2^31, 2 <= div < 2^31); a flat index has magic = 0 (quotient 0).
 struct DIdx {
     long long s_hi, s_lo;
-    unsigned div;
-    unsigned pad_;
+    unsigned div, magic, shift, flat;
 };
 
 __host__ __device__ __forceinline__ long long didx_off(const DIdx& c, unsigned i) {
-    unsigned q = i / c.div;
-    unsigned r = i - q * c.div;
+#ifdef __CUDA_ARCH__
+    const unsigned q = __umulhi(i, c.magic) >> c.shift;
+#else
+    const unsigned q = (unsigned)(((unsigned long long)i * c.magic) >> 32) >> c.shift;
+#endif
+    const unsigned r = i - q * c.div;
     return (long long)q * c.s_hi + (long long)r * c.s_lo;
 }
 
 static inline DIdx to_didx(const pccb_cidx& c, long long extent) {
     DIdx d;
     long long div = c.div;
-    if (div <= 0 || div >= extent) {   // flat
-        d.div = 0x7fffffffu;
-        d.s_hi = 0;
-    } else {
-        d.div = (unsigned)div;
-        d.s_hi = c.s_hi;
-    }
     d.s_lo = c.s_lo;
-    d.pad_ = 0;
+    if (div <= 1 || div >= extent) {   // flat
+        d.div = 0;
+        d.magic = 0;
+        d.shift = 0;
+        d.s_hi = 0;
+        d.flat = 1;
+        if (div == 1 && extent > 1) {  // degenerate "inner extent 1": index is the outer one
+            d.s_lo = c.s_hi;
+        }
+        return d;
+    }
+    unsigned s = 0;
+    while ((1ll << s) < div) ++s;                         // s = ceil(log2 div) >= 1
+    const unsigned long long m = ((1ull << (31 + s)) + (unsigned long long)div - 1) / (unsigned long long)div;
+    d.div = (unsigned)div;
+    d.magic = (unsigned)m;                               // < 2^32, see contract.cu header
+    d.shift = s - 1;
+    d.s_hi = c.s_hi;
+    d.flat = 0;
     return d;
 }
 

@@ -9,15 +9,22 @@
 //   * FP64 has no tcgen05/TMEM path on Blackwell; the FP64 tensor instruction is the
 //     warp-synchronous DMMA.8x8x4 (PTX mma.sync.m8n8k4.f64), one issue per 16 cycles per SM
 //     sub-partition = 37.0 TFLOP/s per GPU; cuBLAS DGEMM reaches 35.5.
-//   * CTA tile 128x128x16, 8 warps as 2(M) x 4(N), warp tile 64x32: 32 DMMA per 12 LDS.64, so
-//     the tensor pipe, not shared memory or issue slots, is the limiter.
-//   * operand tiles are staged with cp.async (LDGSTS, zero-fill for edges) through a 4-stage
-//     shared-memory ring; because a DMMA occupies the pipe for 16 cycles the per-element
-//     address arithmetic of compound (two-level) einsum indices is free, which is what lets a
-//     tile walk e.g. the (i,a) x (m,e) view of t2[i,m,a,e] without any transpose in HBM.
+//   * CTA tile (16*MI) x 128 x 16 with MI in {1,2,4,5,6,8} chosen per launch to minimise padded
+//     rows (o^2 = 400 -> five 80-row tiles); 8 warps as 2(M) x 4(N), warp tile (8*MI) x 32:
+//     4*MI DMMA per MI+4 LDS.64, so the tensor pipe, not shared memory, is the limiter.
+//   * operand tiles are staged with cp.async (LDGSTS, zero-fill at the edges) through a 4-stage
+//     shared-memory ring guarded by mbarriers (full: cp.async.mbarrier.arrive of all threads,
+//     empty: one arrive per warp), so warps drift up to two k-tiles apart instead of meeting
+//     at a CTA barrier every 16 k.  The loader is branch-free straight-line code issued
+//     between the DMMA groups: a DMMA holds the pipe for 16 cycles, so the per-chunk address
+//     arithmetic of compound (two-level) einsum indices rides in otherwise idle issue slots.
+//     That is what lets a tile walk e.g. the (i,a) x (m,e) view of t2[i,m,a,e] without any
+//     transpose in HBM.
 //   * shared tiles keep the global-contiguous direction contiguous ("K-major" [row][k] with
-//     pitch 20 doubles, or "MN-major" [k][row] with pitch 132): both pitches are = 4 mod 16
+//     pitch 20 doubles, or "MN-major" [k][row] with pitch rows+4): both pitches are = 4 mod 16
 //     eight-byte words, which makes the DMMA fragment loads bank-conflict free.
+//   * per-segment scale factors never touch the FP64 pipe in the main loop: the accumulators
+//     are rescaled once when the k-loop crosses a segment boundary.
 //   * small outputs (Fae, Fmi, Wmnij ...) use deterministic split-K through a caller-owned
 //     workspace, reduced in fixed order together with the alpha/beta/gamma epilogue.
 #include <climits>
@@ -27,11 +34,8 @@
 
 namespace {
 
-constexpr int BM = 128, BN = 128, BK = 16, NTHREADS = 256, STAGES = 4;
-constexpr int PK = BK + 4;    // pitch of a K-major tile row   (doubles)
-constexpr int PM = BM + 4;    // pitch of an MN-major tile row (doubles); BM == BN
-constexpr int STAGE_ELEMS = BM * PK;   // 2560 doubles >= BK*PM = 2112
-constexpr long long INVALID_ROW = LLONG_MIN;
+constexpr int BN = 128, BK = 16, NTHREADS = 256, STAGES = 4;
+constexpr int PK = BK + 4;    // pitch of a K-major tile row (doubles)
 
 struct DSeg {
     const double* A;
@@ -41,8 +45,9 @@ struct DSeg {
     double scale;
     unsigned K;
     int kt_begin;          // first global k-tile of this segment
-    int a_mn_major, a_vec; // layout of the A tile in shared memory / cp.async width (doubles)
-    int b_mn_major, b_vec;
+    int a_mn_major;        // A tile in shared memory: 0 = [row][k], 1 = [k][row]
+    int b_mn_major;
+    int pad_;
 };
 
 struct DParams {
@@ -60,80 +65,88 @@ struct DParams {
 };
 
 __device__ __forceinline__ void cp_async16(unsigned dst, const void* src, int bytes) {
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(bytes));
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void cp_async8(unsigned dst, const void* src, int bytes) {
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(dst), "l"(src), "r"(bytes));
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() {
-    asm volatile("cp.async.wait_group %0;\n" ::"n"(N));
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
 }
 __device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
     asm("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
         : "+d"(c0), "+d"(c1)
         : "d"(a), "d"(b));
 }
-
-// Stage one operand tile (128 rows x 16 k) of the current segment into shared memory.
-//   rows[]  : element offset of each tile row (INVALID_ROW beyond the edge), batch offset included
-//   K-major : tile[row][k], pitch PK;   MN-major: tile[k][row], pitch PM
-template <int VEC>
-__device__ __forceinline__ void load_tile_kmajor(double* tile, const double* base, const long long* rows,
-                                                 const DIdx& kidx, unsigned k0, unsigned K, int tid) {
-    constexpr int CH = BK / VEC;            // chunks per row
-    constexpr int RPP = NTHREADS / CH;      // rows per pass
-    const int kc = tid % CH, r0 = tid / CH;
-    const unsigned k = k0 + kc * VEC;
-    int kbytes = 0;
-    long long koff = 0;
-    if (k < K) {
-        koff = didx_off(kidx, k);
-        kbytes = (VEC == 2 && k + 1 < K) ? 16 : 8;
-    }
-    const unsigned sbase = (unsigned)__cvta_generic_to_shared(tile + kc * VEC);
-#pragma unroll
-    for (int p = 0; p < BM / RPP; ++p) {
-        const int row = r0 + p * RPP;
-        const long long ro = rows[row];
-        const int bytes = (ro == INVALID_ROW) ? 0 : kbytes;
-        const double* src = bytes ? base + ro + koff : base;
-        const unsigned dst = sbase + row * (PK * 8);
-        if (VEC == 2) cp_async16(dst, src, bytes);
-        else cp_async8(dst, src, bytes);
-    }
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared.b64 _, [%0];\n" ::"r"(bar) : "memory");
+}
+// arrives on `bar` once all cp.async issued so far by this thread have landed
+__device__ __forceinline__ void cp_async_mbar_arrive(unsigned bar) {
+    asm volatile("cp.async.mbarrier.arrive.noinc.shared.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared.b64 p, [%1], %2;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity)
+            : "memory");
+    } while (!ok);
 }
 
 template <int VEC>
-__device__ __forceinline__ void load_tile_mnmajor(double* tile, const double* base, const long long* rows,
-                                                  const DIdx& kidx, unsigned k0, unsigned K, int tid) {
-    constexpr int CH = BM / VEC;            // chunks per k-row
-    constexpr int KPP = NTHREADS / CH;      // k-rows per pass
-    const int mc = tid % CH, kr0 = tid / CH;
-    const long long ro = rows[mc * VEC];
-    int mbytes = 0;
-    if (ro != INVALID_ROW) mbytes = (VEC == 2 && rows[mc * VEC + 1] != INVALID_ROW) ? 16 : 8;
-    const unsigned sbase = (unsigned)__cvta_generic_to_shared(tile + mc * VEC);
-#pragma unroll
-    for (int p = 0; p < BK / KPP; ++p) {
-        const int kr = kr0 + p * KPP;
-        const unsigned k = k0 + kr;
-        const int bytes = (k < K) ? mbytes : 0;
-        const double* src = bytes ? base + ro + didx_off(kidx, k) : base;
-        const unsigned dst = sbase + kr * (PM * 8);
-        if (VEC == 2) cp_async16(dst, src, bytes);
-        else cp_async8(dst, src, bytes);
-    }
+__device__ __forceinline__ void cp_async_vec(unsigned dst, const void* src, int bytes) {
+    if (VEC == 2) cp_async16(dst, src, bytes);
+    else cp_async8(dst, src, bytes);
 }
 
+// One pass (256 chunks) of staging an operand tile of ROWS rows x BK k into shared memory.
+// Branch-free: layout (K-major / MN-major), validity and the compound-index decode are selects.
+//   rows[]  : element offset of each tile row, batch offset included (rows >= rlim unused)
+template <int VEC, int ROWS>
+__device__ __forceinline__ void stage_chunk(int q, unsigned tile_s, const double* base, const long long* rows,
+                                            int rlim, const DIdx& kidx, unsigned k0, unsigned K, int mn_major) {
+    constexpr int CHK = BK / VEC;          // chunks per row, K-major
+    constexpr int CHM = ROWS / VEC;        // chunks per k-row, MN-major
+    constexpr int PM = ROWS + 4;
+    constexpr int TOTAL = ROWS * BK / VEC;
+    const int fk = q % CHK, sk = q / CHK;  // K-major: (fast = k chunk, slow = row)
+    const int fm = q % CHM, sm = q / CHM;  // MN-major: (fast = row chunk, slow = k)
+    const int row = mn_major ? fm * VEC : sk;
+    const int kk = mn_major ? sm : fk * VEC;
+    const unsigned k = k0 + kk;
+    const int soff = mn_major ? sm * PM + fm * VEC : sk * PK + fk * VEC;
+    const bool in = (TOTAL % NTHREADS == 0) || (q < TOTAL);
+    const int r0 = (in && row < rlim && k < K) ? 1 : 0;
+    int r1 = 0;
+    if (VEC == 2) r1 = mn_major ? (row + 1 < rlim) : (k + 1 < K);
+    const int bytes = r0 * 8 * (1 + r1);
+    const long long ro = rows[in ? row : 0];
+    const double* src = bytes ? base + ro + didx_off(kidx, k) : base;
+    if (in) cp_async_vec<VEC>(tile_s + soff * 8, src, bytes);
+}
+
+template <int VEC, int MI>
 __global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_constant__ DParams p) {
+    constexpr int BM = 16 * MI;
+    constexpr int PMA = BM + 4, PMB = BN + 4;
+    constexpr int A_STAGE = (BM * PK > BK * PMA) ? BM * PK : BK * PMA;   // doubles
+    constexpr int B_STAGE = (BN * PK > BK * PMB) ? BN * PK : BK * PMB;
+    constexpr int A_PASSES = (BM * BK / VEC + NTHREADS - 1) / NTHREADS;
+    constexpr int B_PASSES = (BN * BK / VEC + NTHREADS - 1) / NTHREADS;
+
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* sA = reinterpret_cast<double*>(smem_raw);
-    double* sB = sA + STAGES * STAGE_ELEMS;
-    long long* rowA = reinterpret_cast<long long*>(sB + STAGES * STAGE_ELEMS);
+    double* sB = sA + STAGES * A_STAGE;
+    long long* rowA = reinterpret_cast<long long*>(sB + STAGES * B_STAGE);
     long long* rowB = rowA + BM;
-    int* sSeg = reinterpret_cast<int*>(rowB + BN);     // segment id of the tile held by each stage
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(rowB + BN);   // full[S], empty[S]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int wm = warp >> 2, wn = warp & 3;
@@ -142,116 +155,164 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_
     const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
     const int kt_hi = (int)(((long long)p.total_kt * (split + 1)) / p.splits);
     const int nkt = kt_hi - kt_lo;
+    const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
 
-    double acc[8][4][2];
+    const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
+    const unsigned sB_s = (unsigned)__cvta_generic_to_shared(sB);
+    const unsigned full_s = (unsigned)__cvta_generic_to_shared(bars);
+    const unsigned empty_s = full_s + 8 * STAGES;
+
+    if (tid == 0) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+        for (int s = 0; s < STAGES; ++s) {
+            mbar_init(full_s + 8 * s, NTHREADS);
+            mbar_init(empty_s + 8 * s, NTHREADS / 32);
+        }
+    }
+
+    double acc[MI][4][2];
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
     int cur_seg = -1;   // segment whose row tables are in shared memory (CTA-uniform)
 
-    auto load_tile = [&](int kt, int st) {
+    // segment of global k-tile kt
+    auto seg_of = [&](int kt) {
         int s = 0;
 #pragma unroll
         for (int q = 1; q < PCCB_MAX_SEGMENTS; ++q)
             if (q < p.nseg && kt >= p.seg[q].kt_begin) s = q;
+        return s;
+    };
+    // (re)build the per-row offset tables when the load front enters a new segment (CTA-uniform)
+    auto set_rows = [&](int s) {
         const DSeg& sg = p.seg[s];
-        if (s != cur_seg) {   // uniform: (re)build the per-row offset tables for this segment
-            __syncthreads();
-            if (tid < BM) {
-                const unsigned m = m0 + tid;
-                rowA[tid] = (m < p.M) ? didx_off(sg.am, m) + (long long)batch * sg.a_batch : INVALID_ROW;
+        __syncthreads();
+        for (int r = tid; r < BM + BN; r += NTHREADS) {
+            if (r < BM) {
+                const unsigned m = m0 + r;
+                rowA[r] = (m < p.M) ? didx_off(sg.am, m) + (long long)batch * sg.a_batch : 0;
             } else {
-                const unsigned n = n0 + (tid - BM);
-                rowB[tid - BM] = (n < p.N) ? didx_off(sg.bn, n) + (long long)batch * sg.b_batch : INVALID_ROW;
+                const unsigned n = n0 + (r - BM);
+                rowB[r - BM] = (n < p.N) ? didx_off(sg.bn, n) + (long long)batch * sg.b_batch : 0;
             }
-            __syncthreads();
-            cur_seg = s;
         }
+        __syncthreads();
+        cur_seg = s;
+    };
+    // issue this thread's share of the copies for global k-tile kt into stage st
+    auto issue_tile = [&](int kt, int st, int s) {
+        const DSeg& sg = p.seg[s];
         const unsigned k0 = (unsigned)(kt - sg.kt_begin) * BK;
-        double* ta = sA + st * STAGE_ELEMS;
-        double* tb = sB + st * STAGE_ELEMS;
-        if (sg.a_mn_major) {
-            if (sg.a_vec == 2) load_tile_mnmajor<2>(ta, sg.A, rowA, sg.ak, k0, sg.K, tid);
-            else load_tile_mnmajor<1>(ta, sg.A, rowA, sg.ak, k0, sg.K, tid);
-        } else {
-            if (sg.a_vec == 2) load_tile_kmajor<2>(ta, sg.A, rowA, sg.ak, k0, sg.K, tid);
-            else load_tile_kmajor<1>(ta, sg.A, rowA, sg.ak, k0, sg.K, tid);
-        }
-        if (sg.b_mn_major) {
-            if (sg.b_vec == 2) load_tile_mnmajor<2>(tb, sg.B, rowB, sg.bk, k0, sg.K, tid);
-            else load_tile_mnmajor<1>(tb, sg.B, rowB, sg.bk, k0, sg.K, tid);
-        } else {
-            if (sg.b_vec == 2) load_tile_kmajor<2>(tb, sg.B, rowB, sg.bk, k0, sg.K, tid);
-            else load_tile_kmajor<1>(tb, sg.B, rowB, sg.bk, k0, sg.K, tid);
-        }
-        if (tid == 0) sSeg[st] = s;
+        const unsigned ta = sA_s + st * (A_STAGE * 8), tb = sB_s + st * (B_STAGE * 8);
+#pragma unroll
+        for (int ps = 0; ps < A_PASSES; ++ps)
+            stage_chunk<VEC, BM>(tid + ps * NTHREADS, ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, sg.a_mn_major);
+#pragma unroll
+        for (int ps = 0; ps < B_PASSES; ++ps)
+            stage_chunk<VEC, BN>(tid + ps * NTHREADS, tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, sg.b_mn_major);
+        cp_async_mbar_arrive(full_s + 8 * st);
     };
 
+    // prologue: tiles 0 .. STAGES-2   (set_rows' barriers also publish the mbarrier inits)
 #pragma unroll 1
     for (int s = 0; s < STAGES - 1; ++s) {
-        if (s < nkt) load_tile(kt_lo + s, s);
-        cp_async_commit();
+        if (s < nkt) {
+            const int sg = seg_of(kt_lo + s);
+            if (sg != cur_seg) set_rows(sg);
+            issue_tile(kt_lo + s, s, sg);
+        }
     }
+    if (cur_seg < 0) __syncthreads();   // nkt == 0 cannot happen (host), kept for safety
 
     const int frow = lane >> 2, fk = lane & 3;
+    int seg_acc = -1;            // segment the accumulators are currently scaled for
+    double scale_acc = 1.0;
 #pragma unroll 1
     for (int it = 0; it < nkt; ++it) {
-        cp_async_wait<STAGES - 2>();
-        __syncthreads();
-        const int nxt = it + STAGES - 1;
-        if (nxt < nkt) load_tile(kt_lo + nxt, nxt % STAGES);
-        cp_async_commit();
-
         const int st = it % STAGES;
-        const DSeg& sg = p.seg[sSeg[st]];
-        const double scale = sg.scale;
-        const int a_rs = sg.a_mn_major ? 1 : PK, a_ks = sg.a_mn_major ? PM : 1;
-        const int b_rs = sg.b_mn_major ? 1 : PK, b_ks = sg.b_mn_major ? PM : 1;
-        const double* ap = sA + st * STAGE_ELEMS + (wm * 64 + frow) * a_rs + fk * a_ks;
-        const double* bp = sB + st * STAGE_ELEMS + (wn * 32 + frow) * b_rs + fk * b_ks;
+        mbar_wait(full_s + 8 * st, (it / STAGES) & 1);
+        const int sgi = seg_of(kt_lo + it);
+        const DSeg& sg = p.seg[sgi];
+        if (sgi != seg_acc) {    // rare, warp-uniform: acc holds sum/scale_acc; re-express for the new scale
+            if (seg_acc >= 0 && sg.scale != scale_acc) {
+                const double r = scale_acc / sg.scale;
 #pragma unroll
-        for (int ks = 0; ks < BK / 4; ++ks) {
-            double a[8], b[4];
+                for (int i = 0; i < MI; ++i)
 #pragma unroll
-            for (int i = 0; i < 8; ++i) a[i] = ap[i * 8 * a_rs + ks * 4 * a_ks];
+                    for (int j = 0; j < 4; ++j) { acc[i][j][0] *= r; acc[i][j][1] *= r; }
+            }
+            seg_acc = sgi;
+            scale_acc = sg.scale;
+        }
+        const int a_rs = sg.a_mn_major ? 1 : PK, a_ks = sg.a_mn_major ? PMA : 1;
+        const int b_rs = sg.b_mn_major ? 1 : PK, b_ks = sg.b_mn_major ? PMB : 1;
+        const double* ap = sA + st * A_STAGE + (wm * (8 * MI) + frow) * a_rs + fk * a_ks;
+        const double* bp = sB + st * B_STAGE + (wn * 32 + frow) * b_rs + fk * b_ks;
+
+        // next tile to fetch: it + STAGES - 1 into the stage tile it-1 occupied
+        const int nxt = it + STAGES - 1;
+        const bool have_next = nxt < nkt;
+        int nseg_id = 0;
+        if (have_next) {
+            nseg_id = seg_of(kt_lo + nxt);
+            if (nseg_id != cur_seg) set_rows(nseg_id);
+        }
+
+        double a[MI], b[4];
+        // k-step 0 first, so the other warps get time to release the stage we refill next
+#pragma unroll
+        for (int i = 0; i < MI; ++i) a[i] = ap[i * 8 * a_rs];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) b[j] = bp[j * 8 * b_rs];
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+
+        if (have_next && it >= 1) mbar_wait(empty_s + 8 * (nxt % STAGES), ((it - 1) / STAGES) & 1);
+        if (have_next) issue_tile(kt_lo + nxt, nxt % STAGES, nseg_id);
+
+#pragma unroll
+        for (int ks = 1; ks < BK / 4; ++ks) {
+#pragma unroll
+            for (int i = 0; i < MI; ++i) a[i] = ap[i * 8 * a_rs + ks * 4 * a_ks];
 #pragma unroll
             for (int j = 0; j < 4; ++j) b[j] = bp[j * 8 * b_rs + ks * 4 * b_ks];
-            if (scale != 1.0) {
 #pragma unroll
-                for (int i = 0; i < 8; ++i) a[i] *= scale;
-            }
-#pragma unroll
-            for (int i = 0; i < 8; ++i)
+            for (int i = 0; i < MI; ++i)
 #pragma unroll
                 for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
         }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_s + 8 * st);
     }
-    cp_async_wait<0>();
 
     // ---- epilogue ----------------------------------------------------------------------
     const unsigned colbase = n0 + wn * 32 + 2 * fk;
     if (p.splits > 1) {
         double* ws = p.ws + (size_t)blockIdx.z * p.M * p.N;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            const unsigned row = m0 + wm * 64 + i * 8 + frow;
+        for (int i = 0; i < MI; ++i) {
+            const unsigned row = m0 + wm * (8 * MI) + i * 8 + frow;
             if (row >= p.M) continue;
 #pragma unroll
             for (int j = 0; j < 4; ++j)
 #pragma unroll
                 for (int e = 0; e < 2; ++e) {
                     const unsigned col = colbase + j * 8 + e;
-                    if (col < p.N) ws[(size_t)row * p.N + col] = acc[i][j][e];
+                    if (col < p.N) ws[(size_t)row * p.N + col] = scale_acc * acc[i][j][e];
                 }
         }
         return;
     }
-    long long roff[8], droff[8];
+    const double alpha = p.alpha * scale_acc;
+    long long roff[MI], droff[MI];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-        const unsigned row = m0 + wm * 64 + i * 8 + frow;
+    for (int i = 0; i < MI; ++i) {
+        const unsigned row = m0 + wm * (8 * MI) + i * 8 + frow;
         roff[i] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
         droff[i] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
     }
@@ -264,9 +325,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_
             const long long co = didx_off(p.cn, col);
             const long long dco = p.D ? didx_off(p.dn, col) : 0;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
+            for (int i = 0; i < MI; ++i) {
                 if (roff[i] < 0) continue;
-                double v = p.alpha * acc[i][j][e];
+                double v = alpha * acc[i][j][e];
                 double* c = p.C + roff[i] + co;
                 if (p.beta != 0.0) v += p.beta * (*c);
                 if (p.D) v += p.gamma * p.D[droff[i] + dco];
@@ -318,34 +379,80 @@ __global__ void contract_f64_naive_kernel(const __grid_constant__ DParams p, lon
     }
 }
 
-constexpr size_t SMEM_BYTES = (size_t)2 * STAGES * STAGE_ELEMS * sizeof(double) + (BM + BN) * sizeof(long long) +
-                              STAGES * sizeof(int) + 16;
+template <int MI>
+constexpr size_t smem_bytes() {
+    constexpr int BM = 16 * MI;
+    constexpr int A_STAGE = (BM * PK > BK * (BM + 4)) ? BM * PK : BK * (BM + 4);
+    constexpr int B_STAGE = (BN * PK > BK * (BN + 4)) ? BN * PK : BK * (BN + 4);
+    return (size_t)STAGES * (A_STAGE + B_STAGE) * sizeof(double) + (BM + BN) * sizeof(long long) +
+           2 * STAGES * sizeof(unsigned long long) + 16;
+}
 
 bool even(long long x) { return (x & 1) == 0; }
 
-// Decide shared-memory layout and cp.async width of one operand of one segment.
-//   mn: index walking the tile rows (M or N), k: contraction index, extent_mn/extent_k: sizes.
-void choose_layout(const void* base, const DIdx& mn, long long extent_mn, const DIdx& k, long long extent_k,
-                   long long batch_stride, long long nbatch, int* mn_major, int* vec) {
+// Shared-memory layout of one operand of one segment and whether 16-byte copies are legal.
+//   mn: index walking the tile rows (M or N), k: contraction index.
+void choose_layout(const void* base, const DIdx& mn, const DIdx& k, long long batch_stride, long long nbatch,
+                   int* mn_major, bool* vec2_ok) {
     const bool base16 = (reinterpret_cast<uintptr_t>(base) & 15) == 0;
-    const bool mn_flat = mn.div >= (unsigned)extent_mn, k_flat = k.div >= (unsigned)extent_k;
     const bool batch_ok = nbatch <= 1 || even(batch_stride);
     if (k.s_lo == 1) {   // K-contiguous: tile[row][k]
         *mn_major = 0;
-        const bool ok = base16 && batch_ok && (k_flat || (even(k.div) && even(k.s_hi))) &&
-                        (mn_flat ? true : even(mn.s_hi)) && even(mn.s_lo);
-        *vec = ok ? 2 : 1;
+        *vec2_ok = base16 && batch_ok && (k.flat || (even(k.div) && even(k.s_hi))) && (mn.flat || even(mn.s_hi)) &&
+                   even(mn.s_lo);
         return;
     }
     if (mn.s_lo == 1) {  // row-contiguous: tile[k][row]
         *mn_major = 1;
-        const bool ok = base16 && batch_ok && (mn_flat || (even(mn.div) && even(mn.s_hi))) &&
-                        (k_flat ? true : even(k.s_hi)) && even(k.s_lo);
-        *vec = ok ? 2 : 1;
+        *vec2_ok = base16 && batch_ok && (mn.flat || (even(mn.div) && even(mn.s_hi))) && (k.flat || even(k.s_hi)) &&
+                   even(k.s_lo);
         return;
     }
     *mn_major = 0;       // no contiguous direction: element-wise gather
-    *vec = 1;
+    *vec2_ok = false;
+}
+
+template <int VEC, int MI>
+int launch_tile_kernel(pccb_ctx* ctx, const DParams& p, long long batch) {
+    constexpr int BM = 16 * MI;
+    constexpr size_t SMEM = smem_bytes<MI>();
+    static bool attr_set = false;
+    if (!attr_set) {
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_kernel<VEC, MI>,
+                                            cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+        attr_set = true;
+    }
+    dim3 grid((unsigned)((p.M + BM - 1) / BM), (unsigned)((p.N + BN - 1) / BN), (unsigned)(batch * p.splits));
+    contract_f64_kernel<VEC, MI><<<grid, NTHREADS, SMEM, ctx->stream>>>(p);
+    PCCB_CHECK_LAUNCH(ctx, "contract_f64_kernel");
+    return PCCB_OK;
+}
+
+template <int VEC>
+int dispatch_mi(pccb_ctx* ctx, const DParams& p, long long batch, int mi) {
+    switch (mi) {
+        case 1: return launch_tile_kernel<VEC, 1>(ctx, p, batch);
+        case 2: return launch_tile_kernel<VEC, 2>(ctx, p, batch);
+        case 4: return launch_tile_kernel<VEC, 4>(ctx, p, batch);
+        case 5: return launch_tile_kernel<VEC, 5>(ctx, p, batch);
+        case 6: return launch_tile_kernel<VEC, 6>(ctx, p, batch);
+        default: return launch_tile_kernel<VEC, 8>(ctx, p, batch);
+    }
+}
+
+// rows per CTA tile: minimise padded rows, prefer the taller tile on ties (more operand reuse)
+int choose_mi(long long M) {
+    static const int cand[] = {8, 6, 5, 4, 2, 1};
+    int best = 8;
+    long long best_cost = LLONG_MAX;
+    for (int mi : cand) {
+        const long long bm = 16 * mi;
+        long long padded = ((M + bm - 1) / bm) * bm;
+        // shorter tiles re-read the B operand more often: small penalty so that 128 wins near-ties
+        long long cost = padded * 64 + padded * (8 - mi);
+        if (cost < best_cost) { best_cost = cost; best = mi; }
+    }
+    return best;
 }
 
 }  // namespace
@@ -354,7 +461,7 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
     if (!ctx) return PCCB_ERR_ARG;
     PCCB_REQUIRE(ctx, d != nullptr, "pccb_contract: null descriptor");
     PCCB_REQUIRE(ctx, d->dtype == PCCB_F64, "pccb_contract: only PCCB_F64 is implemented (dtype=%d)", d->dtype);
-    PCCB_REQUIRE(ctx, d->nseg >= 1 && d->nseg <= PCCB_MAX_SEGMENTS, "pccb_contract: nseg=%d out of range", d->nseg);
+    PCCB_REQUIRE(ctx, d->nseg >= 0 && d->nseg <= PCCB_MAX_SEGMENTS, "pccb_contract: nseg=%d out of range", d->nseg);
     PCCB_REQUIRE(ctx, d->M > 0 && d->N > 0 && d->batch > 0, "pccb_contract: empty output (M=%lld N=%lld batch=%lld)",
                  (long long)d->M, (long long)d->N, (long long)d->batch);
     PCCB_REQUIRE(ctx, d->M < (1ll << 31) && d->N < (1ll << 31), "pccb_contract: M/N too large");
@@ -365,10 +472,11 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
     p.M = (unsigned)d->M;
     p.N = (unsigned)d->N;
     int kt = 0, ns = 0;
+    bool vec2 = true;
     for (int s = 0; s < d->nseg; ++s) {
         const pccb_segment& g = d->seg[s];
         PCCB_REQUIRE(ctx, g.K >= 0 && g.K < (1ll << 31), "pccb_contract: segment %d K out of range", s);
-        if (g.K == 0) continue;
+        if (g.K == 0 || g.scale == 0.0) continue;
         PCCB_REQUIRE(ctx, g.A_dev && g.B_dev, "pccb_contract: segment %d has a null operand", s);
         DSeg& o = p.seg[ns++];
         o.A = static_cast<const double*>(g.A_dev);
@@ -383,8 +491,10 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
         o.K = (unsigned)g.K;
         o.kt_begin = kt;
         kt += (int)((g.K + BK - 1) / BK);
-        choose_layout(o.A, o.am, d->M, o.ak, g.K, o.a_batch, d->batch, &o.a_mn_major, &o.a_vec);
-        choose_layout(o.B, o.bn, d->N, o.bk, g.K, o.b_batch, d->batch, &o.b_mn_major, &o.b_vec);
+        bool va, vb;
+        choose_layout(o.A, o.am, o.ak, o.a_batch, d->batch, &o.a_mn_major, &va);
+        choose_layout(o.B, o.bn, o.bk, o.b_batch, d->batch, &o.b_mn_major, &vb);
+        vec2 = vec2 && va && vb;
     }
     p.nseg = ns;
     p.total_kt = kt;
@@ -404,7 +514,7 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
 
     const long long total = (long long)d->M * d->N * d->batch;
     if (ctx->impl == PCCB_IMPL_NAIVE || ns == 0) {
-        // ns == 0: pure epilogue (alpha*0 + beta*C + gamma*D)
+        // ns == 0: pure epilogue (beta*C + gamma*D)
         const int threads = 256;
         long long blocks = (total + threads - 1) / threads;
         if (blocks > 148 * 64) blocks = 148 * 64;
@@ -413,7 +523,9 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
         return PCCB_OK;
     }
 
-    const long long gm = (d->M + BM - 1) / BM, gn = (d->N + BN - 1) / BN;
+    const int mi = choose_mi(d->M);
+    const long long bm = 16 * mi;
+    const long long gm = (d->M + bm - 1) / bm, gn = (d->N + BN - 1) / BN;
     PCCB_REQUIRE(ctx, gn <= 65535, "pccb_contract: N=%lld needs more than 65535 column tiles", (long long)d->N);
     const long long tiles = gm * gn * d->batch;
     int splits = 1;
@@ -429,15 +541,8 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
                  (long long)d->batch * splits);
     p.splits = splits;
 
-    static bool attr_set = false;
-    if (!attr_set) {
-        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                            (int)SMEM_BYTES));
-        attr_set = true;
-    }
-    dim3 grid((unsigned)gm, (unsigned)gn, (unsigned)(d->batch * splits));
-    contract_f64_kernel<<<grid, NTHREADS, SMEM_BYTES, ctx->stream>>>(p);
-    PCCB_CHECK_LAUNCH(ctx, "contract_f64_kernel");
+    int rc = vec2 ? dispatch_mi<2>(ctx, p, d->batch, mi) : dispatch_mi<1>(ctx, p, d->batch, mi);
+    if (rc != PCCB_OK) return rc;
     if (splits > 1) {
         const int threads = 256;
         long long blocks = (total + threads - 1) / threads;

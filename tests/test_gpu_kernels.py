@@ -36,6 +36,10 @@ CASES = [
     ("C[mn] = A[mk]*B[nk]", dict(A=(300, 500), B=(260, 500), C=(300, 260))),
     ("C[mn] = A[km]*B[kn]", dict(A=(333, 129), B=(333, 257), C=(129, 257))),                      # odd, MN-major, vec 1
     ("C[mn] = A[km]*B[nk]", dict(A=(64, 130), B=(258, 64), C=(130, 258))),
+    ("C[abc] = 0.5*A[eab]*B[ce] + 2.0*A2[eba]*B2[ce] - 3.0*A3[mc]*B3[mab]",
+     dict(A=(20, 22, 22), B=(22, 20), A2=(20, 22, 22), B2=(22, 20), A3=(6, 22), B3=(6, 22, 22), C=(22, 22, 22))),
+    ("C[ijab] = 0.5*A[ijef]*B[abef]", dict(A=(9, 9, 24, 24), B=(24, 24, 24, 24), C=(9, 9, 24, 24))),   # MI=6 tiles
+    ("C[ijab] = A[ijef]*B[abef]", dict(A=(20, 20, 16, 16), B=(16, 16, 16, 16), C=(20, 20, 16, 16))),    # MI=5 tiles
     ("C[abc] = A[eab]*B[ce] + A2[eba]*B2[ce] - A3[mc]*B3[mab]",
      dict(A=(20, 20, 20), B=(20, 20), A2=(20, 20, 20), B2=(20, 20), A3=(6, 20), B3=(6, 20, 20), C=(20, 20, 20))),
 ]
