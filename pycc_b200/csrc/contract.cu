@@ -28,6 +28,7 @@
 //   * small outputs (Fae, Fmi, Wmnij ...) use deterministic split-K through a caller-owned
 //     workspace, reduced in fixed order together with the alpha/beta/gamma epilogue.
 #include <climits>
+#include <cstdlib>
 #include <cstring>
 
 #include "common.cuh"
@@ -35,6 +36,7 @@
 namespace {
 
 constexpr int BN = 128, BK = 16, NTHREADS = 256, STAGES = 4;
+constexpr int DIST = STAGES - 2;   // prefetch distance in k-tiles: one spare stage of slack between warps
 constexpr int PK = BK + 4;    // pitch of a K-major tile row (doubles)
 
 struct DSeg {
@@ -106,30 +108,60 @@ __device__ __forceinline__ void cp_async_vec(unsigned dst, const void* src, int 
     else cp_async8(dst, src, bytes);
 }
 
-// One pass (256 chunks) of staging an operand tile of ROWS rows x BK k into shared memory.
-// Branch-free: layout (K-major / MN-major), validity and the compound-index decode are selects.
+// Stage an operand tile of ROWS rows x BK k into shared memory (this thread's share).
 //   rows[]  : element offset of each tile row, batch offset included (rows >= rlim unused)
+//   K-major : tile[row][k], pitch PK - a thread owns one k-chunk column, walks the rows
+//   MN-major: tile[k][row], pitch ROWS+4 - a thread owns one row chunk, walks the k rows
 template <int VEC, int ROWS>
-__device__ __forceinline__ void stage_chunk(int q, unsigned tile_s, const double* base, const long long* rows,
-                                            int rlim, const DIdx& kidx, unsigned k0, unsigned K, int mn_major) {
-    constexpr int CHK = BK / VEC;          // chunks per row, K-major
-    constexpr int CHM = ROWS / VEC;        // chunks per k-row, MN-major
+__device__ __forceinline__ void load_tile_kmajor(unsigned tile_s, const double* base, const long long* rows,
+                                                 int rlim, const DIdx& kidx, unsigned k0, unsigned K, int tid) {
+    constexpr int CH = BK / VEC;            // chunks per row
+    constexpr int RPP = NTHREADS / CH;      // rows per pass
+    constexpr int PASSES = (ROWS + RPP - 1) / RPP;
+    const int kc = tid % CH, r0 = tid / CH;
+    const unsigned k = k0 + kc * VEC;
+    int kbytes = 0;
+    const double* bk = base;
+    if (k < K) {
+        bk = base + didx_off(kidx, k);
+        kbytes = (VEC == 2 && k + 1 < K) ? 16 : 8;
+    }
+    const unsigned dst0 = tile_s + (r0 * PK + kc * VEC) * 8;
+#pragma unroll
+    for (int ps = 0; ps < PASSES; ++ps) {
+        const int row = r0 + ps * RPP;
+        if (ROWS % RPP == 0 || row < ROWS) {
+            const int bytes = (row < rlim) ? kbytes : 0;
+            const double* src = bytes ? bk + rows[row] : base;
+            cp_async_vec<VEC>(dst0 + ps * (RPP * PK * 8), src, bytes);
+        }
+    }
+}
+
+template <int VEC, int ROWS>
+__device__ __forceinline__ void load_tile_mnmajor(unsigned tile_s, const double* base, const long long* rows,
+                                                  int rlim, const DIdx& kidx, unsigned k0, unsigned K, int tid) {
     constexpr int PM = ROWS + 4;
-    constexpr int TOTAL = ROWS * BK / VEC;
-    const int fk = q % CHK, sk = q / CHK;  // K-major: (fast = k chunk, slow = row)
-    const int fm = q % CHM, sm = q / CHM;  // MN-major: (fast = row chunk, slow = k)
-    const int row = mn_major ? fm * VEC : sk;
-    const int kk = mn_major ? sm : fk * VEC;
-    const unsigned k = k0 + kk;
-    const int soff = mn_major ? sm * PM + fm * VEC : sk * PK + fk * VEC;
-    const bool in = (TOTAL % NTHREADS == 0) || (q < TOTAL);
-    const int r0 = (in && row < rlim && k < K) ? 1 : 0;
-    int r1 = 0;
-    if (VEC == 2) r1 = mn_major ? (row + 1 < rlim) : (k + 1 < K);
-    const int bytes = r0 * 8 * (1 + r1);
-    const long long ro = rows[in ? row : 0];
-    const double* src = bytes ? base + ro + didx_off(kidx, k) : base;
-    if (in) cp_async_vec<VEC>(tile_s + soff * 8, src, bytes);
+    constexpr int CH = ROWS / VEC;                                   // chunks per k-row
+    constexpr int KPP = (NTHREADS / CH) < BK ? (NTHREADS / CH) : BK; // k-rows per pass
+    constexpr int PASSES = (BK + KPP - 1) / KPP;
+    const int mc = tid % CH, kr0 = tid / CH;
+    const int row = mc * VEC;
+    if (kr0 >= KPP) return;
+    int mbytes = 0;
+    if (row < rlim) mbytes = (VEC == 2 && row + 1 < rlim) ? 16 : 8;
+    const double* bm = base + rows[row];
+    const unsigned dst0 = tile_s + (kr0 * PM + row) * 8;
+#pragma unroll
+    for (int ps = 0; ps < PASSES; ++ps) {
+        const int kr = kr0 + ps * KPP;
+        if (BK % KPP == 0 || kr < BK) {
+            const unsigned k = k0 + kr;
+            const int bytes = (k < K) ? mbytes : 0;
+            const double* src = bytes ? bm + didx_off(kidx, k) : base;
+            cp_async_vec<VEC>(dst0 + ps * (KPP * PM * 8), src, bytes);
+        }
+    }
 }
 
 template <int VEC, int MI>
@@ -138,8 +170,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_
     constexpr int PMA = BM + 4, PMB = BN + 4;
     constexpr int A_STAGE = (BM * PK > BK * PMA) ? BM * PK : BK * PMA;   // doubles
     constexpr int B_STAGE = (BN * PK > BK * PMB) ? BN * PK : BK * PMB;
-    constexpr int A_PASSES = (BM * BK / VEC + NTHREADS - 1) / NTHREADS;
-    constexpr int B_PASSES = (BN * BK / VEC + NTHREADS - 1) / NTHREADS;
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* sA = reinterpret_cast<double*>(smem_raw);
@@ -207,18 +237,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_
         const DSeg& sg = p.seg[s];
         const unsigned k0 = (unsigned)(kt - sg.kt_begin) * BK;
         const unsigned ta = sA_s + st * (A_STAGE * 8), tb = sB_s + st * (B_STAGE * 8);
-#pragma unroll
-        for (int ps = 0; ps < A_PASSES; ++ps)
-            stage_chunk<VEC, BM>(tid + ps * NTHREADS, ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, sg.a_mn_major);
-#pragma unroll
-        for (int ps = 0; ps < B_PASSES; ++ps)
-            stage_chunk<VEC, BN>(tid + ps * NTHREADS, tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, sg.b_mn_major);
+        if (sg.a_mn_major) load_tile_mnmajor<VEC, BM>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, tid);
+        else load_tile_kmajor<VEC, BM>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, tid);
+        if (sg.b_mn_major) load_tile_mnmajor<VEC, BN>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, tid);
+        else load_tile_kmajor<VEC, BN>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, tid);
         cp_async_mbar_arrive(full_s + 8 * st);
     };
 
-    // prologue: tiles 0 .. STAGES-2   (set_rows' barriers also publish the mbarrier inits)
+    // prologue: tiles 0 .. DIST-1   (set_rows' barriers also publish the mbarrier inits)
 #pragma unroll 1
-    for (int s = 0; s < STAGES - 1; ++s) {
+    for (int s = 0; s < DIST; ++s) {
         if (s < nkt) {
             const int sg = seg_of(kt_lo + s);
             if (sg != cur_seg) set_rows(sg);
@@ -228,66 +256,96 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_
     if (cur_seg < 0) __syncthreads();   // nkt == 0 cannot happen (host), kept for safety
 
     const int frow = lane >> 2, fk = lane & 3;
+
+    // Fragment addressing of the tile held by a stage (layout is a per-segment property).
+    struct FragPtr {
+        const double* ap;
+        const double* bp;
+        int a_rs, a_ks, b_rs, b_ks;
+    };
+    auto frag_ptr = [&](int it_) {
+        const DSeg& sg = p.seg[seg_of(kt_lo + it_)];
+        const int st = it_ % STAGES;
+        FragPtr f;
+        f.a_rs = sg.a_mn_major ? 1 : PK;
+        f.a_ks = sg.a_mn_major ? PMA : 1;
+        f.b_rs = sg.b_mn_major ? 1 : PK;
+        f.b_ks = sg.b_mn_major ? PMB : 1;
+        f.ap = sA + st * A_STAGE + (wm * (8 * MI) + frow) * f.a_rs + fk * f.a_ks;
+        f.bp = sB + st * B_STAGE + (wn * 32 + frow) * f.b_rs + fk * f.b_ks;
+        return f;
+    };
+
+    // Software pipeline over (k-tile, k-step): the fragments of step g+1 are fetched from shared
+    // memory while the DMMAs of step g issue (a[i] is refilled right after its last use, only b
+    // is double-buffered), so a warp never waits on LDS latency between DMMA groups.
+    double a[MI], b[4], bnx[4];
+    mbar_wait(full_s, 0);
+    FragPtr fp = frag_ptr(0);
+#pragma unroll
+    for (int i = 0; i < MI; ++i) a[i] = fp.ap[i * 8 * fp.a_rs];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) b[j] = fp.bp[j * 8 * fp.b_rs];
+
     int seg_acc = -1;            // segment the accumulators are currently scaled for
     double scale_acc = 1.0;
 #pragma unroll 1
     for (int it = 0; it < nkt; ++it) {
         const int st = it % STAGES;
-        mbar_wait(full_s + 8 * st, (it / STAGES) & 1);
-        const int sgi = seg_of(kt_lo + it);
-        const DSeg& sg = p.seg[sgi];
-        if (sgi != seg_acc) {    // rare, warp-uniform: acc holds sum/scale_acc; re-express for the new scale
-            if (seg_acc >= 0 && sg.scale != scale_acc) {
-                const double r = scale_acc / sg.scale;
+        {
+            const int sgi = seg_of(kt_lo + it);
+            if (sgi != seg_acc) {    // rare, warp-uniform: acc holds sum/scale_acc; re-express for the new scale
+                const double sc = p.seg[sgi].scale;
+                if (seg_acc >= 0 && sc != scale_acc) {
+                    const double r = scale_acc / sc;
 #pragma unroll
-                for (int i = 0; i < MI; ++i)
+                    for (int i = 0; i < MI; ++i)
 #pragma unroll
-                    for (int j = 0; j < 4; ++j) { acc[i][j][0] *= r; acc[i][j][1] *= r; }
+                        for (int j = 0; j < 4; ++j) { acc[i][j][0] *= r; acc[i][j][1] *= r; }
+                }
+                seg_acc = sgi;
+                scale_acc = sc;
             }
-            seg_acc = sgi;
-            scale_acc = sg.scale;
         }
-        const int a_rs = sg.a_mn_major ? 1 : PK, a_ks = sg.a_mn_major ? PMA : 1;
-        const int b_rs = sg.b_mn_major ? 1 : PK, b_ks = sg.b_mn_major ? PMB : 1;
-        const double* ap = sA + st * A_STAGE + (wm * (8 * MI) + frow) * a_rs + fk * a_ks;
-        const double* bp = sB + st * B_STAGE + (wn * 32 + frow) * b_rs + fk * b_ks;
-
-        // next tile to fetch: it + STAGES - 1 into the stage tile it-1 occupied
-        const int nxt = it + STAGES - 1;
-        const bool have_next = nxt < nkt;
-        int nseg_id = 0;
-        if (have_next) {
-            nseg_id = seg_of(kt_lo + nxt);
-            if (nseg_id != cur_seg) set_rows(nseg_id);
-        }
-
-        double a[MI], b[4];
-        // k-step 0 first, so the other warps get time to release the stage we refill next
+        FragPtr fn = fp;
 #pragma unroll
-        for (int i = 0; i < MI; ++i) a[i] = ap[i * 8 * a_rs];
+        for (int ks = 0; ks < BK / 4; ++ks) {
+            const int nks = (ks + 1) % (BK / 4);
+            bool more = true;
+            if (ks == BK / 4 - 1) {          // next step lives in the next k-tile
+                more = it + 1 < nkt;
+                if (more) {
+                    mbar_wait(full_s + 8 * ((it + 1) % STAGES), ((it + 1) / STAGES) & 1);
+                    fn = frag_ptr(it + 1);
+                }
+            }
+            if (more) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) b[j] = bp[j * 8 * b_rs];
+                for (int j = 0; j < 4; ++j) bnx[j] = fn.bp[j * 8 * fn.b_rs + nks * 4 * fn.b_ks];
+            }
 #pragma unroll
-        for (int i = 0; i < MI; ++i)
-#pragma unroll
-            for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
-
-        if (have_next && it >= 1) mbar_wait(empty_s + 8 * (nxt % STAGES), ((it - 1) / STAGES) & 1);
-        if (have_next) issue_tile(kt_lo + nxt, nxt % STAGES, nseg_id);
-
-#pragma unroll
-        for (int ks = 1; ks < BK / 4; ++ks) {
-#pragma unroll
-            for (int i = 0; i < MI; ++i) a[i] = ap[i * 8 * a_rs + ks * 4 * a_ks];
-#pragma unroll
-            for (int j = 0; j < 4; ++j) b[j] = bp[j * 8 * b_rs + ks * 4 * b_ks];
-#pragma unroll
-            for (int i = 0; i < MI; ++i)
+            for (int i = 0; i < MI; ++i) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                if (more) a[i] = fn.ap[i * 8 * fn.a_rs + nks * 4 * fn.a_ks];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bnx[j];
+
+            if (ks == 0) {
+                // refill: k-tile it + DIST goes into the stage that tile it + DIST - STAGES occupied
+                const int nxt = it + DIST;
+                if (nxt < nkt) {
+                    const int nseg_id = seg_of(kt_lo + nxt);
+                    if (nseg_id != cur_seg) set_rows(nseg_id);
+                    if (nxt >= STAGES) mbar_wait(empty_s + 8 * (nxt % STAGES), ((nxt - STAGES) / STAGES) & 1);
+                    issue_tile(kt_lo + nxt, nxt % STAGES, nseg_id);
+                }
+            }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(empty_s + 8 * st);
+        fp = fn;
     }
 
     // ---- epilogue ----------------------------------------------------------------------
@@ -442,6 +500,9 @@ int dispatch_mi(pccb_ctx* ctx, const DParams& p, long long batch, int mi) {
 
 // rows per CTA tile: minimise padded rows, prefer the taller tile on ties (more operand reuse)
 int choose_mi(long long M) {
+    // tuning hook for tools/bench_contract.py: PCCB_MI=<1|2|4|5|6|8> forces the tile height
+    static const int forced = [] { const char* e = getenv("PCCB_MI"); return e ? atoi(e) : 0; }();
+    if (forced == 1 || forced == 2 || forced == 4 || forced == 5 || forced == 6 || forced == 8) return forced;
     static const int cand[] = {8, 6, 5, 4, 2, 1};
     int best = 8;
     long long best_cost = LLONG_MAX;

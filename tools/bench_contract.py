@@ -7,6 +7,7 @@ from pycc_b200.backend import CudaBackend
 from pycc_b200.dsl import plan
 
 o, v = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (20, 150)
+only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
 be = CudaBackend()
 dev = be.device
 R = lambda *s: torch.randn(s, dtype=torch.float64, device=dev)
@@ -22,6 +23,7 @@ tests = [("ladder", "r2[ijab] += 0.5*tau[ijef]*vvvv[abef]", 2.0 * o * o * v ** 4
          ("t1ovvv", "r2[ijab] += t1[ie]*ovvv[jabe]", 2.0 * o ** 2 * v ** 3)]
 res = {}
 for name, stmt, fl in tests:
+    if only and name not in only: continue
     Ls = plan(stmt, T)
     for _ in range(2):
         for L in Ls: be.contract(L.desc)
