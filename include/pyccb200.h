@@ -135,14 +135,15 @@ int pccb_lincomb(pccb_ctx* ctx, int dtype, void* out_dev, const void* const* vec
                  const double* coef_host, int nvec, int64_t n); /* out = sum_k coef[k]*vec[k] */
 
 /* ---- (T): disconnected triples + Lee-Rendell energy reduction -----------------------------
- * For `ntrip` occupied triplets (i>=j>=k given in ijk_host[3*ntrip]) whose connected W[a,b,c]
- * (pycc/cctriples.py:10-22, built by 3 pccb_contract launches each) sit in w_dev[t][a][b][c]:
- * forms V = W + t3d_ijk (cctriples.py:69-74), the X/Y/Z combinations and the restricted sum
- * over a>=b>=c with the occupation factor and denominator (cctriples.py:124-150).
- * et_host[t] receives each triplet's energy contribution.  Host-returning. */
-int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, const int32_t* ijk_host, int ntrip,
+ * For `ntrip` occupied triplets (i>=j>=k, device array ijk_dev[3*ntrip]) whose connected W[a,b,c]
+ * (pycc/cctriples.py:10-22, built by 3 pccb_contract launches per batch) sit in
+ * w_dev[t][a][b][c]: forms V = W + t3d_ijk (cctriples.py:69-74), the X/Y/Z combinations and
+ * the restricted sum over a>=b>=c with the occupation factor and denominator
+ * (cctriples.py:124-150).  et_dev[t] (DEVICE, always double) receives each triplet's energy.
+ * Asynchronous: the caller sums et_dev after pccb_synchronize(). */
+int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, const int32_t* ijk_dev, int ntrip,
                         const void* t1_dev, const void* t2_dev, const void* oovv_dev, const void* fov_dev,
-                        int64_t ld_fov, const void* eps_dev, int64_t no, int64_t nv, double* et_host);
+                        int64_t ld_fov, const void* eps_dev, int64_t no, int64_t nv, double* et_dev);
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,10 @@
+"""
+pycc_b200: B200-native engine for PyCC's RHF-CCSD amplitude iteration and (T) correction.
+Public names mirror ``pycc/__init__.py:9-18`` for the path it covers.
+"""
+from .ccwfn import ccwfn
+from .cctriples import t_tjl, t_vikings, t3c_ijk, t3d_ijk
+from .utils import helper_diis, cc_contract
+from .hamiltonian import Hamiltonian
+
+__all__ = ["ccwfn", "t_tjl", "t_vikings", "t3c_ijk", "t3d_ijk", "helper_diis", "cc_contract", "Hamiltonian"]

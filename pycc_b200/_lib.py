@@ -84,7 +84,7 @@ def load():
     lib.pccb_dot.argtypes = [vp, i32, vp, vp, i64, pd]
     lib.pccb_axpby.argtypes = [vp, i32, vp, dbl, vp, dbl, vp, i64]
     lib.pccb_lincomb.argtypes = [vp, i32, vp, C.POINTER(vp), pd, i32, i64]
-    lib.pccb_triples_energy.argtypes = [vp, i32, vp, C.POINTER(C.c_int32), i32, vp, vp, vp, vp, i64, vp, i64, i64, pd]
+    lib.pccb_triples_energy.argtypes = [vp, i32, vp, vp, i32, vp, vp, vp, vp, i64, vp, i64, i64, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
         if name not in ("pccb_last_error",):

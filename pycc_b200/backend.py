@@ -135,12 +135,9 @@ class CudaBackend(object):
         cs = (C.c_double * n)(*[float(c) for c in coefs])
         self._check(self.lib.pccb_lincomb(self.h, dtype_code(out), out.data_ptr(), ptrs, cs, n, out.numel()))
 
-    def triples_energy(self, W, ijk, t1, t2, oovv, fov, ld_fov, eps, no, nv):
-        """W: [ntrip, nv, nv, nv]; ijk: list of (i,j,k).  Returns a list of per-triplet energies."""
-        n = len(ijk)
-        flat = (C.c_int32 * (3 * n))(*[int(x) for t in ijk for x in t])
-        out = (C.c_double * n)()
-        self._check(self.lib.pccb_triples_energy(self.h, dtype_code(W), W.data_ptr(), flat, n, t1.data_ptr(),
-                                                 t2.data_ptr(), oovv.data_ptr(), fov.data_ptr(), ld_fov,
-                                                 eps.data_ptr(), no, nv, out))
-        return list(out)
+    def triples_energy(self, W, ijk_dev, ntrip, t1, t2, oovv, fov, ld_fov, eps, no, nv, et_dev):
+        """W: [>=ntrip, nv, nv, nv]; ijk_dev: int32 device tensor [3*ntrip]; et_dev: float64 device tensor
+        [ntrip] that receives the per-triplet energies (asynchronously)."""
+        self._check(self.lib.pccb_triples_energy(self.h, dtype_code(W), W.data_ptr(), ijk_dev.data_ptr(), ntrip,
+                                                 t1.data_ptr(), t2.data_ptr(), oovv.data_ptr(), fov.data_ptr(),
+                                                 ld_fov, eps.data_ptr(), no, nv, et_dev.data_ptr()))

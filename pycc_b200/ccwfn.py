@@ -1,0 +1,300 @@
+"""
+ccwfn.py: CC T-amplitude solver, API-compatible with ``pycc/ccwfn.py`` for the RHF-CCSD and
+CCSD(T) models, executing on the B200 engine (``pycc_b200.engine`` over libpyccb200.so).
+
+    wfn = ccwfn(scf_wfn, model='CCSD(T)')            # psi4 wavefunction (needs psi4), or
+    wfn = ccwfn.from_arrays(F, ERI, no)              # full Dirac ERI (n,n,n,n), or
+    wfn = ccwfn.from_arrays(F, blocks, no)           # dict of the six blocks (see hamiltonian.py)
+    ecc = wfn.solve_cc(e_conv=1e-7, r_conv=1e-7, maxiter=100, max_diis=8, start_diis=1)
+
+Same constructor kwargs, method names, argument orders, printed iteration lines and return
+conventions as the reference (``pycc/ccwfn.py:62-329``); arrays are ``torch.Tensor`` on the
+device (``.cpu().numpy()`` gives the reference's ndarrays).  There is no CPU path: without the
+CUDA library or a B200 the constructor raises.
+"""
+import time
+
+import numpy as np
+import torch
+
+from . import _lib
+from .engine import CCSDEngine
+from .hamiltonian import Hamiltonian, BLOCKS
+from .utils import helper_diis, cc_contract
+
+
+class ccwfn(object):
+    """An RHF-CC wave function and energy object (see module docstring).
+
+    Attributes mirror the reference (``pycc/ccwfn.py:23-52``): ref, eref, nfzc, no, nv, nmo, nact,
+    H, o, v, Dia, Dijab, t1, t2, ecc, model, local, precision, device, contract.
+    """
+
+    valid_cc_models = ['CCD', 'CC2', 'CCSD', 'CCSD(T)', 'CC3']
+    engine_models = ['CCSD', 'CCSD(T)']
+
+    def __init__(self, scf_wfn, **kwargs):
+        try:
+            import psi4  # noqa: F401
+        except ImportError:
+            raise Exception("ccwfn(scf_wfn) needs psi4 for the MO integrals (pycc/hamiltonian.py:32-38); "
+                            "use ccwfn.from_arrays(F, ERI_or_blocks, no) instead.")
+        import psi4
+        time_init = time.time()
+        ref = scf_wfn
+        nfzc = ref.frzcpi()[0]
+        no = ref.doccpi()[0] - nfzc
+        nmo = ref.nmo()
+        nv = nmo - no - nfzc
+        C = ref.Ca_subset("AO", "ACTIVE")
+        npC = np.asarray(C)
+        # Hamiltonian arrays exactly as pycc/hamiltonian.py:32-38 builds them
+        F = npC.T @ np.asarray(ref.Fa()) @ npC
+        mints = psi4.core.MintsHelper(ref.basisset())
+        ERI = np.asarray(mints.mo_eri(C, C, C, C)).swapaxes(1, 2)
+        self._setup(F, ERI, no, nv, kwargs, eref=ref.energy(), nfzc=nfzc, ref=ref, C=C, time_init=time_init)
+
+    @classmethod
+    def from_arrays(cls, F, ERI_or_blocks, no, eref=0.0, **kwargs):
+        """psi4-free constructor: ``F`` (n,n) Fock matrix, ``ERI_or_blocks`` either the full Dirac
+        array ``<pq|rs>`` (n,n,n,n) or a dict with the six blocks oooo, ooov, oovv, ovov, ovvv, vvvv
+        (NumPy or torch, host or device), ``no`` active occupied orbitals."""
+        self = object.__new__(cls)
+        n = F.shape[0]
+        self._setup(F, ERI_or_blocks, int(no), int(n - no), kwargs, eref=eref, nfzc=0, ref=None, C=None,
+                    time_init=time.time())
+        return self
+
+    # -----------------------------------------------------------------------------------------
+    def _setup(self, F, ERI, no, nv, kwargs, eref, nfzc, ref, C, time_init):
+        model = kwargs.pop('model', 'CCSD').upper()
+        if model not in self.valid_cc_models:
+            raise Exception("%s is not an allowed CC model." % (model))
+        if model not in self.engine_models:
+            raise Exception("%s is not available in the B200 engine yet (CCSD and CCSD(T) are)." % (model))
+        self.model = model
+        self.need_singles = ['CCSD', 'CCSD(T)', 'CC2', 'CC3']
+        self.need_t1_transform = ['CC3']
+        self.make_t3_density = kwargs.pop('make_t3_density', False)
+        if self.make_t3_density:
+            raise Exception("make_t3_density (Lambda/(T) densities) is outside the B200 engine's scope.")
+        self.real_time = kwargs.pop('real_time', False)
+
+        valid_local_models = [None, 'PNO', 'PAO', 'CPNO++', 'PNO++']
+        local = kwargs.pop('local', None)
+        if local not in valid_local_models:
+            raise Exception("%s is not an allowed local-CC model." % (local))
+        if local is not None:
+            raise Exception("local-correlation models are outside the B200 engine's scope (local=None only).")
+        self.local = local
+        self.local_cutoff = kwargs.pop('local_cutoff', 1e-5)
+        valid_local_MOs = ['PIPEK_MEZEY', 'BOYS']
+        local_MOs = kwargs.pop('local_mos', 'PIPEK_MEZEY')
+        if local_MOs not in valid_local_MOs:
+            raise Exception("%s is not an allowed MO localization method." % (local_MOs))
+        self.local_MOs = local_MOs
+        it2_opt = kwargs.pop('it2_opt', True)
+        if it2_opt not in [True, False]:
+            raise Exception("%s is not an allowed initial t2 amplitudes." % (it2_opt))
+        self.it2_opt = it2_opt
+        filt = kwargs.pop('filter', False)
+        if filt not in [True, False]:
+            raise Exception("%s is not an allowed local filter." % (filt))
+        self.filter = filt
+
+        valid_precision = ['SP', 'DP']
+        precision = kwargs.pop('precision', 'DP')
+        if precision.upper() not in valid_precision:
+            raise Exception('%s is not an allowed precision arithmetic.' % (precision))
+        self.precision = precision.upper()
+        if self.precision == 'SP':
+            raise Exception("precision='SP' (FP32 contractions) is not implemented in the B200 engine yet.")
+        valid_device = ['CPU', 'GPU']
+        device = kwargs.pop('device', 'GPU')
+        if device.upper() not in valid_device:
+            raise Exception("%s is not an allowed device." % (device))
+        # the engine has one execution path: the B200.  device='CPU' is accepted for call-site
+        # compatibility with the reference (its default) but does not select a CPU implementation.
+        self.device = 'GPU'
+
+        backend = kwargs.pop('_backend', None)
+        if backend is None:
+            from .backend import CudaBackend
+            backend = CudaBackend()
+        self.backend = backend
+        self.device0 = torch.device('cpu')
+        self.device1 = backend.device
+
+        self.ref = ref
+        self.eref = eref
+        self.nfzc = nfzc
+        self.no, self.nv = no, nv
+        self.nmo = no + nv + nfzc
+        self.nact = no + nv
+        print("NMO = %d; NACT = %d; NO = %d; NV = %d" % (self.nmo, self.nact, self.no, self.nv))
+        self.o = slice(0, no)
+        self.v = slice(no, no + nv)
+        self.C = C
+
+        dtype = torch.float64
+        if isinstance(ERI, dict):
+            self.H = Hamiltonian.from_blocks(F, ERI, no, backend.device, dtype)
+        else:
+            if tuple(ERI.shape) != (no + nv,) * 4:
+                raise Exception("ERI must be the full (n,n,n,n) Dirac array or a dict of blocks %s" % (BLOCKS,))
+            self.H = Hamiltonian.from_full(F, ERI, no, backend.device, dtype)
+        self.engine = CCSDEngine(backend, self.H.F, self.H.blocks, no, nv, dtype)
+        self.H.F = self.engine.F
+        self._triples = None
+
+        # first-order amplitudes (pycc/ccwfn.py:170-175): t1 = 0, t2 = <ij|ab>/Dijab
+        self.t1, self.t2 = self.engine.t1, self.engine.t2
+        self.t1.zero_()
+        self.t2.zero_()
+        zero1 = backend.zeros((no, nv), dtype)
+        backend.bind_stream()
+        backend.update_amplitudes(self.t1, self.t2, zero1, self.H.blocks["oovv"], self.engine.eps, no, nv, False)
+        self.contract = cc_contract(device=self.device, backend=backend)
+        self.ecc = None
+        print("CCWFN object initialized in %.3f seconds." % (time.time() - time_init))
+
+    # denominators (pycc/ccwfn.py:164-167), materialised on demand for API compatibility; the
+    # engine's kernels recompute them from the Fock diagonal instead of reading N2-sized arrays
+    @property
+    def Dia(self):
+        eps = self.engine.eps
+        return eps[:self.no].reshape(-1, 1) - eps[self.no:]
+
+    @property
+    def Dijab(self):
+        eps = self.engine.eps
+        eo, ev = eps[:self.no], eps[self.no:]
+        return eo.reshape(-1, 1, 1, 1) + eo.reshape(-1, 1, 1) - ev.reshape(-1, 1) - ev
+
+    # -----------------------------------------------------------------------------------------
+    def solve_cc(self, e_conv=1e-7, r_conv=1e-7, maxiter=100, max_diis=8, start_diis=1):
+        """Solve the CC amplitude equations (pycc/ccwfn.py:234-329).  Returns the correlation
+        energy (plus E(T) for model 'CCSD(T)'), or None when not converged in ``maxiter``."""
+        ccsd_tstart = time.time()
+        eng = self.engine
+        ecc = eng.energy()
+        print("CC Iter %3d: CC Ecorr = %.15f  dE = % .5E  MP2" % (0, ecc, -ecc))
+        diis = helper_diis(self.t1, self.t2, max_diis, self.precision, backend=self.backend)
+        self.iteration_log = []
+        for niter in range(1, maxiter + 1):
+            ecc_last = ecc
+            eng.residuals(symmetrize=False)
+            # t += r/D with the pair symmetrisation of r2 (ccwfn.py:621) folded into the update
+            rms = np.sqrt(eng.update(symmetrize_on_the_fly=True))
+            ecc = eng.energy()
+            ediff = ecc - ecc_last
+            print("CC Iter %3d: CC Ecorr = %.15f  dE = % .5E  rms = % .5E" % (niter, ecc, ediff, rms))
+            self.iteration_log.append((niter, ecc, ediff, rms))
+            if (abs(ediff) < e_conv) and abs(rms) < r_conv:
+                print("\nCCWFN converged in %.3f seconds.\n" % (time.time() - ccsd_tstart))
+                print("E(REF)  = %20.15f" % self.eref)
+                if self.model == 'CCSD(T)':
+                    print("E(CCSD) = %20.15f" % ecc)
+                    from .cctriples import t_tjl
+                    et = t_tjl(self)
+                    print("E(T)    = %20.15f" % et)
+                    ecc = ecc + et
+                else:
+                    print("E(%s) = %20.15f" % (self.model, ecc))
+                self.ecc = ecc
+                print("E(TOT)  = %20.15f" % (ecc + self.eref))
+                return ecc
+            diis.add_error_vector(self.t1, self.t2)
+            if niter >= start_diis:
+                self.t1, self.t2 = diis.extrapolate(self.t1, self.t2)
+
+    def _load(self, F, t1, t2):
+        eng = self.engine
+        if F is not None and F is not eng.F:
+            eng.set_fock(F)
+        if t1 is not eng.t1:
+            eng.t1.copy_(torch.as_tensor(t1).to(eng.t1.device, eng.dtype))
+        if t2 is not eng.t2:
+            eng.t2.copy_(torch.as_tensor(t2).to(eng.t2.device, eng.dtype))
+
+    def residuals(self, F, t1, t2, real_time=False):
+        """r1, r2 = <mu|HBAR|0> for the given Fock operator and amplitudes (pycc/ccwfn.py:331-406).
+        Pure with respect to the stored amplitudes when called with its own copies; returns new
+        tensors."""
+        self._load(F, t1, t2)
+        r1, r2 = self.engine.residuals(symmetrize=True)
+        return r1.clone(), r2.clone()
+
+    def build_tau(self, t1, t2, fact1=1.0, fact2=1.0):
+        out = self.backend.empty(tuple(t2.shape), self.engine.dtype)
+        t1d = torch.as_tensor(t1).to(out.device, out.dtype).contiguous()
+        t2d = torch.as_tensor(t2).to(out.device, out.dtype).contiguous()
+        self.backend.bind_stream()
+        self.backend.pair_combine(out, t2d, fact1, 0.0, t1d, t1d, fact2, self.no, self.nv)
+        return out
+
+    # Builders keep the reference's signatures (pycc/ccwfn.py:413-537).  The integral arguments
+    # (ERI, L) are accepted for call-site compatibility; the engine uses the blocks of self.H.
+    def _builder(self, name, F, t1, t2):
+        self._load(F, t1, t2)
+        self.engine.run_builder(name)
+
+    def build_Fae(self, o, v, F, L, t1, t2):
+        self._builder("Fae", F, t1, t2)
+        return self.engine.Fae.clone()
+
+    def build_Fmi(self, o, v, F, L, t1, t2):
+        self._builder("Fmi", F, t1, t2)
+        return self.engine.Fmi.clone()
+
+    def build_Fme(self, o, v, F, L, t1):
+        self._builder("Fme", F, t1, self.engine.t2)
+        return self.engine.Fme.clone()
+
+    def build_Wmnij(self, o, v, ERI, t1, t2):
+        self._builder("Wmnij", None, t1, t2)
+        return self.engine.Wmnij.clone()
+
+    def build_Wmbej(self, o, v, ERI, L, t1, t2):
+        self._builder("Wmbej", None, t1, t2)
+        return self.engine.Wmbej_view().contiguous()
+
+    def build_Wmbje(self, o, v, ERI, t1, t2):
+        self._builder("Wmbje", None, t1, t2)
+        return self.engine.Wmbje_view().contiguous()
+
+    def build_Zmbij(self, o, v, ERI, t1, t2):
+        self._builder("Zmbij", None, t1, t2)
+        return self.engine.Zmbij_view().contiguous()
+
+    def r_T1(self, o, v, F, ERI, L, t1, t2, Fae, Fme, Fmi):
+        eng = self.engine
+        self._load(F, t1, t2)
+        eng.be.bind_stream()
+        eng.prepare()
+        eng.Fae.copy_(torch.as_tensor(Fae).to(eng.Fae.device, eng.dtype))
+        eng.Fme.copy_(torch.as_tensor(Fme).to(eng.Fme.device, eng.dtype))
+        eng.Fmi.copy_(torch.as_tensor(Fmi).to(eng.Fmi.device, eng.dtype))
+        eng._run("r_T1")
+        return eng.r1.clone()
+
+    def r_T2(self, o, v, F, ERI, L, t1, t2, Fae, Fme, Fmi, Wmnij, Wmbej, Wmbje, Zmbij):
+        eng = self.engine
+        self._load(F, t1, t2)
+        eng.be.bind_stream()
+        eng.prepare()
+        dev = lambda x: torch.as_tensor(x).to(eng.t2.device, eng.dtype)
+        eng.Fae.copy_(dev(Fae))
+        eng.Fme.copy_(dev(Fme))
+        eng.Fmi.copy_(dev(Fmi))
+        eng.Wmnij.copy_(dev(Wmnij))
+        eng.Wmbej_view().copy_(dev(Wmbej))
+        eng.Wmbje_view().copy_(dev(Wmbje))
+        eng.Zmbij_view().copy_(dev(Zmbij))
+        eng._run("r_T2")
+        eng.be.pair_symmetrize(eng.r2, self.no, self.nv)
+        return eng.r2.clone()
+
+    def cc_energy(self, o, v, F, L, t1, t2):
+        self._load(F, t1, t2)
+        return self.engine.energy()

@@ -151,21 +151,16 @@ __global__ void sum_rows_kernel(const double* __restrict__ partials, int n, doub
 }
 
 template <typename T>
-int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_host, int ntrip, const void* t1,
+int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_dev, int ntrip, const void* t1,
                      const void* t2, const void* g, const void* fov, int64_t ld_fov, const void* eps, int64_t no,
-                     int64_t nv, double* et_host) {
+                     int64_t nv, double* et_dev) {
     const int nb = (int)((nv + TB_ - 1) / TB_);
     const int npair = nb * (nb + 1) / 2;
     PCCB_REQUIRE(ctx, ntrip >= 1 && ntrip <= 65535, "pccb_triples_energy: ntrip=%d out of range", ntrip);
     PCCB_REQUIRE(ctx, nb <= 65535, "pccb_triples_energy: nv too large");
-    // scratch: partials [ntrip*npair] | results [ntrip] | ijk (as ints) [3*ntrip]
-    const size_t need = (size_t)ntrip * npair + ntrip + (3 * (size_t)ntrip + 1) / 2 + 8;
-    int rc = pccb_ensure_partials(ctx, need);
+    int rc = pccb_ensure_partials(ctx, (size_t)ntrip * npair + 8);
     if (rc) return rc;
     double* partials = ctx->partial_dev;
-    double* results = partials + (size_t)ntrip * npair;
-    int* ijk_dev = reinterpret_cast<int*>(results + ntrip);
-    PCCB_CUDA(ctx, cudaMemcpyAsync(ijk_dev, ijk_host, sizeof(int) * 3 * ntrip, cudaMemcpyHostToDevice, ctx->stream));
     TriplesArgs<T> a;
     a.W = (const T*)w_dev; a.ijk = ijk_dev; a.t1 = (const T*)t1; a.t2 = (const T*)t2; a.g = (const T*)g;
     a.fov = (const T*)fov; a.eps = (const T*)eps; a.ld_fov = ld_fov; a.no = (int)no; a.nv = (int)nv; a.nb = nb;
@@ -174,31 +169,25 @@ int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_host, 
     dim3 grid(nb, nb, ntrip);
     triples_energy_kernel<T><<<grid, 512, 0, ctx->stream>>>(a);
     PCCB_CHECK_LAUNCH(ctx, "triples_energy_kernel");
-    sum_rows_kernel<<<ntrip, 256, 0, ctx->stream>>>(partials, npair, results);
+    sum_rows_kernel<<<ntrip, 256, 0, ctx->stream>>>(partials, npair, et_dev);
     PCCB_CHECK_LAUNCH(ctx, "sum_rows_kernel");
-    PCCB_CUDA(ctx, cudaMemcpyAsync(et_host, results, sizeof(double) * ntrip, cudaMemcpyDeviceToHost, ctx->stream));
-    PCCB_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return PCCB_OK;
 }
 
 }  // namespace
 
-extern "C" int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, const int32_t* ijk_host, int ntrip,
+extern "C" int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, const int32_t* ijk_dev, int ntrip,
                                    const void* t1_dev, const void* t2_dev, const void* oovv_dev, const void* fov_dev,
-                                   int64_t ld_fov, const void* eps_dev, int64_t no, int64_t nv, double* et_host) {
+                                   int64_t ld_fov, const void* eps_dev, int64_t no, int64_t nv, double* et_dev) {
     if (!ctx) return PCCB_ERR_ARG;
-    PCCB_REQUIRE(ctx, w_dev && ijk_host && t1_dev && t2_dev && oovv_dev && fov_dev && eps_dev && et_host,
+    PCCB_REQUIRE(ctx, w_dev && ijk_dev && t1_dev && t2_dev && oovv_dev && fov_dev && eps_dev && et_dev,
                  "pccb_triples_energy: null argument");
     PCCB_REQUIRE(ctx, no > 0 && nv > 0, "pccb_triples_energy: bad sizes");
-    for (int t = 0; t < ntrip; ++t)
-        for (int q = 0; q < 3; ++q)
-            PCCB_REQUIRE(ctx, ijk_host[3 * t + q] >= 0 && ijk_host[3 * t + q] < no,
-                         "pccb_triples_energy: triplet %d has an occupied index out of range", t);
     if (dtype == PCCB_F64)
-        return triples_energy_t<double>(ctx, w_dev, ijk_host, ntrip, t1_dev, t2_dev, oovv_dev, fov_dev, ld_fov,
-                                        eps_dev, no, nv, et_host);
+        return triples_energy_t<double>(ctx, w_dev, ijk_dev, ntrip, t1_dev, t2_dev, oovv_dev, fov_dev, ld_fov,
+                                        eps_dev, no, nv, et_dev);
     if (dtype == PCCB_F32)
-        return triples_energy_t<float>(ctx, w_dev, ijk_host, ntrip, t1_dev, t2_dev, oovv_dev, fov_dev, ld_fov,
-                                       eps_dev, no, nv, et_host);
+        return triples_energy_t<float>(ctx, w_dev, ijk_dev, ntrip, t1_dev, t2_dev, oovv_dev, fov_dev, ld_fov,
+                                       eps_dev, no, nv, et_dev);
     PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
 }

@@ -1,0 +1,149 @@
+"""
+(T) engine: Lee-Rendell closed-shell perturbative triples (pycc/cctriples.py:106-152, t_tjl)
+without ever holding an o^3 v^3 tensor.
+
+For every occupied pair (i >= j) the connected W^{ijk}_{abc} of ALL k <= j are built in one
+batched pass of three ``pccb_contract`` launches (the twelve einsums of t3c_ijk,
+cctriples.py:10-22, K-concatenated by their output structure):
+
+    N = c :  W[abc]  = Vi[bae] tkj[ce] + Vj[abe] tki[ce] - ti[mab] Ojk[mc] - tTj[mab] Oik[mc]
+    N = b :  W[abc] += Vi[cae] tjk[be] + Vk[ace] tji[be] - ti[mac] Okj[mb] - tTk[mac] Oij[mb]
+    N = a :  W[abc] += Vk[bce] tij[ae] + Vj[cbe] tik[ae] - tTk[mbc] Oji[ma] - tj[mbc] Oki[ma]
+
+with Vi[x,y,e] = <xy|ei> = ovvv[i,x,y,e] (8-fold symmetry of the stored <mb|ef> block),
+O_jk[m,c] = <mc|jk> = ooov[j,k,m,c], t_kj = t2[k,j], ti = t2[i] and tT = t2 with its virtual
+pair swapped (so every operand tile is read along a contiguous direction).  The batch dimension
+of the launch is k; the per-(i,j,k) operand addresses are affine in (i,j,k), so the three
+descriptors are planned once and only their base pointers are patched per (i,j).
+The W batch ([o][v][v][v], 8*o*v^3 bytes) is then consumed by ``pccb_triples_energy``, which
+adds the disconnected part and reduces to one energy per triplet.
+"""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from .dsl import TRef, plan
+
+_STATEMENTS = (
+    "W[abc] = Vi[bae]*tkj[ce] + Vj[abe]*tki[ce] - ti[mab]*Ojk[mc] - tTj[mab]*Oik[mc]",
+    "W[abc] += Vi[cae]*tjk[be] + Vk[ace]*tji[be] - ti[mac]*Okj[mb] - tTk[mac]*Oij[mb]",
+    "W[abc] += Vk[bce]*tij[ae] + Vj[cbe]*tik[ae] - tTk[mbc]*Oji[ma] - tj[mbc]*Oki[ma]",
+)
+
+
+def _ptr_fields(desc):
+    """(getter, setter) pairs for every device pointer of a descriptor."""
+    out = []
+    for q in range(desc.nseg):
+        out.append(("seg%dA" % q, q, "A_dev"))
+        out.append(("seg%dB" % q, q, "B_dev"))
+    out.append(("C", None, "C_dev"))
+    return out
+
+
+def _get(desc, f):
+    _, q, name = f
+    return getattr(desc.seg[q], name) if q is not None else getattr(desc, name)
+
+
+def _set(desc, f, val):
+    _, q, name = f
+    if q is not None:
+        setattr(desc.seg[q], name, val)
+    else:
+        setattr(desc, name, val)
+
+
+class TriplesEngine(object):
+    def __init__(self, ccsd_engine):
+        self.eng = eng = ccsd_engine
+        self.be = eng.be
+        o, v = eng.no, eng.nv
+        self.t2T = self.be.empty((o, o, v, v), eng.dtype)
+        self.W = self.be.empty((o, v, v, v), eng.dtype)          # batch over k
+        self._plan()
+
+    def _tensors(self, i, j, k):
+        e = self.eng
+        t2, tT, V, O = e.t2, self.t2T, e.blk["ovvv"], e.blk["ooov"]
+        d = dict(W=self.W[k], Vi=V[i], Vj=V[j], Vk=V[k],
+                 tij=t2[i, j], tik=t2[i, k], tji=t2[j, i], tjk=t2[j, k], tki=t2[k, i], tkj=t2[k, j],
+                 ti=t2[i], tj=t2[j], tTj=tT[j], tTk=tT[k],
+                 Oij=O[i, j], Oik=O[i, k], Oji=O[j, i], Ojk=O[j, k], Oki=O[k, i], Okj=O[k, j])
+        return {n: TRef.of(t, n) for n, t in d.items()}
+
+    def _plan(self):
+        """Plan at (0,0,0) and difference the pointers at unit steps of i, j, k."""
+        o = self.eng.no
+        dcode = self.eng.dcode
+        base = [plan(s, self._tensors(0, 0, 0), dcode) for s in _STATEMENTS]
+        for L in base:
+            if len(L) != 1 or L[0].desc.batch != 1:
+                raise RuntimeError("unexpected (T) plan structure")
+        self.templates = []
+        step = 1 if o > 1 else 0
+        shifted = []
+        for unit in ((step, 0, 0), (0, step, 0), (0, 0, step)):
+            shifted.append([plan(s, self._tensors(*unit), dcode)[0].desc for s in _STATEMENTS])
+        for n, L in enumerate(base):
+            d0 = L[0].desc
+            fields = _ptr_fields(d0)
+            deriv = {}
+            for f in fields:
+                p0 = _get(d0, f)
+                deriv[f[0]] = tuple((_get(shifted[ax][n], f) - p0) if step else 0 for ax in range(3))
+            self.templates.append((L[0], fields, deriv))
+        self._keep = base
+        self.itemsize = self.eng.t2.element_size()
+
+    def _launch_pair(self, i, j):
+        """W[k] for k = 0..j of the pair (i, j): three batched contractions."""
+        for (L, fields, deriv) in self.templates:
+            d = _lib.Contraction()
+            C.memmove(C.byref(d), C.byref(L.desc), C.sizeof(d))
+            for f in fields:
+                di, dj, dk = deriv[f[0]]
+                _set(d, f, _get(L.desc, f) + i * di + j * dj)
+                name, q, _ = f
+                if q is None:
+                    d.c_batch = dk // self.itemsize
+                elif name.endswith("A"):
+                    d.seg[q].a_batch = dk // self.itemsize
+                else:
+                    d.seg[q].b_batch = dk // self.itemsize
+            d.batch = j + 1
+            self.be.contract(d)
+
+    def pairs(self):
+        o = self.eng.no
+        return [(i, j) for i in range(o) for j in range(i + 1)]
+
+    def energy(self, pairs=None):
+        """E(T) summed over the triplets (i, j, k<=j) of the given occupied pairs (default: all).
+        Returns (total, per-triplet energies as a CPU tensor, triplet list)."""
+        eng, be = self.eng, self.be
+        o, v = eng.no, eng.nv
+        be.bind_stream()
+        if pairs is None:
+            pairs = self.pairs()
+        trip = [(i, j, k) for (i, j) in pairs for k in range(j + 1)]
+        if not trip:
+            return 0.0, torch.zeros(0, dtype=torch.float64), trip
+        ijk = torch.tensor(trip, dtype=torch.int32).reshape(-1).to(be.device)
+        et = be.zeros((len(trip),), torch.float64)
+        be.pair_combine(self.t2T, eng.t2, 0.0, 1.0, None, None, 0.0, o, v)
+        fov = eng.F[:o, o:]
+        pos = 0
+        for (i, j) in pairs:
+            n = j + 1
+            self._launch_pair(i, j)
+            be.triples_energy(self.W, ijk[3 * pos:], n, eng.t1, eng.t2, eng.blk["oovv"], fov, eng.F.stride(0),
+                              eng.eps, o, v, et[pos:])
+            pos += n
+        be.synchronize()
+        et_host = et.cpu()
+        total = 0.0
+        for x in et_host.tolist():      # fixed summation order
+            total += x
+        return total, et_host, trip

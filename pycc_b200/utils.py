@@ -1,0 +1,174 @@
+"""
+utils.py: DIIS extrapolation and the generalized contraction operator, API-compatible with
+``pycc/utils.py`` (helper_diis :6-139, cc_contract :141-187) but executing on the B200 engine.
+"""
+import numpy as np
+import torch
+
+from . import _lib
+from .dsl import TRef, plan
+
+
+class helper_diis(object):
+    """Pulay DIIS on the concatenated (t1, t2) amplitude vector; same bookkeeping as the
+    reference (``pycc/utils.py:6-139``):
+
+      * the error vector of an iteration is the difference between the new amplitudes and the
+        previous (extrapolated) ones (:26-46);
+      * at most ``max_diis`` error vectors are kept, oldest dropped first, and the amplitude
+        list stays one entry longer so that ``vals[k+1]`` pairs with ``errs[k]`` (:54-57);
+      * B is bordered with -1 / 0, its error block divided by its largest absolute entry (:103-116);
+      * the new amplitudes are sum_k c_k vals[k+1] and become the reference point for the next
+        error vector (:129-137).
+
+    History vectors live in device memory; the Gram matrix entries are fixed-order FP64 dot
+    products (``pccb_dot``), each computed once and cached; the (m+1)x(m+1) solve is done on the
+    host in FP64 for both precisions (the reference's SP mode solves in float32, :104-105).
+    """
+
+    def __init__(self, t1, t2, max_diis, precision='DP', backend=None):
+        if backend is None:
+            raise _lib.EngineError("helper_diis needs the engine back end that owns t1/t2")
+        self.be = backend
+        self.max_diis = max_diis
+        self.precision = precision
+        self.n1, self.n2 = t1.numel(), t2.numel()
+        self.shape1, self.shape2 = tuple(t1.shape), tuple(t2.shape)
+        self.dtype = t2.dtype
+        self.diis_size = 0
+        self.old = self._pack(t1, t2)
+        self.diis_vals = [self.old.clone()]
+        self.diis_errors = []
+        self._gram = {}          # (id_a, id_b) -> <e_a, e_b>
+        self._ids = []           # identity tags of the error vectors, parallel to diis_errors
+        self._next_id = 0
+
+    def _pack(self, t1, t2):
+        v = self.be.empty((self.n1 + self.n2,), self.dtype)
+        v[:self.n1].copy_(t1.reshape(-1))
+        v[self.n1:].copy_(t2.reshape(-1))
+        return v
+
+    def add_error_vector(self, t1, t2):
+        cur = self._pack(t1, t2)
+        self.diis_vals.append(cur)
+        err = self.be.empty((self.n1 + self.n2,), self.dtype)
+        self.be.bind_stream()
+        self.be.axpby(err, 1.0, cur, -1.0, self.old)
+        self.diis_errors.append(err)
+        self._ids.append(self._next_id)
+        self._next_id += 1
+        self.old = cur        # cur is never modified afterwards
+
+    def extrapolate(self, t1, t2):
+        if self.max_diis == 0:
+            return t1, t2
+        if len(self.diis_errors) > self.max_diis:
+            del self.diis_vals[0]
+            del self.diis_errors[0]
+            dead = self._ids.pop(0)
+            self._gram = {k: v for k, v in self._gram.items() if dead not in k}
+        self.diis_size = m = len(self.diis_errors)
+        self.be.bind_stream()
+        B = -np.ones((m + 1, m + 1))
+        B[-1, -1] = 0.0
+        for p in range(m):
+            for q in range(p, m):
+                key = (self._ids[p], self._ids[q])
+                if key not in self._gram:
+                    self._gram[key] = self.be.dot(self.diis_errors[p], self.diis_errors[q])
+                B[p, q] = B[q, p] = self._gram[key]
+        B[:-1, :-1] /= np.abs(B[:-1, :-1]).max()
+        resid = np.zeros(m + 1)
+        resid[-1] = -1.0
+        ci = np.linalg.solve(B, resid)
+        new = self.be.empty((self.n1 + self.n2,), self.dtype)
+        self.be.lincomb(new, [self.diis_vals[k + 1] for k in range(m)], [ci[k] for k in range(m)])
+        self.old = new
+        # the caller's amplitude tensors are updated in place (they are the engine's buffers)
+        t1.copy_(new[:self.n1].reshape(self.shape1))
+        t2.copy_(new[self.n1:].reshape(self.shape2))
+        return t1, t2
+
+
+class cc_contract(object):
+    """``contract = cc_contract(device)``; ``contract(subscripts, *operands)`` with numpy.einsum
+    string semantics (``pycc/utils.py:141-187``).  Two-operand contractions run as one
+    ``pccb_contract`` launch on the operands' existing strides; NumPy operands are moved to the
+    device first (the reference's GPU mode does the same, :181-183).  Returns a new tensor."""
+
+    def __init__(self, device='GPU', backend=None):
+        self.device = device
+        self.be = backend
+        if backend is not None:
+            self.device0 = torch.device('cpu')
+            self.device1 = backend.device
+
+    def _backend(self):
+        if self.be is None:
+            from .backend import CudaBackend
+            self.be = CudaBackend()
+            self.device0 = torch.device('cpu')
+            self.device1 = self.be.device
+        return self.be
+
+    def __call__(self, subscripts, *operands):
+        be = self._backend()
+        spec = subscripts.replace(" ", "")
+        if "->" not in spec:
+            raise ValueError("cc_contract needs an explicit output ('->') in %r" % subscripts)
+        lhs, out_idx = spec.split("->")
+        ins = lhs.split(",")
+        if len(ins) != len(operands):
+            raise ValueError("einsum string %r does not match %d operands" % (subscripts, len(operands)))
+        ops = []
+        for x in operands:
+            if not isinstance(x, torch.Tensor):
+                x = torch.as_tensor(np.asarray(x))
+            if x.device != be.device:
+                x = x.to(be.device)
+            ops.append(x)
+        dtype = ops[0].dtype
+        if dtype not in (torch.float64,):
+            raise ValueError("cc_contract: float64 operands only (got %s)" % dtype)
+        if len(ops) == 1:
+            perm = [ins[0].index(c) for c in out_idx]
+            if len(perm) != len(ins[0]):
+                raise ValueError("cc_contract: single-operand reductions are not supported: %r" % subscripts)
+            return ops[0].permute(perm).contiguous()
+        if len(ops) != 2:
+            # chain left to right, keeping every index still needed by the output or a later operand
+            cur, cur_idx = ops[0], ins[0]
+            for n in range(1, len(ops)):
+                later = set(out_idx).union(*[set(s) for s in ins[n + 1:]]) if n + 1 < len(ops) else set(out_idx)
+                keep = "".join(c for c in dict.fromkeys(cur_idx + ins[n]) if c in later)
+                cur = self("%s,%s->%s" % (cur_idx, ins[n], keep), cur, ops[n])
+                cur_idx = keep
+            return cur
+        ext = {}
+        for idx, x in zip(ins, ops):
+            if len(idx) != x.dim():
+                raise ValueError("operand has %d dimensions but subscripts %r" % (x.dim(), idx))
+            for c, n in zip(idx, x.shape):
+                if ext.setdefault(c, n) != n:
+                    raise ValueError("size mismatch for index %r in %r" % (c, subscripts))
+        for c in out_idx:
+            if c not in ext:
+                raise ValueError("output index %r does not appear in the operands (%r)" % (c, subscripts))
+        # indices summed over a single operand are reduced first (rare; not on the CCSD path)
+        for n in (0, 1):
+            other = ins[1 - n]
+            lone = [c for c in ins[n] if c not in other and c not in out_idx]
+            if lone:
+                ops[n] = ops[n].sum(dim=[ins[n].index(c) for c in lone])
+                ins[n] = "".join(c for c in ins[n] if c not in lone)
+        out = be.empty(tuple(ext[c] for c in out_idx), dtype)
+        if out_idx == "":
+            out = be.empty((1,), dtype)
+            T = {"C": TRef(out.data_ptr(), (), (), out.element_size(), "C", out), "A": ops[0], "B": ops[1]}
+        else:
+            T = {"C": out, "A": ops[0], "B": ops[1]}
+        be.bind_stream()
+        for L in plan("C[%s] = A[%s]*B[%s]" % (out_idx, ins[0], ins[1]), T, _lib.F64):
+            be.contract(L.desc)
+        return out.reshape(()) if out_idx == "" else out

@@ -121,21 +121,21 @@ class InterpBackend(object):
             acc += c * v.double()
         out.copy_(acc.to(out.dtype))
 
-    def triples_energy(self, W, ijk, t1, t2, oovv, fov, ld_fov, eps, no, nv):
+    def triples_energy(self, W, ijk_dev, ntrip, t1, t2, oovv, fov, ld_fov, eps, no, nv, et_dev):
         from oracle import triples_oracle as ot   # test-side checker
         F = np.zeros((no + nv, no + nv))
         F[np.arange(no + nv), np.arange(no + nv)] = eps.numpy()
         F[:no, no:] = fov.numpy()
-        out = []
         idx = np.arange(nv)
         a, b, c = idx[:, None, None], idx[None, :, None], idx[None, None, :]
+        ijk = ijk_dev.numpy().reshape(-1, 3)[:ntrip]
+
+        class _B(object):
+            pass
+        blk = _B()
+        blk.oovv, blk.no, blk.nv = oovv.numpy(), no, nv
         for t, (i, j, k) in enumerate(ijk):
             Wt = W[t].numpy().astype(np.float64)
-
-            class _B(object):
-                pass
-            blk = _B()
-            blk.oovv, blk.no, blk.nv = oovv.numpy(), no, nv
             V = (ot.v_disconnected(F, blk, t1.numpy(), t2.numpy(), i, j, k) + Wt) / (1.0 + (a == b) + (a == c) + (b == c))
             X = Wt * V
             for p in ((0, 2, 1), (1, 0, 2), (1, 2, 0), (2, 0, 1), (2, 1, 0)):
@@ -147,5 +147,4 @@ class InterpBackend(object):
             den = ot.triples_denominator(F, no, i, j, k)
             occ = 2.0 - ((i == j) + (i == k) + (j == k))
             term = ((Y - 2.0 * Z) * Wc + (Z - 2.0 * Y) * Wa + 3.0 * X) * occ / den
-            out.append(float(term[(a >= b) & (b >= c)].sum()))
-        return out
+            et_dev[t] = float(term[(a >= b) & (b >= c)].sum())

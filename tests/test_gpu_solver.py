@@ -1,0 +1,138 @@
+"""GPU parity of the full path through the public API (ccwfn / cctriples) and the C ABI:
+golden vectors produced by the reference itself, then larger seeded systems against the CPU
+oracle (which is pinned to those golden vectors by tests/test_oracle_golden.py).
+FP64 bars (BASELINE.json north_star): energies within 1e-10 Eh, T1/T2 within 1e-9 max-abs."""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+E_TOL, T_TOL = 1e-10, 1e-9
+
+
+def _wfn(F, blocks, no, model="CCSD"):
+    import pycc_b200
+    with contextlib.redirect_stdout(io.StringIO()):
+        return pycc_b200.ccwfn.from_arrays(F, blocks, no, model=model)
+
+
+def test_golden_solve_and_triples(golden):
+    import pycc_b200
+    g = golden
+    w = _wfn(g.F, g.blocks, g.no, "CCSD(T)")
+    with contextlib.redirect_stdout(io.StringIO()):
+        e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+    ref_log = g["solve_iter_log"]
+    assert len(w.iteration_log) == ref_log.shape[0]
+    for (it, ecc, de, rms), row in zip(w.iteration_log, ref_log):
+        assert abs(ecc - row[0]) < 1e-11
+    assert abs(e - float(g["solve_eccsd_t_total"])) < E_TOL
+    assert np.abs(w.t1.cpu().numpy() - g["solve_t1"]).max() < T_TOL
+    assert np.abs(w.t2.cpu().numpy() - g["solve_t2"]).max() < T_TOL
+    assert abs(pycc_b200.t_tjl(w) - float(g["solve_et"])) < E_TOL
+    assert abs(pycc_b200.t_vikings(w) - float(g["solve_et_vikings"])) < E_TOL
+
+
+@pytest.mark.parametrize("tag", ["sym", "gen"])
+def test_golden_triples_on_test_amplitudes(golden, tag):
+    import pycc_b200
+    g = golden
+    w = _wfn(g.F, g.blocks, g.no)
+    w._load(None, g[tag + "_t1"], g[tag + "_t2"])
+    assert abs(pycc_b200.t_tjl(w) - float(g[tag + "_et_tjl"])) < E_TOL
+
+
+def test_golden_builder_api_and_operator(golden):
+    import pycc_b200
+    g = golden
+    w = _wfn(g.F, g.blocks, g.no)
+    t1, t2 = g["gen_t1"], g["gen_t2"]
+    o, v, H, F = w.o, w.v, w.H, g.F
+    got = dict(Fae=w.build_Fae(o, v, F, H.L, t1, t2), Fmi=w.build_Fmi(o, v, F, H.L, t1, t2),
+               Fme=w.build_Fme(o, v, F, H.L, t1), Wmnij=w.build_Wmnij(o, v, H.ERI, t1, t2),
+               Wmbej=w.build_Wmbej(o, v, H.ERI, H.L, t1, t2), Wmbje=w.build_Wmbje(o, v, H.ERI, t1, t2),
+               Zmbij=w.build_Zmbij(o, v, H.ERI, t1, t2))
+    for k, t in got.items():
+        assert np.abs(t.cpu().numpy() - g["gen_" + k]).max() < 1e-12, k
+    r1, r2 = w.residuals(F, t1, t2)
+    assert np.abs(r1.cpu().numpy() - g["gen_r1"]).max() < 1e-12
+    assert np.abs(r2.cpu().numpy() - g["gen_r2"]).max() < 1e-12
+    c = w.contract
+    x = c('ijef,abef->ijab', w.t2, H.ERI[v, v, v, v])
+    assert np.abs(x.cpu().numpy() - np.einsum('ijef,abef->ijab', t2, g.blocks["vvvv"])).max() < 1e-12
+    assert abs(float(c('ia,ia->', w.t1, w.t1)) - float((t1 ** 2).sum())) < 1e-13
+    W = pycc_b200.t3c_ijk(o, v, g.no - 1, 1, 0, w.t2, H.ERI[v, v, v, o], H.ERI[o, v, o, o], H.F, c, False)
+    from oracle import triples_oracle as ot
+    from oracle.ccsd_oracle import Blocks
+    assert np.abs(W.cpu().numpy() - ot.w_connected(Blocks(g.blocks), t2, g.no - 1, 1, 0)).max() < 1e-12
+
+
+@pytest.mark.parametrize("no,nv,offdiag", [(8, 30, True), (10, 44, False), (7, 51, True)])
+def test_seeded_systems_vs_oracle(no, nv, offdiag):
+    """Sizes the reference itself would need minutes for; the oracle (pinned) does them in seconds."""
+    import pycc_b200
+    from pycc_b200.synthetic import SyntheticSystem
+    from oracle import ccsd_oracle as oc, triples_oracle as ot
+    s = SyntheticSystem(no, nv, seed=no + nv, fock_offdiag=offdiag)
+    w = _wfn(s.F, s.blocks, no)
+    with contextlib.redirect_stdout(io.StringIO()):
+        e = w.solve_cc(e_conv=1e-11, r_conv=1e-11, maxiter=100)
+    log = []
+    eo, t1, t2, niter = oc.solve_cc(s.F, s.blocks, 1e-11, 1e-11, maxiter=100, log=log)
+    assert len(w.iteration_log) == niter
+    assert abs(e - eo) < E_TOL
+    assert np.abs(w.t1.cpu().numpy() - t1).max() < T_TOL
+    assert np.abs(w.t2.cpu().numpy() - t2).max() < T_TOL
+    # (T): full sum at the small shape, a seeded sample of triplets otherwise
+    tri = pycc_b200.cctriples._engine(w)
+    rng = np.random.default_rng(0)
+    pairs = tri.pairs()
+    sample = [pairs[q] for q in sorted(rng.choice(len(pairs), size=min(6, len(pairs)), replace=False))]
+    et, per, trip = tri.energy(sample)
+    blk = oc.Blocks(s.blocks)
+    for x, (i, j, k) in zip(per.tolist(), trip):
+        assert abs(x - ot.et_triplet(s.F, blk, t1, t2, i, j, k)) < 1e-12
+    # size-independent property: the sum over all pairs equals the sum of any partition of them
+    et_all = pycc_b200.t_tjl(w)
+    half = len(pairs) // 2
+    et_a, _, _ = tri.energy(pairs[:half])
+    et_b, _, _ = tri.energy(pairs[half:])
+    assert abs(et_all - (et_a + et_b)) < 1e-13
+
+
+def test_residual_properties_at_scale():
+    """(16, 100): no CPU oracle in the test budget -> size-independent properties.
+    (1) pair symmetry r2[ijab] = r2[jiba]; (2) the ladder term equals the factorised checker
+    sum_Q built from the density-fitting factor (O(o^2 v^3 naux) instead of o^2 v^4);
+    (3) the tensor-core kernel agrees with the naive one-thread-per-element kernel."""
+    from pycc_b200.synthetic import SyntheticSystem
+    no, nv = 16, 100
+    s = SyntheticSystem(no, nv, seed=5)
+    w = _wfn(s.F, s.blocks, no)
+    eng, be = w.engine, w.backend
+    g = torch.Generator().manual_seed(1)
+    t1 = 0.05 * torch.randn(no, nv, generator=g, dtype=torch.float64)
+    t2 = 0.02 * torch.randn(no, no, nv, nv, generator=g, dtype=torch.float64)
+    t2 = 0.5 * (t2 + t2.permute(1, 0, 3, 2))
+    r1, r2 = w.residuals(s.F, t1, t2)
+    assert (r2 - r2.permute(1, 0, 3, 2)).abs().max().item() < 1e-12
+    be.use_naive_contract(True)
+    try:
+        n1, n2 = w.residuals(s.F, t1, t2)
+    finally:
+        be.use_naive_contract(False)
+    assert (r1 - n1).abs().max().item() < 1e-11
+    assert (r2 - n2).abs().max().item() < 1e-11
+    # ladder through the factor: sum_ef tau[ijef] <ab|ef> = sum_Q (sum_e tau[ijef] B[Q,a,e]) B[Q,b,f]
+    from pycc_b200.dsl import plan
+    out = torch.zeros_like(eng.r2)
+    eng.prepare()
+    for L in plan("out[ijab] = tau[ijef]*vvvv[abef]", dict(out=out, tau=eng.tau, vvvv=eng.blk["vvvv"])):
+        be.contract(L.desc)
+    Bv = torch.as_tensor(s.B[:, no:, no:]).to(be.device)
+    chk = torch.einsum('ijef,Qae,Qbf->ijab', eng.tau, Bv, Bv)
+    assert (out - chk).abs().max().item() < 1e-11

@@ -1,0 +1,118 @@
+"""Host logic of the solver seam (ccwfn / cctriples / helper_diis / cc_contract mirrors) checked
+on the CPU through the NumPy interpreter back end: iteration-by-iteration agreement with the
+reference's own solve_cc log, converged amplitudes, DIIS variants, E(T), builder API."""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+import torch
+
+from tests.interp_backend import InterpBackend
+import pycc_b200
+
+
+def _wfn(g, model="CCSD"):
+    with contextlib.redirect_stdout(io.StringIO()):
+        return pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model=model, _backend=InterpBackend())
+
+
+def test_solve_cc_iterations_match_reference(golden):
+    g = golden
+    w = _wfn(g, "CCSD(T)")
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+    ref_log = g["solve_iter_log"]
+    assert len(w.iteration_log) == ref_log.shape[0]
+    for (it, ecc, de, rms), row in zip(w.iteration_log, ref_log):
+        assert abs(ecc - row[0]) < 1e-12
+        assert abs(rms - row[2]) < 2e-5 * row[2]      # the reference prints rms with 5 decimals
+    assert abs(e - float(g["solve_eccsd_t_total"])) < 1e-12
+    assert np.abs(w.t1.numpy() - g["solve_t1"]).max() < 1e-11
+    assert np.abs(w.t2.numpy() - g["solve_t2"]).max() < 1e-11
+    # same printed lines as the reference (ccwfn.py:266,298,311-324)
+    out = buf.getvalue()
+    assert "CC Iter   0: CC Ecorr = " in out and "MP2" in out
+    assert "E(CCSD) = " in out and "E(T)    = " in out and "E(TOT)  = " in out
+
+
+@pytest.mark.parametrize("tag,kw", [("nodiis", dict(max_diis=0)), ("diis3s2", dict(max_diis=3, start_diis=2))])
+def test_diis_variants(golden, tag, kw):
+    g = golden
+    w = _wfn(g)
+    with contextlib.redirect_stdout(io.StringIO()):
+        e = w.solve_cc(e_conv=1e-10, r_conv=1e-10, maxiter=200, **kw)
+    assert len(w.iteration_log) == int(g["solve_%s_niter" % tag])
+    assert abs(e - float(g["solve_%s_ecc" % tag])) < 1e-12
+
+
+def test_not_converged_returns_none(golden):
+    w = _wfn(golden)
+    with contextlib.redirect_stdout(io.StringIO()):
+        assert w.solve_cc(e_conv=1e-14, r_conv=1e-14, maxiter=2) is None
+
+
+def test_builder_api(golden):
+    g = golden
+    w = _wfn(g)
+    t1, t2 = g["gen_t1"], g["gen_t2"]
+    o, v, H = w.o, w.v, w.H
+    F = g.F
+    Fae = w.build_Fae(o, v, F, H.L, t1, t2)
+    Fmi = w.build_Fmi(o, v, F, H.L, t1, t2)
+    Fme = w.build_Fme(o, v, F, H.L, t1)
+    Wmnij = w.build_Wmnij(o, v, H.ERI, t1, t2)
+    Wmbej = w.build_Wmbej(o, v, H.ERI, H.L, t1, t2)
+    Wmbje = w.build_Wmbje(o, v, H.ERI, t1, t2)
+    Zmbij = w.build_Zmbij(o, v, H.ERI, t1, t2)
+    for k, t in dict(Fae=Fae, Fmi=Fmi, Fme=Fme, Wmnij=Wmnij, Wmbej=Wmbej, Wmbje=Wmbje, Zmbij=Zmbij).items():
+        assert tuple(t.shape) == g["gen_" + k].shape
+        assert np.abs(t.numpy() - g["gen_" + k]).max() < 1e-12, k
+    r1 = w.r_T1(o, v, F, H.ERI, H.L, t1, t2, Fae, Fme, Fmi)
+    r2 = w.r_T2(o, v, F, H.ERI, H.L, t1, t2, Fae, Fme, Fmi, Wmnij, Wmbej, Wmbje, Zmbij)
+    assert np.abs(r1.numpy() - g["gen_r1"]).max() < 1e-12
+    assert np.abs(r2.numpy() - g["gen_r2"]).max() < 1e-12
+    rr1, rr2 = w.residuals(F, t1, t2)
+    assert np.abs(rr2.numpy() - g["gen_r2"]).max() < 1e-12
+    assert np.abs(w.build_tau(t1, t2, 1.0, 0.5).numpy() - g["gen_tau_1_h"]).max() < 1e-15
+    assert abs(w.cc_energy(o, v, F, H.L, t1, t2) - float(g["gen_energy"])) < 1e-12
+    # Dia / Dijab attributes
+    eps = np.diag(g.F)
+    assert np.abs(w.Dia.numpy() - (eps[:g.no, None] - eps[None, g.no:])).max() == 0.0
+    assert tuple(w.Dijab.shape) == (g.no, g.no, g.nv, g.nv)
+
+
+def test_kwargs_validation(golden):
+    g = golden
+    for kw, msg in ((dict(model="CCSDT"), "not an allowed CC model"), (dict(local="XYZ"), "not an allowed local-CC"),
+                    (dict(precision="HP"), "not an allowed precision"), (dict(device="TPU"), "not an allowed device"),
+                    (dict(model="CC3"), "not available in the B200 engine")):
+        with pytest.raises(Exception, match=msg):
+            with contextlib.redirect_stdout(io.StringIO()):
+                pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, _backend=InterpBackend(), **kw)
+
+
+def test_contract_operator_and_triples_builders(golden):
+    """cc_contract with einsum strings + the per-triplet builders written on top of it."""
+    from oracle import triples_oracle as ot
+    from oracle.ccsd_oracle import Blocks
+    g = golden
+    w = _wfn(g)
+    w._load(None, g["sym_t1"], g["sym_t2"])
+    c = w.contract
+    t2 = w.t2
+    x = c('ijef,abef->ijab', t2, w.H.ERI[w.v, w.v, w.v, w.v])
+    ref = np.einsum('ijef,abef->ijab', g["sym_t2"], g.blocks["vvvv"])
+    assert np.abs(x.numpy() - ref).max() < 1e-12
+    s = c('ia,ia->', w.t1, w.t1)
+    assert abs(float(s) - float((g["sym_t1"] ** 2).sum())) < 1e-13
+    y = c('ie,ma->imea', w.t1, w.t1)
+    assert np.abs(y.numpy() - np.einsum('ie,ma->imea', g["sym_t1"], g["sym_t1"])).max() < 1e-15
+    i, j, k = g.no - 1, 1, 0
+    W = pycc_b200.t3c_ijk(w.o, w.v, i, j, k, t2, w.H.ERI[w.v, w.v, w.v, w.o], w.H.ERI[w.o, w.v, w.o, w.o], w.H.F, c, False)
+    blk = Blocks(g.blocks)
+    assert np.abs(W.numpy() - ot.w_connected(blk, g["sym_t2"], i, j, k)).max() < 1e-12
+    V = pycc_b200.t3d_ijk(w.o, w.v, i, j, k, w.t1, t2, w.H.ERI[w.o, w.o, w.v, w.v], w.H.F, c, False)
+    assert np.abs(V.numpy() - ot.v_disconnected(g.F, blk, g["sym_t1"], g["sym_t2"], i, j, k)).max() < 1e-13
+    assert abs(pycc_b200.t_vikings(w) - float(g["sym_et_tjl"])) < 1e-12
