@@ -21,8 +21,7 @@ def _engine(ccwfn):
 
 def t_tjl(ccwfn):
     """Lee and Rendell's formulation (pycc/cctriples.py:106-152) on the amplitudes held by ``ccwfn``."""
-    et, _, _ = _engine(ccwfn).energy()
-    return et
+    return _engine(ccwfn).energy_all_ranks()
 
 
 def t_vikings(ccwfn):

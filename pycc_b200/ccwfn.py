@@ -117,6 +117,10 @@ class ccwfn(object):
         # compatibility with the reference (its default) but does not select a CPU implementation.
         self.device = 'GPU'
 
+        # engine-only kwarg: group=None (one GPU), or 'world' / a torch.distributed process group
+        # (one process per GPU; the virtual index and the (T) triplets are sharded over its ranks)
+        from .parallel import Comm
+        self.comm = Comm(kwargs.pop('group', None))
         backend = kwargs.pop('_backend', None)
         if backend is None:
             from .backend import CudaBackend
@@ -137,13 +141,17 @@ class ccwfn(object):
         self.C = C
 
         dtype = torch.float64
+        from .parallel import virtual_slice
+        vslice = virtual_slice(nv, self.comm.rank, self.comm.world)
+        keep_ovvv = (model == 'CCSD(T)' or self.comm.world == 1)
         if isinstance(ERI, dict):
-            self.H = Hamiltonian.from_blocks(F, ERI, no, backend.device, dtype)
+            self.H = Hamiltonian.from_blocks(F, ERI, no, backend.device, dtype, vslice, keep_ovvv)
         else:
             if tuple(ERI.shape) != (no + nv,) * 4:
                 raise Exception("ERI must be the full (n,n,n,n) Dirac array or a dict of blocks %s" % (BLOCKS,))
-            self.H = Hamiltonian.from_full(F, ERI, no, backend.device, dtype)
-        self.engine = CCSDEngine(backend, self.H.F, self.H.blocks, no, nv, dtype)
+            self.H = Hamiltonian.from_full(F, ERI, no, backend.device, dtype, vslice, keep_ovvv)
+        self.engine = CCSDEngine(backend, self.H.F, self.H.blocks, no, nv, dtype, comm=self.comm,
+                                 keep_full_ovvv=keep_ovvv)
         self.H.F = self.engine.F
         self._triples = None
 

@@ -28,64 +28,101 @@ import torch
 
 from . import _lib
 from .dsl import TRef, plan
+from .parallel import Comm, virtual_slice
 
 
 class CCSDEngine(object):
-    def __init__(self, backend, F, blocks, no, nv, dtype=torch.float64):
+    def __init__(self, backend, F, blocks, no, nv, dtype=torch.float64, comm=None, keep_full_ovvv=True):
+        """``comm``: pycc_b200.parallel.Comm (None = one GPU).  With more than one rank this rank
+        works on the virtual slice [vlo, vhi); ``blocks['vvvv']`` may then be either the full block
+        or just the rank's rows ``<ab|ef>, a in slice`` (shape (vhi-vlo, v, v, v)), and likewise
+        ``blocks['ovvv']`` (full, or (o, vhi-vlo, v, v)); a full ovvv is needed for (T)."""
         self.be = be = backend
         self.no, self.nv, self.dtype = int(no), int(nv), dtype
         self.dcode = _lib.F64 if dtype == torch.float64 else _lib.F32
+        self.comm = comm if comm is not None else Comm(None)
         o, v = self.no, self.nv
         n = o + v
+        self.vlo, self.vhi = virtual_slice(v, self.comm.rank, self.comm.world)
+        vl = self.vl = self.vhi - self.vlo
         self.F = be.to_device(F, dtype)
         if tuple(self.F.shape) != (n, n):
             raise ValueError("F must be (%d,%d)" % (n, n))
         self.eps = torch.diagonal(self.F).contiguous()
         shapes = dict(oooo=(o, o, o, o), ooov=(o, o, o, v), oovv=(o, o, v, v), ovov=(o, v, o, v),
                       ovvv=(o, v, v, v), vvvv=(v, v, v, v))
+        local = dict(ovvv=(o, vl, v, v), vvvv=(vl, v, v, v))
         self.blk = {}
         for k, shp in shapes.items():
             if k not in blocks:
                 raise ValueError("missing ERI block %r" % k)
-            t = be.to_device(blocks[k], dtype)
-            if tuple(t.shape) != shp:
+            src = blocks[k]
+            if tuple(src.shape) == shp and k in local and self.comm.world > 1 and not (k == "ovvv" and keep_full_ovvv):
+                # keep only this rank's rows on the device
+                src = src[self.vlo:self.vhi] if k == "vvvv" else src[:, self.vlo:self.vhi]
+            t = be.to_device(src, dtype)
+            if tuple(t.shape) != shp and not (k in local and tuple(t.shape) == local[k]):
                 raise ValueError("ERI block %s has shape %s, expected %s" % (k, tuple(t.shape), shp))
             self.blk[k] = t
+        # this rank's rows of the two big blocks (views when the full block is resident)
+        self.vvvv_loc = self.blk["vvvv"]
+        self.ovvv_full = self.blk["ovvv"] if self.blk["ovvv"].shape[1] == v else None
+        self.ovvv_loc = self.blk["ovvv"][:, self.vlo:self.vhi] if self.ovvv_full is not None else self.blk["ovvv"]
         # spin-adapted constants
         self.Loovv = be.empty((o, o, v, v), dtype)
         be.pair_combine(self.Loovv, self.blk["oovv"], 2.0, -1.0, None, None, 0.0, o, v)
         self.Looov = be.empty((o, o, o, v), dtype)
         be.permute4(self.Looov, self.blk["ooov"], 2.0, 0.0)
         be.permute4(self.Looov, self.blk["ooov"].permute(1, 0, 2, 3), -1.0, 1.0)
-        # amplitudes and per-iteration buffers
+        # amplitudes and per-iteration buffers (intermediates carrying the sliced index are local-sized)
         E = lambda *s: be.zeros(s, dtype)
         self.t1, self.t2 = E(o, v), E(o, o, v, v)
         self.tau, self.tauh, self.tauW, self.t2s = E(o, o, v, v), E(o, o, v, v), E(o, o, v, v), E(o, o, v, v)
-        self.Fae, self.Fmi, self.Fme = E(v, v), E(o, o), E(o, v)
-        self.Fae2, self.Fmi2 = E(v, v), E(o, o)
+        self.Fae, self.Fmi, self.Fme = E(vl, v), E(o, o), E(o, v)
+        self.Fae2, self.Fmi2 = E(vl, v), E(o, o)
         self.Wmnij = E(o, o, o, o)
-        self.Wr1, self.Wr2 = E(o, v, o, v), E(o, v, o, v)       # [j,b,m,e]
-        self.Zr = E(o, o, o, v)                                  # [m,i,j,b]
-        self.Y1, self.Y2 = E(o, o, o, v), E(o, o, v, o)          # [i,m,j,b], [i,m,a,j]
+        self.Wr1, self.Wr2 = E(o, vl, o, v), E(o, vl, o, v)      # [j,b,m,e]
+        self.Zr = E(o, o, o, vl)                                 # [m,i,j,b]
+        self.Y1, self.Y2 = E(o, o, o, vl), E(o, o, vl, o)        # [i,m,j,b], [i,m,a,j]
         self.r1, self.r2 = E(o, v), E(o, o, v, v)
+        self.ladder_events = None    # bench.py: list that receives (start, end) CUDA events per ladder launch
         self._build_plans()
 
     # ---------------------------------------------------------------------------------------
-    def _tensors(self):
+    def _tensors(self, names):
+        """Name -> strided view.  ``X_sK`` is tensor X restricted to this rank's virtual slice
+        along dimension K (the whole tensor on one GPU)."""
         o = self.no
         F = self.F
-        d = dict(self.blk)
+        d = dict(oooo=self.blk["oooo"], ooov=self.blk["ooov"], oovv=self.blk["oovv"], ovov=self.blk["ovov"])
         d.update(Foo=F[:o, :o], Fov=F[:o, o:], Fvv=F[o:, o:], Loovv=self.Loovv, Looov=self.Looov,
                  t1=self.t1, t2=self.t2, tau=self.tau, tauh=self.tauh, tauW=self.tauW, t2s=self.t2s,
                  Fae=self.Fae, Fmi=self.Fmi, Fme=self.Fme, Fae2=self.Fae2, Fmi2=self.Fmi2, Wmnij=self.Wmnij,
                  Wr1=self.Wr1, Wr2=self.Wr2, Zr=self.Zr, Y1=self.Y1, Y2=self.Y2, r1=self.r1, r2=self.r2)
-        return {k: TRef.of(t, k) for k, t in d.items()}
+        out = {}
+        for nm in names:
+            if nm == "vvvv_s0":
+                t = self.vvvv_loc
+            elif nm == "ovvv_s1":
+                t = self.ovvv_loc
+            elif nm in d:
+                t = d[nm]
+            else:
+                base, dim = nm[:-3], int(nm[-1])
+                if nm[-3:-1] != "_s" or base not in d:
+                    raise KeyError("unknown tensor %r" % nm)
+                t = d[base].narrow(dim, self.vlo, self.vl)
+            out[nm] = TRef.of(t, nm)
+        return out
 
-    # Statements, grouped per reference builder.  Index letters as in the reference.
+    # Statements, grouped per reference builder.  Index letters as in the reference; an upper-case
+    # A / B is the virtual index restricted to this rank's slice (extent vl), and ``X_sK`` the
+    # matching view of X.  r1 / r2 are zeroed first and every term accumulates, so that the
+    # per-rank partial results add up under the allreduce.
     STATEMENTS = {
-        # build_Fae (pycc/ccwfn.py:421-428); L[o,v,v,v] = 2<ma|fe> - <ma|ef>
-        "Fae": ["Fae[ae] = Fvv[ae] - 0.5*t1[ma]*Fov[me] - tauh[mnaf]*Loovv[mnef]",
-                "Fae[ae] += 2.0*t1[mf]*ovvv[mafe] - t1[mf]*ovvv[maef]"],
+        # build_Fae (pycc/ccwfn.py:421-428), rows A only; L[o,v,v,v] = 2<ma|fe> - <ma|ef>
+        "Fae": ["Fae[Ae] = Fvv_s0[Ae] - 0.5*t1_s1[mA]*Fov[me] - tauh_s2[mnAf]*Loovv[mnef]",
+                "Fae[Ae] += 2.0*t1[mf]*ovvv_s1[mAfe] - t1[mf]*ovvv_s1[mAef]"],
         # build_Fmi (:441-447); L[o,o,o,v] = Looov
         "Fmi": ["Fmi[mi] = Foo[mi] + 0.5*Fov[me]*t1[ie] + Loovv[mnef]*tauh[inef]",
                 "Fmi[mi] += t1[ne]*Looov[mnie]"],
@@ -95,50 +132,73 @@ class CCSDEngine(object):
         "Wmnij": ["Wmnij[mnij] = oooo[mnij] + oovv[mnef]*tau[ijef]",
                   "Wmnij[mnij] += ooov[mnie]*t1[je]",
                   "Wmnij[mnij] += ooov[nmje]*t1[ie]"],
-        # build_Wmbej (:498-505) in ring layout Wr1[jbme]; <mb|ej> = <mj|eb>, <mn|ej> = <nm|je>
-        "Wmbej": ["Wr1[jbme] = oovv[mjeb] - tauW[jnfb]*oovv[mnef] + 0.5*t2[njfb]*Loovv[mnef]",
-                  "Wr1[jbme] += t1[jf]*ovvv[mbef]",
-                  "Wr1[jbme] -= t1[nb]*ooov[nmje]"],
-        # build_Wmbje (:520-526) in ring layout Wr2[jbme] = Wmbje[mbje]
-        "Wmbje": ["Wr2[jbme] = -1.0*ovov[mbje] + tauW[jnfb]*oovv[mnfe]",
-                  "Wr2[jbme] -= t1[jf]*ovvv[mbfe]",
-                  "Wr2[jbme] += t1[nb]*ooov[mnje]"],
-        # build_Zmbij (:537) as Zr[mijb]
-        "Zmbij": ["Zr[mijb] = ovvv[mbef]*tau[ijef]"],
-        # r_T1 (:548-557); L[o,v,v,o][nafi] = 2<ni|fa> - <na|if>; L[o,o,v,o][nmei] = Looov[mnie]
-        "r_T1": ["r1[ia] = Fov[ia] + t1[ie]*Fae[ae] - Fmi[mi]*t1[ma] + t2s[mief]*ovvv[maef] - Looov[mnie]*t2[mnae]",
-                 "r1[ia] += t2s[imae]*Fme[me]",
-                 "r1[ia] += 2.0*t1[nf]*oovv[nifa] - t1[nf]*ovov[naif]"],
+        # build_Wmbej (:498-505) in ring layout Wr1[jbme], b in slice; <mb|ej> = <mj|eb>, <mn|ej> = <nm|je>
+        "Wmbej": ["Wr1[jBme] = oovv_s3[mjeB] - tauW_s3[jnfB]*oovv[mnef] + 0.5*t2_s3[njfB]*Loovv[mnef]",
+                  "Wr1[jBme] += t1[jf]*ovvv_s1[mBef]",
+                  "Wr1[jBme] -= t1_s1[nB]*ooov[nmje]"],
+        # build_Wmbje (:520-526) in ring layout Wr2[jbme] = Wmbje[mbje], b in slice
+        "Wmbje": ["Wr2[jBme] = -1.0*ovov_s1[mBje] + tauW_s3[jnfB]*oovv[mnfe]",
+                  "Wr2[jBme] -= t1[jf]*ovvv_s1[mBfe]",
+                  "Wr2[jBme] += t1_s1[nB]*ooov[mnje]"],
+        # build_Zmbij (:537) as Zr[mijb], b in slice
+        "Zmbij": ["Zr[mijB] = ovvv_s1[mBef]*tau[ijef]"],
+        # r_T1 (:548-557), columns A; L[o,v,v,o][nafi] = 2<ni|fa> - <na|if>; L[o,o,v,o][nmei] = Looov[mnie]
+        "r_T1": ["r1_s1[iA] += Fov_s1[iA] + t1[ie]*Fae[Ae] - Fmi[mi]*t1_s1[mA] + t2s[mief]*ovvv_s1[mAef]"
+                 " - Looov[mnie]*t2_s2[mnAe]",
+                 "r1_s1[iA] += t2s_s2[imAe]*Fme[me]",
+                 "r1_s1[iA] += 2.0*t1[nf]*oovv_s3[nifA] - t1[nf]*ovov_s1[nAif]"],
         # r_T2 (:596-616), unsymmetrised; <ab|ej> = <ja|be>, <mb|ij> = <ij|mb>
-        "r_T2": ["Fae2[be] = Fae[be] - 0.5*t1[mb]*Fme[me]",
+        "r_T2": ["Fae2[Be] = Fae[Be] - 0.5*t1_s1[mB]*Fme[me]",
                  "Fmi2[mj] = Fmi[mj] + 0.5*Fme[me]*t1[je]",
-                 "r2[ijab] = 0.5*oovv[ijab] + 0.5*tau[ijef]*vvvv[abef]",
-                 "r2[ijab] += 0.5*Wmnij[mnij]*tau[mnab]",
-                 "r2[ijab] += t2s[imae]*Wr1[jbme] + t2[imae]*Wr2[jbme]",
-                 "r2[ijab] += t2[mjae]*Wr2[ibme]",
-                 "r2[ijab] += t2[ijae]*Fae2[be]",
-                 "r2[ijab] -= Fmi2[mj]*t2[imab]",
-                 "r2[ijab] -= t1[ma]*Zr[mijb]",
-                 "Y1[imjb] = t1[ie]*oovv[mjeb]",
-                 "r2[ijab] -= t1[ma]*Y1[imjb]",
-                 "Y2[imaj] = t1[ie]*ovov[maje]",
-                 "r2[ijab] -= Y2[imaj]*t1[mb]",
-                 "r2[ijab] += t1[ie]*ovvv[jabe]",
-                 "r2[ijab] -= t1[ma]*ooov[ijmb]"],
+                 "r2_s2[ijAb] += 0.5*oovv_s2[ijAb] + 0.5*tau[ijef]*vvvv_s0[Abef]",
+                 "r2_s2[ijAb] += 0.5*Wmnij[mnij]*tau_s2[mnAb]",
+                 "r2_s3[ijaB] += t2s[imae]*Wr1[jBme] + t2[imae]*Wr2[jBme]",
+                 "r2_s3[ijaB] += t2[mjae]*Wr2[iBme]",
+                 "r2_s3[ijaB] += t2[ijae]*Fae2[Be]",
+                 "r2_s2[ijAb] -= Fmi2[mj]*t2_s2[imAb]",
+                 "r2_s3[ijaB] -= t1[ma]*Zr[mijB]",
+                 "Y1[imjB] = t1[ie]*oovv_s3[mjeB]",
+                 "r2_s3[ijaB] -= t1[ma]*Y1[imjB]",
+                 "Y2[imAj] = t1[ie]*ovov_s1[mAje]",
+                 "r2_s2[ijAb] -= Y2[imAj]*t1[mb]",
+                 "r2_s2[ijAb] += t1[ie]*ovvv_s1[jAbe]",
+                 "r2_s2[ijAb] -= t1_s1[mA]*ooov[ijmb]"],
     }
 
     def _build_plans(self):
-        T = self._tensors()
+        import re
         self.plans = {}
         for name, stmts in self.STATEMENTS.items():
             launches = []
             for s in stmts:
-                launches += plan(s, T, self.dcode)
+                T = self._tensors(set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s)))
+                for L in plan(s, T, self.dcode):
+                    L.is_ladder = "vvvv_s0" in s
+                    launches.append(L)
             self.plans[name] = launches
 
     def _run(self, name):
+        if name == "r_T1":
+            self.r1.zero_()
+        elif name == "r_T2":
+            self.r2.zero_()
+        self._launch(name)
+        # the one exchange step of the iteration: sum the per-rank partial residuals
+        if name == "r_T1":
+            self.comm.allreduce_(self.r1)
+        elif name == "r_T2":
+            self.comm.allreduce_(self.r2)
+
+    def _launch(self, name):
         for L in self.plans[name]:
-            self.be.contract(L.desc)
+            if self.ladder_events is not None and L.is_ladder:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                self.be.contract(L.desc)
+                e1.record()
+                self.ladder_events.append((e0, e1))
+            else:
+                self.be.contract(L.desc)
 
     # ---- amplitude-dependent element-wise preparations ---------------------------------------
     def prepare(self):

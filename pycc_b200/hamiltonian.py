@@ -104,15 +104,28 @@ class Hamiltonian(object):
         return torch.as_tensor(np.ascontiguousarray(x), dtype=dtype).to(device)
 
     @classmethod
-    def from_blocks(cls, F, blocks, no, device, dtype=torch.float64):
+    def from_blocks(cls, F, blocks, no, device, dtype=torch.float64, vslice=None, keep_full_ovvv=True):
+        """``vslice=(lo, hi)`` (multi-GPU): only rows lo..hi of the leading virtual index of ``vvvv``
+        (and of the ``b`` index of ``ovvv`` unless ``keep_full_ovvv``) are uploaded; blocks that are
+        already given in that local shape are taken as they are.  ``H.ERI[v,v,v,v]`` then yields
+        this rank's rows only."""
         nv = blocks["oovv"].shape[2]
         dev_blocks = {}
         for k in BLOCKS:
             if k not in blocks:
                 raise ValueError("missing ERI block %r (need %s)" % (k, ", ".join(BLOCKS)))
-            dev_blocks[k] = cls._to_dev(blocks[k], device, dtype)
-        return cls(cls._to_dev(F, device, dtype), dev_blocks, no, nv, device, dtype)
+            src = blocks[k]
+            if vslice is not None and tuple(vslice) != (0, nv):
+                lo, hi = vslice
+                if k == "vvvv" and src.shape[0] == nv:
+                    src = src[lo:hi]
+                elif k == "ovvv" and not keep_full_ovvv and src.shape[1] == nv:
+                    src = src[:, lo:hi]
+            dev_blocks[k] = cls._to_dev(src, device, dtype)
+        H = cls(cls._to_dev(F, device, dtype), dev_blocks, no, nv, device, dtype)
+        H.vslice = tuple(vslice) if vslice is not None else (0, nv)
+        return H
 
     @classmethod
-    def from_full(cls, F, ERI, no, device, dtype=torch.float64):
-        return cls.from_blocks(F, blocks_from_full(ERI, no), no, device, dtype)
+    def from_full(cls, F, ERI, no, device, dtype=torch.float64, vslice=None, keep_full_ovvv=True):
+        return cls.from_blocks(F, blocks_from_full(ERI, no), no, device, dtype, vslice, keep_full_ovvv)

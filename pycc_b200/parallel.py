@@ -1,0 +1,85 @@
+"""
+Multi-GPU plumbing: one process per GPU (torchrun-style), ``torch.distributed`` over NCCL/NVLink
+on the B200 box (``gloo`` on CPU in the host-logic tests).
+
+The reference is single-process, single-device; the partitioning below is
+the engine's own:
+
+  * CCSD iteration - rank g owns a contiguous slice [lo, hi) of the VIRTUAL index: it stores
+    ``<ab|ef>`` for a in the slice and ``<mb|ef>`` for b in the slice, and computes every term of
+    r1 / r2 whose sliced virtual index falls in its range (the unsymmetrised r2 may carry a term
+    in either pair orientation, because the final r2 + r2^T (pycc/ccwfn.py:621) restores it).
+    One exchange step per iteration: a sum-allreduce of the partial (r1, r2).
+  * (T) - the occupied pairs (i >= j), each standing for its j+1 triplets (i, j, k <= j), are
+    dealt to the ranks by cost; one allreduce of a single double.
+"""
+import torch
+
+
+def virtual_slice(nv, rank, world):
+    """[lo, hi) of the virtual index owned by ``rank``.  Boundaries are kept even when nv is even
+    so that slices of stride-1 virtual dimensions stay 16-byte aligned (vectorised copies)."""
+    if world <= 1:
+        return 0, nv
+    unit = 2 if (nv % 2 == 0 and nv // 2 >= world) else 1
+    n = nv // unit
+    lo = (n * rank) // world * unit
+    hi = (n * (rank + 1)) // world * unit
+    return lo, hi
+
+
+def deal_pairs(no, rank, world):
+    """Occupied pairs (i >= j) for ``rank``: longest-processing-time-first by the cost j+1
+    (number of triplets k <= j), ties broken by order, so every rank gets the same list."""
+    pairs = [(i, j) for i in range(no) for j in range(i + 1)]
+    if world <= 1:
+        return pairs
+    order = sorted(range(len(pairs)), key=lambda q: (-(pairs[q][1] + 1), q))
+    load = [0] * world
+    mine = []
+    for q in order:
+        r = min(range(world), key=lambda x: (load[x], x))
+        load[r] += pairs[q][1] + 1
+        if r == rank:
+            mine.append(q)
+    return [pairs[q] for q in sorted(mine)]
+
+
+class Comm(object):
+    """Sum-allreduce over a ``torch.distributed`` process group (None = single process)."""
+
+    def __init__(self, group=None):
+        self.group = None
+        self.rank, self.world = 0, 1
+        if group is not None:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                raise RuntimeError("torch.distributed is not initialised (launch with torchrun / init_process_group)")
+            self.group = dist.group.WORLD if group in ("world", True) else group
+            self.rank = dist.get_rank(self.group)
+            self.world = dist.get_world_size(self.group)
+        self.bytes_reduced = 0
+
+    def allreduce_(self, *tensors):
+        """In-place sum over the ranks; identical bits on every rank (NCCL / gloo guarantee)."""
+        if self.world <= 1:
+            return
+        import torch.distributed as dist
+        for t in tensors:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+            self.bytes_reduced += t.numel() * t.element_size()
+
+    def allreduce_scalar(self, x):
+        if self.world <= 1:
+            return float(x)
+        import torch.distributed as dist
+        dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(self.group) == "nccl" \
+            else torch.device("cpu")
+        t = torch.tensor([float(x)], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return float(t.item())
+
+    def barrier(self):
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(group=self.group)

@@ -24,6 +24,7 @@ import torch
 
 from . import _lib
 from .dsl import TRef, plan
+from .parallel import deal_pairs
 
 _STATEMENTS = (
     "W[abc] = Vi[bae]*tkj[ce] + Vj[abe]*tki[ce] - ti[mab]*Ojk[mc] - tTj[mab]*Oik[mc]",
@@ -60,13 +61,15 @@ class TriplesEngine(object):
         self.eng = eng = ccsd_engine
         self.be = eng.be
         o, v = eng.no, eng.nv
+        if eng.ovvv_full is None:
+            raise ValueError("(T) needs the full <mb|ef> block on every rank (only this rank's slice was given)")
         self.t2T = self.be.empty((o, o, v, v), eng.dtype)
         self.W = self.be.empty((o, v, v, v), eng.dtype)          # batch over k
         self._plan()
 
     def _tensors(self, i, j, k):
         e = self.eng
-        t2, tT, V, O = e.t2, self.t2T, e.blk["ovvv"], e.blk["ooov"]
+        t2, tT, V, O = e.t2, self.t2T, e.ovvv_full, e.blk["ooov"]
         d = dict(W=self.W[k], Vi=V[i], Vj=V[j], Vk=V[k],
                  tij=t2[i, j], tik=t2[i, k], tji=t2[j, i], tjk=t2[j, k], tki=t2[k, i], tkj=t2[k, j],
                  ti=t2[i], tj=t2[j], tTj=tT[j], tTk=tT[k],
@@ -116,8 +119,19 @@ class TriplesEngine(object):
             self.be.contract(d)
 
     def pairs(self):
+        """All occupied pairs (i >= j)."""
         o = self.eng.no
         return [(i, j) for i in range(o) for j in range(i + 1)]
+
+    def my_pairs(self):
+        """The pairs this rank evaluates (all of them on one GPU)."""
+        c = self.eng.comm
+        return deal_pairs(self.eng.no, c.rank, c.world)
+
+    def energy_all_ranks(self):
+        """E(T): every rank sums its own pairs, then one allreduce of a single double."""
+        et, _, _ = self.energy(self.my_pairs())
+        return self.eng.comm.allreduce_scalar(et)
 
     def energy(self, pairs=None):
         """E(T) summed over the triplets (i, j, k<=j) of the given occupied pairs (default: all).
