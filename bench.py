@@ -1,0 +1,409 @@
+#!/usr/bin/env python
+"""
+bench.py - the driver-facing benchmark of the pycc_b200 hot path.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload o,v]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Metric (BASELINE.json): CCSD seconds per iteration (+ (T) seconds and FP64 tensor TFLOP/s vs peak)
+on synthetic, symmetry-correct RHF integrals; default workload = configs[1], o=20 v=150 FP64.
+One "step" = one pass of the solve_cc loop body (pycc/ccwfn.py:274-329): residuals, amplitude
+update + norm, energy, DIIS push + extrapolation.  Prints ONE JSON line (rank 0).
+
+  value        seconds per CCSD iteration, amplitudes and integrals resident in HBM
+  e2e          the same iteration with the amplitudes living in pinned HOST memory: H2D of
+               (F, t1, t2) and D2H of the updated (t1, t2) + energy inside the timed region
+  roofline     the o^2 v^4 particle-particle ladder kernel (contract_f64_kernel): algorithmic
+               2 o^2 v^3 v_local flops / CUDA-event time of that launch, against the FP64
+               tensor (DMMA) issue-rate peak measured on this pool (profiles/r01_peaks.json)
+  cpu_baseline the NumPy oracle (a port of the reference's algorithm) timed on the host cores
+  triples      (T) seconds (t_tjl over i>=j>=k) and its TFLOP/s, timed after the K steps
+
+``--impl reference`` times the reference's CPU algorithm (the oracle port; the reference itself
+is pure Python + psi4 and cannot be imported on the GPU box) on the same workload.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+DMMA_PEAK_FALLBACK = 37.0   # TFLOP/s, profiles/r01_peaks.json (measured on this pool's B200)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="20,150", help="o,v (default: BASELINE.json configs[1])")
+    ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--no-triples", action="store_true", help="skip the (T) timing")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    return ap.parse_args()
+
+
+def flops_ccsd_iteration(o, v):
+    """Algorithmic flops of one reference residuals() call."""
+    return 2 * (o**2 * v**4 + 9 * o**3 * v**3 + 2 * o**4 * v**2 + 7 * o**2 * v**3 + 8 * o**3 * v**2
+                + o * v**3 + 2 * o**4 * v + 12 * o**2 * v**2 + o**3 * v + 3 * o * v**2 + 3 * o**2 * v)
+
+
+def flops_triples(o, v):
+    return (o * (o + 1) * (o + 2) // 6) * (12 * v**4 + 12 * o * v**3)
+
+
+def dmma_peak():
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "r01_peaks.json")))
+        return float(d["dmma_w8_c2_tflops"]), "measured DMMA issue-rate peak, profiles/r01_peaks.json"
+    except Exception:
+        return DMMA_PEAK_FALLBACK, "fallback 37.0 TFLOP/s (earlier DMMA measurement on this pool)"
+
+
+class ClockSampler(object):
+    """Samples SM clock and clock-event reasons of one GPU every 100 ms while running."""
+
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+               0x4: "sw_power_cap", 0x80: "hw_power_brake", 0x2: "applications_clocks_setting"}
+
+    def __init__(self, index):
+        self.samples, self.mask, self.max_mhz, self.ok = [], 0, None, False
+        self._stop = threading.Event()
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception:
+            self.ok = False
+        self.thread = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                self.samples.append(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM))
+                try:
+                    self.mask |= int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                except Exception:
+                    self.mask |= int(self.nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h))
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        if self.ok:
+            self.thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self.ok:
+            self.thread.join(timeout=2)
+        s = sorted(self.samples)
+        med = s[len(s) // 2] if s else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz,
+                "reasons": [n for b, n in self.REASONS.items() if self.mask & b], "samples": len(s)}
+
+
+def make_factor(o, v, seed):
+    """Seeded factor B (scaled so that E_MP2 = -0.10 Eh), Fock matrix F."""
+    from pycc_b200.synthetic import make_factor as mf, calibrated_scale
+    import numpy as np
+    B, eps, P = mf(o, v, seed)
+    s = calibrated_scale(B, eps, o, -0.10)
+    return B * s, np.diag(eps).copy(), s
+
+
+def set_host_threads():
+    """All host cores for the NumPy oracle (torchrun exports OMP_NUM_THREADS=1)."""
+    n = os.cpu_count() or 1
+    try:
+        from threadpoolctl import threadpool_limits
+        threadpool_limits(limits=n)
+    except Exception:
+        pass
+    return n
+
+
+def warm_numpy():
+    """Tiny oracle iteration so that NumPy/BLAS thread pools exist before anything is timed."""
+    import numpy as np
+    from pycc_b200.synthetic import SyntheticSystem
+    s = SyntheticSystem(3, 6, seed=1)
+    oracle_iteration(s.F, s.blocks, np.zeros((3, 6)), 0.01 * s.blocks["oovv"])
+
+
+def oracle_iteration(F, blocks, t1, t2):
+    """One reference iteration on the CPU: residuals + update + energy (pycc/ccwfn.py:274-296)."""
+    import numpy as np
+    from oracle import ccsd_oracle as oc
+    blk = blocks if isinstance(blocks, oc.Blocks) else oc.Blocks(blocks)
+    Dia, Dijab = oc.denominators(F, blk.no)
+    r1, r2 = oc.residuals(F, blk, t1, t2)
+    i1, i2 = r1 / Dia, r2 / Dijab
+    t1n, t2n = t1 + i1, t2 + i2
+    rms = float(np.sqrt((i1 * i1).sum() + (i2 * i2).sum()))
+    return r1, r2, t1n, t2n, oc.cc_energy(F, blk, t1n, t2n), rms
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import contextlib
+    import io
+    o, v = [int(x) for x in args.workload.split(",")]
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the pycc_b200 engine has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    group = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+        group = "world"
+    import pycc_b200
+    from pycc_b200.parallel import virtual_slice
+    from pycc_b200.synthetic import device_blocks
+    from pycc_b200.utils import helper_diis
+
+    B, F, scale = make_factor(o, v, args.seed)
+    vslice = virtual_slice(v, rank, world)
+    want_t = not args.no_triples
+    blocks = device_blocks(B, o, dev, vslice=vslice, keep_full_ovvv=True)
+    sink = io.StringIO()
+    with contextlib.redirect_stdout(sink):
+        w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD(T)" if want_t else "CCSD", group=group)
+    eng, be = w.engine, w.backend
+    diis = helper_diis(w.t1, w.t2, 8, "DP", backend=be)
+
+    def barrier():
+        torch.cuda.synchronize()
+        w.comm.barrier()
+        torch.cuda.synchronize()
+
+    # ---- warm-up + K timed steps (amplitudes and integrals resident in HBM) ------------------
+    niter = 0
+    for _ in range(max(args.warmup, 0)):
+        niter += 1
+        w._iteration(diis, niter, 1)
+    clocks = ClockSampler(local_rank)
+    barrier()
+    clocks.start()
+    launches0 = be.launch_count()
+    eng.ladder_events = []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    last = None
+    for _ in range(args.steps):
+        niter += 1
+        last = w._iteration(diis, niter, 1)
+    e1.record()
+    barrier()
+    ms_total = e0.elapsed_time(e1)
+    clk = clocks.stop()
+    launches = be.launch_count() - launches0
+    ladder_ms = [a.elapsed_time(b) for a, b in eng.ladder_events]
+    eng.ladder_events = None
+    tt = torch.tensor([ms_total], dtype=torch.float64, device=dev)
+    if world > 1:
+        import torch.distributed as dist
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    ms_step = float(tt.item()) / max(args.steps, 1)
+
+    # ---- roofline of the dominant kernel (ladder launch on this rank) ------------------------
+    peak, peak_src = dmma_peak()
+    vl = vslice[1] - vslice[0]
+    lad_flops = 2.0 * o * o * vl * v**3
+    lad_ms = sum(ladder_ms) / max(len(ladder_ms), 1)
+    lad_tf = lad_flops / (lad_ms * 1e-3) / 1e12 if lad_ms > 0 else 0.0
+    roofline = {"bound": "tensor", "kernel": "contract_f64_kernel (ladder r2 += 1/2 tau <ab|ef>)",
+                "achieved": round(lad_tf, 3), "peak": peak, "unit": "TFLOP/s", "frac": round(lad_tf / peak, 4),
+                "traffic": None, "launch_ms": round(lad_ms, 4), "flops_per_launch": lad_flops,
+                "peak_source": peak_src + " (FP64 has no entry in MEASURED_PEAKS.json; cuBLAS DGEMM on the "
+                "same box: 35.5 TFLOP/s)"}
+
+    # ---- e2e: amplitudes live in pinned host memory between iterations -------------------------
+    e2e = None
+    if not args.no_e2e:
+        F_pin = torch.as_tensor(F).pin_memory()
+        t1_pin = w.t1.detach().cpu().pin_memory()
+        t2_pin = w.t2.detach().cpu().pin_memory()
+        h2d = (F_pin.numel() + t1_pin.numel() + t2_pin.numel()) * 8
+        d2h = (t1_pin.numel() + t2_pin.numel()) * 8 + 16
+
+        def e2e_step(n):
+            eng.F.copy_(F_pin, non_blocking=True)
+            eng.eps.copy_(torch.diagonal(eng.F))
+            eng.t1.copy_(t1_pin, non_blocking=True)
+            eng.t2.copy_(t2_pin, non_blocking=True)
+            ecc, rms = w._iteration(diis, n, 1)          # energy and norm come back as host scalars
+            t1_pin.copy_(eng.t1, non_blocking=True)
+            t2_pin.copy_(eng.t2, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return ecc
+
+        niter += 1
+        e2e_step(niter)
+        barrier()
+        ksteps = max(min(args.steps, 5), 1)
+        t0 = time.perf_counter()
+        for _ in range(ksteps):
+            niter += 1
+            e2e_step(niter)
+        barrier()
+        dt = torch.tensor([(time.perf_counter() - t0) / ksteps], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        e2e = {"value": round(float(dt.item()), 6), "unit": "s/iteration", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": d2h, "steps": ksteps}
+
+    # ---- (T): timed once after the CCSD steps (all ranks; max over ranks) ---------------------
+    triples = None
+    if want_t:
+        import pycc_b200.cctriples as cct
+        tri = cct._engine(w)
+        tri.energy(tri.my_pairs()[:1])                 # warm-up: one occupied pair
+        barrier()
+        t0 = time.perf_counter()
+        et = cct.t_tjl(w)
+        barrier()
+        dt = torch.tensor([time.perf_counter() - t0], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        tsec = float(dt.item())
+        triples = {"seconds": round(tsec, 4), "E_T": et, "flops": flops_triples(o, v),
+                   "tflops": round(flops_triples(o, v) / tsec / 1e12, 3),
+                   "frac_of_peak": round(flops_triples(o, v) / tsec / 1e12 / (peak * world), 4)}
+
+    # ---- CPU baseline (rank 0, N=1 only): the oracle on the host cores + parity of the step -----
+    cpu_baseline, parity = None, None
+    if world == 1 and not args.no_cpu_baseline:
+        from oracle import ccsd_oracle as oc
+        cores = set_host_threads()
+        hb = {k: t.cpu().numpy() for k, t in w.H.blocks.items()}
+        t1h, t2h = w.t1.cpu().numpy().copy(), w.t2.cpu().numpy().copy()
+        # the GPU's answer for the same amplitudes
+        r1g, r2g = w.residuals(F, t1h, t2h)
+        blk = oc.Blocks(hb)
+        warm_numpy()
+        t0 = time.perf_counter()
+        r1c, r2c, _, _, ecpu, _ = oracle_iteration(F, blk, t1h, t2h)
+        cpu_s = time.perf_counter() - t0
+        parity = {"max_abs_dr1": float(np.abs(r1g.cpu().numpy() - r1c).max()),
+                  "max_abs_dr2": float(np.abs(r2g.cpu().numpy() - r2c).max()),
+                  "checked": "residuals() of the timed engine vs the oracle on the same (t1, t2), o=%d v=%d" % (o, v)}
+        cpu_baseline = {"value": round(cpu_s, 4), "unit": "s/iteration", "cores": cores, "kind": "port",
+                        "sample": "1 full CCSD iteration (residuals + update + energy) of the NumPy oracle "
+                                  "(port of pycc/ccwfn.py:331-366) at o=%d v=%d, after a tiny warm-up" % (o, v)}
+        if want_t:
+            from oracle import triples_oracle as ot
+            ns = 4
+            trip = [(o - 1, o // 2, 0), (o - 1, o - 1, o - 2), (o // 2, 1, 1), (3, 2, 1)][:ns]
+            t0 = time.perf_counter()
+            for (i, j, k) in trip:
+                ot.et_triplet(F, blk, t1h, t2h, i, j, k)
+            per = (time.perf_counter() - t0) / ns
+            ntrip = o * (o + 1) * (o + 2) // 6
+            cpu_baseline["triples"] = {"value": round(per * ntrip, 2), "unit": "s", "extrapolated": True,
+                                       "sample": "%d triplets timed (vectorised t_tjl body), x %d triplets" % (ns, ntrip)}
+
+    if rank == 0:
+        fl = flops_ccsd_iteration(o, v)
+        out = {"metric": "ccsd_seconds_per_iteration", "value": round(ms_step * 1e-3, 6), "unit": "s/iteration",
+               "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+               "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+               "data": "synthetic (seeded factorised 8-fold-symmetric ERIs, diagonal Fock; SURVEY.md 8(d))",
+               "config": {"workload": "RHF-CCSD iteration o=%d v=%d FP64" % (o, v), "o": o, "v": v,
+                          "parallelism": "virtual-index sharding x%d + allreduce(r1,r2)" % world if world > 1 else "1 GPU",
+                          "l2": "inputs larger than L2 (vvvv rows %.2f GB per rank)" % (vl * v**3 * 8 / 1e9),
+                          "seed": args.seed, "eri_scale": round(scale, 6), "diis": 8},
+               "tflops": round(fl / (ms_step * 1e-3) / 1e12, 3),
+               "tflops_frac_of_peak": round(fl / (ms_step * 1e-3) / 1e12 / (peak * world), 4),
+               "flops_per_iteration": fl, "flops_issued": eng.flops_issued(),
+               "energy": last[0] if last else None, "rms": last[1] if last else None,
+               "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "e2e": e2e,
+               "triples": triples, "cpu_baseline": cpu_baseline, "parity": parity}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_reference(args):
+    """The reference's CPU algorithm for the same workload, on all host cores.  The reference
+    itself (pure Python + psi4 + opt_einsum) is not importable on the GPU box, so this is the
+    oracle port (kind='port'); each step is one full CCSD iteration incl. DIIS, and the number of
+    steps is cut down when the first one shows that K+W of them would not finish in ~4 minutes."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import numpy as np
+    from oracle import ccsd_oracle as oc
+    from pycc_b200.synthetic import _blk
+    o, v = [int(x) for x in args.workload.split(",")]
+    cores = set_host_threads()
+    B, F, scale = make_factor(o, v, args.seed)
+    oo, vv = slice(0, o), slice(o, o + v)
+    blocks = {"oooo": _blk(B, oo, oo, oo, oo), "ooov": _blk(B, oo, oo, oo, vv), "oovv": _blk(B, oo, oo, vv, vv),
+              "ovov": _blk(B, oo, vv, oo, vv), "ovvv": _blk(B, oo, vv, vv, vv), "vvvv": _blk(B, vv, vv, vv, vv)}
+    blk = oc.Blocks(blocks)
+    Dia, Dijab = oc.denominators(F, o)
+    t1 = np.zeros((o, v))
+    t2 = blocks["oovv"] / Dijab
+    diis = oc.Diis(t1, t2, 8)
+    warm_numpy()
+
+    def step(t1, t2):
+        _, _, t1, t2, e, rms = oracle_iteration(F, blk, t1, t2)
+        diis.add_error_vector(t1, t2)
+        t1, t2 = diis.extrapolate(t1, t2)
+        return t1, t2, e
+
+    t0 = time.perf_counter()
+    t1, t2, e = step(t1, t2)                      # first (warm-up) step, also the calibration
+    first = time.perf_counter() - t0
+    budget = 240.0
+    warm = max(min(args.warmup - 1, int((0.25 * budget) / max(first, 1e-3))), 0)
+    for _ in range(warm):
+        t1, t2, e = step(t1, t2)
+    steps = max(min(args.steps, int((budget - (1 + warm) * first) / max(first, 1e-3))), 1)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        t1, t2, e = step(t1, t2)
+    sec = (time.perf_counter() - t0) / steps
+    fl = flops_ccsd_iteration(o, v)
+    out = {"impl": "reference", "metric": "ccsd_seconds_per_iteration", "value": round(sec, 4), "unit": "s/iteration",
+           "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": steps, "warmup": 1 + warm,
+           "ms_per_step": round(sec * 1e3, 2), "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+           "dtype": "f64", "data": "synthetic (same seeded system as the GPU arm)",
+           "config": {"workload": "RHF-CCSD iteration o=%d v=%d FP64" % (o, v), "o": o, "v": v, "seed": args.seed,
+                      "eri_scale": round(scale, 6), "diis": 8},
+           "tflops": round(fl / sec / 1e12, 4), "energy": float(e), "gpu_launches": 0,
+           "cpu_baseline": {"value": round(sec, 4), "unit": "s/iteration", "cores": cores, "kind": "port",
+                            "sample": "%d full CCSD iterations (residuals + update + energy + DIIS) of the NumPy "
+                                      "oracle at o=%d v=%d (requested %d; bounded to ~4 min)" % (steps, o, v, args.steps)},
+           "e2e": {"value": round(sec, 4), "unit": "s/iteration", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(out), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

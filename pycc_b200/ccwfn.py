@@ -191,10 +191,7 @@ class ccwfn(object):
         self.iteration_log = []
         for niter in range(1, maxiter + 1):
             ecc_last = ecc
-            eng.residuals(symmetrize=False)
-            # t += r/D with the pair symmetrisation of r2 (ccwfn.py:621) folded into the update
-            rms = np.sqrt(eng.update(symmetrize_on_the_fly=True))
-            ecc = eng.energy()
+            ecc, rms = self._iteration(diis, niter, start_diis, extrapolate=False)
             ediff = ecc - ecc_last
             print("CC Iter %3d: CC Ecorr = %.15f  dE = % .5E  rms = % .5E" % (niter, ecc, ediff, rms))
             self.iteration_log.append((niter, ecc, ediff, rms))
@@ -212,9 +209,25 @@ class ccwfn(object):
                 self.ecc = ecc
                 print("E(TOT)  = %20.15f" % (ecc + self.eref))
                 return ecc
-            diis.add_error_vector(self.t1, self.t2)
-            if niter >= start_diis:
-                self.t1, self.t2 = diis.extrapolate(self.t1, self.t2)
+            self._diis_step(diis, niter, start_diis)
+
+    def _iteration(self, diis, niter, start_diis, extrapolate=True):
+        """One pass of the solve_cc loop body (pycc/ccwfn.py:274-296, 327-329): residuals, t += r/D
+        with the pair symmetrisation of r2 (:621) folded into the update, the increment norm, the
+        energy and (``extrapolate``) the DIIS step.  Returns (ecc, rms).  This is the unit bench.py
+        times as one step."""
+        eng = self.engine
+        eng.residuals(symmetrize=False)
+        rms = np.sqrt(eng.update(symmetrize_on_the_fly=True))
+        ecc = eng.energy()
+        if extrapolate:
+            self._diis_step(diis, niter, start_diis)
+        return ecc, rms
+
+    def _diis_step(self, diis, niter, start_diis):
+        diis.add_error_vector(self.t1, self.t2)
+        if niter >= start_diis:
+            self.t1, self.t2 = diis.extrapolate(self.t1, self.t2)
 
     def _load(self, F, t1, t2):
         eng = self.engine

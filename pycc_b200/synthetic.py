@@ -90,3 +90,38 @@ class SyntheticSystem(object):
         n = self.no + self.nv
         a = slice(0, n)
         return _blk(self.B, a, a, a, a)
+
+
+def device_blocks(B, no, device, vslice=None, keep_full_ovvv=True, dtype=None):
+    """The six blocks built ON THE DEVICE from the (scaled) factor ``B`` (set-up only, untimed:
+    plain ``torch`` GEMMs; at o=40, v=400 the host cannot hold the 205 GB ``vvvv`` block, each rank
+    manufactures just its own rows).  ``vslice=(lo, hi)`` restricts ``vvvv`` to rows a in [lo, hi)
+    (and ``ovvv`` to b in [lo, hi) unless ``keep_full_ovvv``).  Same numbers as ``_blk``."""
+    import torch
+    dtype = dtype or torch.float64
+    Bd = torch.as_tensor(B).to(device=device, dtype=torch.float64)
+    n = Bd.shape[1]
+    nv = n - no
+    o, v = slice(0, no), slice(no, n)
+    lo, hi = (0, nv) if vslice is None else vslice
+    vs = slice(no + lo, no + hi)
+
+    def blk(p, q, r, s, chunk=None):
+        X = Bd[:, p, r]
+        Y = Bd[:, q, s]
+        naux = Bd.shape[0]
+        P, R, Q, S = X.shape[1], X.shape[2], Y.shape[1], Y.shape[2]
+        out = torch.empty((P, Q, R, S), dtype=dtype, device=device)
+        Ym = Y.reshape(naux, -1)
+        step = chunk or P
+        for p0 in range(0, P, step):        # chunked over p to bound the temporary
+            p1 = min(P, p0 + step)
+            tmp = (X[:, p0:p1].reshape(naux, -1).T @ Ym).reshape(p1 - p0, R, Q, S)
+            out[p0:p1].copy_(tmp.permute(0, 2, 1, 3))
+        return out
+
+    blocks = {"oooo": blk(o, o, o, o), "ooov": blk(o, o, o, v), "oovv": blk(o, o, v, v),
+              "ovov": blk(o, v, o, v),
+              "ovvv": blk(o, v if keep_full_ovvv else vs, v, v, chunk=4),
+              "vvvv": blk(vs, v, v, v, chunk=8)}
+    return blocks
