@@ -165,7 +165,7 @@ __device__ __forceinline__ void load_tile_mnmajor(unsigned tile_s, const double*
 }
 
 template <int VEC, int MI>
-__global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_constant__ DParams p) {
+__global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kernel(const __grid_constant__ DParams p) {
     constexpr int BM = 16 * MI;
     constexpr int PMA = BM + 4, PMB = BN + 4;
     constexpr int A_STAGE = (BM * PK > BK * PMA) ? BM * PK : BK * PMA;   // doubles
@@ -374,24 +374,37 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f64_kernel(const __grid_
         roff[i] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
         droff[i] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
     }
+    // Two-phase per column group: all loads of C / D for the group are issued before the first
+    // store, so their latencies overlap (a store to C may alias the next load of C as far as the
+    // compiler knows; interleaving them serialises ~8*MI round trips to L2/HBM per thread).
+    const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
 #pragma unroll
-    for (int j = 0; j < 4; ++j)
+    for (int j = 0; j < 4; ++j) {
+        long long co[2], dco[2];
+        bool cok[2];
+        double add[2][MI];
 #pragma unroll
         for (int e = 0; e < 2; ++e) {
             const unsigned col = colbase + j * 8 + e;
-            if (col >= p.N) continue;
-            const long long co = didx_off(p.cn, col);
-            const long long dco = p.D ? didx_off(p.dn, col) : 0;
+            cok[e] = col < p.N;
+            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
+            dco[e] = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
 #pragma unroll
             for (int i = 0; i < MI; ++i) {
-                if (roff[i] < 0) continue;
-                double v = alpha * acc[i][j][e];
-                double* c = p.C + roff[i] + co;
-                if (p.beta != 0.0) v += p.beta * (*c);
-                if (p.D) v += p.gamma * p.D[droff[i] + dco];
-                *c = v;
+                double v = 0.0;
+                if (cok[e] && roff[i] >= 0) {
+                    if (use_beta) v = p.beta * p.C[roff[i] + co[e]];
+                    if (use_d) v += p.gamma * p.D[droff[i] + dco[e]];
+                }
+                add[e][i] = v;
             }
         }
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+                if (cok[e] && roff[i] >= 0) p.C[roff[i] + co[e]] = alpha * acc[i][j][e] + add[e][i];
+    }
 }
 
 // fixed-order reduction of the split-K partial tiles + epilogue

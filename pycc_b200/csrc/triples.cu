@@ -35,13 +35,17 @@ struct TriplesArgs {
     double* partials;     // [ntrip][nb*(nb+1)/2]
 };
 
-// brick(x0,y0,z0) of W -> s[x][y][z] (padded), zero beyond nv
+// element (x0+x, y0+y, z0+z) of W for this thread's (x,y,z), zero beyond nv
 template <typename T>
-__device__ __forceinline__ void load_brick(double* s, const T* W, int nv, int x0, int y0, int z0, int tid) {
+__device__ __forceinline__ double fetch_brick(const T* W, int nv, int x0, int y0, int z0, int tid) {
     const int z = tid & 7, y = (tid >> 3) & 7, x = tid >> 6;
     const int gx = x0 + x, gy = y0 + y, gz = z0 + z;
     double v = 0.0;
-    if (gx < nv && gy < nv && gz < nv) v = (double)W[((long long)gx * nv + gy) * nv + gz];
+    if (gx < nv && gy < nv && gz < nv) v = (double)__ldg(&W[((long long)gx * nv + gy) * nv + gz]);
+    return v;
+}
+__device__ __forceinline__ void store_brick(double* s, double v, int tid) {
+    const int z = tid & 7, y = (tid >> 3) & 7, x = tid >> 6;
     s[(x * TB_ + y) * (TB_ + 1) + z] = v;
 }
 
@@ -80,17 +84,27 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
     const int a = A0 + la, b = B0 + lb;
     double esum = 0.0;
 
+    // the six permuted bricks of the NEXT c-tile are fetched into registers while the current
+    // one is being consumed from shared memory (hides the global-load latency of this
+    // HBM/L2-bound pass)
+    double nxt[6];
+    auto fetch = [&](int C0) {
+        nxt[0] = fetch_brick(W, nv, A0, B0, C0, tid);   // [a][b][c]
+        nxt[1] = fetch_brick(W, nv, A0, C0, B0, tid);   // [a][c][b]
+        nxt[2] = fetch_brick(W, nv, B0, A0, C0, tid);   // [b][a][c]
+        nxt[3] = fetch_brick(W, nv, B0, C0, A0, tid);   // [b][c][a]
+        nxt[4] = fetch_brick(W, nv, C0, A0, B0, tid);   // [c][a][b]
+        nxt[5] = fetch_brick(W, nv, C0, B0, A0, tid);   // [c][b][a]
+    };
+    fetch(0);
     for (int TCk = 0; TCk <= TBk; ++TCk) {
         const int C0 = TCk * TB_;
         const int c = C0 + lc;
         __syncthreads();
-        load_brick(sW[0], W, nv, A0, B0, C0, tid);   // [a][b][c]
-        load_brick(sW[1], W, nv, A0, C0, B0, tid);   // [a][c][b]
-        load_brick(sW[2], W, nv, B0, A0, C0, tid);   // [b][a][c]
-        load_brick(sW[3], W, nv, B0, C0, A0, tid);   // [b][c][a]
-        load_brick(sW[4], W, nv, C0, A0, B0, tid);   // [c][a][b]
-        load_brick(sW[5], W, nv, C0, B0, A0, tid);   // [c][b][a]
+#pragma unroll
+        for (int q = 0; q < 6; ++q) store_brick(sW[q], nxt[q], tid);
         __syncthreads();
+        if (TCk < TBk) fetch(C0 + TB_);
         if (a < nv && b < nv && c < nv && a >= b && b >= c) {
             const double Wabc = brick_at(sW[0], la, lb, lc);
             const double Wacb = brick_at(sW[1], la, lc, lb);

@@ -207,7 +207,24 @@ def plan(stmt, tensors, dtype=_lib.F64):
                 break
         if not placed:
             # first term of a new launch: let N carry the output's fastest index (coalesced stores)
-            cands.sort(key=lambda c: 0 if smallest in c[3] else 1)
+            # tile waste first (the kernel's CTA tile is (16*MI) x 128, MI in {1,2,4,5,6,8}: a
+            # 150-wide index belongs on M as 2 x 80, not on N as 2 x 128), then coalesced stores
+            letters = {}
+            for (nm, idx) in (fx, fy, (out_name, out_idx)):
+                for letter, n in zip(idx, ref(nm).shape):
+                    letters[letter] = n
+
+            def padded(c):
+                Mx = Nx = 1
+                for x in c[2]:
+                    Mx *= letters[x]
+                for x in c[3]:
+                    Nx *= letters[x]
+                pm = min(-(-Mx // bm) * bm for bm in (128, 96, 80, 64, 32, 16))
+                return pm * (-(-Nx // 128) * 128)
+
+            best = min(padded(c) for c in cands)
+            cands.sort(key=lambda c: (0 if padded(c) <= 1.03 * best else 1, 0 if smallest in c[3] else 1))
             fa, fb, M, N, K, batch = cands[0]
             groups.append(dict(M=M, N=N, batch=batch, segs=[(coef, fa, fb, K)]))
 

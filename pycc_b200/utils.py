@@ -36,36 +36,56 @@ class helper_diis(object):
         self.shape1, self.shape2 = tuple(t1.shape), tuple(t2.shape)
         self.dtype = t2.dtype
         self.diis_size = 0
+        # every history vector the bookkeeping can hold at once (max_diis+2 amplitude vectors,
+        # max_diis+1 error vectors, the extrapolated one) is allocated now and recycled, so no
+        # device allocation happens inside the iteration
+        self._pool = [self.be.empty((self.n1 + self.n2,), self.dtype) for _ in range(2 * max_diis + 4)] \
+            if max_diis > 0 else []
+        self.diis_vals = []
+        self.old = None
         self.old = self._pack(t1, t2)
-        self.diis_vals = [self.old.clone()]
+        first = self._alloc()
+        first.copy_(self.old)
+        self.diis_vals = [first]
         self.diis_errors = []
         self._gram = {}          # (id_a, id_b) -> <e_a, e_b>
         self._ids = []           # identity tags of the error vectors, parallel to diis_errors
         self._next_id = 0
 
+    def _alloc(self):
+        return self._pool.pop() if self._pool else self.be.empty((self.n1 + self.n2,), self.dtype)
+
+    def _release(self, v):
+        if v is not None and not any(v is x for x in self.diis_vals) and v is not self.old:
+            self._pool.append(v)
+
     def _pack(self, t1, t2):
-        v = self.be.empty((self.n1 + self.n2,), self.dtype)
+        v = self._alloc()
         v[:self.n1].copy_(t1.reshape(-1))
         v[self.n1:].copy_(t2.reshape(-1))
         return v
 
     def add_error_vector(self, t1, t2):
+        if self.max_diis == 0:
+            return        # the history is never read (extrapolate returns at once, utils.py:50-51)
         cur = self._pack(t1, t2)
         self.diis_vals.append(cur)
-        err = self.be.empty((self.n1 + self.n2,), self.dtype)
+        err = self._alloc()
         self.be.bind_stream()
         self.be.axpby(err, 1.0, cur, -1.0, self.old)
         self.diis_errors.append(err)
         self._ids.append(self._next_id)
         self._next_id += 1
-        self.old = cur        # cur is never modified afterwards
+        prev, self.old = self.old, cur        # cur is never modified afterwards
+        self._release(prev)
 
     def extrapolate(self, t1, t2):
         if self.max_diis == 0:
             return t1, t2
         if len(self.diis_errors) > self.max_diis:
-            del self.diis_vals[0]
-            del self.diis_errors[0]
+            v0, e0 = self.diis_vals.pop(0), self.diis_errors.pop(0)
+            self._pool.append(e0)
+            self._release(v0)
             dead = self._ids.pop(0)
             self._gram = {k: v for k, v in self._gram.items() if dead not in k}
         self.diis_size = m = len(self.diis_errors)
@@ -82,9 +102,10 @@ class helper_diis(object):
         resid = np.zeros(m + 1)
         resid[-1] = -1.0
         ci = np.linalg.solve(B, resid)
-        new = self.be.empty((self.n1 + self.n2,), self.dtype)
+        new = self._alloc()
         self.be.lincomb(new, [self.diis_vals[k + 1] for k in range(m)], [ci[k] for k in range(m)])
-        self.old = new
+        prev, self.old = self.old, new
+        self._release(prev)
         # the caller's amplitude tensors are updated in place (they are the engine's buffers)
         t1.copy_(new[:self.n1].reshape(self.shape1))
         t2.copy_(new[self.n1:].reshape(self.shape2))

@@ -27,7 +27,8 @@ def test_solve_cc_iterations_match_reference(golden):
     assert len(w.iteration_log) == ref_log.shape[0]
     for (it, ecc, de, rms), row in zip(w.iteration_log, ref_log):
         assert abs(ecc - row[0]) < 1e-12
-        assert abs(rms - row[2]) < 2e-5 * row[2]      # the reference prints rms with 5 decimals
+        # the reference prints rms with 5 decimals; below 1e-10 the increment norm is rounding noise
+        assert abs(rms - row[2]) < 2e-5 * row[2] + 1e-10
     assert abs(e - float(g["solve_eccsd_t_total"])) < 1e-12
     assert np.abs(w.t1.numpy() - g["solve_t1"]).max() < 1e-11
     assert np.abs(w.t2.numpy() - g["solve_t2"]).max() < 1e-11
