@@ -107,8 +107,9 @@ class ccwfn(object):
         if precision.upper() not in valid_precision:
             raise Exception('%s is not an allowed precision arithmetic.' % (precision))
         self.precision = precision.upper()
-        if self.precision == 'SP':
-            raise Exception("precision='SP' (FP32 contractions) is not implemented in the B200 engine yet.")
+        # 'SP' = the engine's mixed-precision mode: FP32 storage and contractions (3xTF32 on the tensor
+        # cores), FP64 accumulation of the energy, the increment norm and the DIIS algebra.  (The
+        # reference's SP mode keeps everything in float32: pycc/ccwfn.py:189-196, utils.py:104-105.)
         valid_device = ['CPU', 'GPU']
         device = kwargs.pop('device', 'GPU')
         if device.upper() not in valid_device:
@@ -140,7 +141,7 @@ class ccwfn(object):
         self.v = slice(no, no + nv)
         self.C = C
 
-        dtype = torch.float64
+        dtype = torch.float32 if self.precision == 'SP' else torch.float64
         from .parallel import virtual_slice
         vslice = virtual_slice(nv, self.comm.rank, self.comm.world)
         keep_ovvv = (model == 'CCSD(T)' or self.comm.world == 1)

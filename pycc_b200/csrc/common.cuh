@@ -98,3 +98,6 @@ static inline DIdx to_didx(const pccb_cidx& c, long long extent) {
 
 // fixed-order two-stage sum reduction helpers (reduce.cu)
 int pccb_ensure_partials(pccb_ctx* ctx, size_t ndoubles);
+
+// FP32-operand contraction (contract_f32.cu); arguments already validated by pccb_contract
+int pccb_contract_f32(pccb_ctx* ctx, const pccb_contraction* desc);

@@ -534,12 +534,13 @@ int choose_mi(long long M) {
 extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
     if (!ctx) return PCCB_ERR_ARG;
     PCCB_REQUIRE(ctx, d != nullptr, "pccb_contract: null descriptor");
-    PCCB_REQUIRE(ctx, d->dtype == PCCB_F64, "pccb_contract: only PCCB_F64 is implemented (dtype=%d)", d->dtype);
+    PCCB_REQUIRE(ctx, d->dtype == PCCB_F64 || d->dtype == PCCB_F32, "pccb_contract: unknown dtype %d", d->dtype);
     PCCB_REQUIRE(ctx, d->nseg >= 0 && d->nseg <= PCCB_MAX_SEGMENTS, "pccb_contract: nseg=%d out of range", d->nseg);
     PCCB_REQUIRE(ctx, d->M > 0 && d->N > 0 && d->batch > 0, "pccb_contract: empty output (M=%lld N=%lld batch=%lld)",
                  (long long)d->M, (long long)d->N, (long long)d->batch);
     PCCB_REQUIRE(ctx, d->M < (1ll << 31) && d->N < (1ll << 31), "pccb_contract: M/N too large");
     PCCB_REQUIRE(ctx, d->C_dev != nullptr, "pccb_contract: C_dev is null");
+    if (d->dtype == PCCB_F32) return pccb_contract_f32(ctx, d);   // 3xTF32 tensor-core kernel (contract_f32.cu)
 
     DParams p;
     memset(&p, 0, sizeof(p));

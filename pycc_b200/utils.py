@@ -150,8 +150,10 @@ class cc_contract(object):
                 x = x.to(be.device)
             ops.append(x)
         dtype = ops[0].dtype
-        if dtype not in (torch.float64,):
-            raise ValueError("cc_contract: float64 operands only (got %s)" % dtype)
+        if dtype not in (torch.float64, torch.float32):
+            raise ValueError("cc_contract: float64 / float32 operands only (got %s)" % dtype)
+        ops = [x if x.dtype == dtype else x.to(dtype) for x in ops]
+        dcode = _lib.F64 if dtype == torch.float64 else _lib.F32
         if len(ops) == 1:
             perm = [ins[0].index(c) for c in out_idx]
             if len(perm) != len(ins[0]):
@@ -190,6 +192,6 @@ class cc_contract(object):
         else:
             T = {"C": out, "A": ops[0], "B": ops[1]}
         be.bind_stream()
-        for L in plan("C[%s] = A[%s]*B[%s]" % (out_idx, ins[0], ins[1]), T, _lib.F64):
+        for L in plan("C[%s] = A[%s]*B[%s]" % (out_idx, ins[0], ins[1]), T, dcode):
             be.contract(L.desc)
         return out.reshape(()) if out_idx == "" else out

@@ -75,6 +75,52 @@ def test_contract_vs_einsum(be, case, naive):
     assert (got2 - (ref + C0)).abs().max().item() < 1e-12 * max(scale, 1.0) * 50
 
 
+F32_EXTRA = [
+    # shapes that allow 16-byte (4-float) and 8-byte (2-float) cp.async chunks in the FP32 kernel
+    ("C[ijab] = 0.5*A[ijef]*B[abef]", dict(A=(6, 6, 12, 12), B=(12, 12, 12, 12), C=(6, 6, 12, 12))),
+    ("C[mn] = A[mk]*B[nk]", dict(A=(200, 512), B=(136, 512), C=(200, 136))),
+    ("C[mn] = A[km]*B[kn]", dict(A=(320, 132), B=(320, 264), C=(132, 264))),
+    ("C[ijab] = A[imae]*B[jbme] + A2[imae]*B2[jbme]",
+     dict(A=(4, 4, 16, 16), A2=(4, 4, 16, 16), B=(4, 16, 4, 16), B2=(4, 16, 4, 16), C=(4, 4, 16, 16))),
+]
+
+
+@pytest.mark.parametrize("naive", [False, True])
+@pytest.mark.parametrize("case", range(len(CASES) + len(F32_EXTRA)))
+def test_contract_f32_vs_einsum(be, case, naive):
+    """FP32 operands (precision='SP'): 3xTF32 tensor-core kernel and the FP32 naive kernel against an
+    FP64 einsum of the same FP32 inputs.  Tolerance: FP32 rounding of a length-K dot product."""
+    from pycc_b200.dsl import parse, plan
+    from pycc_b200 import _lib
+    stmt, shapes = (CASES + F32_EXTRA)[case]
+    g = torch.Generator(device="cpu").manual_seed(100 + case)
+    T = {k: torch.randn(s, generator=g, dtype=torch.float32).to(be.device) for k, s in shapes.items()}
+    out_name, out_idx, acc, terms = parse(stmt)
+    ref = torch.zeros(shapes[out_name], dtype=torch.float64, device=be.device)
+    mag = torch.zeros_like(ref)
+    for coef, fac in terms:
+        spec = ",".join(f[1] for f in fac) + "->" + out_idx
+        ref += coef * torch.einsum(spec, *[T[f[0]].double() for f in fac])
+        mag += abs(coef) * torch.einsum(spec, *[T[f[0]].double().abs() for f in fac])
+    be.use_naive_contract(naive)
+    try:
+        T[out_name].fill_(float("nan"))
+        for L in plan(stmt, T, _lib.F32):
+            be.contract(L.desc)
+        got1 = T[out_name].double().clone()
+        C0 = torch.randn(shapes[out_name], generator=g, dtype=torch.float32).to(be.device)
+        T[out_name].copy_(C0)
+        for L in plan(stmt.replace(" = ", " += ", 1), T, _lib.F32):
+            be.contract(L.desc)
+        got2 = T[out_name].double().clone()
+    finally:
+        be.use_naive_contract(False)
+    # |error| <= c * eps32 * sum|a||b| (3xTF32 drops only the lo*lo term, ~2^-22 relative)
+    tol = 4e-6 * mag + 1e-6
+    assert ((got1 - ref).abs() <= tol).all()
+    assert ((got2 - (ref + C0.double())).abs() <= tol + 1e-6 * C0.double().abs()).all()
+
+
 def test_elementwise_vs_torch(be):
     no, nv = 5, 37
     g = torch.Generator(device="cpu").manual_seed(3)

@@ -136,3 +136,44 @@ def test_residual_properties_at_scale():
     Bv = torch.as_tensor(s.B[:, no:, no:]).to(be.device)
     chk = torch.einsum('ijef,Qae,Qbf->ijab', eng.tau, Bv, Bv)
     assert (out - chk).abs().max().item() < 1e-11
+
+
+def test_mixed_precision_mode(golden):
+    """precision='SP': FP32 storage + 3xTF32 contractions, FP64 energy / norm / DIIS.
+    Bar (BASELINE.json north_star): |E - E_DP(reference)| <= 1e-6 Eh; the reference's own
+    all-float32 SP energy on the same input is reported next to it."""
+    import pycc_b200
+    g = golden
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CCSD(T)", precision="SP")
+        e = w.solve_cc(e_conv=1e-7, r_conv=1e-7, maxiter=100)
+    assert e is not None
+    assert w.t2.dtype == torch.float32
+    assert abs(e - float(g["solve_eccsd_t_total"])) < 1e-6
+    assert abs((e - pycc_b200.t_tjl(w)) - float(g["solve_sp_ecc"])) < 5e-6     # reference SP mode, all float32
+    assert np.abs(w.t2.cpu().numpy().astype(np.float64) - g["solve_t2"]).max() < 1e-5
+
+
+def test_mixed_precision_seeded():
+    import pycc_b200
+    from pycc_b200.synthetic import SyntheticSystem
+    from oracle import ccsd_oracle as oc
+    no, nv = 8, 36
+    s = SyntheticSystem(no, nv, seed=11, fock_offdiag=True)
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(s.F, s.blocks, no, precision="SP")
+        e = w.solve_cc(e_conv=1e-7, r_conv=1e-7, maxiter=100)
+    eo, t1, t2, niter = oc.solve_cc(s.F, s.blocks, 1e-10, 1e-10)
+    assert abs(e - eo) < 1e-6
+    # the 3xTF32 kernel against the plain-FP32 naive kernel on one residual call
+    be = w.backend
+    r1, r2 = w.residuals(s.F, t1, t2)
+    be.use_naive_contract(True)
+    try:
+        n1, n2 = w.residuals(s.F, t1, t2)
+    finally:
+        be.use_naive_contract(False)
+    r1o, r2o = oc.residuals(s.F, oc.Blocks(s.blocks), t1, t2)
+    assert np.abs(r2.cpu().numpy() - r2o).max() < 2e-6
+    assert np.abs(n2.cpu().numpy() - r2o).max() < 2e-6
+    assert np.abs(r1.cpu().numpy() - r1o).max() < 2e-6

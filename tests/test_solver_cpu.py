@@ -117,3 +117,14 @@ def test_contract_operator_and_triples_builders(golden):
     V = pycc_b200.t3d_ijk(w.o, w.v, i, j, k, w.t1, t2, w.H.ERI[w.o, w.o, w.v, w.v], w.H.F, c, False)
     assert np.abs(V.numpy() - ot.v_disconnected(g.F, blk, g["sym_t1"], g["sym_t2"], i, j, k)).max() < 1e-13
     assert abs(pycc_b200.t_vikings(w) - float(g["sym_et_tjl"])) < 1e-12
+
+
+def test_sp_mode_host_logic(golden):
+    """precision='SP' through the interpreter back end: FP32 storage, FP64 energy/norm/DIIS."""
+    g = golden
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, precision="SP", _backend=InterpBackend())
+        e = w.solve_cc(e_conv=1e-7, r_conv=1e-7, maxiter=100)
+    assert w.t2.dtype == torch.float32 and w.precision == "SP"
+    assert abs(e - float(g["solve_eccsd"])) < 1e-6
+    assert abs(e - float(g["solve_sp_ecc"])) < 5e-6
