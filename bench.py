@@ -44,6 +44,8 @@ def parse_args():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="20,150", help="o,v (default: BASELINE.json configs[1])")
     ap.add_argument("--seed", type=int, default=0)
+    ap.add_argument("--precision", default="DP", choices=["DP", "SP"],
+                    help="SP = mixed mode: FP32 contractions (3xTF32), FP64 energy/norm/DIIS")
     ap.add_argument("--no-triples", action="store_true", help="skip the (T) timing")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -181,12 +183,15 @@ def run_ours(args):
     B, F, scale = make_factor(o, v, args.seed)
     vslice = virtual_slice(v, rank, world)
     want_t = not args.no_triples
-    blocks = device_blocks(B, o, dev, vslice=vslice, keep_full_ovvv=True)
+    sp = args.precision == "SP"
+    blocks = device_blocks(B, o, dev, vslice=vslice, keep_full_ovvv=want_t or world == 1,
+                           dtype=torch.float32 if sp else torch.float64)
     sink = io.StringIO()
     with contextlib.redirect_stdout(sink):
-        w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD(T)" if want_t else "CCSD", group=group)
+        w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD(T)" if want_t else "CCSD", group=group,
+                                        precision=args.precision)
     eng, be = w.engine, w.backend
-    diis = helper_diis(w.t1, w.t2, 8, "DP", backend=be)
+    diis = helper_diis(w.t1, w.t2, 8, args.precision, backend=be)
 
     def barrier():
         torch.cuda.synchronize()
@@ -224,15 +229,22 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel (ladder launch on this rank) ------------------------
     peak, peak_src = dmma_peak()
+    if sp:
+        try:
+            peak = json.load(open(os.path.join(ROOT, "profiles", "r01_peaks.json")))["mma_sync_tf32_tflops"] / 3.0
+        except Exception:
+            peak = 92.5
+        peak_src = "measured mma.sync TF32 rate / 3 (3xTF32 split), profiles/r01_peaks.json"
     vl = vslice[1] - vslice[0]
     lad_flops = 2.0 * o * o * vl * v**3
     lad_ms = sum(ladder_ms) / max(len(ladder_ms), 1)
     lad_tf = lad_flops / (lad_ms * 1e-3) / 1e12 if lad_ms > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "contract_f64_kernel (ladder r2 += 1/2 tau <ab|ef>)",
+    roofline = {"bound": "tensor", "kernel": "contract_f%s_kernel (ladder r2 += 1/2 tau <ab|ef>)" % ("32" if sp else "64"),
                 "achieved": round(lad_tf, 3), "peak": peak, "unit": "TFLOP/s", "frac": round(lad_tf / peak, 4),
                 "traffic": None, "launch_ms": round(lad_ms, 4), "flops_per_launch": lad_flops,
-                "peak_source": peak_src + " (FP64 has no entry in MEASURED_PEAKS.json; cuBLAS DGEMM on the "
-                "same box: 35.5 TFLOP/s)"}
+                "peak_source": peak_src + (" (cuBLAS SGEMM on the same box: 63.9 TFLOP/s)" if sp else
+                                           " (FP64 has no entry in MEASURED_PEAKS.json; cuBLAS DGEMM on the "
+                                           "same box: 35.5 TFLOP/s)")}
 
     # ---- e2e: amplitudes live in pinned host memory between iterations -------------------------
     e2e = None
@@ -240,8 +252,9 @@ def run_ours(args):
         F_pin = torch.as_tensor(F).pin_memory()
         t1_pin = w.t1.detach().cpu().pin_memory()
         t2_pin = w.t2.detach().cpu().pin_memory()
-        h2d = (F_pin.numel() + t1_pin.numel() + t2_pin.numel()) * 8
-        d2h = (t1_pin.numel() + t2_pin.numel()) * 8 + 16
+        w_ = t2_pin.element_size()
+        h2d = F_pin.numel() * 8 + (t1_pin.numel() + t2_pin.numel()) * w_
+        d2h = (t1_pin.numel() + t2_pin.numel()) * w_ + 16
 
         def e2e_step(n):
             eng.F.copy_(F_pin, non_blocking=True)
@@ -292,8 +305,8 @@ def run_ours(args):
     if world == 1 and not args.no_cpu_baseline:
         from oracle import ccsd_oracle as oc
         cores = set_host_threads()
-        hb = {k: t.cpu().numpy() for k, t in w.H.blocks.items()}
-        t1h, t2h = w.t1.cpu().numpy().copy(), w.t2.cpu().numpy().copy()
+        hb = {k: t.double().cpu().numpy() for k, t in w.H.blocks.items()}
+        t1h, t2h = w.t1.double().cpu().numpy().copy(), w.t2.double().cpu().numpy().copy()
         # the GPU's answer for the same amplitudes
         r1g, r2g = w.residuals(F, t1h, t2h)
         blk = oc.Blocks(hb)
@@ -301,8 +314,8 @@ def run_ours(args):
         t0 = time.perf_counter()
         r1c, r2c, _, _, ecpu, _ = oracle_iteration(F, blk, t1h, t2h)
         cpu_s = time.perf_counter() - t0
-        parity = {"max_abs_dr1": float(np.abs(r1g.cpu().numpy() - r1c).max()),
-                  "max_abs_dr2": float(np.abs(r2g.cpu().numpy() - r2c).max()),
+        parity = {"max_abs_dr1": float(np.abs(r1g.double().cpu().numpy() - r1c).max()),
+                  "max_abs_dr2": float(np.abs(r2g.double().cpu().numpy() - r2c).max()),
                   "checked": "residuals() of the timed engine vs the oracle on the same (t1, t2), o=%d v=%d" % (o, v)}
         cpu_baseline = {"value": round(cpu_s, 4), "unit": "s/iteration", "cores": cores, "kind": "port",
                         "sample": "1 full CCSD iteration (residuals + update + energy) of the NumPy oracle "
@@ -323,10 +336,10 @@ def run_ours(args):
         fl = flops_ccsd_iteration(o, v)
         out = {"metric": "ccsd_seconds_per_iteration", "value": round(ms_step * 1e-3, 6), "unit": "s/iteration",
                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
-               "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+               "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f32" if sp else "f64",
                "data": "synthetic (seeded factorised 8-fold-symmetric ERIs, diagonal Fock; SURVEY.md 8(d))",
-               "config": {"workload": "RHF-CCSD iteration o=%d v=%d FP64" % (o, v), "o": o, "v": v,
-                          "parallelism": "virtual-index sharding x%d + allreduce(r1,r2)" % world if world > 1 else "1 GPU",
+               "config": {"workload": "RHF-CCSD iteration o=%d v=%d %s" % (o, v, "FP32 contractions / FP64 energy+DIIS" if sp else "FP64"),
+                          "o": o, "v": v, "parallelism": "virtual-index sharding x%d + allreduce(r1,r2)" % world if world > 1 else "1 GPU",
                           "l2": "inputs larger than L2 (vvvv rows %.2f GB per rank)" % (vl * v**3 * 8 / 1e9),
                           "seed": args.seed, "eri_scale": round(scale, 6), "diis": 8},
                "tflops": round(fl / (ms_step * 1e-3) / 1e12, 3),
