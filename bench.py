@@ -226,6 +226,10 @@ def run_ours(args):
         import torch.distributed as dist
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
     ms_step = float(tt.item()) / max(args.steps, 1)
+    fi = torch.tensor([float(eng.flops_issued())], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(fi, op=dist.ReduceOp.SUM)
+    flops_issued = float(fi.item())
 
     # ---- roofline of the dominant kernel (ladder launch on this rank) ------------------------
     peak, peak_src = dmma_peak()
@@ -344,7 +348,9 @@ def run_ours(args):
                           "seed": args.seed, "eri_scale": round(scale, 6), "diis": 8},
                "tflops": round(fl / (ms_step * 1e-3) / 1e12, 3),
                "tflops_frac_of_peak": round(fl / (ms_step * 1e-3) / 1e12 / (peak * world), 4),
-               "flops_per_iteration": fl, "flops_issued": eng.flops_issued(),
+               "flops_per_iteration": fl, "flops_issued": flops_issued,
+               "tflops_issued": round(flops_issued / (ms_step * 1e-3) / 1e12, 3),
+               "tflops_issued_frac_of_peak": round(flops_issued / (ms_step * 1e-3) / 1e12 / (peak * world), 4),
                "energy": last[0] if last else None, "rms": last[1] if last else None,
                "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "e2e": e2e,
                "triples": triples, "cpu_baseline": cpu_baseline, "parity": parity}
