@@ -112,11 +112,11 @@ __device__ __forceinline__ void cp_async_vec(unsigned dst, const void* src, int 
 //   rows[]  : element offset of each tile row, batch offset included (rows >= rlim unused)
 //   K-major : tile[row][k], pitch PK - a thread owns one k-chunk column, walks the rows
 //   MN-major: tile[k][row], pitch ROWS+4 - a thread owns one row chunk, walks the k rows
-template <int VEC, int ROWS>
+template <int VEC, int ROWS, int NT = NTHREADS>
 __device__ __forceinline__ void load_tile_kmajor(unsigned tile_s, const double* base, const long long* rows,
                                                  int rlim, const DIdx& kidx, unsigned k0, unsigned K, int tid) {
     constexpr int CH = BK / VEC;            // chunks per row
-    constexpr int RPP = NTHREADS / CH;      // rows per pass
+    constexpr int RPP = NT / CH;            // rows per pass
     constexpr int PASSES = (ROWS + RPP - 1) / RPP;
     const int kc = tid % CH, r0 = tid / CH;
     const unsigned k = k0 + kc * VEC;
@@ -138,12 +138,12 @@ __device__ __forceinline__ void load_tile_kmajor(unsigned tile_s, const double* 
     }
 }
 
-template <int VEC, int ROWS>
+template <int VEC, int ROWS, int NT = NTHREADS>
 __device__ __forceinline__ void load_tile_mnmajor(unsigned tile_s, const double* base, const long long* rows,
                                                   int rlim, const DIdx& kidx, unsigned k0, unsigned K, int tid) {
     constexpr int PM = ROWS + 4;
     constexpr int CH = ROWS / VEC;                                   // chunks per k-row
-    constexpr int KPP = (NTHREADS / CH) < BK ? (NTHREADS / CH) : BK; // k-rows per pass
+    constexpr int KPP = (NT / CH) < BK ? (NT / CH) : BK; // k-rows per pass
     constexpr int PASSES = (BK + KPP - 1) / KPP;
     const int mc = tid % CH, kr0 = tid / CH;
     const int row = mc * VEC;
@@ -407,6 +407,247 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
     }
 }
 
+// ---- warp-specialised variant ------------------------------------------------------------------
+// 8 consumer warps (2(M) x 4(N), DMMA + LDS.64 only) + 4 producer warps that own the whole
+// operand staging: compound-index address arithmetic, cp.async (LDGSTS) issue and the
+// full/empty mbarrier hand-shake.  The consumers' instruction stream is then DMMA-dense, and the
+// producers run up to WS_STAGES k-tiles ahead.  Registers are re-balanced with setmaxnreg
+// (producers 56, consumers 216 per thread).
+constexpr int NCONS = 256, NPROD = 128, NTHREADS_WS = NCONS + NPROD, WS_STAGES = 4;
+
+__device__ __forceinline__ void bar_sync_producers() {
+    asm volatile("bar.sync 1, %0;\n" ::"n"(NPROD) : "memory");
+}
+
+template <int VEC, int MI>
+__global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const __grid_constant__ DParams p) {
+    constexpr int BM = 16 * MI;
+    constexpr int PMA = BM + 4, PMB = BN + 4;
+    constexpr int A_STAGE = (BM * PK > BK * PMA) ? BM * PK : BK * PMA;   // doubles
+    constexpr int B_STAGE = (BN * PK > BK * PMB) ? BN * PK : BK * PMB;
+    constexpr int S = WS_STAGES;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* sA = reinterpret_cast<double*>(smem_raw);
+    double* sB = sA + S * A_STAGE;
+    long long* rowA = reinterpret_cast<long long*>(sB + S * B_STAGE);
+    long long* rowB = rowA + BM;
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(rowB + BN);   // full[S], empty[S]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const int batch = blockIdx.z / p.splits, split = blockIdx.z % p.splits;
+    const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
+    const int kt_hi = (int)(((long long)p.total_kt * (split + 1)) / p.splits);
+    const int nkt = kt_hi - kt_lo;
+
+    const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
+    const unsigned sB_s = (unsigned)__cvta_generic_to_shared(sB);
+    const unsigned full_s = (unsigned)__cvta_generic_to_shared(bars);
+    const unsigned empty_s = full_s + 8 * S;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            mbar_init(full_s + 8 * s, NPROD);
+            mbar_init(empty_s + 8 * s, NCONS / 32);
+        }
+    }
+    __syncthreads();
+
+    auto seg_of = [&](int kt) {
+        int s = 0;
+#pragma unroll
+        for (int q = 1; q < PCCB_MAX_SEGMENTS; ++q)
+            if (q < p.nseg && kt >= p.seg[q].kt_begin) s = q;
+        return s;
+    };
+
+    if (warp >= NCONS / 32) {
+        // ================================ producers ================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;\n");
+        const int ptid = tid - NCONS;
+        const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
+        int cur_seg = -1;
+#pragma unroll 1
+        for (int it = 0; it < nkt; ++it) {
+            const int s = seg_of(kt_lo + it);
+            const DSeg& sg = p.seg[s];
+            if (s != cur_seg) {      // per-row offset tables of the segment (producer-private)
+                bar_sync_producers();
+                for (int r = ptid; r < BM + BN; r += NPROD) {
+                    if (r < BM) {
+                        const unsigned m = m0 + r;
+                        rowA[r] = (m < p.M) ? didx_off(sg.am, m) + (long long)batch * sg.a_batch : 0;
+                    } else {
+                        const unsigned n = n0 + (r - BM);
+                        rowB[r - BM] = (n < p.N) ? didx_off(sg.bn, n) + (long long)batch * sg.b_batch : 0;
+                    }
+                }
+                bar_sync_producers();
+                cur_seg = s;
+            }
+            const int st = it % S;
+            if (it >= S) mbar_wait(empty_s + 8 * st, ((it - S) / S) & 1);
+            const unsigned k0 = (unsigned)(kt_lo + it - sg.kt_begin) * BK;
+            const unsigned ta = sA_s + st * (A_STAGE * 8), tb = sB_s + st * (B_STAGE * 8);
+            if (sg.a_mn_major) load_tile_mnmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);
+            else load_tile_kmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);
+            if (sg.b_mn_major) load_tile_mnmajor<VEC, BN, NPROD>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, ptid);
+            else load_tile_kmajor<VEC, BN, NPROD>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, ptid);
+            cp_async_mbar_arrive(full_s + 8 * st);
+        }
+        asm volatile("cp.async.wait_all;\n" ::: "memory");
+        return;
+    }
+
+    // ================================ consumers ================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;\n");
+    const int wm = warp >> 2, wn = warp & 3;
+
+    double acc[MI][4][2];
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    const int frow = lane >> 2, fk = lane & 3;
+    struct FragPtr {
+        const double* ap;
+        const double* bp;
+        int a_rs, a_ks, b_rs, b_ks;
+    };
+    auto frag_ptr = [&](int it_) {
+        const DSeg& sg = p.seg[seg_of(kt_lo + it_)];
+        const int st = it_ % S;
+        FragPtr f;
+        f.a_rs = sg.a_mn_major ? 1 : PK;
+        f.a_ks = sg.a_mn_major ? PMA : 1;
+        f.b_rs = sg.b_mn_major ? 1 : PK;
+        f.b_ks = sg.b_mn_major ? PMB : 1;
+        f.ap = sA + st * A_STAGE + (wm * (8 * MI) + frow) * f.a_rs + fk * f.a_ks;
+        f.bp = sB + st * B_STAGE + (wn * 32 + frow) * f.b_rs + fk * f.b_ks;
+        return f;
+    };
+
+    double a[MI], b[4], bnx[4];
+    mbar_wait(full_s, 0);
+    FragPtr fp = frag_ptr(0);
+#pragma unroll
+    for (int i = 0; i < MI; ++i) a[i] = fp.ap[i * 8 * fp.a_rs];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) b[j] = fp.bp[j * 8 * fp.b_rs];
+
+    int seg_acc = -1;
+    double scale_acc = 1.0;
+#pragma unroll 1
+    for (int it = 0; it < nkt; ++it) {
+        const int st = it % S;
+        {
+            const int sgi = seg_of(kt_lo + it);
+            if (sgi != seg_acc) {
+                const double sc = p.seg[sgi].scale;
+                if (seg_acc >= 0 && sc != scale_acc) {
+                    const double r = scale_acc / sc;
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { acc[i][j][0] *= r; acc[i][j][1] *= r; }
+                }
+                seg_acc = sgi;
+                scale_acc = sc;
+            }
+        }
+        FragPtr fn = fp;
+#pragma unroll
+        for (int ks = 0; ks < BK / 4; ++ks) {
+            const int nks = (ks + 1) % (BK / 4);
+            bool more = true;
+            if (ks == BK / 4 - 1) {
+                more = it + 1 < nkt;
+                if (more) {
+                    mbar_wait(full_s + 8 * ((it + 1) % S), ((it + 1) / S) & 1);
+                    fn = frag_ptr(it + 1);
+                }
+            }
+            if (more) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bnx[j] = fn.bp[j * 8 * fn.b_rs + nks * 4 * fn.b_ks];
+            }
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                if (more) a[i] = fn.ap[i * 8 * fn.a_rs + nks * 4 * fn.a_ks];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bnx[j];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_s + 8 * st);
+        fp = fn;
+    }
+
+    // ---- epilogue ----------------------------------------------------------------------
+    const unsigned colbase = n0 + wn * 32 + 2 * fk;
+    if (p.splits > 1) {
+        double* ws = p.ws + (size_t)blockIdx.z * p.M * p.N;
+#pragma unroll
+        for (int i = 0; i < MI; ++i) {
+            const unsigned row = m0 + wm * (8 * MI) + i * 8 + frow;
+            if (row >= p.M) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const unsigned col = colbase + j * 8 + e;
+                    if (col < p.N) ws[(size_t)row * p.N + col] = scale_acc * acc[i][j][e];
+                }
+        }
+        return;
+    }
+    const double alpha = p.alpha * scale_acc;
+    long long roff[MI], droff[MI];
+#pragma unroll
+    for (int i = 0; i < MI; ++i) {
+        const unsigned row = m0 + wm * (8 * MI) + i * 8 + frow;
+        roff[i] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
+        droff[i] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
+    }
+    // Two-phase per column group: all loads of C / D for the group are issued before the first
+    // store, so their latencies overlap (a store to C may alias the next load of C as far as the
+    // compiler knows; interleaving them serialises ~8*MI round trips to L2/HBM per thread).
+    const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        long long co[2], dco[2];
+        bool cok[2];
+        double add[2][MI];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const unsigned col = colbase + j * 8 + e;
+            cok[e] = col < p.N;
+            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
+            dco[e] = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                double v = 0.0;
+                if (cok[e] && roff[i] >= 0) {
+                    if (use_beta) v = p.beta * p.C[roff[i] + co[e]];
+                    if (use_d) v += p.gamma * p.D[droff[i] + dco[e]];
+                }
+                add[e][i] = v;
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+                if (cok[e] && roff[i] >= 0) p.C[roff[i] + co[e]] = alpha * acc[i][j][e] + add[e][i];
+    }
+}
+
+
 // fixed-order reduction of the split-K partial tiles + epilogue
 __global__ void splitk_reduce_kernel(const __grid_constant__ DParams p, long long total) {
     const long long MN = (long long)p.M * p.N;
@@ -494,6 +735,19 @@ int launch_tile_kernel(pccb_ctx* ctx, const DParams& p, long long batch) {
         attr_set = true;
     }
     dim3 grid((unsigned)((p.M + BM - 1) / BM), (unsigned)((p.N + BN - 1) / BN), (unsigned)(batch * p.splits));
+    // tuning hook: PCCB_WS=0 selects the non-specialised kernel (all 8 warps load and compute)
+    static const bool use_ws = [] { const char* e = getenv("PCCB_WS"); return e ? atoi(e) != 0 : true; }();
+    if (use_ws && MI > 2) {
+        static bool attr_ws = false;
+        if (!attr_ws) {
+            PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_ws_kernel<VEC, MI>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+            attr_ws = true;
+        }
+        contract_f64_ws_kernel<VEC, MI><<<grid, NTHREADS_WS, SMEM, ctx->stream>>>(p);
+        PCCB_CHECK_LAUNCH(ctx, "contract_f64_ws_kernel");
+        return PCCB_OK;
+    }
     contract_f64_kernel<VEC, MI><<<grid, NTHREADS, SMEM, ctx->stream>>>(p);
     PCCB_CHECK_LAUNCH(ctx, "contract_f64_kernel");
     return PCCB_OK;
