@@ -54,7 +54,7 @@ struct DSeg {
 
 struct DParams {
     unsigned M, N;
-    int nseg, total_kt, splits, pad_;
+    int nseg, total_kt, splits, nz;    // nz = batch * splits (grid.z of the non-persistent kernel)
     DSeg seg[PCCB_MAX_SEGMENTS];
     double* C;
     DIdx cm, cn;
@@ -435,11 +435,11 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     unsigned long long* bars = reinterpret_cast<unsigned long long*>(rowB + BN);   // full[S], empty[S]
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const unsigned m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
-    const int batch = blockIdx.z / p.splits, split = blockIdx.z % p.splits;
-    const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
-    const int kt_hi = (int)(((long long)p.total_kt * (split + 1)) / p.splits);
-    const int nkt = kt_hi - kt_lo;
+    // persistent CTA: walks the output tiles (m fastest, so that the CTAs of one wave share B
+    // tiles in L2); the shared-memory ring and its barrier phases run on across tiles, which lets
+    // the producers stage the next tile while the consumers are still in this tile's epilogue.
+    const unsigned gm = (p.M + BM - 1) / BM, gn = (p.N + BN - 1) / BN;
+    const long long ntiles = (long long)gm * gn * p.nz;
 
     const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
     const unsigned sB_s = (unsigned)__cvta_generic_to_shared(sB);
@@ -467,10 +467,20 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
         // ================================ producers ================================
         asm volatile("setmaxnreg.dec.sync.aligned.u32 56;\n");
         const int ptid = tid - NCONS;
+        unsigned g = 0;     // k-tiles staged so far by this CTA (ring position)
+#pragma unroll 1
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const unsigned mx = (unsigned)(tile % gm);
+        const long long rest = tile / gm;
+        const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+        const int z = (int)(rest / gn);
+        const int batch = z / p.splits, split = z % p.splits;
+        const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
+        const int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
         const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
         int cur_seg = -1;
 #pragma unroll 1
-        for (int it = 0; it < nkt; ++it) {
+        for (int it = 0; it < nkt; ++it, ++g) {
             const int s = seg_of(kt_lo + it);
             const DSeg& sg = p.seg[s];
             if (s != cur_seg) {      // per-row offset tables of the segment (producer-private)
@@ -487,8 +497,8 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
                 bar_sync_producers();
                 cur_seg = s;
             }
-            const int st = it % S;
-            if (it >= S) mbar_wait(empty_s + 8 * st, ((it - S) / S) & 1);
+            const int st = g % S;
+            if (g >= S) mbar_wait(empty_s + 8 * st, ((g - S) / S) & 1);
             const unsigned k0 = (unsigned)(kt_lo + it - sg.kt_begin) * BK;
             const unsigned ta = sA_s + st * (A_STAGE * 8), tb = sB_s + st * (B_STAGE * 8);
             if (sg.a_mn_major) load_tile_mnmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);
@@ -497,6 +507,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
             else load_tile_kmajor<VEC, BN, NPROD>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, ptid);
             cp_async_mbar_arrive(full_s + 8 * st);
         }
+        }
         asm volatile("cp.async.wait_all;\n" ::: "memory");
         return;
     }
@@ -504,6 +515,17 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     // ================================ consumers ================================
     asm volatile("setmaxnreg.inc.sync.aligned.u32 216;\n");
     const int wm = warp >> 2, wn = warp & 3;
+    const int frow = lane >> 2, fk = lane & 3;
+    unsigned g0 = 0;    // ring position of this tile's first k-tile
+#pragma unroll 1
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const unsigned mx = (unsigned)(tile % gm);
+    const long long rest = tile / gm;
+    const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+    const int z = (int)(rest / gn);
+    const int batch = z / p.splits, split = z % p.splits;
+    const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
+    const int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
 
     double acc[MI][4][2];
 #pragma unroll
@@ -511,7 +533,6 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
 #pragma unroll
         for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
 
-    const int frow = lane >> 2, fk = lane & 3;
     struct FragPtr {
         const double* ap;
         const double* bp;
@@ -519,7 +540,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     };
     auto frag_ptr = [&](int it_) {
         const DSeg& sg = p.seg[seg_of(kt_lo + it_)];
-        const int st = it_ % S;
+        const int st = (g0 + it_) % S;
         FragPtr f;
         f.a_rs = sg.a_mn_major ? 1 : PK;
         f.a_ks = sg.a_mn_major ? PMA : 1;
@@ -531,7 +552,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     };
 
     double a[MI], b[4], bnx[4];
-    mbar_wait(full_s, 0);
+    mbar_wait(full_s + 8 * (g0 % S), (g0 / S) & 1);
     FragPtr fp = frag_ptr(0);
 #pragma unroll
     for (int i = 0; i < MI; ++i) a[i] = fp.ap[i * 8 * fp.a_rs];
@@ -542,7 +563,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     double scale_acc = 1.0;
 #pragma unroll 1
     for (int it = 0; it < nkt; ++it) {
-        const int st = it % S;
+        const int st = (g0 + it) % S;
         {
             const int sgi = seg_of(kt_lo + it);
             if (sgi != seg_acc) {
@@ -566,7 +587,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
             if (ks == BK / 4 - 1) {
                 more = it + 1 < nkt;
                 if (more) {
-                    mbar_wait(full_s + 8 * ((it + 1) % S), ((it + 1) / S) & 1);
+                    mbar_wait(full_s + 8 * ((g0 + it + 1) % S), ((g0 + it + 1) / S) & 1);
                     fn = frag_ptr(it + 1);
                 }
             }
@@ -587,11 +608,12 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
         if (lane == 0) mbar_arrive(empty_s + 8 * st);
         fp = fn;
     }
+    g0 += nkt;
 
     // ---- epilogue ----------------------------------------------------------------------
     const unsigned colbase = n0 + wn * 32 + 2 * fk;
     if (p.splits > 1) {
-        double* ws = p.ws + (size_t)blockIdx.z * p.M * p.N;
+        double* ws = p.ws + (size_t)z * p.M * p.N;
 #pragma unroll
         for (int i = 0; i < MI; ++i) {
             const unsigned row = m0 + wm * (8 * MI) + i * 8 + frow;
@@ -604,7 +626,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
                     if (col < p.N) ws[(size_t)row * p.N + col] = scale_acc * acc[i][j][e];
                 }
         }
-        return;
+        continue;
     }
     const double alpha = p.alpha * scale_acc;
     long long roff[MI], droff[MI];
@@ -645,8 +667,8 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
             for (int i = 0; i < MI; ++i)
                 if (cok[e] && roff[i] >= 0) p.C[roff[i] + co[e]] = alpha * acc[i][j][e] + add[e][i];
     }
+    }   // tile loop
 }
-
 
 // fixed-order reduction of the split-K partial tiles + epilogue
 __global__ void splitk_reduce_kernel(const __grid_constant__ DParams p, long long total) {
@@ -744,7 +766,11 @@ int launch_tile_kernel(pccb_ctx* ctx, const DParams& p, long long batch) {
                                                 cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
             attr_ws = true;
         }
-        contract_f64_ws_kernel<VEC, MI><<<grid, NTHREADS_WS, SMEM, ctx->stream>>>(p);
+        DParams q = p;
+        q.nz = (int)(batch * p.splits);
+        const long long ntiles = (long long)grid.x * grid.y * grid.z;
+        const unsigned nctas = (unsigned)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+        contract_f64_ws_kernel<VEC, MI><<<nctas, NTHREADS_WS, SMEM, ctx->stream>>>(q);
         PCCB_CHECK_LAUNCH(ctx, "contract_f64_ws_kernel");
         return PCCB_OK;
     }
