@@ -640,32 +640,41 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     // store, so their latencies overlap (a store to C may alias the next load of C as far as the
     // compiler knows; interleaving them serialises ~8*MI round trips to L2/HBM per thread).
     const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
+    // column groups of JG*8 columns: every load of C / D of a group is issued before its first store
+    // (the consumers own 216 registers, so up to MI = 4 the whole tile is one group, MI = 5, 6 two groups: fewer L2/HBM round
+    // trips per tile)
+    constexpr int JG = (MI <= 4) ? 4 : ((MI <= 5) ? 2 : 1);
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        long long co[2], dco[2];
-        bool cok[2];
-        double add[2][MI];
+    for (int j0 = 0; j0 < 4; j0 += JG) {
+        long long co[JG][2];
+        bool cok[JG][2];
+        double add[JG][2][MI];
 #pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const unsigned col = colbase + j * 8 + e;
-            cok[e] = col < p.N;
-            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
-            dco[e] = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
+        for (int jj = 0; jj < JG; ++jj)
 #pragma unroll
-            for (int i = 0; i < MI; ++i) {
-                double v = 0.0;
-                if (cok[e] && roff[i] >= 0) {
-                    if (use_beta) v = p.beta * p.C[roff[i] + co[e]];
-                    if (use_d) v += p.gamma * p.D[droff[i] + dco[e]];
+            for (int e = 0; e < 2; ++e) {
+                const unsigned col = colbase + (j0 + jj) * 8 + e;
+                cok[jj][e] = col < p.N;
+                co[jj][e] = cok[jj][e] ? didx_off(p.cn, col) : 0;
+                const long long dco = (cok[jj][e] && use_d) ? didx_off(p.dn, col) : 0;
+#pragma unroll
+                for (int i = 0; i < MI; ++i) {
+                    double v = 0.0;
+                    if (cok[jj][e] && roff[i] >= 0) {
+                        if (use_beta) v = p.beta * p.C[roff[i] + co[jj][e]];
+                        if (use_d) v += p.gamma * p.D[droff[i] + dco];
+                    }
+                    add[jj][e][i] = v;
                 }
-                add[e][i] = v;
             }
-        }
 #pragma unroll
-        for (int e = 0; e < 2; ++e)
+        for (int jj = 0; jj < JG; ++jj)
 #pragma unroll
-            for (int i = 0; i < MI; ++i)
-                if (cok[e] && roff[i] >= 0) p.C[roff[i] + co[e]] = alpha * acc[i][j][e] + add[e][i];
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int i = 0; i < MI; ++i)
+                    if (cok[jj][e] && roff[i] >= 0)
+                        p.C[roff[i] + co[jj][e]] = alpha * acc[i][j0 + jj][e] + add[jj][e][i];
     }
     }   // tile loop
 }
