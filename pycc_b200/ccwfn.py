@@ -31,7 +31,7 @@ class ccwfn(object):
     """
 
     valid_cc_models = ['CCD', 'CC2', 'CCSD', 'CCSD(T)', 'CC3']
-    engine_models = ['CCSD', 'CCSD(T)']
+    engine_models = ['CCD', 'CC2', 'CCSD', 'CCSD(T)']
 
     def __init__(self, scf_wfn, **kwargs):
         try:
@@ -152,7 +152,7 @@ class ccwfn(object):
                 raise Exception("ERI must be the full (n,n,n,n) Dirac array or a dict of blocks %s" % (BLOCKS,))
             self.H = Hamiltonian.from_full(F, ERI, no, backend.device, dtype, vslice, keep_ovvv)
         self.engine = CCSDEngine(backend, self.H.F, self.H.blocks, no, nv, dtype, comm=self.comm,
-                                 keep_full_ovvv=keep_ovvv)
+                                 keep_full_ovvv=keep_ovvv, model=model)
         self.H.F = self.engine.F
         self._triples = None
 
@@ -258,35 +258,48 @@ class ccwfn(object):
     # Builders keep the reference's signatures (pycc/ccwfn.py:413-537).  The integral arguments
     # (ERI, L) are accepted for call-site compatibility; the engine uses the blocks of self.H.
     def _builder(self, name, F, t1, t2):
+        """False when the model has no such intermediate (the reference's builders return None then:
+        CCD has no Fme / Zmbij, CC2 no Wmbej / Wmbje; pycc/ccwfn.py:453-454, 494-496, 516-518, 532-533)."""
+        if name not in self.engine.plans or name not in self.engine.builder_order() or \
+                (self.model == 'CCD' and name in ('Fme', 'Zmbij')):
+            return False
         self._load(F, t1, t2)
         self.engine.run_builder(name)
+        return True
 
     def build_Fae(self, o, v, F, L, t1, t2):
-        self._builder("Fae", F, t1, t2)
+        if not self._builder("Fae", F, t1, t2):
+            return None
         return self.engine.Fae.clone()
 
     def build_Fmi(self, o, v, F, L, t1, t2):
-        self._builder("Fmi", F, t1, t2)
+        if not self._builder("Fmi", F, t1, t2):
+            return None
         return self.engine.Fmi.clone()
 
     def build_Fme(self, o, v, F, L, t1):
-        self._builder("Fme", F, t1, self.engine.t2)
+        if not self._builder("Fme", F, t1, self.engine.t2):
+            return None
         return self.engine.Fme.clone()
 
     def build_Wmnij(self, o, v, ERI, t1, t2):
-        self._builder("Wmnij", None, t1, t2)
+        if not self._builder("Wmnij", None, t1, t2):
+            return None
         return self.engine.Wmnij.clone()
 
     def build_Wmbej(self, o, v, ERI, L, t1, t2):
-        self._builder("Wmbej", None, t1, t2)
+        if not self._builder("Wmbej", None, t1, t2):
+            return None
         return self.engine.Wmbej_view().contiguous()
 
     def build_Wmbje(self, o, v, ERI, t1, t2):
-        self._builder("Wmbje", None, t1, t2)
+        if not self._builder("Wmbje", None, t1, t2):
+            return None
         return self.engine.Wmbje_view().contiguous()
 
     def build_Zmbij(self, o, v, ERI, t1, t2):
-        self._builder("Zmbij", None, t1, t2)
+        if not self._builder("Zmbij", None, t1, t2):
+            return None
         return self.engine.Zmbij_view().contiguous()
 
     def r_T1(self, o, v, F, ERI, L, t1, t2, Fae, Fme, Fmi):

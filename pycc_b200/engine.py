@@ -32,12 +32,16 @@ from .parallel import Comm, virtual_slice
 
 
 class CCSDEngine(object):
-    def __init__(self, backend, F, blocks, no, nv, dtype=torch.float64, comm=None, keep_full_ovvv=True):
+    def __init__(self, backend, F, blocks, no, nv, dtype=torch.float64, comm=None, keep_full_ovvv=True,
+                 model='CCSD'):
         """``comm``: pycc_b200.parallel.Comm (None = one GPU).  With more than one rank this rank
         works on the virtual slice [vlo, vhi); ``blocks['vvvv']`` may then be either the full block
         or just the rank's rows ``<ab|ef>, a in slice`` (shape (vhi-vlo, v, v, v)), and likewise
         ``blocks['ovvv']`` (full, or (o, vhi-vlo, v, v)); a full ovvv is needed for (T)."""
         self.be = be = backend
+        self.model = 'CCSD' if model == 'CCSD(T)' else model
+        if self.model not in ('CCD', 'CC2', 'CCSD'):
+            raise ValueError("engine models: CCD, CC2, CCSD, CCSD(T) (got %r)" % (model,))
         self.no, self.nv, self.dtype = int(no), int(nv), dtype
         self.dcode = _lib.F64 if dtype == torch.float64 else _lib.F32
         self.comm = comm if comm is not None else Comm(None)
@@ -85,6 +89,8 @@ class CCSDEngine(object):
         self.Zr = E(o, o, o, vl)                                 # [m,i,j,b]
         self.Y1, self.Y2 = E(o, o, o, vl), E(o, o, vl, o)        # [i,m,j,b], [i,m,a,j]
         self.r1, self.r2 = E(o, v), E(o, o, v, v)
+        if self.model == 'CC2':      # t1 t1 products and the two factorised intermediates of the CC2 r_T2
+            self.T11, self.Yw, self.Xv = E(o, o, v, v), E(o, o, o, vl), E(vl, v, o, v)
         self.ladder_events = None    # bench.py: list that receives (start, end) CUDA events per ladder launch
         self._build_plans()
 
@@ -99,6 +105,8 @@ class CCSDEngine(object):
                  t1=self.t1, t2=self.t2, tau=self.tau, tauh=self.tauh, tauW=self.tauW, t2s=self.t2s,
                  Fae=self.Fae, Fmi=self.Fmi, Fme=self.Fme, Fae2=self.Fae2, Fmi2=self.Fmi2, Wmnij=self.Wmnij,
                  Wr1=self.Wr1, Wr2=self.Wr2, Zr=self.Zr, Y1=self.Y1, Y2=self.Y2, r1=self.r1, r2=self.r2)
+        if self.model == 'CC2':
+            d.update(T11=self.T11, Yw=self.Yw, Xv=self.Xv)
         out = {}
         for nm in names:
             if nm == "vvvv_s0":
@@ -165,10 +173,55 @@ class CCSDEngine(object):
                  "r2_s2[ijAb] -= t1_s1[mA]*ooov[ijmb]"],
     }
 
+    # CC2 branch of the same builders (pycc/ccwfn.py:478-479, 495-496, 517-518, 534-535, 575-592):
+    # Fae / Fmi / Fme / r_T1 as in CCSD; Wmnij and Zmbij with t1 t1 in place of tau; no Wmbej / Wmbje;
+    # r_T2 with bare Fock matrices and the doubles-into-doubles terms dropped.  T11[ijef] = t1[ie] t1[jf].
+    STATEMENTS_CC2 = {
+        "Wmnij": ["Wmnij[mnij] = oooo[mnij] + oovv[mnef]*T11[ijef]",
+                  "Wmnij[mnij] += ooov[mnie]*t1[je]",
+                  "Wmnij[mnij] += ooov[nmje]*t1[ie]"],
+        "Zmbij": ["Zr[mijB] = ovvv_s1[mBef]*T11[ijef]"],
+        # (:575-592); the two terms in t2 Fvv-like / Foo-like matrices are merged:
+        #   Fae2[be] = Fvv[be] - t1[mb] Fov[me],  Fmi2[mj] = Foo[mj] + Fov[me] t1[je]
+        "r_T2": ["Fae2[Be] = Fvv_s0[Be] - t1_s1[mB]*Fov[me]",
+                 "Fmi2[mj] = Foo[mj] + Fov[me]*t1[je]",
+                 "r2_s2[ijAb] += 0.5*oovv_s2[ijAb]",
+                 "r2_s3[ijaB] += t2[ijae]*Fae2[Be]",
+                 "r2_s2[ijAb] -= Fmi2[mj]*t2_s2[imAb]",
+                 "Yw[mijB] = Wmnij[mnij]*t1_s1[nB]",
+                 "r2_s3[ijaB] += 0.5*t1[ma]*Yw[mijB]",
+                 "Xv[Abif] = t1[ie]*vvvv_s0[Abef]",
+                 "r2_s2[ijAb] += 0.5*Xv[Abif]*t1[jf]",
+                 "r2_s3[ijaB] -= t1[ma]*Zr[mijB]",
+                 "Y1[imjB] = t1[ie]*oovv_s3[mjeB]",
+                 "r2_s3[ijaB] -= t1[ma]*Y1[imjB]",
+                 "Y2[imAj] = t1[ie]*ovov_s1[mAje]",
+                 "r2_s2[ijAb] -= Y2[imAj]*t1[mb]",
+                 "r2_s2[ijAb] += t1[ie]*ovvv_s1[jAbe]",
+                 "r2_s2[ijAb] -= t1_s1[mA]*ooov[ijmb]"],
+    }
+
+    def builder_order(self):
+        """Builders run by residuals(), in the reference's order (pycc/ccwfn.py:357-366).
+        CCD (:415-420, 434-439, 466-471, 488-496, 511-518, 563-573) is the CCSD algebra with
+        t1 = 0 and r1 = 0; its t1-carrying launches then contribute exact zeros."""
+        if self.model == 'CC2':
+            return ("Fae", "Fmi", "Fme", "Wmnij", "Zmbij", "r_T1", "r_T2")
+        if self.model == 'CCD':
+            return ("Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij", "r_T2")
+        return ("Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij", "r_T1", "r_T2")
+
+    def _statements(self):
+        st = dict(self.STATEMENTS)
+        if self.model == 'CC2':
+            st.update(self.STATEMENTS_CC2)
+            del st["Wmbej"], st["Wmbje"]
+        return st
+
     def _build_plans(self):
         import re
         self.plans = {}
-        for name, stmts in self.STATEMENTS.items():
+        for name, stmts in self._statements().items():
             launches = []
             for s in stmts:
                 T = self._tensors(set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s)))
@@ -208,6 +261,8 @@ class CCSDEngine(object):
         be.pair_combine(self.tauh, self.t2, 1.0, 0.0, self.t1, self.t1, 0.5, o, v)
         be.pair_combine(self.tauW, self.t2, 0.5, 0.0, self.t1, self.t1, 1.0, o, v)
         be.pair_combine(self.t2s, self.t2, 2.0, -1.0, None, None, 0.0, o, v)
+        if self.model == 'CC2':
+            be.pair_combine(self.T11, self.t2, 0.0, 0.0, self.t1, self.t1, 1.0, o, v)
 
     def set_amplitudes(self, t1, t2):
         self.t1.copy_(torch.as_tensor(t1).to(self.t1.device, self.dtype))
@@ -222,7 +277,10 @@ class CCSDEngine(object):
         """r1, r2 for the amplitudes held in self.t1 / self.t2 (pycc/ccwfn.py:357-366)."""
         self.be.bind_stream()
         self.prepare()
-        for name in ("Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij", "r_T1", "r_T2"):
+        if self.model == 'CCD':
+            self.t1.zero_()          # CCD carries no singles (ccwfn.py:543-546)
+            self.r1.zero_()
+        for name in self.builder_order():
             self._run(name)
         if symmetrize:
             self.be.pair_symmetrize(self.r2, self.no, self.nv)       # ccwfn.py:621
@@ -233,7 +291,7 @@ class CCSDEngine(object):
         self.prepare()
         deps = {"Fae": [], "Fmi": [], "Fme": [], "Wmnij": [], "Wmbej": [], "Wmbje": [], "Zmbij": [],
                 "r_T1": ["Fae", "Fmi", "Fme"],
-                "r_T2": ["Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij"]}
+                "r_T2": [b for b in self.builder_order() if b not in ("r_T1", "r_T2")]}
         for d in deps[name]:
             self._run(d)
         self._run(name)

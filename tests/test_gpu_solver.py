@@ -177,3 +177,27 @@ def test_mixed_precision_seeded():
     assert np.abs(r2.cpu().numpy() - r2o).max() < 2e-6
     assert np.abs(n2.cpu().numpy() - r2o).max() < 2e-6
     assert np.abs(r1.cpu().numpy() - r1o).max() < 2e-6
+
+
+@pytest.mark.parametrize("model", ["CCD", "CC2"])
+@pytest.mark.parametrize("name", ["o4v8", "o5v19_offdiag", "o6v13"])
+def test_ccd_cc2_models(name, model):
+    """CCD / CC2 branches of the builders on the GPU against the reference's own vectors."""
+    import os
+    import pycc_b200
+    from tests.conftest import GOLDEN_DIR, Golden
+    g = Golden(name)
+    z = np.load(os.path.join(GOLDEN_DIR, "models", name + ".npz"))
+    tag = model.lower()
+    w = _wfn(g.F, g.blocks, g.no, model)
+    t1 = np.zeros_like(g["gen_t1"]) if model == "CCD" else g["gen_t1"]
+    r1, r2 = w.residuals(g.F, t1, g["gen_t2"])
+    assert np.abs(r1.cpu().numpy() - z[tag + "_r1"]).max() < 1e-12
+    assert np.abs(r2.cpu().numpy() - z[tag + "_r2"]).max() < 1e-12
+    w = _wfn(g.F, g.blocks, g.no, model)
+    with contextlib.redirect_stdout(io.StringIO()):
+        e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+    assert len(w.iteration_log) == int(z[tag + "_solve_niter"])
+    assert abs(e - float(z[tag + "_solve_ecc"])) < E_TOL
+    assert np.abs(w.t1.cpu().numpy() - z[tag + "_solve_t1"]).max() < T_TOL
+    assert np.abs(w.t2.cpu().numpy() - z[tag + "_solve_t2"]).max() < T_TOL
