@@ -102,6 +102,22 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
     } while (!ok);
 }
 
+// producer-side wait: the hardware may suspend the warp for up to ~1 us per try instead of spinning
+// on the issue port the consumer warps need
+__device__ __forceinline__ void mbar_wait_relaxed(unsigned bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared.b64 p, [%1], %2, %3;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(1000u)
+            : "memory");
+    } while (!ok);
+}
 template <int VEC>
 __device__ __forceinline__ void cp_async_vec(unsigned dst, const void* src, int bytes) {
     if (VEC == 2) cp_async16(dst, src, bytes);
@@ -498,7 +514,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
                 cur_seg = s;
             }
             const int st = g % S;
-            if (g >= S) mbar_wait(empty_s + 8 * st, ((g - S) / S) & 1);
+            if (g >= S) mbar_wait_relaxed(empty_s + 8 * st, ((g - S) / S) & 1);
             const unsigned k0 = (unsigned)(kt_lo + it - sg.kt_begin) * BK;
             const unsigned ta = sA_s + st * (A_STAGE * 8), tb = sB_s + st * (B_STAGE * 8);
             if (sg.a_mn_major) load_tile_mnmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);

@@ -39,7 +39,7 @@ struct FSeg {
 
 struct FParams {
     unsigned M, N;
-    int nseg, total_kt, splits, pad_;
+    int nseg, total_kt, splits, nz;
     FSeg seg[PCCB_MAX_SEGMENTS];
     float* C;
     DIdx cm, cn;
@@ -83,15 +83,35 @@ __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
             : "memory");
     } while (!ok);
 }
+// producer-side wait: the hardware may suspend the warp for up to ~1 us per try instead of spinning
+// on the issue port the consumer warps need
+__device__ __forceinline__ void mbar_wait_relaxed(unsigned bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile(
+            "{\n"
+            ".reg .pred p;\n"
+            "mbarrier.try_wait.parity.shared.b64 p, [%1], %2, %3;\n"
+            "selp.u32 %0, 1, 0, p;\n"
+            "}\n"
+            : "=r"(ok)
+            : "r"(bar), "r"(parity), "r"(1000u)
+            : "memory");
+    } while (!ok);
+}
 __device__ __forceinline__ unsigned to_tf32(float x) {
     unsigned r;
     asm("cvt.rna.tf32.f32 %0, %1;\n" : "=r"(r) : "f"(x));
     return r;
 }
-// x = hi + lo with hi, lo representable in TF32 (lo carries the next 11 mantissa bits)
+// x = hi + lo exactly, hi = x with its 13 low mantissa bits cleared (what the tensor core reads when it
+// is handed an FP32 register as a TF32 operand), lo = x - hi.  lo is passed to the MMA as it is: the
+// hardware again reads its top 10 mantissa bits, so the pair carries ~21 bits of x for one LOP3 and
+// one FADD per element (cvt.rna.tf32 is a multi-instruction sequence on sm_100a and made the consumer
+// warps issue-bound: profiles/r01_ncu_ladder_f32_*).
 __device__ __forceinline__ void split_tf32(float x, unsigned& hi, unsigned& lo) {
-    hi = to_tf32(x);
-    lo = to_tf32(x - __uint_as_float(hi));
+    hi = __float_as_uint(x) & 0xffffe000u;
+    lo = __float_as_uint(x - __uint_as_float(hi));
 }
 __device__ __forceinline__ void mma_tf32(float (&c)[4], const unsigned (&a)[4], const unsigned (&b)[2]) {
     asm("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};\n"
@@ -100,11 +120,11 @@ __device__ __forceinline__ void mma_tf32(float (&c)[4], const unsigned (&a)[4], 
 }
 
 // K-major tile[row][k] (pitch PK): a thread owns one k-chunk column and walks the rows
-template <int VEC, int ROWS>
+template <int VEC, int ROWS, int NT = NTHREADS>
 __device__ __forceinline__ void load_tile_kmajor(unsigned tile_s, const float* base, const long long* rows, int rlim,
                                                  const DIdx& kidx, unsigned k0, unsigned K, int tid) {
     constexpr int CH = BK / VEC;
-    constexpr int RPP = NTHREADS / CH;
+    constexpr int RPP = NT / CH;
     constexpr int PASSES = (ROWS + RPP - 1) / RPP;
     const int kc = tid % CH, r0 = tid / CH;
     const unsigned k = k0 + kc * VEC;
@@ -128,12 +148,12 @@ __device__ __forceinline__ void load_tile_kmajor(unsigned tile_s, const float* b
 }
 
 // MN-major tile[k][row] (pitch ROWS+8): a thread owns one row chunk and walks the k rows
-template <int VEC, int ROWS>
+template <int VEC, int ROWS, int NT = NTHREADS>
 __device__ __forceinline__ void load_tile_mnmajor(unsigned tile_s, const float* base, const long long* rows, int rlim,
                                                   const DIdx& kidx, unsigned k0, unsigned K, int tid) {
     constexpr int PM = ROWS + 8;
     constexpr int CH = ROWS / VEC;
-    constexpr int KPP = (NTHREADS / CH) < BK ? (NTHREADS / CH) : BK;
+    constexpr int KPP = (NT / CH) < BK ? (NT / CH) : BK;
     constexpr int PASSES = (BK + KPP - 1) / KPP;
     const int mc = tid % CH, kr0 = tid / CH;
     const int row = mc * VEC;
@@ -375,6 +395,271 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f32_kernel(const __grid_
     }
 }
 
+// ---- warp-specialised, persistent variant (see contract.cu): 4 producer warps stage the tiles,
+// 8 consumer warps split the FP32 fragments into TF32 hi/lo pairs and issue the three MMAs ----------
+constexpr int NCONS = 256, NPROD = 128, NTHREADS_WS = NCONS + NPROD;
+
+__device__ __forceinline__ void bar_sync_producers() {
+    asm volatile("bar.sync 1, %0;\n" ::"n"(NPROD) : "memory");
+}
+
+template <int VEC, int MJ>
+__global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f32_ws_kernel(const __grid_constant__ FParams p) {
+    constexpr int BM = 32 * MJ;
+    constexpr int PMA = BM + 8, PMB = BN + 8;
+    constexpr int A_STAGE = (BM * PK > BK * PMA) ? BM * PK : BK * PMA;   // floats
+    constexpr int B_STAGE = (BN * PK > BK * PMB) ? BN * PK : BK * PMB;
+    constexpr int S = STAGES;
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    float* sA = reinterpret_cast<float*>(smem_raw);
+    float* sB = sA + S * A_STAGE;
+    long long* rowA = reinterpret_cast<long long*>(sB + S * B_STAGE);
+    long long* rowB = rowA + BM;
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(rowB + BN);
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned gm = (p.M + BM - 1) / BM, gn = (p.N + BN - 1) / BN;
+    const long long ntiles = (long long)gm * gn * p.nz;
+
+    const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
+    const unsigned sB_s = (unsigned)__cvta_generic_to_shared(sB);
+    const unsigned full_s = (unsigned)__cvta_generic_to_shared(bars);
+    const unsigned empty_s = full_s + 8 * S;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            mbar_init(full_s + 8 * s, NPROD);
+            mbar_init(empty_s + 8 * s, NCONS / 32);
+        }
+    }
+    __syncthreads();
+
+    auto seg_of = [&](int kt) {
+        int s = 0;
+#pragma unroll
+        for (int q = 1; q < PCCB_MAX_SEGMENTS; ++q)
+            if (q < p.nseg && kt >= p.seg[q].kt_begin) s = q;
+        return s;
+    };
+
+    if (warp >= NCONS / 32) {
+        // ================================ producers ================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;\n");
+        const int ptid = tid - NCONS;
+        unsigned g = 0;
+#pragma unroll 1
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+            const unsigned mx = (unsigned)(tile % gm);
+            const long long rest = tile / gm;
+            const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+            const int z = (int)(rest / gn);
+            const int batch = z / p.splits, split = z % p.splits;
+            const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
+            const int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
+            const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
+            int cur_seg = -1;
+#pragma unroll 1
+            for (int it = 0; it < nkt; ++it, ++g) {
+                const int s = seg_of(kt_lo + it);
+                const FSeg& sg = p.seg[s];
+                if (s != cur_seg) {
+                    bar_sync_producers();
+                    for (int r = ptid; r < BM + BN; r += NPROD) {
+                        if (r < BM) {
+                            const unsigned m = m0 + r;
+                            rowA[r] = (m < p.M) ? didx_off(sg.am, m) + (long long)batch * sg.a_batch : 0;
+                        } else {
+                            const unsigned n = n0 + (r - BM);
+                            rowB[r - BM] = (n < p.N) ? didx_off(sg.bn, n) + (long long)batch * sg.b_batch : 0;
+                        }
+                    }
+                    bar_sync_producers();
+                    cur_seg = s;
+                }
+                const int st = g % S;
+                if (g >= S) mbar_wait_relaxed(empty_s + 8 * st, ((g - S) / S) & 1);
+                const unsigned k0 = (unsigned)(kt_lo + it - sg.kt_begin) * BK;
+                const unsigned ta = sA_s + st * (A_STAGE * 4), tb = sB_s + st * (B_STAGE * 4);
+                if (sg.a_mn_major) load_tile_mnmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);
+                else load_tile_kmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);
+                if (sg.b_mn_major) load_tile_mnmajor<VEC, BN, NPROD>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, ptid);
+                else load_tile_kmajor<VEC, BN, NPROD>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, ptid);
+                cp_async_mbar_arrive(full_s + 8 * st);
+            }
+        }
+        asm volatile("cp.async.wait_all;\n" ::: "memory");
+        return;
+    }
+
+    // ================================ consumers ================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 216;\n");
+    const int wm = warp >> 2, wn = warp & 3;
+    const int g = lane >> 2, t = lane & 3;
+    unsigned g0 = 0;
+#pragma unroll 1
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const unsigned mx = (unsigned)(tile % gm);
+    const long long rest = tile / gm;
+    const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+    const int z = (int)(rest / gn);
+    const int batch = z / p.splits, split = z % p.splits;
+    const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
+    const int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
+
+    float acc[MJ][4][4];
+#pragma unroll
+    for (int i = 0; i < MJ; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int e = 0; e < 4; ++e) acc[i][j][e] = 0.f;
+
+    int seg_acc = -1;
+    float scale_acc = 1.f;
+#pragma unroll 1
+    for (int it = 0; it < nkt; ++it) {
+        const int st = (g0 + it) % S;
+        const int sgi = seg_of(kt_lo + it);
+        if (sgi != seg_acc) {
+            const float sc = p.seg[sgi].scale;
+            if (seg_acc >= 0 && sc != scale_acc) {
+                const float r = scale_acc / sc;
+#pragma unroll
+                for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+#pragma unroll
+                        for (int e = 0; e < 4; ++e) acc[i][j][e] *= r;
+            }
+            seg_acc = sgi;
+            scale_acc = sc;
+        }
+        mbar_wait(full_s + 8 * st, ((g0 + it) / S) & 1);
+        const FSeg& sg = p.seg[sgi];
+        const int a_rs = sg.a_mn_major ? 1 : PK, a_ks = sg.a_mn_major ? PMA : 1;
+        const int b_rs = sg.b_mn_major ? 1 : PK, b_ks = sg.b_mn_major ? PMB : 1;
+        const float* ap = sA + st * A_STAGE + (wm * (16 * MJ) + g) * a_rs + t * a_ks;
+        const float* bp = sB + st * B_STAGE + (wn * 32 + g) * b_rs + t * b_ks;
+        // raw FP32 fragments of step ks+1 are fetched while the 12*MJ MMAs of step ks issue
+        float ra[MJ][4], rb[4][2];
+        auto fetch = [&](int ks) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float* q = bp + (j * 8) * b_rs + (ks * 8) * b_ks;
+                rb[j][0] = q[0];
+                rb[j][1] = q[4 * b_ks];
+            }
+#pragma unroll
+            for (int i = 0; i < MJ; ++i) {
+                const float* q = ap + (i * 16) * a_rs + (ks * 8) * a_ks;
+                ra[i][0] = q[0];
+                ra[i][1] = q[8 * a_rs];
+                ra[i][2] = q[4 * a_ks];
+                ra[i][3] = q[8 * a_rs + 4 * a_ks];
+            }
+        };
+        fetch(0);
+#pragma unroll
+        for (int ks = 0; ks < BK / 8; ++ks) {
+            unsigned bh[4][2], bl[4][2], ah[MJ][4], al[MJ][4];
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                split_tf32(rb[j][0], bh[j][0], bl[j][0]);
+                split_tf32(rb[j][1], bh[j][1], bl[j][1]);
+            }
+#pragma unroll
+            for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                for (int e = 0; e < 4; ++e) split_tf32(ra[i][e], ah[i][e], al[i][e]);
+            if (ks + 1 < BK / 8) fetch(ks + 1);
+            // the three products of one accumulator are dependent: sweep all 4*MJ accumulators per
+            // product so that consecutive MMAs are independent (small terms first)
+#pragma unroll
+            for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mma_tf32(acc[i][j], al[i], bh[j]);
+#pragma unroll
+            for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mma_tf32(acc[i][j], ah[i], bl[j]);
+#pragma unroll
+            for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                for (int j = 0; j < 4; ++j) mma_tf32(acc[i][j], ah[i], bh[j]);
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_s + 8 * st);
+    }
+    g0 += nkt;
+
+    // ---- epilogue (two-phase per column group, see contract.cu) -----------------------------------
+    const unsigned colbase = n0 + wn * 32 + 2 * t;
+    if (p.splits > 1) {
+        float* ws = p.ws + (size_t)z * p.M * p.N;
+#pragma unroll
+        for (int i = 0; i < MJ; ++i)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+                const unsigned row = m0 + wm * (16 * MJ) + i * 16 + h * 8 + g;
+                if (row >= p.M) continue;
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int e = 0; e < 2; ++e) {
+                        const unsigned col = colbase + j * 8 + e;
+                        if (col < p.N) ws[(size_t)row * p.N + col] = scale_acc * acc[i][j][2 * h + e];
+                    }
+            }
+        continue;
+    }
+    const float alpha = p.alpha * scale_acc;
+    long long roff[MJ][2], droff[MJ][2];
+#pragma unroll
+    for (int i = 0; i < MJ; ++i)
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+            const unsigned row = m0 + wm * (16 * MJ) + i * 16 + h * 8 + g;
+            roff[i][h] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
+            droff[i][h] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
+        }
+    const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        long long co[2], dco[2];
+        bool cok[2];
+        float add[2][MJ][2];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const unsigned col = colbase + j * 8 + e;
+            cok[e] = col < p.N;
+            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
+            dco[e] = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
+#pragma unroll
+            for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    float v = 0.f;
+                    if (cok[e] && roff[i][h] >= 0) {
+                        if (use_beta) v = p.beta * p.C[roff[i][h] + co[e]];
+                        if (use_d) v += p.gamma * p.D[droff[i][h] + dco[e]];
+                    }
+                    add[e][i][h] = v;
+                }
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+                    if (cok[e] && roff[i][h] >= 0)
+                        p.C[roff[i][h] + co[e]] = alpha * acc[i][j][2 * h + e] + add[e][i][h];
+    }
+    }   // tile loop
+}
+
 __global__ void splitk_reduce_f32_kernel(const __grid_constant__ FParams p, long long total) {
     const long long MN = (long long)p.M * p.N;
     for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
@@ -456,6 +741,22 @@ int launch_tile_kernel(pccb_ctx* ctx, const FParams& p, long long batch) {
         attr_set = true;
     }
     dim3 grid((unsigned)((p.M + BM - 1) / BM), (unsigned)((p.N + BN - 1) / BN), (unsigned)(batch * p.splits));
+    static const bool use_ws = [] { const char* e = getenv("PCCB_WS"); return e ? atoi(e) != 0 : true; }();
+    if (use_ws) {
+        static bool attr_ws = false;
+        if (!attr_ws) {
+            PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f32_ws_kernel<VEC, MJ>,
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+            attr_ws = true;
+        }
+        FParams q = p;
+        q.nz = (int)(batch * p.splits);
+        const long long ntiles = (long long)grid.x * grid.y * grid.z;
+        const unsigned nctas = (unsigned)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+        contract_f32_ws_kernel<VEC, MJ><<<nctas, NTHREADS_WS, SMEM, ctx->stream>>>(q);
+        PCCB_CHECK_LAUNCH(ctx, "contract_f32_ws_kernel");
+        return PCCB_OK;
+    }
     contract_f32_kernel<VEC, MJ><<<grid, NTHREADS, SMEM, ctx->stream>>>(p);
     PCCB_CHECK_LAUNCH(ctx, "contract_f32_kernel");
     return PCCB_OK;
@@ -472,12 +773,16 @@ int dispatch_mj(pccb_ctx* ctx, const FParams& p, long long batch, int mj) {
 }
 
 int choose_mj(long long M) {
+    // rows per CTA tile = 32*mj: padded rows weighted by the measured relative efficiency of the tile
+    // height (a 32-row tile re-reads B four times as often and has a quarter of the MMAs per fragment load)
+    static const int forced = [] { const char* e = getenv("PCCB_MJ"); return e ? atoi(e) : 0; }();
+    if (forced >= 1 && forced <= 4) return forced;
+    static const double eff[5] = {0.0, 0.60, 0.85, 0.95, 1.00};
     int best = 4;
-    long long best_cost = LLONG_MAX;
+    double best_cost = 1e300;
     for (int mj : {4, 3, 2, 1}) {
         const long long bm = 32 * mj;
-        const long long padded = ((M + bm - 1) / bm) * bm;
-        const long long cost = padded * 64 + padded * (4 - mj) * 2;
+        const double cost = (double)(((M + bm - 1) / bm) * bm) / eff[mj];
         if (cost < best_cost) { best_cost = cost; best = mj; }
     }
     return best;

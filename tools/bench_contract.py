@@ -10,7 +10,10 @@ o, v = (int(sys.argv[1]), int(sys.argv[2])) if len(sys.argv) > 2 else (20, 150)
 only = sys.argv[3].split(",") if len(sys.argv) > 3 else None
 be = CudaBackend()
 dev = be.device
-R = lambda *s: torch.randn(s, dtype=torch.float64, device=dev)
+F32 = os.environ.get("PCCB_BENCH_DTYPE", "f64") == "f32"
+DT = torch.float32 if F32 else torch.float64
+from pycc_b200 import _lib
+R = lambda *s: torch.randn(s, dtype=DT, device=dev)
 T = dict(tau=R(o, o, v, v), vvvv=R(v, v, v, v), r2=R(o, o, v, v), t2=R(o, o, v, v), Wr=R(o, v, o, v),
          ovvv=R(o, v, v, v), Zr=R(o, o, o, v), Wmnij=R(o, o, o, o), Loovv=R(o, o, v, v), Fae=R(v, v), t1=R(o, v))
 tests = [("ladder", "r2[ijab] += 0.5*tau[ijef]*vvvv[abef]", 2.0 * o * o * v ** 4),
@@ -24,7 +27,7 @@ tests = [("ladder", "r2[ijab] += 0.5*tau[ijef]*vvvv[abef]", 2.0 * o * o * v ** 4
 res = {}
 for name, stmt, fl in tests:
     if only and name not in only: continue
-    Ls = plan(stmt, T)
+    Ls = plan(stmt, T, _lib.F32 if F32 else _lib.F64)
     for _ in range(2):
         for L in Ls: be.contract(L.desc)
     torch.cuda.synchronize()
