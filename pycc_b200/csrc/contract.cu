@@ -31,6 +31,8 @@
 #include <cstdlib>
 #include <cstring>
 
+#include <cuda.h>
+
 #include "common.cuh"
 
 namespace {
@@ -695,6 +697,255 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     }   // tile loop
 }
 
+// ---- TMA-staged variant (plain 2-D operands: the o^2 v^4 ladder, Wmnij, Zmbij) ------------------
+// When both operands of every segment are K-contiguous matrices with a uniform row stride, the
+// producer is ONE thread issuing two cp.async.bulk.tensor (TMA) copies per k-tile; completion is
+// counted in bytes on the stage's full barrier.  Tiles land dense ([row][16 doubles] = 128-byte
+// rows) under the 128-byte swizzle: 16-byte chunk c of row r sits at chunk c ^ (r & 7).  The DMMA
+// fragment loads (8 rows x 4 k per instruction, LDS.64) stay bank-conflict free because fragment
+// row g of every 8-row group is mapped to tile row perm(g) = 2(g & 3) + (g >> 2): the rows a
+// half-warp touches are then {0,2,4,6} or {1,3,5,7}, whose XOR patterns hit 8 distinct chunks.
+// The epilogue applies the same relabeling to the output rows / columns.
+constexpr int TMA_THREADS = NCONS + 128, TMA_STAGES = 6;   // producer warpgroup: one working thread (setmaxnreg needs 4 warps)
+
+struct alignas(64) TmaMaps {
+    CUtensorMap a[PCCB_MAX_SEGMENTS];
+    CUtensorMap b[PCCB_MAX_SEGMENTS];
+};
+
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n"
+        ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar)
+        : "memory");
+}
+
+template <int MI>
+__global__ void __launch_bounds__(TMA_THREADS, 1)
+contract_f64_tma_kernel(const __grid_constant__ DParams p, const __grid_constant__ TmaMaps maps) {
+    constexpr int BM = 16 * MI;
+    constexpr int A_STAGE = BM * BK, B_STAGE = BN * BK;       // doubles; rows of 128 bytes
+    constexpr int S = TMA_STAGES;
+
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    // dynamic shared memory is only guaranteed 16-byte aligned: align the ring to 1024 by hand
+    const unsigned raw_s = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned pad = (1024u - (raw_s & 1023u)) & 1023u;
+    double* sA = reinterpret_cast<double*>(smem_raw + pad);
+    double* sB = sA + S * A_STAGE;
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(sB + S * B_STAGE);   // full[S], empty[S]
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned gm = (p.M + BM - 1) / BM, gn = (p.N + BN - 1) / BN;
+    const long long ntiles = (long long)gm * gn * p.nz;
+
+    const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
+    const unsigned sB_s = (unsigned)__cvta_generic_to_shared(sB);
+    const unsigned full_s = (unsigned)__cvta_generic_to_shared(bars);
+    const unsigned empty_s = full_s + 8 * S;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            mbar_init(full_s + 8 * s, 1);
+            mbar_init(empty_s + 8 * s, NCONS / 32);
+        }
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    }
+    __syncthreads();
+
+    auto seg_of = [&](int kt) {
+        int s = 0;
+#pragma unroll
+        for (int q = 1; q < PCCB_MAX_SEGMENTS; ++q)
+            if (q < p.nseg && kt >= p.seg[q].kt_begin) s = q;
+        return s;
+    };
+
+    if (warp >= NCONS / 32) {
+        // ================================ TMA producer (one thread) ================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
+        if (warp == NCONS / 32 && lane == 0) {
+            unsigned g = 0;
+#pragma unroll 1
+            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                const unsigned mx = (unsigned)(tile % gm);
+                const long long rest = tile / gm;
+                const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+                const int z = (int)(rest / gn);
+                const int split = z % p.splits;
+                const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
+                const int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
+#pragma unroll 1
+                for (int it = 0; it < nkt; ++it, ++g) {
+                    const int s = seg_of(kt_lo + it);
+                    const int st = g % S;
+                    if (g >= S) mbar_wait_relaxed(empty_s + 8 * st, ((g - S) / S) & 1);
+                    const int k0 = (kt_lo + it - p.seg[s].kt_begin) * BK;
+                    const unsigned bar = full_s + 8 * st;
+                    mbar_expect_tx(bar, (unsigned)((A_STAGE + B_STAGE) * sizeof(double)));
+                    tma_load_2d(sA_s + st * (A_STAGE * 8), &maps.a[s], k0, (int)m0, bar);
+                    tma_load_2d(sB_s + st * (B_STAGE * 8), &maps.b[s], k0, (int)n0, bar);
+                }
+            }
+        }
+        return;
+    }
+
+    // ================================ consumers ================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 224;\n");
+    const int wm = warp >> 2, wn = warp & 3;
+    const int frow = lane >> 2, fk = lane & 3;
+    const int pf = ((frow & 3) << 1) | (frow >> 2);          // tile row (within its 8-row group) of fragment row frow
+    // offset (doubles) of this lane's element inside a 128-byte row, per k-step: chunk (2ks + fk/2) ^ pf
+    int koff[BK / 4];
+#pragma unroll
+    for (int ks = 0; ks < BK / 4; ++ks) koff[ks] = ((((2 * ks) + (fk >> 1)) ^ pf) << 1) | (fk & 1);
+    const int arow = (wm * (8 * MI) + pf) * BK, brow = (wn * 32 + pf) * BK;
+
+    unsigned g0 = 0;
+#pragma unroll 1
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+    const unsigned mx = (unsigned)(tile % gm);
+    const long long rest = tile / gm;
+    const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+    const int z = (int)(rest / gn);
+    const int batch = z / p.splits, split = z % p.splits;
+    const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
+    const int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
+
+    double acc[MI][4][2];
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    double a[MI], b[4], bnx[4];
+    mbar_wait(full_s + 8 * (g0 % S), (g0 / S) & 1);
+    const double* ap = sA + (g0 % S) * A_STAGE + arow;
+    const double* bp = sB + (g0 % S) * B_STAGE + brow;
+#pragma unroll
+    for (int i = 0; i < MI; ++i) a[i] = ap[i * 8 * BK + koff[0]];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) b[j] = bp[j * 8 * BK + koff[0]];
+
+    int seg_acc = -1;
+    double scale_acc = 1.0;
+#pragma unroll 1
+    for (int it = 0; it < nkt; ++it) {
+        const int st = (g0 + it) % S;
+        {
+            const int sgi = seg_of(kt_lo + it);
+            if (sgi != seg_acc) {
+                const double sc = p.seg[sgi].scale;
+                if (seg_acc >= 0 && sc != scale_acc) {
+                    const double r = scale_acc / sc;
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { acc[i][j][0] *= r; acc[i][j][1] *= r; }
+                }
+                seg_acc = sgi;
+                scale_acc = sc;
+            }
+        }
+        const double* an = ap;
+        const double* bn = bp;
+#pragma unroll
+        for (int ks = 0; ks < BK / 4; ++ks) {
+            const int nks = (ks + 1) % (BK / 4);
+            bool more = true;
+            if (ks == BK / 4 - 1) {
+                more = it + 1 < nkt;
+                if (more) {
+                    const unsigned gn1 = g0 + it + 1;
+                    mbar_wait(full_s + 8 * (gn1 % S), (gn1 / S) & 1);
+                    an = sA + (gn1 % S) * A_STAGE + arow;
+                    bn = sB + (gn1 % S) * B_STAGE + brow;
+                }
+            }
+            if (more) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bnx[j] = bn[j * 8 * BK + koff[nks]];
+            }
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                if (more) a[i] = an[i * 8 * BK + koff[nks]];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bnx[j];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_s + 8 * st);
+        ap = an;
+        bp = bn;
+    }
+    g0 += nkt;
+
+    // ---- epilogue: accumulator (frow, 2 fk + e) of an 8x8 block is tile element (perm(frow), perm(2 fk + e))
+    const int pc0 = (((2 * fk) & 3) << 1) | ((2 * fk) >> 2), pc1 = (((2 * fk + 1) & 3) << 1) | ((2 * fk + 1) >> 2);
+    const unsigned colbase = n0 + wn * 32;
+    if (p.splits > 1) {
+        double* ws = p.ws + (size_t)z * p.M * p.N;
+#pragma unroll
+        for (int i = 0; i < MI; ++i) {
+            const unsigned row = m0 + wm * (8 * MI) + i * 8 + pf;
+            if (row >= p.M) continue;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const unsigned col = colbase + j * 8 + (e ? pc1 : pc0);
+                    if (col < p.N) ws[(size_t)row * p.N + col] = scale_acc * acc[i][j][e];
+                }
+        }
+        continue;
+    }
+    const double alpha = p.alpha * scale_acc;
+    long long roff[MI], droff[MI];
+#pragma unroll
+    for (int i = 0; i < MI; ++i) {
+        const unsigned row = m0 + wm * (8 * MI) + i * 8 + pf;
+        roff[i] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
+        droff[i] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
+    }
+    const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        long long co[2];
+        bool cok[2];
+        double add[2][MI];
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+            const unsigned col = colbase + j * 8 + (e ? pc1 : pc0);
+            cok[e] = col < p.N;
+            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
+            const long long dco = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+                double v = 0.0;
+                if (cok[e] && roff[i] >= 0) {
+                    if (use_beta) v = p.beta * p.C[roff[i] + co[e]];
+                    if (use_d) v += p.gamma * p.D[droff[i] + dco];
+                }
+                add[e][i] = v;
+            }
+        }
+#pragma unroll
+        for (int e = 0; e < 2; ++e)
+#pragma unroll
+            for (int i = 0; i < MI; ++i)
+                if (cok[e] && roff[i] >= 0) p.C[roff[i] + co[e]] = alpha * acc[i][j][e] + add[e][i];
+    }
+    }   // tile loop
+}
+
 // fixed-order reduction of the split-K partial tiles + epilogue
 __global__ void splitk_reduce_kernel(const __grid_constant__ DParams p, long long total) {
     const long long MN = (long long)p.M * p.N;
@@ -816,6 +1067,94 @@ int dispatch_mi(pccb_ctx* ctx, const DParams& p, long long batch, int mi) {
     }
 }
 
+// ---- TMA path: eligibility, tensor maps, launch --------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+// operand = K-contiguous matrix with one uniform, 16-byte-aligned row stride
+bool tma_operand_ok(const void* base, const DIdx& mn, const DIdx& k, long long rows) {
+    if (!(k.flat && k.s_lo == 1 && mn.flat)) return false;
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return false;
+    if (rows > 1 && (mn.s_lo <= 0 || (mn.s_lo & 1))) return false;     // stride in doubles, must be even
+    return true;
+}
+
+bool make_map(CUtensorMap* m, const void* base, long long rows, long long K, long long row_stride, int box_rows) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    if (rows <= 1) row_stride = ((K + 1) / 2) * 2;       // a single row: any legal stride
+    if (row_stride < K) return false;                     // overlapping rows are not a tensor
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)row_stride * sizeof(double)};
+    const cuuint32_t box[2] = {(cuuint32_t)BK, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, const_cast<void*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+template <int MI>
+constexpr size_t smem_bytes_tma() {
+    return (size_t)TMA_STAGES * (16 * MI + BN) * BK * sizeof(double) + 2 * TMA_STAGES * sizeof(unsigned long long) + 1024;
+}
+
+template <int MI>
+int launch_tma_kernel(pccb_ctx* ctx, const DParams& p, const TmaMaps& maps, long long batch) {
+    constexpr int BM = 16 * MI;
+    constexpr size_t SMEM = smem_bytes_tma<MI>();
+    static bool attr_set = false;
+    if (!attr_set) {
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_tma_kernel<MI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)SMEM));
+        attr_set = true;
+    }
+    DParams q = p;
+    q.nz = (int)(batch * p.splits);
+    const long long ntiles = (long long)((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * q.nz;
+    const unsigned nctas = (unsigned)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+    contract_f64_tma_kernel<MI><<<nctas, TMA_THREADS, SMEM, ctx->stream>>>(q, maps);
+    PCCB_CHECK_LAUNCH(ctx, "contract_f64_tma_kernel");
+    return PCCB_OK;
+}
+
+// returns 1 when the TMA kernel was launched, 0 when the contraction is not eligible, < 0 on error
+int try_tma(pccb_ctx* ctx, const DParams& p, const pccb_contraction* d, int mi) {
+    static const bool use_tma = [] { const char* e = getenv("PCCB_TMA"); return e ? atoi(e) != 0 : true; }();
+    if (!use_tma || mi <= 2 || d->batch != 1 || p.nseg < 1) return 0;
+    for (int s = 0; s < p.nseg; ++s) {
+        const DSeg& g = p.seg[s];
+        if (!tma_operand_ok(g.A, g.am, g.ak, p.M) || !tma_operand_ok(g.B, g.bn, g.bk, p.N)) return 0;
+    }
+    TmaMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    for (int s = 0; s < p.nseg; ++s) {
+        const DSeg& g = p.seg[s];
+        if (!make_map(&maps.a[s], g.A, p.M, g.K, g.am.s_lo, 16 * mi)) return 0;
+        if (!make_map(&maps.b[s], g.B, p.N, g.K, g.bn.s_lo, BN)) return 0;
+    }
+    int rc;
+    switch (mi) {
+        case 4: rc = launch_tma_kernel<4>(ctx, p, maps, d->batch); break;
+        case 5: rc = launch_tma_kernel<5>(ctx, p, maps, d->batch); break;
+        case 6: rc = launch_tma_kernel<6>(ctx, p, maps, d->batch); break;
+        default: rc = launch_tma_kernel<8>(ctx, p, maps, d->batch); break;
+    }
+    return rc == PCCB_OK ? 1 : rc;
+}
+
 // rows per CTA tile: minimise padded rows, prefer the taller tile on ties (more operand reuse)
 int choose_mi(long long M) {
     // tuning hook for tools/bench_contract.py: PCCB_MI=<1|2|4|5|6|8> forces the tile height
@@ -921,8 +1260,12 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
                  (long long)d->batch * splits);
     p.splits = splits;
 
-    int rc = vec2 ? dispatch_mi<2>(ctx, p, d->batch, mi) : dispatch_mi<1>(ctx, p, d->batch, mi);
-    if (rc != PCCB_OK) return rc;
+    int rc = try_tma(ctx, p, d, mi);      // plain 2-D operands: TMA-staged kernel
+    if (rc < 0) return rc;
+    if (rc == 0) {
+        rc = vec2 ? dispatch_mi<2>(ctx, p, d->batch, mi) : dispatch_mi<1>(ctx, p, d->batch, mi);
+        if (rc != PCCB_OK) return rc;
+    }
     if (splits > 1) {
         const int threads = 256;
         long long blocks = (total + threads - 1) / threads;
