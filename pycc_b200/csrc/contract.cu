@@ -1249,12 +1249,21 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
     const long long tiles = gm * gn * d->batch;
     int splits = 1;
     if (tiles < 2ll * ctx->sm_count && kt >= 16) {
-        long long want = (2ll * ctx->sm_count + tiles - 1) / tiles;
-        long long by_k = kt / 8;                       // at least 8 k-tiles (128 k) per split
-        long long by_ws = ctx->ws ? (long long)(ctx->ws_bytes / ((size_t)total * sizeof(double))) : 1;
-        long long sK = want < by_k ? want : by_k;
-        if (sK > by_ws) sK = by_ws;
-        if (sK > 1) splits = (int)sK;
+        // deterministic split-K for outputs with too few tiles: among the admissible split counts pick
+        // the one whose tiles*splits fills whole waves of the persistent grid best (ties: fewer splits)
+        const long long by_k = kt / 8;                       // at least 8 k-tiles (128 k) per split
+        const long long by_ws = ctx->ws ? (long long)(ctx->ws_bytes / ((size_t)total * sizeof(double))) : 1;
+        long long smax = (8ll * ctx->sm_count + tiles - 1) / tiles;
+        if (smax > by_k) smax = by_k;
+        if (smax > by_ws) smax = by_ws;
+        double best = 0.0;
+        for (long long sK = 1; sK <= smax; ++sK) {
+            const long long work = tiles * sK, waves = (work + ctx->sm_count - 1) / ctx->sm_count;
+            double eff = (double)work / (double)(waves * ctx->sm_count);
+            if (waves < 2) eff *= 0.97;                      // a single wave has no tail overlap at all
+            eff -= 0.004 * (double)sK;                       // reduction traffic grows with the split count
+            if (eff > best + 1e-9) { best = eff; splits = (int)sK; }
+        }
     }
     PCCB_REQUIRE(ctx, (long long)d->batch * splits <= 65535, "pccb_contract: batch*splits=%lld exceeds grid.z",
                  (long long)d->batch * splits);
