@@ -72,7 +72,7 @@ typedef struct pccb_segment {
 typedef struct pccb_contraction {
     int64_t M, N, batch;
     int32_t nseg;
-    int32_t dtype; /* PCCB_F64 or PCCB_F32 (operands, output and accumulation type) */
+    int32_t dtype; /* PCCB_F64 (DMMA) or PCCB_F32 (3xTF32 tensor-core products, FP32 accumulation) */
     pccb_segment seg[PCCB_MAX_SEGMENTS];
     void* C_dev;
     pccb_cidx cm, cn;

@@ -10,23 +10,29 @@
 //     warp-synchronous DMMA.8x8x4 (PTX mma.sync.m8n8k4.f64), one issue per 16 cycles per SM
 //     sub-partition = 37.0 TFLOP/s per GPU; cuBLAS DGEMM reaches 35.5.
 //   * CTA tile (16*MI) x 128 x 16 with MI in {1,2,4,5,6,8} chosen per launch to minimise padded
-//     rows (o^2 = 400 -> five 80-row tiles); 8 warps as 2(M) x 4(N), warp tile (8*MI) x 32:
+//     rows (o^2 = 400 -> five 80-row tiles); 8 DMMA warps as 2(M) x 4(N), warp tile (8*MI) x 32:
 //     4*MI DMMA per MI+4 LDS.64, so the tensor pipe, not shared memory, is the limiter.
-//   * operand tiles are staged with cp.async (LDGSTS, zero-fill at the edges) through a 4-stage
-//     shared-memory ring guarded by mbarriers (full: cp.async.mbarrier.arrive of all threads,
-//     empty: one arrive per warp), so warps drift up to two k-tiles apart instead of meeting
-//     at a CTA barrier every 16 k.  The loader is branch-free straight-line code issued
-//     between the DMMA groups: a DMMA holds the pipe for 16 cycles, so the per-chunk address
-//     arithmetic of compound (two-level) einsum indices rides in otherwise idle issue slots.
-//     That is what lets a tile walk e.g. the (i,a) x (m,e) view of t2[i,m,a,e] without any
-//     transpose in HBM.
-//   * shared tiles keep the global-contiguous direction contiguous ("K-major" [row][k] with
-//     pitch 20 doubles, or "MN-major" [k][row] with pitch rows+4): both pitches are = 4 mod 16
-//     eight-byte words, which makes the DMMA fragment loads bank-conflict free.
+//   * three kernels behind the one entry point (all persistent over output tiles):
+//       contract_f64_tma_kernel  plain 2-D operands (o^2 v^4 ladder, Wmnij, Zmbij): one producer
+//                                thread issues cp.async.bulk.tensor (TMA) copies, 128-byte swizzle,
+//                                fragment rows permuted so that LDS.64 stays conflict free
+//                                (35.1 TFLOP/s = 0.95 of peak on the ladder);
+//       contract_f64_ws_kernel   compound (gathered) operands: 4 producer warps do the index
+//                                arithmetic + cp.async (LDGSTS, zero-fill at the edges), 8 consumer
+//                                warps run DMMA + LDS only (30.5-32.9 TFLOP/s);
+//       contract_f64_kernel      MI <= 2 (skinny, memory-bound launches): all warps load and
+//                                compute, two CTAs per SM.
+//     Stages are guarded by full/empty mbarriers; registers are re-balanced with setmaxnreg.
+//   * compound (two-level) einsum indices are resolved per 16-byte chunk by the producers; that is
+//     what lets a tile walk e.g. the (i,a) x (m,e) view of t2[i,m,a,e] without any transpose in HBM.
+//   * shared tiles of the cp.async kernels keep the global-contiguous direction contiguous
+//     ("K-major" [row][k] with pitch 20 doubles, or "MN-major" [k][row] with pitch rows+4): both
+//     pitches are = 4 mod 16 eight-byte words, which makes the DMMA fragment loads conflict free.
 //   * per-segment scale factors never touch the FP64 pipe in the main loop: the accumulators
 //     are rescaled once when the k-loop crosses a segment boundary.
-//   * small outputs (Fae, Fmi, Wmnij ...) use deterministic split-K through a caller-owned
-//     workspace, reduced in fixed order together with the alpha/beta/gamma epilogue.
+//   * small outputs (Fae, Fmi, Wmnij ...) use deterministic split-K (wave-aware split count)
+//     through a caller-owned workspace, reduced in fixed order with the alpha/beta/gamma epilogue.
+//   * FP32 operands (precision='SP') are routed to contract_f32.cu (3xTF32 tensor-core kernel).
 #include <climits>
 #include <cstdlib>
 #include <cstring>
