@@ -145,6 +145,14 @@ int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, const int32
                         const void* t1_dev, const void* t2_dev, const void* oovv_dev, const void* fov_dev,
                         int64_t ld_fov, const void* eps_dev, int64_t no, int64_t nv, double* et_dev);
 
+/* ---- CC3 (next row): t3 = W / D for k = k0 .. k0+nk-1 of the occupied pair (i, j) and the
+ * two combinations contracted into r1 / r2 (pycc/ccwfn.py:387-398, pycc/cctriples.py:24-33):
+ *   a1[k][a][b][c] = t3[abc] - t3[cba],   a2[k][a][b][c] = 2 t3[abc] - t3[acb] - t3[cba].
+ * w_dev holds the connected triples W[k][a][b][c] built by pccb_contract from the T1-dressed
+ * integrals (ccwfn.py:625-710).  Asynchronous. */
+int pccb_t3_combine(pccb_ctx* ctx, int dtype, const void* w_dev, int nk, int k0, int i, int j, const void* eps_dev,
+                    int64_t no, int64_t nv, void* a1_dev, void* a2_dev);
+
 #ifdef __cplusplus
 }
 #endif

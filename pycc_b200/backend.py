@@ -141,3 +141,8 @@ class CudaBackend(object):
         self._check(self.lib.pccb_triples_energy(self.h, dtype_code(W), W.data_ptr(), ijk_dev.data_ptr(), ntrip,
                                                  t1.data_ptr(), t2.data_ptr(), oovv.data_ptr(), fov.data_ptr(),
                                                  ld_fov, eps.data_ptr(), no, nv, et_dev.data_ptr()))
+
+    def t3_combine(self, W, nk, k0, i, j, eps, no, nv, A1, A2):
+        """A1 / A2 combinations of t3 = W / D for the pair (i, j), k = k0 .. k0+nk-1 (CC3)."""
+        self._check(self.lib.pccb_t3_combine(self.h, dtype_code(W), W.data_ptr(), nk, k0, i, j, eps.data_ptr(),
+                                             no, nv, A1.data_ptr(), A2.data_ptr()))

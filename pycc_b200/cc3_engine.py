@@ -1,0 +1,118 @@
+"""
+CC3 contributions to the singles and doubles residuals: the
+reference's per-iteration loop over all occupied triplets (pycc/ccwfn.py:371-404) with T1-dressed
+integrals (``build_cc3_*``, :625-710), on the engine's kernels:
+
+  * the five dressed intermediates are planned statements over the stored ERI blocks; they are kept
+    in the layouts the (T) machinery consumes, ``Wv[i][a][b][e] = Wabei[a,b,e,i]`` and
+    ``Wo[i][j][m][b] = Wmbij[m,b,i,j]``, so the connected triples of a whole k-batch come from the
+    same three batched ``pccb_contract`` launches per occupied pair (i, j) as in (T);
+  * ``pccb_t3_combine`` divides by the triples denominator and forms ``t3 - t3^(ac)`` and
+    ``2 t3 - t3^(bc) - t3^(ac)`` for the batch;
+  * four contractions per pair, with k folded into the contracted index, add X1 / X2 (:395-398)
+    straight into the unsymmetrised r1 / r2 (the final r2 + r2^T supplies X2^T, :401).
+
+No o^3 v^3 tensor exists at any time (three o v^3 buffers).  Single GPU only for now.
+"""
+import torch
+
+from .dsl import TRef, plan
+from .triples_engine import TriplesEngine
+
+
+class CC3Engine(object):
+    # dressed intermediates (index letters as in the reference)
+    STATEMENTS = (
+        # build_cc3_Wmnij (:625-635)
+        "Wmnij3[mnij] = oooo[mnij] + oovv[mnef]*T11[ijef]",
+        "Wmnij3[mnij] += ooov[mnie]*t1[je]",
+        "Wmnij3[mnij] += ooov[nmje]*t1[ie]",
+        # build_cc3_Wmbij (:637-650) as Wo[ijmb]; <mb|ij> = <ij|mb>, <mb|ej> = <mj|eb>
+        "X[mbej] = ovvv[mbef]*t1[jf]",
+        "Wo[ijmb] = ooov[ijmb] - Wmnij3[mnij]*t1[nb]",
+        "Wo[ijmb] += ovov[mbie]*t1[je]",
+        "Wo[ijmb] += t1[ie]*X[mbej]",
+        "Wo[ijmb] += t1[ie]*oovv[mjeb]",
+        # build_cc3_Wmnie (:652-659)
+        "Wmnie3[mnie] = ooov[mnie] + t1[if]*oovv[mnfe]",
+        # build_cc3_Wamef (:661-668) as Wk[maef]; <am|ef> = <ma|fe>  (the bare part is set by a permuted copy)
+        "Wk[maef] -= t1[na]*oovv[nmef]",
+        # build_cc3_Wabei (:670-710) as Wv[iabe] = Wabei[a,b,e,i]; P, Q, R start as permuted copies of
+        # <ei|am> = ovov[i,e,m,a], <mn|ei> = ooov[n,m,i,e], <mb|ei> = oovv[m,i,e,b]
+        "P[imae] += ovvv[mafe]*t1[if]",
+        "Q[imne] += oovv[mnef]*t1[if]",
+        "Qa[iane] = t1[ma]*Q[imne]",
+        "R[imbe] += ovvv[mbef]*t1[if]",
+        "Wv[iabe] += t1[if]*vvvv[abef]",
+        "Wv[iabe] -= P[imae]*t1[mb]",
+        "Wv[iabe] += Qa[iane]*t1[nb]",
+        "Wv[iabe] -= t1[ma]*R[imbe]",
+    )
+
+    def __init__(self, eng):
+        if eng.comm.world > 1:
+            raise ValueError("model='CC3' runs on one GPU for now (the dressed <ab|ei> needs every row of <ab|ef>)")
+        if eng.ovvv_full is None:
+            raise ValueError("model='CC3' needs the full <mb|ef> block")
+        self.eng, self.be = eng, eng.be
+        o, v, dt = eng.no, eng.nv, eng.dtype
+        E = lambda *s: self.be.zeros(s, dt)
+        self.T11 = E(o, o, v, v)
+        self.Wmnij3, self.Wo, self.Wmnie3 = E(o, o, o, o), E(o, o, o, v), E(o, o, o, v)
+        self.X, self.P, self.R, self.Qa = E(o, v, v, o), E(o, o, v, v), E(o, o, v, v), E(o, v, o, v)
+        self.Q = E(o, o, o, v)
+        self.Wk, self.Wv = E(o, v, v, v), E(o, v, v, v)
+        self.A1, self.A2 = E(o, v, v, v), E(o, v, v, v)
+        b = eng.blk
+        T = dict(oooo=b["oooo"], ooov=b["ooov"], oovv=b["oovv"], ovov=b["ovov"], ovvv=eng.ovvv_full, vvvv=eng.vvvv_loc,
+                 t1=eng.t1, T11=self.T11, Wmnij3=self.Wmnij3, Wo=self.Wo, Wmnie3=self.Wmnie3, X=self.X, P=self.P,
+                 R=self.R, Q=self.Q, Qa=self.Qa, Wk=self.Wk, Wv=self.Wv)
+        T = {k: TRef.of(t, k) for k, t in T.items()}
+        self.launches = []
+        for s in self.STATEMENTS:
+            self.launches += plan(s, T, eng.dcode)
+        self.tri = TriplesEngine(eng, V=self.Wv, O=self.Wo)
+        self._pair_plans = {}
+
+    def build_intermediates(self):
+        eng, be = self.eng, self.be
+        o, v = eng.no, eng.nv
+        b = eng.blk
+        be.pair_combine(self.T11, eng.t2, 0.0, 0.0, eng.t1, eng.t1, 1.0, o, v)
+        # bare parts that are permuted views of the stored blocks
+        be.permute4(self.Wk, eng.ovvv_full.permute(0, 1, 3, 2))        # <am|ef> = ovvv[m,a,f,e]
+        be.permute4(self.P, b["ovov"].permute(0, 2, 3, 1))             # <ei|am> = ovov[i,e,m,a]
+        be.permute4(self.Q, b["ooov"].permute(2, 1, 0, 3))             # <mn|ei> = ooov[n,m,i,e]
+        be.permute4(self.R, b["oovv"].permute(1, 0, 3, 2))             # <mb|ei> = oovv[m,i,e,b]
+        be.permute4(self.Wv, eng.ovvv_full.permute(0, 3, 2, 1))        # <ei|ab> = ovvv[i,e,b,a]
+        for L in self.launches:
+            be.contract(L.desc)
+
+    def _plans_for(self, i, j):
+        key = (i, j)
+        if key not in self._pair_plans:
+            eng = self.eng
+            T = dict(A1=self.A1, A2=self.A2, Lj=eng.Loovv[j], Fme=eng.Fme, Wk=self.Wk, Wj=self.Wmnie3[j],
+                     r1i=eng.r1[i], r2ij=eng.r2[i, j], r2i=eng.r2[i])
+            T = {k: TRef.of(t, k) for k, t in T.items()}
+            ls = []
+            for s in ("r1i[a] += A1[kabc]*Lj[kbc]",                    # X1 (:395)
+                      "r2ij[ab] += A1[kabc]*Fme[kc]",                  # X2 (:396)
+                      "r2ij[ad] += A2[kabc]*Wk[kdbc]",                 # X2 (:397)
+                      "r2i[lab] -= A2[kabc]*Wj[klc]"):                 # X2 (:398)
+                ls += plan(s, T, eng.dcode)
+            self._pair_plans[key] = ls
+        return self._pair_plans[key]
+
+    def contribute(self):
+        """r1 += X1, r2(unsymmetrised) += X2 for the amplitudes held by the engine; Fme must be current."""
+        eng, be = self.eng, self.be
+        o, v = eng.no, eng.nv
+        self.build_intermediates()
+        self.tri.refresh_t2T()
+        for i in range(o):
+            for j in range(o):
+                self.tri._launch_pair(i, j, nk=o)
+                be.t3_combine(self.tri.W, o, 0, i, j, eng.eps, o, v, self.A1, self.A2)
+                for L in self._plans_for(i, j):
+                    be.contract(L.desc)

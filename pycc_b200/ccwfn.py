@@ -31,7 +31,7 @@ class ccwfn(object):
     """
 
     valid_cc_models = ['CCD', 'CC2', 'CCSD', 'CCSD(T)', 'CC3']
-    engine_models = ['CCD', 'CC2', 'CCSD', 'CCSD(T)']
+    engine_models = ['CCD', 'CC2', 'CCSD', 'CCSD(T)', 'CC3']
 
     def __init__(self, scf_wfn, **kwargs):
         try:
@@ -71,7 +71,7 @@ class ccwfn(object):
         if model not in self.valid_cc_models:
             raise Exception("%s is not an allowed CC model." % (model))
         if model not in self.engine_models:
-            raise Exception("%s is not available in the B200 engine yet (CCSD and CCSD(T) are)." % (model))
+            raise Exception("%s is not available in the B200 engine." % (model))
         self.model = model
         self.need_singles = ['CCSD', 'CCSD(T)', 'CC2', 'CC3']
         self.need_t1_transform = ['CC3']
@@ -144,7 +144,7 @@ class ccwfn(object):
         dtype = torch.float32 if self.precision == 'SP' else torch.float64
         from .parallel import virtual_slice
         vslice = virtual_slice(nv, self.comm.rank, self.comm.world)
-        keep_ovvv = (model == 'CCSD(T)' or self.comm.world == 1)
+        keep_ovvv = (model in ('CCSD(T)', 'CC3') or self.comm.world == 1)
         if isinstance(ERI, dict):
             self.H = Hamiltonian.from_blocks(F, ERI, no, backend.device, dtype, vslice, keep_ovvv)
         else:

@@ -164,6 +164,31 @@ __global__ void sum_rows_kernel(const double* __restrict__ partials, int n, doub
     }
 }
 
+
+// ---- CC3: amplitudes t3 = W / D for a batch of k and the two spin-adapted combinations the
+// residual contractions need (pycc/ccwfn.py:387-398):
+//   A1[k][a][b][c] = t3[abc] - t3[cba]                 (t3 - t3.swapaxes(0,2))
+//   A2[k][a][b][c] = 2 t3[abc] - t3[acb] - t3[cba]     (2 t3 - t3.swapaxes(1,2) - t3.swapaxes(0,2))
+// D^{ijk}_{abc} (pycc/cctriples.py:24-33) is invariant under permutations of (a,b,c).
+template <typename T>
+__global__ void t3_combine_kernel(const T* __restrict__ W, int nk, int k0, int i, int j, const T* __restrict__ eps,
+                                  int no, int nv, T* __restrict__ A1, T* __restrict__ A2) {
+    const long long v2 = (long long)nv * nv, v3 = v2 * nv, total = v3 * nk;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const int kk = (int)(idx / v3);
+        const long long r = idx - (long long)kk * v3;
+        const int a = (int)(r / v2), b = (int)((r / nv) % nv), c = (int)(r % nv);
+        const T* Wk = W + (long long)kk * v3;
+        const double d = (double)eps[i] + (double)eps[j] + (double)eps[k0 + kk] - (double)eps[no + a] -
+                         (double)eps[no + b] - (double)eps[no + c];
+        const double abc = (double)Wk[r], cba = (double)Wk[c * v2 + (long long)b * nv + a],
+                     acb = (double)Wk[a * v2 + (long long)c * nv + b];
+        A1[idx] = (T)((abc - cba) / d);
+        A2[idx] = (T)((2.0 * abc - acb - cba) / d);
+    }
+}
+
 template <typename T>
 int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_dev, int ntrip, const void* t1,
                      const void* t2, const void* g, const void* fov, int64_t ld_fov, const void* eps, int64_t no,
@@ -204,4 +229,27 @@ extern "C" int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, 
         return triples_energy_t<float>(ctx, w_dev, ijk_dev, ntrip, t1_dev, t2_dev, oovv_dev, fov_dev, ld_fov,
                                        eps_dev, no, nv, et_dev);
     PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
+}
+
+extern "C" int pccb_t3_combine(pccb_ctx* ctx, int dtype, const void* w_dev, int nk, int k0, int i, int j,
+                               const void* eps_dev, int64_t no, int64_t nv, void* a1_dev, void* a2_dev) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, w_dev && eps_dev && a1_dev && a2_dev && nk >= 1 && no > 0 && nv > 0 && i >= 0 && j >= 0 &&
+                          k0 >= 0 && k0 + nk <= no && i < no && j < no,
+                 "pccb_t3_combine: bad arguments");
+    const long long total = (long long)nk * nv * nv * nv;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (dtype == PCCB_F64)
+        t3_combine_kernel<double><<<(unsigned)blocks, 256, 0, ctx->stream>>>((const double*)w_dev, nk, k0, i, j,
+                                                                             (const double*)eps_dev, (int)no, (int)nv,
+                                                                             (double*)a1_dev, (double*)a2_dev);
+    else if (dtype == PCCB_F32)
+        t3_combine_kernel<float><<<(unsigned)blocks, 256, 0, ctx->stream>>>((const float*)w_dev, nk, k0, i, j,
+                                                                            (const float*)eps_dev, (int)no, (int)nv,
+                                                                            (float*)a1_dev, (float*)a2_dev);
+    else
+        PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
+    PCCB_CHECK_LAUNCH(ctx, "t3_combine_kernel");
+    return PCCB_OK;
 }

@@ -40,8 +40,8 @@ class CCSDEngine(object):
         ``blocks['ovvv']`` (full, or (o, vhi-vlo, v, v)); a full ovvv is needed for (T)."""
         self.be = be = backend
         self.model = 'CCSD' if model == 'CCSD(T)' else model
-        if self.model not in ('CCD', 'CC2', 'CCSD'):
-            raise ValueError("engine models: CCD, CC2, CCSD, CCSD(T) (got %r)" % (model,))
+        if self.model not in ('CCD', 'CC2', 'CCSD', 'CC3'):
+            raise ValueError("engine models: CCD, CC2, CCSD, CCSD(T), CC3 (got %r)" % (model,))
         self.no, self.nv, self.dtype = int(no), int(nv), dtype
         self.dcode = _lib.F64 if dtype == torch.float64 else _lib.F32
         self.comm = comm if comm is not None else Comm(None)
@@ -91,6 +91,7 @@ class CCSDEngine(object):
         self.r1, self.r2 = E(o, v), E(o, o, v, v)
         if self.model == 'CC2':      # t1 t1 products and the two factorised intermediates of the CC2 r_T2
             self.T11, self.Yw, self.Xv = E(o, o, v, v), E(o, o, o, vl), E(vl, v, o, v)
+        self.cc3 = None
         self.ladder_events = None    # bench.py: list that receives (start, end) CUDA events per ladder launch
         self._build_plans()
 
@@ -282,6 +283,11 @@ class CCSDEngine(object):
             self.r1.zero_()
         for name in self.builder_order():
             self._run(name)
+        if self.model == 'CC3':      # triples contributions X1, X2 (pycc/ccwfn.py:371-401)
+            if self.cc3 is None:
+                from .cc3_engine import CC3Engine
+                self.cc3 = CC3Engine(self)
+            self.cc3.contribute()
         if symmetrize:
             self.be.pair_symmetrize(self.r2, self.no, self.nv)       # ccwfn.py:621
         return self.r1, self.r2

@@ -57,19 +57,24 @@ def _set(desc, f, val):
 
 
 class TriplesEngine(object):
-    def __init__(self, ccsd_engine):
+    def __init__(self, ccsd_engine, V=None, O=None):
+        """``V`` [i][x][y][e] = Wvvvo[x,y,e,i] and ``O`` [j][k][m][c] = Wovoo[m,c,j,k] default to the bare
+        integrals (views of the stored <mb|ef> / <mn|ie> blocks by the 8-fold symmetry); CC3 passes its
+        T1-dressed intermediates in the same layouts (pycc/ccwfn.py:637-710)."""
         self.eng = eng = ccsd_engine
         self.be = eng.be
         o, v = eng.no, eng.nv
-        if eng.ovvv_full is None:
+        if V is None and eng.ovvv_full is None:
             raise ValueError("(T) needs the full <mb|ef> block on every rank (only this rank's slice was given)")
+        self.V = V if V is not None else eng.ovvv_full
+        self.O = O if O is not None else eng.blk["ooov"]
         self.t2T = self.be.empty((o, o, v, v), eng.dtype)
         self.W = self.be.empty((o, v, v, v), eng.dtype)          # batch over k
         self._plan()
 
     def _tensors(self, i, j, k):
         e = self.eng
-        t2, tT, V, O = e.t2, self.t2T, e.ovvv_full, e.blk["ooov"]
+        t2, tT, V, O = e.t2, self.t2T, self.V, self.O
         d = dict(W=self.W[k], Vi=V[i], Vj=V[j], Vk=V[k],
                  tij=t2[i, j], tik=t2[i, k], tji=t2[j, i], tjk=t2[j, k], tki=t2[k, i], tkj=t2[k, j],
                  ti=t2[i], tj=t2[j], tTj=tT[j], tTk=tT[k],
@@ -100,8 +105,12 @@ class TriplesEngine(object):
         self._keep = base
         self.itemsize = self.eng.t2.element_size()
 
-    def _launch_pair(self, i, j):
-        """W[k] for k = 0..j of the pair (i, j): three batched contractions."""
+    def refresh_t2T(self):
+        o, v = self.eng.no, self.eng.nv
+        self.be.pair_combine(self.t2T, self.eng.t2, 0.0, 1.0, None, None, 0.0, o, v)
+
+    def _launch_pair(self, i, j, nk=None):
+        """W[k] for k = 0..nk-1 (default: 0..j) of the pair (i, j): three batched contractions."""
         for (L, fields, deriv) in self.templates:
             d = _lib.Contraction()
             C.memmove(C.byref(d), C.byref(L.desc), C.sizeof(d))
@@ -115,7 +124,7 @@ class TriplesEngine(object):
                     d.seg[q].a_batch = dk // self.itemsize
                 else:
                     d.seg[q].b_batch = dk // self.itemsize
-            d.batch = j + 1
+            d.batch = (j + 1) if nk is None else nk
             self.be.contract(d)
 
     def pairs(self):

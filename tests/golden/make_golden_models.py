@@ -27,7 +27,7 @@ def run_case(name, no, nv, seed, offdiag):
     ERI = s.full_eri()
     out = dict(no=no, nv=nv, seed=seed)
     t1, t2 = test_amplitudes(s, seed, False)
-    for model in ("CCD", "CC2"):
+    for model in ("CCD", "CC2", "CC3"):
         tag = model.lower()
         w = reference_ccwfn_from_arrays(s.F, ERI, no, model=model)
         o, v, F, L = w.o, w.v, w.H.F, w.H.L
@@ -36,6 +36,13 @@ def run_case(name, no, nv, seed, offdiag):
         out[tag + "_r1"], out[tag + "_r2"] = r1, r2
         out[tag + "_energy"] = w.cc_energy(o, v, F, L, x1, t2)
         out[tag + "_Wmnij"] = w.build_Wmnij(o, v, w.H.ERI, x1, t2)
+        if model == "CC3":
+            W3 = w.build_cc3_Wmnij(o, v, w.H.ERI, x1)
+            out["cc3_Wmnij3"] = W3
+            out["cc3_Wmbij"] = w.build_cc3_Wmbij(o, v, w.H.ERI, x1, W3)
+            out["cc3_Wmnie"] = w.build_cc3_Wmnie(o, v, w.H.ERI, x1)
+            out["cc3_Wamef"] = w.build_cc3_Wamef(o, v, w.H.ERI, x1)
+            out["cc3_Wabei"] = w.build_cc3_Wabei(o, v, w.H.ERI, x1)
         if model == "CC2":
             out[tag + "_Zmbij"] = w.build_Zmbij(o, v, w.H.ERI, x1, t2)
         w = reference_ccwfn_from_arrays(s.F, ERI, no, model=model)

@@ -148,3 +148,12 @@ class InterpBackend(object):
             occ = 2.0 - ((i == j) + (i == k) + (j == k))
             term = ((Y - 2.0 * Z) * Wc + (Z - 2.0 * Y) * Wa + 3.0 * X) * occ / den
             et_dev[t] = float(term[(a >= b) & (b >= c)].sum())
+
+    def t3_combine(self, W, nk, k0, i, j, eps, no, nv, A1, A2):
+        e = eps.double()
+        ev = e[no:]
+        for kk in range(nk):
+            d = e[i] + e[j] + e[k0 + kk] - (ev[:, None, None] + ev[None, :, None] + ev[None, None, :])
+            t3 = W[kk].double() / d
+            A1[kk].copy_((t3 - t3.permute(2, 1, 0)).to(A1.dtype))
+            A2[kk].copy_((2.0 * t3 - t3.permute(0, 2, 1) - t3.permute(2, 1, 0)).to(A2.dtype))

@@ -201,3 +201,25 @@ def test_ccd_cc2_models(name, model):
     assert abs(e - float(z[tag + "_solve_ecc"])) < E_TOL
     assert np.abs(w.t1.cpu().numpy() - z[tag + "_solve_t1"]).max() < T_TOL
     assert np.abs(w.t2.cpu().numpy() - z[tag + "_solve_t2"]).max() < T_TOL
+
+
+@pytest.mark.parametrize("name", ["o4v8", "o5v19_offdiag", "o6v13"])
+def test_cc3_model(name):
+    """CC3 (per-iteration triples loop with T1-dressed integrals) on the GPU against the reference's vectors."""
+    import os
+    from tests.conftest import GOLDEN_DIR, Golden
+    g = Golden(name)
+    z = np.load(os.path.join(GOLDEN_DIR, "models", name + ".npz"))
+    w = _wfn(g.F, g.blocks, g.no, "CC3")
+    r1, r2 = w.residuals(g.F, g["gen_t1"], g["gen_t2"])
+    assert np.abs(r1.cpu().numpy() - z["cc3_r1"]).max() < 1e-12
+    assert np.abs(r2.cpu().numpy() - z["cc3_r2"]).max() < 1e-12
+    c = w.engine.cc3
+    assert np.abs(c.Wv.permute(1, 2, 3, 0).cpu().numpy() - z["cc3_Wabei"]).max() < 1e-12
+    w = _wfn(g.F, g.blocks, g.no, "CC3")
+    with contextlib.redirect_stdout(io.StringIO()):
+        e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+    assert len(w.iteration_log) == int(z["cc3_solve_niter"])
+    assert abs(e - float(z["cc3_solve_ecc"])) < E_TOL
+    assert np.abs(w.t1.cpu().numpy() - z["cc3_solve_t1"]).max() < T_TOL
+    assert np.abs(w.t2.cpu().numpy() - z["cc3_solve_t2"]).max() < T_TOL

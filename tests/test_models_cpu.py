@@ -47,3 +47,31 @@ def test_model_residuals_and_solve(name, model):
     assert abs(e - float(z[tag + "_solve_ecc"])) < 1e-12
     assert np.abs(w.t1.numpy() - z[tag + "_solve_t1"]).max() < 1e-11
     assert np.abs(w.t2.numpy() - z[tag + "_solve_t2"]).max() < 1e-11
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_cc3_intermediates_and_residuals(name):
+    """CC3: T1-dressed intermediates (pycc/ccwfn.py:625-710) and the triples contributions to r1 / r2."""
+    g, z = load(name)
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CC3", _backend=InterpBackend())
+    r1, r2 = w.residuals(g.F, g["gen_t1"], g["gen_t2"])
+    c = w.engine.cc3
+    assert np.abs(c.Wmnij3.numpy() - z["cc3_Wmnij3"]).max() < 1e-12
+    assert np.abs(c.Wo.permute(2, 3, 0, 1).numpy() - z["cc3_Wmbij"]).max() < 1e-12          # Wo[ijmb] = Wmbij[mbij]
+    assert np.abs(c.Wmnie3.numpy() - z["cc3_Wmnie"]).max() < 1e-12
+    assert np.abs(c.Wk.permute(1, 0, 2, 3).numpy() - z["cc3_Wamef"]).max() < 1e-12          # Wk[maef] = Wamef[amef]
+    assert np.abs(c.Wv.permute(1, 2, 3, 0).numpy() - z["cc3_Wabei"]).max() < 1e-12          # Wv[iabe] = Wabei[abei]
+    assert np.abs(r1.numpy() - z["cc3_r1"]).max() < 1e-12
+    assert np.abs(r2.numpy() - z["cc3_r2"]).max() < 1e-12
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
+def test_cc3_solve(name):
+    g, z = load(name)
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CC3", _backend=InterpBackend())
+        e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+    assert len(w.iteration_log) == int(z["cc3_solve_niter"])
+    assert abs(e - float(z["cc3_solve_ecc"])) < 1e-12
+    assert np.abs(w.t2.numpy() - z["cc3_solve_t2"]).max() < 1e-11

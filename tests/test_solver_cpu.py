@@ -87,8 +87,7 @@ def test_builder_api(golden):
 def test_kwargs_validation(golden):
     g = golden
     for kw, msg in ((dict(model="CCSDT"), "not an allowed CC model"), (dict(local="XYZ"), "not an allowed local-CC"),
-                    (dict(precision="HP"), "not an allowed precision"), (dict(device="TPU"), "not an allowed device"),
-                    (dict(model="CC3"), "not available in the B200 engine")):
+                    (dict(precision="HP"), "not an allowed precision"), (dict(device="TPU"), "not an allowed device")):
         with pytest.raises(Exception, match=msg):
             with contextlib.redirect_stdout(io.StringIO()):
                 pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, _backend=InterpBackend(), **kw)
