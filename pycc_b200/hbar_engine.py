@@ -1,0 +1,302 @@
+"""
+HBAR and Lambda engines: the one- and two-body blocks of the
+similarity-transformed Hamiltonian (pycc/cchbar.py:90-375) and the Lambda residuals
+(pycc/cclambda.py:450-543), planned once into ``pccb_contract`` launches over the six stored ERI
+blocks exactly like the CCSD builders of ``engine.py``.
+
+The reference slices ERI / L into sixteen differently ordered blocks; here every one of them is an
+index relabelling of the six stored blocks by the 8-fold symmetry of real integrals
+(<pq|rs> = <qp|sr> = <rs|pq> = <rq|ps>):
+
+    <am|ef> = ovvv[mafe]   <mn|ej> = ooov[nmje]   <mb|ej> = oovv[mjeb]   <ab|ei> = ovvv[ieba]
+    <am|ei> = ovov[maie]   <bm|ie> = oovv[mieb]   <mb|ij> = ooov[ijmb]
+    L<am|ef> = 2 ovvv[mafe] - ovvv[maef]          L<mn|ie> = Looov[mnie]   L<mn|ef> = Loovv[mnef]
+
+HBAR blocks are held in the reference's index order (Hvvvo[a,b,e,i], ...), except Hvvvv, which is
+stored transposed, HvT[a,b,e,f] = Hvvvv[e,f,a,b], so that the o^2 v^4 Lambda ladder
+``l2[ijef] Hvvvv[efab]`` (cclambda.py:528) reads it with the contracted pair contiguous, like the
+CCSD ladder reads <ab|ef>.  ``Hvvvv`` is exposed as the permuted view.
+
+CCD is the CCSD algebra with t1 = l1 = 0 (every reference CCD branch is the CCSD branch with its
+t1 terms dropped: cchbar.py:92-96, 108-113, ..., cclambda.py:462-466, 497-512).  CC2 has its own
+statements (cchbar.py:163, 186, 241, 263, 285-294, 337-346; cclambda.py:481-486, 522-524).
+Single GPU (one rank) for now.
+"""
+import re
+
+import torch
+
+from .dsl import TRef, plan
+
+
+class HbarEngine(object):
+    ORDER = ("Hov", "Hvv", "Hoo", "Hoooo", "Hvvvv", "Hvovv", "Hooov", "Hovvo", "Hovov", "X", "Hvvvo", "Hovoo")
+
+    STATEMENTS = {
+        # build_Hov (cchbar.py:90-103)
+        "Hov": ["Hov[me] = Fov[me] + t1[nf]*Loovv[mnef]"],
+        # build_Hvv (:106-123)
+        "Hvv": ["Hvv[ae] = Fvv[ae] - t1[ma]*Fov[me] - tau[mnfa]*Loovv[mnfe]",
+                "Hvv[ae] += 2.0*t1[mf]*ovvv[mafe] - t1[mf]*ovvv[maef]"],
+        # build_Hoo (:126-143)
+        "Hoo": ["Hoo[mi] = Foo[mi] + Fov[me]*t1[ie] + Loovv[mnef]*tau[inef]",
+                "Hoo[mi] += t1[ne]*Looov[mnie]"],
+        # build_Hoooo (:146-167)
+        "Hoooo": ["Hoooo[mnij] = oooo[mnij] + oovv[mnef]*tau[ijef]",
+                  "Hoooo[mnij] += ooov[mnie]*t1[je]",
+                  "Hoooo[mnij] += ooov[nmje]*t1[ie]"],
+        # build_Hvvvv (:170-191), stored as HvT[abef] = Hvvvv[efab]; <ef|ab> = <ab|ef>
+        "Hvvvv": ["HvT[abef] = vvvv[abef] + oovv[mnab]*tau[mnef]",
+                  "HvT[abef] -= ovvv[meba]*t1[mf]",
+                  "HvT[abef] -= ovvv[mfab]*t1[me]"],
+        # build_Hvovv (:194-208)
+        "Hvovv": ["Hvovv[amef] = ovvv[mafe] - t1[na]*oovv[nmef]"],
+        # build_Hooov (:211-225)
+        "Hooov": ["Hooov[mnie] = ooov[mnie] + oovv[nmef]*t1[if]"],
+        # build_Hovvo (:228-249)
+        "Hovvo": ["Hovvo[mbej] = oovv[mjeb] - oovv[mnef]*tau[jnfb] + Loovv[mnef]*t2[njfb]",
+                  "Hovvo[mbej] += ovvv[mbef]*t1[jf]",
+                  "Hovvo[mbej] -= t1[nb]*ooov[nmje]"],
+        # build_Hovov (:252-269)
+        "Hovov": ["Hovov[mbje] = ovov[mbje] - oovv[nmef]*tau[jnfb]",
+                  "Hovov[mbje] += ovvv[mbfe]*t1[jf]",
+                  "Hovov[mbje] -= t1[nb]*ooov[mnje]"],
+        # the two o^2 v^2 temporaries of build_Hvvvo (:303-316), which build_Hovoo forms again (:358-370)
+        "X": ["Xa[mbie] = ovov[mbie] - oovv[mnfe]*t2[infb]",
+              "Xb[bmje] = oovv[mjeb] - oovv[mnef]*t2[jnfb] + Loovv[mnef]*t2[njfb]"],
+        # build_Hvvvo (:272-321)
+        "Hvvvo": ["Hvvvo[abei] = ovvv[ieba] - t2[miab]*Hov[me]",
+                  "Hvvvo[abei] += HvT[efab]*t1[if]",
+                  "Hvvvo[abei] += tau[mnab]*ooov[nmie]",
+                  "Hvvvo[abei] -= ovvv[mbef]*t2[imfa]",
+                  "Hvvvo[abei] -= ovvv[mafe]*t2[imfb]",
+                  "Hvvvo[abei] += 2.0*ovvv[mafe]*t2[mifb] - ovvv[maef]*t2[mifb]",
+                  "Hvvvo[abei] -= t1[mb]*Xa[maie]",
+                  "Hvvvo[abei] -= t1[ma]*Xb[bmie]"],
+        # build_Hovoo (:324-375)
+        "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + Hov[me]*t2[ijeb]",
+                  "Hovoo[mbij] -= t1[nb]*Hoooo[mnij]",
+                  "Hovoo[mbij] += ovvv[mbef]*tau[ijef]",
+                  "Hovoo[mbij] -= t2[ineb]*ooov[nmje]",
+                  "Hovoo[mbij] -= t2[jneb]*ooov[mnie]",
+                  "Hovoo[mbij] += t2[njeb]*Looov[mnie]",
+                  "Hovoo[mbij] += Xa[mbie]*t1[je]",
+                  "Hovoo[mbij] += Xb[bmje]*t1[ie]"],
+    }
+
+    # CC2 branches; T11[ijab] = t1[ia] t1[jb]
+    STATEMENTS_CC2 = {
+        "X": [],
+        "Hoooo": ["Hoooo[mnij] = oooo[mnij] + oovv[mnef]*T11[ijef]",
+                  "Hoooo[mnij] += ooov[mnie]*t1[je]",
+                  "Hoooo[mnij] += ooov[nmje]*t1[ie]"],
+        "Hvvvv": ["HvT[abef] = vvvv[abef] + oovv[mnab]*T11[mnef]",
+                  "HvT[abef] -= ovvv[meba]*t1[mf]",
+                  "HvT[abef] -= ovvv[mfab]*t1[me]"],
+        "Hovvo": ["Hovvo[mbej] = oovv[mjeb] + ovvv[mbef]*t1[jf]",
+                  "Hovvo[mbej] -= t1[nb]*ooov[nmje]"],
+        "Hovov": ["Hovov[mbje] = ovov[mbje] + ovvv[mbfe]*t1[jf]",
+                  "Hovov[mbje] -= t1[nb]*ooov[mnje]"],
+        "Hvvvo": ["Hvvvo[abei] = ovvv[ieba] - t2[miab]*Fov[me]",
+                  "Hvvvo[abei] += HvT[efab]*t1[if]",
+                  "Hvvvo[abei] += T11[mnab]*ooov[nmie]",
+                  "Hvvvo[abei] -= t1[mb]*ovov[maie]",
+                  "Hvvvo[abei] -= t1[ma]*oovv[mieb]"],
+        "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + Fov[me]*t2[ijeb]",
+                  "Hovoo[mbij] -= t1[nb]*Hoooo[mnij]",
+                  "Hovoo[mbij] += ovvv[mbef]*T11[ijef]",
+                  "Hovoo[mbij] += ovov[mbie]*t1[je]",
+                  "Hovoo[mbij] += oovv[mjeb]*t1[ie]"],
+    }
+
+    def __init__(self, eng):
+        if eng.comm.world > 1:
+            raise ValueError("HBAR / Lambda run on one GPU for now")
+        if eng.ovvv_full is None or eng.vvvv_loc.shape[0] != eng.nv:
+            raise ValueError("HBAR needs the full <mb|ef> and <ab|ef> blocks")
+        if eng.model not in ('CCD', 'CC2', 'CCSD'):
+            raise ValueError("HBAR / Lambda: models CCD, CC2, CCSD (got %r)" % (eng.model,))
+        self.eng, self.be = eng, eng.be
+        o, v, dt = eng.no, eng.nv, eng.dtype
+        E = lambda *s: self.be.zeros(s, dt)
+        self.Hov, self.Hvv, self.Hoo = E(o, v), E(v, v), E(o, o)
+        self.Hoooo, self.HvT = E(o, o, o, o), E(v, v, v, v)
+        self.Hvovv, self.Hooov = E(v, o, v, v), E(o, o, o, v)
+        self.Hovvo, self.Hovov = E(o, v, v, o), E(o, v, o, v)
+        self.Hvvvo, self.Hovoo = E(v, v, v, o), E(o, v, o, o)
+        self.Xa, self.Xb = E(o, v, o, v), E(v, o, o, v)
+        if eng.model == 'CC2':
+            self.T11 = eng.T11
+        st = dict(self.STATEMENTS)
+        if eng.model == 'CC2':
+            st.update(self.STATEMENTS_CC2)
+        T = self.tensors()
+        self.plans = {}
+        for name in self.ORDER:
+            self.plans[name] = []
+            for s in st[name]:
+                names = set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s))
+                self.plans[name] += plan(s, {k: T[k] for k in names}, eng.dcode)
+
+    def tensors(self):
+        eng = self.eng
+        o = eng.no
+        b, F = eng.blk, eng.F
+        d = dict(oooo=b["oooo"], ooov=b["ooov"], oovv=b["oovv"], ovov=b["ovov"], ovvv=eng.ovvv_full, vvvv=eng.vvvv_loc,
+                 Foo=F[:o, :o], Fov=F[:o, o:], Fvv=F[o:, o:], Loovv=eng.Loovv, Looov=eng.Looov,
+                 t1=eng.t1, t2=eng.t2, tau=eng.tau,
+                 Hov=self.Hov, Hvv=self.Hvv, Hoo=self.Hoo, Hoooo=self.Hoooo, HvT=self.HvT, Hvovv=self.Hvovv,
+                 Hooov=self.Hooov, Hovvo=self.Hovvo, Hovov=self.Hovov, Hvvvo=self.Hvvvo, Hovoo=self.Hovoo,
+                 Xa=self.Xa, Xb=self.Xb)
+        if eng.model == 'CC2':
+            d["T11"] = eng.T11
+        return {k: TRef.of(t, k) for k, t in d.items()}
+
+    @property
+    def Hvvvv(self):
+        return self.HvT.permute(2, 3, 0, 1)
+
+    DEPS = dict(Hvvvo=("Hov", "Hvvvv", "X"), Hovoo=("Hov", "Hoooo", "X"))
+
+    def build(self, only=None):
+        """All blocks, in the reference's order (cchbar.py:73-83), or just the builder ``only`` and
+        what it depends on, for the amplitudes and Fock matrix currently held by the CCSD engine."""
+        eng = self.eng
+        self.be.bind_stream()
+        if eng.model == 'CCD':
+            eng.t1.zero_()
+        eng.prepare()
+        todo = self.ORDER if only is None else [n for n in self.ORDER if n == only or n in self.DEPS.get(only, ())]
+        for name in todo:
+            for L in self.plans[name]:
+                self.be.contract(L.desc)
+
+    def flops_issued(self):
+        tot = 0
+        for ls in self.plans.values():
+            for L in ls:
+                d = L.desc
+                tot += sum(2 * d.M * d.N * d.batch * d.seg[q].K for q in range(d.nseg))
+        return tot
+
+
+class LambdaEngine(object):
+    """Lambda residuals r_L1 / r_L2 (pycc/cclambda.py:450-543) for the HBAR held by ``hbar``."""
+
+    STATEMENTS = {
+        # build_Goo / build_Gvv (cclambda.py:450-457)
+        "G": ["Goo[mi] = t2[mjab]*l2[ijab]",
+              "Gvv[ae] = -1.0*t2[ijeb]*l2[ijab]"],
+        # r_L1 (:460-493)
+        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hvvvo[efam] - l2[mnae]*Hovoo[iemn]",
+                 "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
+                 "r1[ia] += Gvv[ef]*Hvovv[eiaf] - 2.0*Gvv[ef]*Hvovv[eifa]",
+                 "r1[ia] += Goo[mn]*Hooov[imna] - 2.0*Goo[mn]*Hooov[mina]"],
+        # r_L2 (:495-543), before the final r + r^T; Hvvvv[efab] = HvT[abef]
+        "r_L2": ["r2[ijab] = Loovv[ijab] + 2.0*l1[ia]*Hov[jb] - l1[ja]*Hov[ib]",
+                 "r2[ijab] += 2.0*l1[ie]*Hvovv[ejab] - l1[ie]*Hvovv[ejba]",
+                 "r2[ijab] += l1[mb]*Hooov[ijma] - 2.0*l1[mb]*Hooov[jima]",
+                 "r2[ijab] += l2[ijeb]*Hvv[ea] - l2[mjab]*Hoo[im]",
+                 "r2[ijab] += 0.5*l2[mnab]*Hoooo[ijmn]",
+                 "r2[ijab] += 0.5*l2[ijef]*HvT[abef]",
+                 "r2[ijab] += 2.0*l2[mjeb]*Hovvo[ieam] - l2[mjeb]*Hovov[iema]",
+                 "r2[ijab] -= l2[mibe]*Hovov[jema]",
+                 "r2[ijab] -= l2[mieb]*Hovvo[jeam]",
+                 "r2[ijab] += Gvv[ae]*Loovv[ijeb] - Goo[mi]*Loovv[mjab]"],
+    }
+
+    # CC2 (:481-486, 522-524): Goo / Gvv are built but not used; Fa / Fi are the t1-dressed Fock blocks
+    STATEMENTS_CC2 = {
+        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hvvvo[efam] - l2[mnae]*Hovoo[iemn]",
+                 "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
+                 "Ya[nf] = l1[me]*t2[nmfe]",
+                 "Yb[nf] = l1[me]*tau[mnfe]",
+                 "r1[ia] += 2.0*Ya[nf]*Loovv[inaf] - 2.0*Yb[nf]*oovv[inaf] + Yb[nf]*oovv[infa]"],
+        "r_L2": ["r2[ijab] = Loovv[ijab] + 2.0*l1[ia]*Hov[jb] - l1[ja]*Hov[ib]",
+                 "r2[ijab] += 2.0*l1[ie]*Hvovv[ejab] - l1[ie]*Hvovv[ejba]",
+                 "r2[ijab] += l1[mb]*Hooov[ijma] - 2.0*l1[mb]*Hooov[jima]",
+                 "Fa[ea] = Fvv[ea] - Fov[ma]*t1[me]",      # (F_vv - F_ov^T t1)[e,a], index order as the reference uses it
+                 "Fi[im] = Foo[im] + t1[me]*Fov[ie]",
+                 "r2[ijab] += l2[ijeb]*Fa[ea] - l2[mjab]*Fi[im]"],
+    }
+
+    def __init__(self, hbar):
+        self.hbar, self.eng, self.be = hbar, hbar.eng, hbar.be
+        eng = self.eng
+        o, v, dt = eng.no, eng.nv, eng.dtype
+        E = lambda *s: self.be.zeros(s, dt)
+        self.l1, self.l2 = E(o, v), E(o, o, v, v)
+        self.r1, self.r2 = E(o, v), E(o, o, v, v)
+        self.Goo, self.Gvv = E(o, o), E(v, v)
+        self.Ya, self.Yb, self.Fa, self.Fi = E(o, v), E(o, v), E(v, v), E(o, o)
+        st = dict(self.STATEMENTS)
+        if eng.model == 'CC2':
+            st.update(self.STATEMENTS_CC2)
+        T = hbar.tensors()
+        for k in ("l1", "l2", "r1", "r2", "Goo", "Gvv", "Ya", "Yb", "Fa", "Fi"):
+            T[k] = TRef.of(getattr(self, k), k)
+        self.plans = {}
+        for name, stmts in st.items():
+            self.plans[name] = []
+            for s in stmts:
+                names = set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s))
+                for L in plan(s, {k: T[k] for k in names}, eng.dcode):
+                    L.is_ladder = "HvT[" in s
+                    self.plans[name].append(L)
+        self.ladder_events = None
+
+    def guess(self):
+        """l1 = 2 t1, l2 = 2 (2 t2 - t2^T) (cclambda.py:57-58)."""
+        eng = self.eng
+        self.be.bind_stream()
+        self.be.axpby(self.l1, 2.0, eng.t1)
+        self.be.pair_combine(self.l2, eng.t2, 4.0, -2.0, None, None, 0.0, eng.no, eng.nv)
+
+    def _launch(self, name):
+        for L in self.plans[name]:
+            if self.ladder_events is not None and L.is_ladder:
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                self.be.contract(L.desc)
+                e1.record()
+                self.ladder_events.append((e0, e1))
+            else:
+                self.be.contract(L.desc)
+
+    def run(self, name):
+        """One of 'G', 'r_L1', 'r_L2' (the latter two read Goo / Gvv)."""
+        self.be.bind_stream()
+        if self.eng.model == 'CCD':
+            self.l1.zero_()
+        if name == "r_L1" and self.eng.model == 'CCD':
+            self.r1.zero_()          # cclambda.py:462-466
+            return
+        self._launch(name)
+
+    def residuals(self, symmetrize=True):
+        """r1, r2 for the amplitudes in self.l1 / self.l2 (the loop body of cclambda.py:146-151)."""
+        for name in ("G", "r_L1", "r_L2"):
+            self.run(name)
+        if symmetrize:
+            self.be.pair_symmetrize(self.r2, self.eng.no, self.eng.nv)     # :542
+        return self.r1, self.r2
+
+    def pseudoenergy(self):
+        """1/2 <ij|ab> l2[ijab] (cclambda.py:579-581)."""
+        self.be.bind_stream()
+        return 0.5 * self.be.dot(self.eng.blk["oovv"], self.l2)
+
+    def update(self, symmetrize_on_the_fly):
+        """l += r/D; returns the squared increment norm (cclambda.py:244-247)."""
+        eng = self.eng
+        self.be.bind_stream()
+        return self.be.update_amplitudes(self.l1, self.l2, self.r1, self.r2, eng.eps, eng.no, eng.nv,
+                                         symmetrize_on_the_fly)
+
+    def flops_issued(self):
+        tot = 0
+        for ls in self.plans.values():
+            for L in ls:
+                d = L.desc
+                tot += sum(2 * d.M * d.N * d.batch * d.seg[q].K for q in range(d.nseg))
+        return tot

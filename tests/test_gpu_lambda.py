@@ -1,0 +1,67 @@
+"""HBAR and Lambda on the B200 through the C ABI, against reference-generated vectors
+(tests/golden/lambda/, made by tests/golden/make_golden_lambda.py), plus a size-independent
+property at a shape no CPU reference covers."""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+import torch
+
+from tests import lambda_checks as lc
+import pycc_b200
+
+pytestmark = pytest.mark.gpu
+
+
+def make_wfn(g, model):
+    return pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model=model)
+
+
+@pytest.mark.parametrize("model", lc.MODELS)
+@pytest.mark.parametrize("name", lc.CASES)
+def test_hbar_blocks_and_lambda_residuals(name, model):
+    lc.check_blocks_and_residuals(make_wfn, name, model)
+
+
+@pytest.mark.parametrize("model", lc.MODELS)
+@pytest.mark.parametrize("name", lc.CASES)
+def test_solve_lambda(name, model):
+    lc.check_solve(make_wfn, name, model, chain=False, e_tol=1e-10)
+
+
+@pytest.mark.parametrize("name", ["o4v8", "o5v19_offdiag"])
+def test_solve_chain(name):
+    lc.check_solve(make_wfn, name, "CCSD", chain=True, e_tol=1e-10)
+
+
+def test_lambda_linearity_mid_size():
+    """The Lambda residual is affine in (l1, l2): r(a x + (1-a) y) = a r(x) + (1-a) r(y), and the
+    tensor-core path agrees with the library's scalar contraction path, at (o, v) = (10, 72)."""
+    from pycc_b200.synthetic import SyntheticSystem
+    s = SyntheticSystem(10, 72, seed=5)
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(s.F, s.blocks, s.no)
+        for it in range(3):
+            w._iteration(None, it + 1, 1, extrapolate=False)
+        hb = pycc_b200.cchbar(w)
+        lam = pycc_b200.cclambda(w, hb)
+    gen = torch.Generator(device="cpu").manual_seed(3)
+    x1, y1 = [torch.randn(lam.l1.shape, generator=gen, dtype=torch.float64).cuda() * 0.1 for _ in range(2)]
+    x2, y2 = [torch.randn(lam.l2.shape, generator=gen, dtype=torch.float64).cuda() * 0.1 for _ in range(2)]
+    t1, t2 = w.t1.clone(), w.t2.clone()
+    a = 0.3
+    rx = lam.residuals(w.H.F, t1, t2, x1, x2)
+    ry = lam.residuals(w.H.F, t1, t2, y1, y2)
+    rz = lam.residuals(w.H.F, t1, t2, a * x1 + (1 - a) * y1, a * x2 + (1 - a) * y2)
+    for k in range(2):
+        ref = a * rx[k] + (1 - a) * ry[k]
+        assert (rz[k] - ref).abs().max().item() < 1e-11
+    w.backend.use_naive_contract(True)
+    try:
+        hb.engine.build()
+        rn = lam.residuals(w.H.F, t1, t2, x1, x2)
+    finally:
+        w.backend.use_naive_contract(False)
+    for k in range(2):
+        assert (rn[k] - rx[k]).abs().max().item() < 1e-11
