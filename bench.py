@@ -49,6 +49,9 @@ def parse_args():
     ap.add_argument("--no-triples", action="store_true", help="skip the (T) timing")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--path", default="ccsd", choices=["ccsd", "lambda"],
+                    help="ccsd: the north-star CCSD iteration (default); lambda: HBAR build + Lambda iteration "
+                         "(SURVEY.md 8(f) rank 2; one GPU)")
     return ap.parse_args()
 
 
@@ -419,10 +422,168 @@ def run_reference(args):
     print(json.dumps(out), flush=True)
 
 
+def run_lambda(args):
+    """HBAR build + Lambda iterations (pycc/cchbar.py, pycc/cclambda.py:141-260) on one GPU.  A step is
+    one pass of the solve_lambda loop body: Goo/Gvv, r_L1, r_L2, l += r/D with the norm, pseudoenergy,
+    DIIS push + extrapolation.  Same JSON layout as the CCSD line; the roofline entry is the Lambda
+    ladder r2 += 1/2 l2[ijef] Hvvvv[efab]; cpu_baseline is the NumPy oracle (oracle/lambda_oracle.py)."""
+    import numpy as np
+    import torch
+    import contextlib
+    import io
+    o, v = [int(x) for x in args.workload.split(",")]
+    if int(os.environ.get("WORLD_SIZE", "1")) != 1:
+        raise SystemExit("bench.py --path lambda runs on one GPU")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device - the pycc_b200 engine has no CPU fallback")
+    torch.cuda.set_device(0)
+    dev = torch.device("cuda", 0)
+    import pycc_b200
+    from pycc_b200.synthetic import device_blocks
+    from pycc_b200.utils import helper_diis
+    B, F, scale = make_factor(o, v, args.seed)
+    blocks = device_blocks(B, o, dev)
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD")
+        d0 = helper_diis(w.t1, w.t2, 8, "DP", backend=w.backend)
+        for it in range(6):                      # amplitudes a few DIIS iterations from the MP2 guess
+            w._iteration(d0, it + 1, 1)
+        del d0
+        hb = pycc_b200.cchbar(w)
+        lam = pycc_b200.cclambda(w, hb)
+    be, leng = w.backend, lam.engine
+
+    def sync():
+        torch.cuda.synchronize()
+
+    # HBAR build, timed on its own (once per Lambda solve)
+    sync()
+    h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h0.record()
+    for _ in range(3):
+        hb.engine.build()
+    h1.record()
+    sync()
+    hbar_ms = h0.elapsed_time(h1) / 3
+
+    diis = helper_diis(lam.l1, lam.l2, 8, "DP", backend=be)
+
+    def step(n):
+        lecc, rms = lam._iteration()
+        diis.add_error_vector(lam.l1, lam.l2)
+        lam.l1, lam.l2 = diis.extrapolate(lam.l1, lam.l2)
+        return lecc, rms
+
+    niter = 0
+    for _ in range(max(args.warmup, 0)):
+        niter += 1
+        step(niter)
+    clocks = ClockSampler(0)
+    sync()
+    clocks.start()
+    launches0 = be.launch_count()
+    leng.ladder_events = []
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    last = None
+    for _ in range(args.steps):
+        niter += 1
+        last = step(niter)
+    e1.record()
+    sync()
+    ms_step = e0.elapsed_time(e1) / max(args.steps, 1)
+    clk = clocks.stop()
+    launches = be.launch_count() - launches0
+    ladder_ms = [a.elapsed_time(b) for a, b in leng.ladder_events]
+    leng.ladder_events = None
+    peak, peak_src = dmma_peak()
+    lad_flops = 2.0 * o * o * float(v)**4
+    lad_ms = sum(ladder_ms) / max(len(ladder_ms), 1)
+    lad_tf = lad_flops / (lad_ms * 1e-3) / 1e12 if lad_ms > 0 else 0.0
+    roofline = {"bound": "tensor", "kernel": "contract_f64_tma_kernel (Lambda ladder r2 += 1/2 l2 Hvvvv)",
+                "achieved": round(lad_tf, 3), "peak": peak, "unit": "TFLOP/s", "frac": round(lad_tf / peak, 4),
+                "traffic": None, "launch_ms": round(lad_ms, 4), "flops_per_launch": lad_flops, "peak_source": peak_src}
+
+    e2e = None
+    if not args.no_e2e:
+        l1_pin, l2_pin = lam.l1.detach().cpu().pin_memory(), lam.l2.detach().cpu().pin_memory()
+        nb = (l1_pin.numel() + l2_pin.numel()) * 8
+
+        def e2e_step(n):
+            leng.l1.copy_(l1_pin, non_blocking=True)
+            leng.l2.copy_(l2_pin, non_blocking=True)
+            lecc, rms = step(n)
+            l1_pin.copy_(leng.l1, non_blocking=True)
+            l2_pin.copy_(leng.l2, non_blocking=True)
+            torch.cuda.current_stream().synchronize()
+            return lecc
+
+        niter += 1
+        e2e_step(niter)
+        sync()
+        ksteps = max(min(args.steps, 5), 1)
+        t0 = time.perf_counter()
+        for _ in range(ksteps):
+            niter += 1
+            e2e_step(niter)
+        sync()
+        e2e = {"value": round((time.perf_counter() - t0) / ksteps, 6), "unit": "s/iteration",
+               "h2d_bytes_per_step": nb, "d2h_bytes_per_step": nb + 16, "steps": ksteps}
+
+    cpu_baseline, parity = None, None
+    if not args.no_cpu_baseline:
+        from oracle import ccsd_oracle as oc
+        from oracle import lambda_oracle as ol
+        cores = set_host_threads()
+        warm_numpy()
+        blk = oc.Blocks({k: t.double().cpu().numpy() for k, t in w.H.blocks.items()})
+        t1h, t2h = w.t1.cpu().numpy(), w.t2.cpu().numpy()
+        l1h = 1.1 * lam.l1.cpu().numpy() + 0.01
+        l2h = 1.1 * lam.l2.cpu().numpy()
+        r1g, r2g = lam.residuals(F, t1h, t2h, l1h, l2h)          # rebuilds HBAR on the GPU as well
+        t0 = time.perf_counter()
+        H = ol.build_hbar(F, blk, t1h, t2h)
+        cpu_hbar = time.perf_counter() - t0
+        t0 = time.perf_counter()
+        r1c, r2c = ol.lambda_residuals(blk, H, t2h, l1h, l2h)
+        Dia, Dijab = oc.denominators(F, o)
+        l2n = l2h + r2c / Dijab
+        ol.pseudoenergy(blk, l2n)
+        cpu_s = time.perf_counter() - t0
+        parity = {"max_abs_dr1": float(np.abs(r1g.cpu().numpy() - r1c).max()),
+                  "max_abs_dr2": float(np.abs(r2g.cpu().numpy() - r2c).max()), "max_abs_r2": float(np.abs(r2c).max()),
+                  "max_abs_dHvvvo": float(np.abs(hb.Hvvvo.cpu().numpy() - H["Hvvvo"]).max()),
+                  "checked": "HBAR + Lambda residuals of the timed engine vs the oracle on the same perturbed "
+                             "(l1, l2), o=%d v=%d" % (o, v)}
+        cpu_baseline = {"value": round(cpu_s, 4), "unit": "s/iteration", "cores": cores, "kind": "port",
+                        "hbar_seconds": round(cpu_hbar, 3),
+                        "sample": "1 Lambda iteration (Goo/Gvv, r_L1, r_L2, update, pseudoenergy) of the NumPy oracle "
+                                  "(port of pycc/cclambda.py:450-543) at o=%d v=%d; HBAR build timed separately" % (o, v)}
+
+    fi = float(leng.flops_issued())
+    out = {"metric": "lambda_seconds_per_iteration", "value": round(ms_step * 1e-3, 6), "unit": "s/iteration",
+           "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+           "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
+           "data": "synthetic (seeded factorised 8-fold-symmetric ERIs, diagonal Fock; SURVEY.md 8(d))",
+           "config": {"workload": "RHF-CCSD Lambda iteration o=%d v=%d FP64" % (o, v), "o": o, "v": v,
+                      "parallelism": "1 GPU", "l2": "inputs larger than L2 (Hvvvv %.2f GB)" % (v**4 * 8 / 1e9),
+                      "seed": args.seed, "eri_scale": round(scale, 6), "diis": 8},
+           "flops_issued": fi, "tflops_issued": round(fi / (ms_step * 1e-3) / 1e12, 3),
+           "tflops_issued_frac_of_peak": round(fi / (ms_step * 1e-3) / 1e12 / peak, 4),
+           "hbar": {"build_ms": round(hbar_ms, 3), "flops_issued": float(hb.engine.flops_issued()),
+                    "tflops_issued": round(hb.engine.flops_issued() / (hbar_ms * 1e-3) / 1e12, 3)},
+           "pseudoenergy": last[0] if last else None, "rms": last[1] if last else None,
+           "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "e2e": e2e,
+           "cpu_baseline": cpu_baseline, "parity": parity}
+    print(json.dumps(out), flush=True)
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.path == "lambda":
+        run_lambda(args)
     else:
         run_ours(args)
 

@@ -63,6 +63,7 @@ struct DSeg {
 struct DParams {
     unsigned M, N;
     int nseg, total_kt, splits, nz;    // nz = batch * splits (grid.z of the non-persistent kernel)
+    int kchunk;                        // > 0: split-K deals chunks of kchunk k-tiles round-robin (small-tile kernel only)
     DSeg seg[PCCB_MAX_SEGMENTS];
     double* C;
     DIdx cm, cn;
@@ -206,9 +207,20 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
     const int wm = warp >> 2, wn = warp & 3;
     const unsigned m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
     const int batch = blockIdx.z / p.splits, split = blockIdx.z % p.splits;
+    // split-K work assignment.  Contiguous k ranges by default; with p.kchunk the k-tiles are dealt
+    // round-robin in chunks, so that at any moment all CTAs read the same narrow k window of every
+    // operand row (a skinny output with a huge K otherwise has #CTAs x #rows far-apart streams in
+    // flight, which thrashes the TLB and the DRAM pages).
+    const int kchunk = p.kchunk;
     const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
-    const int kt_hi = (int)(((long long)p.total_kt * (split + 1)) / p.splits);
-    const int nkt = kt_hi - kt_lo;
+    int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
+    if (kchunk) {
+        const int nch = (p.total_kt + kchunk - 1) / kchunk;
+        const int mine = split < nch ? (nch - split + p.splits - 1) / p.splits : 0;
+        nkt = mine * kchunk;
+        if (mine > 0 && split + (mine - 1) * p.splits == nch - 1) nkt -= nch * kchunk - p.total_kt;
+    }
+    auto gkt = [&](int l) { return kchunk ? ((l / kchunk) * p.splits + split) * kchunk + (l % kchunk) : kt_lo + l; };
     const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
 
     const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
@@ -272,9 +284,9 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
 #pragma unroll 1
     for (int s = 0; s < DIST; ++s) {
         if (s < nkt) {
-            const int sg = seg_of(kt_lo + s);
+            const int sg = seg_of(gkt(s));
             if (sg != cur_seg) set_rows(sg);
-            issue_tile(kt_lo + s, s, sg);
+            issue_tile(gkt(s), s, sg);
         }
     }
     if (cur_seg < 0) __syncthreads();   // nkt == 0 cannot happen (host), kept for safety
@@ -288,7 +300,7 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
         int a_rs, a_ks, b_rs, b_ks;
     };
     auto frag_ptr = [&](int it_) {
-        const DSeg& sg = p.seg[seg_of(kt_lo + it_)];
+        const DSeg& sg = p.seg[seg_of(gkt(it_))];
         const int st = it_ % STAGES;
         FragPtr f;
         f.a_rs = sg.a_mn_major ? 1 : PK;
@@ -317,7 +329,7 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
     for (int it = 0; it < nkt; ++it) {
         const int st = it % STAGES;
         {
-            const int sgi = seg_of(kt_lo + it);
+            const int sgi = seg_of(gkt(it));
             if (sgi != seg_acc) {    // rare, warp-uniform: acc holds sum/scale_acc; re-express for the new scale
                 const double sc = p.seg[sgi].scale;
                 if (seg_acc >= 0 && sc != scale_acc) {
@@ -360,10 +372,10 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
                 // refill: k-tile it + DIST goes into the stage that tile it + DIST - STAGES occupied
                 const int nxt = it + DIST;
                 if (nxt < nkt) {
-                    const int nseg_id = seg_of(kt_lo + nxt);
+                    const int nseg_id = seg_of(gkt(nxt));
                     if (nseg_id != cur_seg) set_rows(nseg_id);
                     if (nxt >= STAGES) mbar_wait(empty_s + 8 * (nxt % STAGES), ((nxt - STAGES) / STAGES) & 1);
-                    issue_tile(kt_lo + nxt, nxt % STAGES, nseg_id);
+                    issue_tile(gkt(nxt), nxt % STAGES, nseg_id);
                 }
             }
         }
@@ -1274,6 +1286,12 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
     PCCB_REQUIRE(ctx, (long long)d->batch * splits <= 65535, "pccb_contract: batch*splits=%lld exceeds grid.z",
                  (long long)d->batch * splits);
     p.splits = splits;
+    // round-robin chunks pay off for a few skinny tiles with many operand rows and a huge K (Lambda's
+    // l2[imef] Hvvvo[efam]: 2.3 -> 0.8 ms at (20,150)); with few rows contiguous ranges are faster
+    {
+        const long long rows = (d->M < bm ? d->M : bm) + (d->N < BN ? d->N : BN);
+        p.kchunk = (splits > 1 && mi <= 2 && tiles <= 4 && rows >= 96) ? 8 : 0;
+    }
 
     int rc = try_tma(ctx, p, d, mi);      // plain 2-D operands: TMA-staged kernel
     if (rc < 0) return rc;

@@ -12,10 +12,11 @@ index relabelling of the six stored blocks by the 8-fold symmetry of real integr
     <am|ei> = ovov[maie]   <bm|ie> = oovv[mieb]   <mb|ij> = ooov[ijmb]
     L<am|ef> = 2 ovvv[mafe] - ovvv[maef]          L<mn|ie> = Looov[mnie]   L<mn|ef> = Loovv[mnef]
 
-HBAR blocks are held in the reference's index order (Hvvvo[a,b,e,i], ...), except Hvvvv, which is
-stored transposed, HvT[a,b,e,f] = Hvvvv[e,f,a,b], so that the o^2 v^4 Lambda ladder
-``l2[ijef] Hvvvv[efab]`` (cclambda.py:528) reads it with the contracted pair contiguous, like the
-CCSD ladder reads <ab|ef>.  ``Hvvvv`` is exposed as the permuted view.
+HBAR blocks are held in the reference's index order, except the two whose only Lambda consumer
+contracts over their leading indices: Hvvvv is stored transposed, HvT[a,b,e,f] = Hvvvv[e,f,a,b], so
+that the o^2 v^4 ladder ``l2[ijef] Hvvvv[efab]`` (cclambda.py:528) reads it with the contracted
+pair contiguous, like the CCSD ladder reads <ab|ef>; and Hvvvo as Hs[e,i,a,b] = Hvvvo[a,b,e,i], so
+that ``l2[imef] Hvvvo[efam]`` (:473) streams it.  ``Hvvvv`` / ``Hvvvo`` are exposed as permuted views.
 
 CCD is the CCSD algebra with t1 = l1 = 0 (every reference CCD branch is the CCSD branch with its
 t1 terms dropped: cchbar.py:92-96, 108-113, ..., cclambda.py:462-466, 497-512).  CC2 has its own
@@ -46,9 +47,12 @@ class HbarEngine(object):
                   "Hoooo[mnij] += ooov[mnie]*t1[je]",
                   "Hoooo[mnij] += ooov[nmje]*t1[ie]"],
         # build_Hvvvv (:170-191), stored as HvT[abef] = Hvvvv[efab]; <ef|ab> = <ab|ef>
+        # the two t1 terms (K = o only, bound by the v^4 read-modify-write) read <me|ba> and <mf|ab>
+        # from the transposed copies ovA[mabe] = ovvv[meba], ovB[mabf] = ovvv[mfab] so that both
+        # stream HvT and the integrals contiguously
         "Hvvvv": ["HvT[abef] = vvvv[abef] + oovv[mnab]*tau[mnef]",
-                  "HvT[abef] -= ovvv[meba]*t1[mf]",
-                  "HvT[abef] -= ovvv[mfab]*t1[me]"],
+                  "HvT[abef] -= ovA[mabe]*t1[mf]",
+                  "HvT[abef] -= ovB[mabf]*t1[me]"],
         # build_Hvovv (:194-208)
         "Hvovv": ["Hvovv[amef] = ovvv[mafe] - t1[na]*oovv[nmef]"],
         # build_Hooov (:211-225)
@@ -64,15 +68,15 @@ class HbarEngine(object):
         # the two o^2 v^2 temporaries of build_Hvvvo (:303-316), which build_Hovoo forms again (:358-370)
         "X": ["Xa[mbie] = ovov[mbie] - oovv[mnfe]*t2[infb]",
               "Xb[bmje] = oovv[mjeb] - oovv[mnef]*t2[jnfb] + Loovv[mnef]*t2[njfb]"],
-        # build_Hvvvo (:272-321)
-        "Hvvvo": ["Hvvvo[abei] = ovvv[ieba] - t2[miab]*Hov[me]",
-                  "Hvvvo[abei] += HvT[efab]*t1[if]",
-                  "Hvvvo[abei] += tau[mnab]*ooov[nmie]",
-                  "Hvvvo[abei] -= ovvv[mbef]*t2[imfa]",
-                  "Hvvvo[abei] -= ovvv[mafe]*t2[imfb]",
-                  "Hvvvo[abei] += 2.0*ovvv[mafe]*t2[mifb] - ovvv[maef]*t2[mifb]",
-                  "Hvvvo[abei] -= t1[mb]*Xa[maie]",
-                  "Hvvvo[abei] -= t1[ma]*Xb[bmie]"],
+        # build_Hvvvo (:272-321), stored as Hs[eiab] = Hvvvo[abei]; t2x[mifb] = 2 t2[mifb] - t2[imfb] merges
+        # the second and third o^2 v^4 terms (:300-301) into one K-concatenated launch with the fourth
+        "Hvvvo": ["Hs[eiab] = ovvv[ieba] - t2[miab]*Hov[me]",
+                  "Hs[eiab] += HvT[efab]*t1[if]",
+                  "Hs[eiab] += tau[mnab]*ooov[nmie]",
+                  "Hs[eiab] -= ovvv[mbef]*t2[imfa]",
+                  "Hs[eiab] += ovvv[mafe]*t2x[mifb] - ovvv[maef]*t2[mifb]",
+                  "Hs[eiab] -= t1[mb]*Xa[maie]",
+                  "Hs[eiab] -= t1[ma]*Xb[bmie]"],
         # build_Hovoo (:324-375)
         "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + Hov[me]*t2[ijeb]",
                   "Hovoo[mbij] -= t1[nb]*Hoooo[mnij]",
@@ -91,17 +95,17 @@ class HbarEngine(object):
                   "Hoooo[mnij] += ooov[mnie]*t1[je]",
                   "Hoooo[mnij] += ooov[nmje]*t1[ie]"],
         "Hvvvv": ["HvT[abef] = vvvv[abef] + oovv[mnab]*T11[mnef]",
-                  "HvT[abef] -= ovvv[meba]*t1[mf]",
-                  "HvT[abef] -= ovvv[mfab]*t1[me]"],
+                  "HvT[abef] -= ovA[mabe]*t1[mf]",
+                  "HvT[abef] -= ovB[mabf]*t1[me]"],
         "Hovvo": ["Hovvo[mbej] = oovv[mjeb] + ovvv[mbef]*t1[jf]",
                   "Hovvo[mbej] -= t1[nb]*ooov[nmje]"],
         "Hovov": ["Hovov[mbje] = ovov[mbje] + ovvv[mbfe]*t1[jf]",
                   "Hovov[mbje] -= t1[nb]*ooov[mnje]"],
-        "Hvvvo": ["Hvvvo[abei] = ovvv[ieba] - t2[miab]*Fov[me]",
-                  "Hvvvo[abei] += HvT[efab]*t1[if]",
-                  "Hvvvo[abei] += T11[mnab]*ooov[nmie]",
-                  "Hvvvo[abei] -= t1[mb]*ovov[maie]",
-                  "Hvvvo[abei] -= t1[ma]*oovv[mieb]"],
+        "Hvvvo": ["Hs[eiab] = ovvv[ieba] - t2[miab]*Fov[me]",
+                  "Hs[eiab] += HvT[efab]*t1[if]",
+                  "Hs[eiab] += T11[mnab]*ooov[nmie]",
+                  "Hs[eiab] -= t1[mb]*ovov[maie]",
+                  "Hs[eiab] -= t1[ma]*oovv[mieb]"],
         "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + Fov[me]*t2[ijeb]",
                   "Hovoo[mbij] -= t1[nb]*Hoooo[mnij]",
                   "Hovoo[mbij] += ovvv[mbef]*T11[ijef]",
@@ -123,13 +127,15 @@ class HbarEngine(object):
         self.Hoooo, self.HvT = E(o, o, o, o), E(v, v, v, v)
         self.Hvovv, self.Hooov = E(v, o, v, v), E(o, o, o, v)
         self.Hovvo, self.Hovov = E(o, v, v, o), E(o, v, o, v)
-        self.Hvvvo, self.Hovoo = E(v, v, v, o), E(o, v, o, o)
+        self.Hs, self.Hovoo = E(v, o, v, v), E(o, v, o, o)
         self.Xa, self.Xb = E(o, v, o, v), E(v, o, o, v)
+        self.t2x, self.ovA, self.ovB = E(o, o, v, v), E(o, v, v, v), E(o, v, v, v)
         if eng.model == 'CC2':
             self.T11 = eng.T11
         st = dict(self.STATEMENTS)
         if eng.model == 'CC2':
             st.update(self.STATEMENTS_CC2)
+        self._ov_ready = False
         T = self.tensors()
         self.plans = {}
         for name in self.ORDER:
@@ -146,8 +152,8 @@ class HbarEngine(object):
                  Foo=F[:o, :o], Fov=F[:o, o:], Fvv=F[o:, o:], Loovv=eng.Loovv, Looov=eng.Looov,
                  t1=eng.t1, t2=eng.t2, tau=eng.tau,
                  Hov=self.Hov, Hvv=self.Hvv, Hoo=self.Hoo, Hoooo=self.Hoooo, HvT=self.HvT, Hvovv=self.Hvovv,
-                 Hooov=self.Hooov, Hovvo=self.Hovvo, Hovov=self.Hovov, Hvvvo=self.Hvvvo, Hovoo=self.Hovoo,
-                 Xa=self.Xa, Xb=self.Xb)
+                 Hooov=self.Hooov, Hovvo=self.Hovvo, Hovov=self.Hovov, Hs=self.Hs, Hovoo=self.Hovoo,
+                 Xa=self.Xa, Xb=self.Xb, t2x=self.t2x, ovA=self.ovA, ovB=self.ovB)
         if eng.model == 'CC2':
             d["T11"] = eng.T11
         return {k: TRef.of(t, k) for k, t in d.items()}
@@ -155,6 +161,10 @@ class HbarEngine(object):
     @property
     def Hvvvv(self):
         return self.HvT.permute(2, 3, 0, 1)
+
+    @property
+    def Hvvvo(self):
+        return self.Hs.permute(2, 3, 0, 1)
 
     DEPS = dict(Hvvvo=("Hov", "Hvvvv", "X"), Hovoo=("Hov", "Hoooo", "X"))
 
@@ -166,6 +176,13 @@ class HbarEngine(object):
         if eng.model == 'CCD':
             eng.t1.zero_()
         eng.prepare()
+        if only in (None, "Hvvvo"):
+            self.be.permute4(self.t2x, eng.t2, 2.0, 0.0)
+            self.be.permute4(self.t2x, eng.t2.permute(1, 0, 2, 3), -1.0, 1.0)
+        if not self._ov_ready:       # integrals only: formed once
+            self.be.permute4(self.ovA, eng.ovvv_full.permute(0, 3, 2, 1))
+            self.be.permute4(self.ovB, eng.ovvv_full.permute(0, 2, 3, 1))
+            self._ov_ready = True
         todo = self.ORDER if only is None else [n for n in self.ORDER if n == only or n in self.DEPS.get(only, ())]
         for name in todo:
             for L in self.plans[name]:
@@ -188,7 +205,7 @@ class LambdaEngine(object):
         "G": ["Goo[mi] = t2[mjab]*l2[ijab]",
               "Gvv[ae] = -1.0*t2[ijeb]*l2[ijab]"],
         # r_L1 (:460-493)
-        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hvvvo[efam] - l2[mnae]*Hovoo[iemn]",
+        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hs[amef] - l2[mnae]*Hovoo[iemn]",
                  "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
                  "r1[ia] += Gvv[ef]*Hvovv[eiaf] - 2.0*Gvv[ef]*Hvovv[eifa]",
                  "r1[ia] += Goo[mn]*Hooov[imna] - 2.0*Goo[mn]*Hooov[mina]"],
@@ -207,7 +224,7 @@ class LambdaEngine(object):
 
     # CC2 (:481-486, 522-524): Goo / Gvv are built but not used; Fa / Fi are the t1-dressed Fock blocks
     STATEMENTS_CC2 = {
-        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hvvvo[efam] - l2[mnae]*Hovoo[iemn]",
+        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hs[amef] - l2[mnae]*Hovoo[iemn]",
                  "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
                  "Ya[nf] = l1[me]*t2[nmfe]",
                  "Yb[nf] = l1[me]*tau[mnfe]",

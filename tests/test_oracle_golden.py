@@ -55,3 +55,31 @@ def test_diis_variants(golden, tag, kw):
     ecc, t1, t2, niter = oc.solve_cc(g.F, g.blocks, 1e-10, 1e-10, maxiter=200, **kw)
     assert niter == int(g["solve_%s_niter" % tag])
     assert abs(ecc - float(g["solve_%s_ecc" % tag])) < 1e-12
+
+
+def test_lambda_oracle_against_reference_vectors(golden):
+    """oracle/lambda_oracle.py (HBAR + Lambda, CCSD branch) against tests/golden/lambda/*.npz."""
+    import os
+    from oracle import lambda_oracle as ol
+    from tests.conftest import GOLDEN_DIR
+    from tests.lambda_checks import BLOCKS, HVVVV_SUB
+    g = golden
+    z = np.load(os.path.join(GOLDEN_DIR, "lambda", g.name + ".npz"))
+    blk = oc.Blocks(g.blocks)
+    t1, t2 = g["gen_t1"], g["gen_t2"]
+    H = ol.build_hbar(g.F, blk, t1, t2)
+    for b in BLOCKS:
+        x = H[b][HVVVV_SUB] if (b == "Hvvvv" and g.nv > 8) else H[b]
+        assert np.abs(x - z["ccsd_" + b]).max() < 1e-12, b
+    l1, l2 = z["ccsd_l1"], z["ccsd_l2"]
+    assert np.abs(ol.build_Goo(t2, l2) - z["ccsd_Goo"]).max() < 1e-12
+    assert np.abs(ol.build_Gvv(t2, l2) - z["ccsd_Gvv"]).max() < 1e-12
+    r1, r2 = ol.lambda_residuals(blk, H, t2, l1, l2)
+    assert np.abs(r1 - z["ccsd_rl1"]).max() < 1e-12
+    assert np.abs(r2 - z["ccsd_rl2"]).max() < 1e-12
+    assert abs(ol.pseudoenergy(blk, l2) - float(z["ccsd_pseudo"])) < 1e-13
+    # the converged Lambda amplitudes are a fixed point of the iteration
+    ts1, ts2 = z["ccsd_solve_t1"], z["ccsd_solve_t2"]
+    H = ol.build_hbar(g.F, blk, ts1, ts2)
+    n1, n2, lecc, rms = ol.lambda_iteration(g.F, blk, H, ts2, z["ccsd_solve_l1"], z["ccsd_solve_l2"])
+    assert rms < 1e-10 and abs(lecc - float(z["ccsd_solve_lecc"])) < 1e-11
