@@ -23,6 +23,7 @@ class cchbar(object):
         self.o, self.v = ccwfn.o, ccwfn.v
         self.no, self.nv = ccwfn.no, ccwfn.nv
         self.engine = HbarEngine(ccwfn.engine)
+        self.engine.snapshot()
         self.engine.build()
         e = self.engine
         self.Hov, self.Hvv, self.Hoo = e.Hov, e.Hvv, e.Hoo

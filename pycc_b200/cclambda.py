@@ -65,11 +65,31 @@ class cclambda(object):
     def residuals(self, F, t1, t2, l1, l2):
         """L1 and L2 residuals for the given Fock operator and amplitudes; HBAR is rebuilt from
         (F, t1, t2) first (pycc/cclambda.py:281-323).  Returns new tensors."""
-        self.ccwfn._load(F, t1, t2)
+        from .ccwfn import _is_complex
+        if any(_is_complex(x) for x in (F, t1, t2, l1, l2)):
+            # rtcc.f (pycc/rt/rtcc.py:132): complex amplitudes, HBAR rebuilt from them
+            return self.ccwfn._complex().lambda_residuals(F, t1, t2, l1, l2)
+        w, eng, le = self.ccwfn, self.ccwfn.engine, self.engine
+        own_t = t1 is eng.t1 and t2 is eng.t2
+        own_l = l1 is le.l1 and l2 is le.l2
+        self.hbar.engine.snapshot()
+        if not own_t:                    # the objects' amplitudes are put back afterwards (the HBAR
+            kt1, kt2 = eng.t1.clone(), eng.t2.clone()     # blocks keep the values of this call)
+        if not own_l:
+            kl1, kl2 = le.l1.clone(), le.l2.clone()
+        w._load(F, t1, t2)
         self.hbar.engine.build()
         self._load(l1, l2)
-        r1, r2 = self.engine.residuals(symmetrize=True)
-        return r1.clone(), r2.clone()
+        r1, r2 = le.residuals(symmetrize=True)
+        r1, r2 = r1.clone(), r2.clone()
+        if not own_t:
+            eng.t1.copy_(kt1)
+            eng.t2.copy_(kt2)
+        if not own_l:
+            le.l1.copy_(kl1)
+            le.l2.copy_(kl2)
+        eng.set_fock(eng.F0)
+        return r1, r2
 
     def build_Goo(self, t2, l2):
         self.ccwfn._load(None, self.ccwfn.engine.t1, t2)

@@ -23,6 +23,12 @@ from .hamiltonian import Hamiltonian, BLOCKS
 from .utils import helper_diis, cc_contract
 
 
+def _is_complex(x):
+    if x is None:
+        return False
+    return x.is_complex() if isinstance(x, torch.Tensor) else np.iscomplexobj(x)
+
+
 class ccwfn(object):
     """An RHF-CC wave function and energy object (see module docstring).
 
@@ -153,7 +159,7 @@ class ccwfn(object):
             self.H = Hamiltonian.from_full(F, ERI, no, backend.device, dtype, vslice, keep_ovvv)
         self.engine = CCSDEngine(backend, self.H.F, self.H.blocks, no, nv, dtype, comm=self.comm,
                                  keep_full_ovvv=keep_ovvv, model=model)
-        self.H.F = self.engine.F
+        self.H.F = self.engine.F0
         self._triples = None
 
         # first-order amplitudes (pycc/ccwfn.py:170-175): t1 = 0, t2 = <ij|ab>/Dijab
@@ -186,6 +192,7 @@ class ccwfn(object):
         energy (plus E(T) for model 'CCSD(T)'), or None when not converged in ``maxiter``."""
         ccsd_tstart = time.time()
         eng = self.engine
+        eng.set_fock(eng.F0)
         ecc = eng.energy()
         print("CC Iter %3d: CC Ecorr = %.15f  dE = % .5E  MP2" % (0, ecc, -ecc))
         diis = helper_diis(self.t1, self.t2, max_diis, self.precision, backend=self.backend)
@@ -232,7 +239,9 @@ class ccwfn(object):
 
     def _load(self, F, t1, t2):
         eng = self.engine
-        if F is not None and F is not eng.F:
+        if F is None:
+            F = eng.F0                   # the Hamiltonian's own Fock matrix
+        if F is not eng.F:
             eng.set_fock(F)
         if t1 is not eng.t1:
             eng.t1.copy_(torch.as_tensor(t1).to(eng.t1.device, eng.dtype))
@@ -241,11 +250,30 @@ class ccwfn(object):
 
     def residuals(self, F, t1, t2, real_time=False):
         """r1, r2 = <mu|HBAR|0> for the given Fock operator and amplitudes (pycc/ccwfn.py:331-406).
-        Pure with respect to the stored amplitudes when called with its own copies; returns new
-        tensors."""
+        Pure, like the reference's: the object's amplitudes and ``H.F`` are unchanged afterwards
+        (the engine's intermediates hold the values of this call).  Returns new tensors; complex
+        inputs give complex results."""
+        if _is_complex(F) or _is_complex(t1) or _is_complex(t2):
+            # complex amplitudes (real-time propagation, pycc/rt/rtcc.py:125): two real planes
+            return self._complex().residuals(F, t1, t2)
+        eng = self.engine
+        own = t1 is eng.t1 and t2 is eng.t2
+        if not own:                      # pure: the object's amplitudes are put back afterwards
+            keep1, keep2 = eng.t1.clone(), eng.t2.clone()
         self._load(F, t1, t2)
-        r1, r2 = self.engine.residuals(symmetrize=True)
-        return r1.clone(), r2.clone()
+        r1, r2 = eng.residuals(symmetrize=True)
+        r1, r2 = r1.clone(), r2.clone()
+        if not own:
+            eng.t1.copy_(keep1)
+            eng.t2.copy_(keep2)
+        eng.set_fock(eng.F0)
+        return r1, r2
+
+    def _complex(self):
+        if getattr(self, "_cplx", None) is None:
+            from .complex_engine import ComplexResiduals
+            self._cplx = ComplexResiduals(self.engine)
+        return self._cplx
 
     def build_tau(self, t1, t2, fact1=1.0, fact2=1.0):
         out = self.backend.empty(tuple(t2.shape), self.engine.dtype)

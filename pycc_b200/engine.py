@@ -49,9 +49,12 @@ class CCSDEngine(object):
         n = o + v
         self.vlo, self.vhi = virtual_slice(v, self.comm.rank, self.comm.world)
         vl = self.vl = self.vhi - self.vlo
-        self.F = be.to_device(F, dtype)
-        if tuple(self.F.shape) != (n, n):
+        # F0: the Hamiltonian's own Fock matrix (ccwfn.H.F); F: the one the kernels read, which
+        # residuals(F, ...) may replace for one call (a field-dressed F in real-time propagation)
+        self.F0 = be.to_device(F, dtype)
+        if tuple(self.F0.shape) != (n, n):
             raise ValueError("F must be (%d,%d)" % (n, n))
+        self.F = self.F0.clone()
         self.eps = torch.diagonal(self.F).contiguous()
         shapes = dict(oooo=(o, o, o, o), ooov=(o, o, o, v), oovv=(o, o, v, v), ovov=(o, v, o, v),
                       ovvv=(o, v, v, v), vvvv=(v, v, v, v))

@@ -88,7 +88,9 @@ class HbarEngine(object):
                   "Hovoo[mbij] += Xb[bmje]*t1[ie]"],
     }
 
-    # CC2 branches; T11[ijab] = t1[ia] t1[jb]
+    # CC2 branches; T11[ijab] = t1[ia] t1[jb].  The reference's CC2 code reads ``self.ccwfn.H.F`` here
+    # (cchbar.py:289, 341) - the object's own Fock matrix F0, not the F handed to
+    # cclambda.residuals - and so does this.
     STATEMENTS_CC2 = {
         "X": [],
         "Hoooo": ["Hoooo[mnij] = oooo[mnij] + oovv[mnef]*T11[ijef]",
@@ -101,12 +103,12 @@ class HbarEngine(object):
                   "Hovvo[mbej] -= t1[nb]*ooov[nmje]"],
         "Hovov": ["Hovov[mbje] = ovov[mbje] + ovvv[mbfe]*t1[jf]",
                   "Hovov[mbje] -= t1[nb]*ooov[mnje]"],
-        "Hvvvo": ["Hs[eiab] = ovvv[ieba] - t2[miab]*Fov[me]",
+        "Hvvvo": ["Hs[eiab] = ovvv[ieba] - t2[miab]*F0ov[me]",
                   "Hs[eiab] += HvT[efab]*t1[if]",
                   "Hs[eiab] += T11[mnab]*ooov[nmie]",
                   "Hs[eiab] -= t1[mb]*ovov[maie]",
                   "Hs[eiab] -= t1[ma]*oovv[mieb]"],
-        "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + Fov[me]*t2[ijeb]",
+        "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + F0ov[me]*t2[ijeb]",
                   "Hovoo[mbij] -= t1[nb]*Hoooo[mnij]",
                   "Hovoo[mbij] += ovvv[mbef]*T11[ijef]",
                   "Hovoo[mbij] += ovov[mbie]*t1[je]",
@@ -132,6 +134,7 @@ class HbarEngine(object):
         self.t2x, self.ovA, self.ovB = E(o, o, v, v), E(o, v, v, v), E(o, v, v, v)
         if eng.model == 'CC2':
             self.T11 = eng.T11
+            self.t1_0, self.t2_0, self.tau_0 = E(o, v), E(o, o, v, v), E(o, o, v, v)
         st = dict(self.STATEMENTS)
         if eng.model == 'CC2':
             st.update(self.STATEMENTS_CC2)
@@ -155,8 +158,21 @@ class HbarEngine(object):
                  Hooov=self.Hooov, Hovvo=self.Hovvo, Hovov=self.Hovov, Hs=self.Hs, Hovoo=self.Hovoo,
                  Xa=self.Xa, Xb=self.Xb, t2x=self.t2x, ovA=self.ovA, ovB=self.ovB)
         if eng.model == 'CC2':
-            d["T11"] = eng.T11
+            F0 = eng.F0
+            d.update(T11=eng.T11, F0oo=F0[:o, :o], F0ov=F0[:o, o:], F0vv=F0[o:, o:],
+                     t1_0=self.t1_0, t2_0=self.t2_0, tau_0=self.tau_0)
         return {k: TRef.of(t, k) for k, t in d.items()}
+
+    def snapshot(self):
+        """CC2: remember the object's own amplitudes (the engine's current ones) for the terms of
+        the Lambda residual that the reference evaluates with ``self.ccwfn.t1 / .t2``."""
+        if self.eng.model == 'CC2':
+            eng = self.eng
+            self.be.bind_stream()
+            eng.prepare()
+            self.t1_0.copy_(eng.t1)
+            self.t2_0.copy_(eng.t2)
+            self.tau_0.copy_(eng.tau)
 
     @property
     def Hvvvv(self):
@@ -222,18 +238,21 @@ class LambdaEngine(object):
                  "r2[ijab] += Gvv[ae]*Loovv[ijeb] - Goo[mi]*Loovv[mjab]"],
     }
 
-    # CC2 (:481-486, 522-524): Goo / Gvv are built but not used; Fa / Fi are the t1-dressed Fock blocks
+    # CC2 (:481-486, 522-524): Goo / Gvv are built but not used; Fa / Fi are the t1-dressed Fock blocks.
+    # As in the reference these terms read the OBJECT's Fock matrix and amplitudes (self.ccwfn.H.F,
+    # self.ccwfn.t1 / .t2): F0.., t1_0, t2_0, tau_0 - identical to the arguments inside solve_lambda,
+    # different when cclambda.residuals is called with other amplitudes (real-time propagation).
     STATEMENTS_CC2 = {
         "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hs[amef] - l2[mnae]*Hovoo[iemn]",
                  "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
-                 "Ya[nf] = l1[me]*t2[nmfe]",
-                 "Yb[nf] = l1[me]*tau[mnfe]",
+                 "Ya[nf] = l1[me]*t2_0[nmfe]",
+                 "Yb[nf] = l1[me]*tau_0[mnfe]",
                  "r1[ia] += 2.0*Ya[nf]*Loovv[inaf] - 2.0*Yb[nf]*oovv[inaf] + Yb[nf]*oovv[infa]"],
         "r_L2": ["r2[ijab] = Loovv[ijab] + 2.0*l1[ia]*Hov[jb] - l1[ja]*Hov[ib]",
                  "r2[ijab] += 2.0*l1[ie]*Hvovv[ejab] - l1[ie]*Hvovv[ejba]",
                  "r2[ijab] += l1[mb]*Hooov[ijma] - 2.0*l1[mb]*Hooov[jima]",
-                 "Fa[ea] = Fvv[ea] - Fov[ma]*t1[me]",      # (F_vv - F_ov^T t1)[e,a], index order as the reference uses it
-                 "Fi[im] = Foo[im] + t1[me]*Fov[ie]",
+                 "Fa[ea] = F0vv[ea] - F0ov[ma]*t1_0[me]",      # (F_vv - F_ov^T t1)[e,a], index order as the reference uses it
+                 "Fi[im] = F0oo[im] + t1_0[me]*F0ov[ie]",
                  "r2[ijab] += l2[ijeb]*Fa[ea] - l2[mjab]*Fi[im]"],
     }
 
