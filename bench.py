@@ -119,6 +119,19 @@ class ClockSampler(object):
                 "reasons": [n for b, n in self.REASONS.items() if self.mask & b], "samples": len(s)}
 
 
+_OUT_FD = None
+
+
+def emit(obj):
+    """The ONE JSON line, on the process's real stdout (see main)."""
+    line = (json.dumps(obj) + "\n").encode()
+    if _OUT_FD is None:
+        sys.stdout.write(line.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_OUT_FD, line)
+
+
 def make_factor(o, v, seed):
     """Seeded factor B (scaled so that E_MP2 = -0.10 Eh), Fock matrix F."""
     from pycc_b200.synthetic import make_factor as mf, calibrated_scale
@@ -360,7 +373,7 @@ def run_ours(args):
                "energy": last[0] if last else None, "rms": last[1] if last else None,
                "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "e2e": e2e,
                "triples": triples, "cpu_baseline": cpu_baseline, "parity": parity}
-        print(json.dumps(out), flush=True)
+        emit(out)
     if world > 1:
         dist.destroy_process_group()
 
@@ -419,7 +432,7 @@ def run_reference(args):
                             "sample": "%d full CCSD iterations (residuals + update + energy + DIIS) of the NumPy "
                                       "oracle at o=%d v=%d (requested %d; bounded to ~4 min)" % (steps, o, v, args.steps)},
            "e2e": {"value": round(sec, 4), "unit": "s/iteration", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def run_lambda(args):
@@ -575,11 +588,17 @@ def run_lambda(args):
            "pseudoenergy": last[0] if last else None, "rms": last[1] if last else None,
            "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "e2e": e2e,
            "cpu_baseline": cpu_baseline, "parity": parity}
-    print(json.dumps(out), flush=True)
+    emit(out)
 
 
 def main():
+    global _OUT_FD
     args = parse_args()
+    # stdout carries exactly one JSON line: whatever libraries print there (NCCL's version banner
+    # on communicator creation, ...) is sent to stderr instead
+    sys.stdout.flush()
+    _OUT_FD = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     elif args.path == "lambda":
