@@ -51,7 +51,7 @@ def parse_args():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--path", default="ccsd", choices=["ccsd", "lambda"],
                     help="ccsd: the north-star CCSD iteration (default); lambda: HBAR build + Lambda iteration "
-                         "(SURVEY.md 8(f) rank 2; one GPU)")
+                         "(SURVEY.md 8(f) rank 2)")
     return ap.parse_args()
 
 
@@ -266,6 +266,14 @@ def run_ours(args):
                                            " (FP64 has no entry in MEASURED_PEAKS.json; cuBLAS DGEMM on the "
                                            "same box: 35.5 TFLOP/s)")}
 
+    try:        # DRAM bytes of that launch from the committed ncu capture of the same configuration, if any
+        tr = json.load(open(os.path.join(ROOT, "profiles", "r01_ncu_traffic.json")))["%d,%d,%d,%s" % (o, v, world, args.precision)]
+        roofline["traffic"] = tr["traffic_bytes"]
+        roofline["traffic_unit"] = "bytes/launch (algorithmic %d)" % tr["algorithmic_bytes"]
+        roofline["traffic_source"] = tr["source"]
+    except Exception:
+        pass
+
     # ---- e2e: amplitudes live in pinned host memory between iterations -------------------------
     e2e = None
     if not args.no_e2e:
@@ -445,19 +453,26 @@ def run_lambda(args):
     import contextlib
     import io
     o, v = [int(x) for x in args.workload.split(",")]
-    if int(os.environ.get("WORLD_SIZE", "1")) != 1:
-        raise SystemExit("bench.py --path lambda runs on one GPU")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device - the pycc_b200 engine has no CPU fallback")
-    torch.cuda.set_device(0)
-    dev = torch.device("cuda", 0)
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    group = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=dev)
+        group = "world"
     import pycc_b200
+    from pycc_b200.parallel import virtual_slice
     from pycc_b200.synthetic import device_blocks
     from pycc_b200.utils import helper_diis
     B, F, scale = make_factor(o, v, args.seed)
-    blocks = device_blocks(B, o, dev)
+    blocks = device_blocks(B, o, dev, vslice=virtual_slice(v, rank, world), keep_full_ovvv=True)
     with contextlib.redirect_stdout(io.StringIO()):
-        w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD")
+        w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD", group=group, full_ovvv=True)
         d0 = helper_diis(w.t1, w.t2, 8, "DP", backend=w.backend)
         for it in range(6):                      # amplitudes a few DIIS iterations from the MP2 guess
             w._iteration(d0, it + 1, 1)
@@ -468,6 +483,15 @@ def run_lambda(args):
 
     def sync():
         torch.cuda.synchronize()
+        w.comm.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x):
+        if world == 1:
+            return x
+        t = torch.tensor([x], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
 
     # HBAR build, timed on its own (once per Lambda solve)
     sync()
@@ -477,7 +501,7 @@ def run_lambda(args):
         hb.engine.build()
     h1.record()
     sync()
-    hbar_ms = h0.elapsed_time(h1) / 3
+    hbar_ms = max_over_ranks(h0.elapsed_time(h1) / 3)
 
     diis = helper_diis(lam.l1, lam.l2, 8, "DP", backend=be)
 
@@ -491,7 +515,7 @@ def run_lambda(args):
     for _ in range(max(args.warmup, 0)):
         niter += 1
         step(niter)
-    clocks = ClockSampler(0)
+    clocks = ClockSampler(local_rank)
     sync()
     clocks.start()
     launches0 = be.launch_count()
@@ -504,13 +528,13 @@ def run_lambda(args):
         last = step(niter)
     e1.record()
     sync()
-    ms_step = e0.elapsed_time(e1) / max(args.steps, 1)
+    ms_step = max_over_ranks(e0.elapsed_time(e1)) / max(args.steps, 1)
     clk = clocks.stop()
     launches = be.launch_count() - launches0
     ladder_ms = [a.elapsed_time(b) for a, b in leng.ladder_events]
     leng.ladder_events = None
     peak, peak_src = dmma_peak()
-    lad_flops = 2.0 * o * o * float(v)**4
+    lad_flops = 2.0 * o * o * float(w.engine.vl) * float(v)**3        # this rank's rows of Hvvvv
     lad_ms = sum(ladder_ms) / max(len(ladder_ms), 1)
     lad_tf = lad_flops / (lad_ms * 1e-3) / 1e12 if lad_ms > 0 else 0.0
     roofline = {"bound": "tensor", "kernel": "contract_f64_tma_kernel (Lambda ladder r2 += 1/2 l2 Hvvvv)",
@@ -540,11 +564,11 @@ def run_lambda(args):
             niter += 1
             e2e_step(niter)
         sync()
-        e2e = {"value": round((time.perf_counter() - t0) / ksteps, 6), "unit": "s/iteration",
+        e2e = {"value": round(max_over_ranks((time.perf_counter() - t0) / ksteps), 6), "unit": "s/iteration",
                "h2d_bytes_per_step": nb, "d2h_bytes_per_step": nb + 16, "steps": ksteps}
 
     cpu_baseline, parity = None, None
-    if not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline:
         from oracle import ccsd_oracle as oc
         from oracle import lambda_oracle as ol
         cores = set_host_threads()
@@ -574,21 +598,32 @@ def run_lambda(args):
                                   "(port of pycc/cclambda.py:450-543) at o=%d v=%d; HBAR build timed separately" % (o, v)}
 
     fi = float(leng.flops_issued())
+    hfi = float(hb.engine.flops_issued())
+    if world > 1:
+        t = torch.tensor([fi, hfi], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        fi, hfi = float(t[0].item()), float(t[1].item())
+    if rank != 0:
+        dist.destroy_process_group()
+        return
     out = {"metric": "lambda_seconds_per_iteration", "value": round(ms_step * 1e-3, 6), "unit": "s/iteration",
-           "n_gpus": 1, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
+           "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
            "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
            "data": "synthetic (seeded factorised 8-fold-symmetric ERIs, diagonal Fock; SURVEY.md 8(d))",
            "config": {"workload": "RHF-CCSD Lambda iteration o=%d v=%d FP64" % (o, v), "o": o, "v": v,
-                      "parallelism": "1 GPU", "l2": "inputs larger than L2 (Hvvvv %.2f GB)" % (v**4 * 8 / 1e9),
+                      "parallelism": "1 GPU" if world == 1 else "Hvvvv/Hvvvo rows sharded x%d + allreduce(r1,r2)" % world,
+                      "l2": "inputs larger than L2 (Hvvvv rows %.2f GB per rank)" % (w.engine.vl * v**3 * 8 / 1e9),
                       "seed": args.seed, "eri_scale": round(scale, 6), "diis": 8},
            "flops_issued": fi, "tflops_issued": round(fi / (ms_step * 1e-3) / 1e12, 3),
-           "tflops_issued_frac_of_peak": round(fi / (ms_step * 1e-3) / 1e12 / peak, 4),
-           "hbar": {"build_ms": round(hbar_ms, 3), "flops_issued": float(hb.engine.flops_issued()),
-                    "tflops_issued": round(hb.engine.flops_issued() / (hbar_ms * 1e-3) / 1e12, 3)},
+           "tflops_issued_frac_of_peak": round(fi / (ms_step * 1e-3) / 1e12 / (peak * world), 4),
+           "hbar": {"build_ms": round(hbar_ms, 3), "flops_issued": hfi,
+                    "tflops_issued": round(hfi / (hbar_ms * 1e-3) / 1e12, 3)},
            "pseudoenergy": last[0] if last else None, "rms": last[1] if last else None,
            "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "e2e": e2e,
            "cpu_baseline": cpu_baseline, "parity": parity}
     emit(out)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def main():

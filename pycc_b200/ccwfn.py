@@ -150,7 +150,9 @@ class ccwfn(object):
         dtype = torch.float32 if self.precision == 'SP' else torch.float64
         from .parallel import virtual_slice
         vslice = virtual_slice(nv, self.comm.rank, self.comm.world)
-        keep_ovvv = (model in ('CCSD(T)', 'CC3') or self.comm.world == 1)
+        # engine-only kwarg: keep every row of <mb|ef> on each rank (needed by HBAR / Lambda with group=...)
+        full_ovvv = bool(kwargs.pop('full_ovvv', False))
+        keep_ovvv = model in ('CCSD(T)', 'CC3') or self.comm.world == 1 or full_ovvv
         if isinstance(ERI, dict):
             self.H = Hamiltonian.from_blocks(F, ERI, no, backend.device, dtype, vslice, keep_ovvv)
         else:

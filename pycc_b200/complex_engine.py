@@ -259,8 +259,8 @@ class ComplexResiduals(object):
         if eng.model == 'CC2':
             hs.update(HbarEngine.STATEMENTS_CC2)
             ls.update(LambdaEngine.STATEMENTS_CC2)
-        ren = lambda n_: {"r1": "rl1", "r2": "rl2"}.get(n_, n_)
-        self.hbar_prog = [P.compile(hs[name]) for name in HbarEngine.ORDER]
+        ren = lambda n_: {"r1": "rl1", "r2": "rl2"}.get(_strip(n_), _strip(n_))
+        self.hbar_prog = [P.compile(hs[name], _strip) for name in HbarEngine.ORDER]
         self.lam_prog = {name: P.compile(ls[name], ren) for name in ("G", "r_L1", "r_L2")}
         self._lam = True
 
@@ -285,9 +285,9 @@ class ComplexResiduals(object):
             P.load("l1", l1)
         P.load("l2", l2)
         P.run(self.lam_prog["G"])
-        if eng.model == 'CCD':
-            P.cplx["rl1"].zero_()
-        else:
+        P.cplx["rl1"].zero_()
+        P.cplx["rl2"].zero_()
+        if eng.model != 'CCD':
             P.run(self.lam_prog["r_L1"])
         P.run(self.lam_prog["r_L2"])
         for z in range(2):

@@ -21,13 +21,33 @@ that ``l2[imef] Hvvvo[efam]`` (:473) streams it.  ``Hvvvv`` / ``Hvvvo`` are expo
 CCD is the CCSD algebra with t1 = l1 = 0 (every reference CCD branch is the CCSD branch with its
 t1 terms dropped: cchbar.py:92-96, 108-113, ..., cclambda.py:462-466, 497-512).  CC2 has its own
 statements (cchbar.py:163, 186, 241, 263, 285-294, 337-346; cclambda.py:481-486, 522-524).
-Single GPU (one rank) for now.
+
+Multi-GPU (one process per GPU): the two big blocks are sharded by rows over the virtual slice of
+the CCSD engine - HvT[A,b,e,f] and Hs[E,i,a,b] hold a, e in [vlo, vhi) only - everything else is
+replicated; an upper-case A / B / E in a statement is the sliced index and ``X_sK`` the matching
+view of X (as in ``engine.STATEMENTS``).  Every Lambda term then produces the rows a (or columns
+b) of r1 / r2 that belong to the slice, and one allreduce per residual sums the partial results -
+the same exchange step as the CCSD iteration.  CCSD and CCD; CC2 runs on one GPU.
 """
 import re
 
 import torch
 
 from .dsl import TRef, plan
+
+
+def resolve(T, name, eng):
+    """Tensor name of a statement -> strided view.  ``X_sK`` is X restricted to this rank's slice of
+    the virtual index along dimension K (the whole tensor on one GPU); the two blocks stored by
+    rows, <ab|ef> and the local HvT / Hs / ovA / ovB, are addressed by their plain names."""
+    if name == "vvvv_s0":
+        return TRef.of(eng.vvvv_loc, name)
+    if name in T:
+        return TRef.of(T[name], name)
+    base, dim = name[:-3], name[-1]
+    if name[-3:-1] != "_s" or base not in T or not dim.isdigit():
+        raise KeyError("unknown tensor %r" % name)
+    return TRef.of(T[base].narrow(int(dim), eng.vlo, eng.vl), name)
 
 
 class HbarEngine(object):
@@ -50,9 +70,9 @@ class HbarEngine(object):
         # the two t1 terms (K = o only, bound by the v^4 read-modify-write) read <me|ba> and <mf|ab>
         # from the transposed copies ovA[mabe] = ovvv[meba], ovB[mabf] = ovvv[mfab] so that both
         # stream HvT and the integrals contiguously
-        "Hvvvv": ["HvT[abef] = vvvv[abef] + oovv[mnab]*tau[mnef]",
-                  "HvT[abef] -= ovA[mabe]*t1[mf]",
-                  "HvT[abef] -= ovB[mabf]*t1[me]"],
+        "Hvvvv": ["HvT[Abef] = vvvv_s0[Abef] + oovv_s2[mnAb]*tau[mnef]",
+                  "HvT[Abef] -= ovA[mAbe]*t1[mf]",
+                  "HvT[Abef] -= ovB[mAbf]*t1[me]"],
         # build_Hvovv (:194-208)
         "Hvovv": ["Hvovv[amef] = ovvv[mafe] - t1[na]*oovv[nmef]"],
         # build_Hooov (:211-225)
@@ -70,13 +90,13 @@ class HbarEngine(object):
               "Xb[bmje] = oovv[mjeb] - oovv[mnef]*t2[jnfb] + Loovv[mnef]*t2[njfb]"],
         # build_Hvvvo (:272-321), stored as Hs[eiab] = Hvvvo[abei]; t2x[mifb] = 2 t2[mifb] - t2[imfb] merges
         # the second and third o^2 v^4 terms (:300-301) into one K-concatenated launch with the fourth
-        "Hvvvo": ["Hs[eiab] = ovvv[ieba] - t2[miab]*Hov[me]",
-                  "Hs[eiab] += HvT[efab]*t1[if]",
-                  "Hs[eiab] += tau[mnab]*ooov[nmie]",
-                  "Hs[eiab] -= ovvv[mbef]*t2[imfa]",
-                  "Hs[eiab] += ovvv[mafe]*t2x[mifb] - ovvv[maef]*t2[mifb]",
-                  "Hs[eiab] -= t1[mb]*Xa[maie]",
-                  "Hs[eiab] -= t1[ma]*Xb[bmie]"],
+        "Hvvvo": ["Hs[Eiab] = ovvv_s1[iEba] - t2[miab]*Hov_s1[mE]",
+                  "Hs[Eiab] += HvT[Efab]*t1[if]",
+                  "Hs[Eiab] += tau[mnab]*ooov_s3[nmiE]",
+                  "Hs[Eiab] -= ovvv_s2[mbEf]*t2[imfa]",
+                  "Hs[Eiab] += ovvv_s3[mafE]*t2x[mifb] - ovvv_s2[maEf]*t2[mifb]",
+                  "Hs[Eiab] -= t1[mb]*Xa_s3[maiE]",
+                  "Hs[Eiab] -= t1[ma]*Xb_s3[bmiE]"],
         # build_Hovoo (:324-375)
         "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + Hov[me]*t2[ijeb]",
                   "Hovoo[mbij] -= t1[nb]*Hoooo[mnij]",
@@ -96,18 +116,18 @@ class HbarEngine(object):
         "Hoooo": ["Hoooo[mnij] = oooo[mnij] + oovv[mnef]*T11[ijef]",
                   "Hoooo[mnij] += ooov[mnie]*t1[je]",
                   "Hoooo[mnij] += ooov[nmje]*t1[ie]"],
-        "Hvvvv": ["HvT[abef] = vvvv[abef] + oovv[mnab]*T11[mnef]",
-                  "HvT[abef] -= ovA[mabe]*t1[mf]",
-                  "HvT[abef] -= ovB[mabf]*t1[me]"],
+        "Hvvvv": ["HvT[Abef] = vvvv_s0[Abef] + oovv_s2[mnAb]*T11[mnef]",
+                  "HvT[Abef] -= ovA[mAbe]*t1[mf]",
+                  "HvT[Abef] -= ovB[mAbf]*t1[me]"],
         "Hovvo": ["Hovvo[mbej] = oovv[mjeb] + ovvv[mbef]*t1[jf]",
                   "Hovvo[mbej] -= t1[nb]*ooov[nmje]"],
         "Hovov": ["Hovov[mbje] = ovov[mbje] + ovvv[mbfe]*t1[jf]",
                   "Hovov[mbje] -= t1[nb]*ooov[mnje]"],
-        "Hvvvo": ["Hs[eiab] = ovvv[ieba] - t2[miab]*F0ov[me]",
-                  "Hs[eiab] += HvT[efab]*t1[if]",
-                  "Hs[eiab] += T11[mnab]*ooov[nmie]",
-                  "Hs[eiab] -= t1[mb]*ovov[maie]",
-                  "Hs[eiab] -= t1[ma]*oovv[mieb]"],
+        "Hvvvo": ["Hs[Eiab] = ovvv_s1[iEba] - t2[miab]*F0ov_s1[mE]",
+                  "Hs[Eiab] += HvT[Efab]*t1[if]",
+                  "Hs[Eiab] += T11[mnab]*ooov_s3[nmiE]",
+                  "Hs[Eiab] -= t1[mb]*ovov_s3[maiE]",
+                  "Hs[Eiab] -= t1[ma]*oovv_s2[miEb]"],
         "Hovoo": ["Hovoo[mbij] = ooov[ijmb] + F0ov[me]*t2[ijeb]",
                   "Hovoo[mbij] -= t1[nb]*Hoooo[mnij]",
                   "Hovoo[mbij] += ovvv[mbef]*T11[ijef]",
@@ -116,22 +136,21 @@ class HbarEngine(object):
     }
 
     def __init__(self, eng):
-        if eng.comm.world > 1:
-            raise ValueError("HBAR / Lambda run on one GPU for now")
-        if eng.ovvv_full is None or eng.vvvv_loc.shape[0] != eng.nv:
-            raise ValueError("HBAR needs the full <mb|ef> and <ab|ef> blocks")
+        if eng.ovvv_full is None:
+            raise ValueError("HBAR needs the full <mb|ef> block on every rank (ccwfn(..., full_ovvv=True))")
         if eng.model not in ('CCD', 'CC2', 'CCSD'):
             raise ValueError("HBAR / Lambda: models CCD, CC2, CCSD (got %r)" % (eng.model,))
         self.eng, self.be = eng, eng.be
-        o, v, dt = eng.no, eng.nv, eng.dtype
+        o, v, vl, dt = eng.no, eng.nv, eng.vl, eng.dtype
         E = lambda *s: self.be.zeros(s, dt)
+        # the v^4 and o v^3 blocks hold this rank's rows only (HvT[A,b,e,f], Hs[E,i,a,b]); the rest is replicated
         self.Hov, self.Hvv, self.Hoo = E(o, v), E(v, v), E(o, o)
-        self.Hoooo, self.HvT = E(o, o, o, o), E(v, v, v, v)
+        self.Hoooo, self.HvT = E(o, o, o, o), E(vl, v, v, v)
         self.Hvovv, self.Hooov = E(v, o, v, v), E(o, o, o, v)
         self.Hovvo, self.Hovov = E(o, v, v, o), E(o, v, o, v)
-        self.Hs, self.Hovoo = E(v, o, v, v), E(o, v, o, o)
+        self.Hs, self.Hovoo = E(vl, o, v, v), E(o, v, o, o)
         self.Xa, self.Xb = E(o, v, o, v), E(v, o, o, v)
-        self.t2x, self.ovA, self.ovB = E(o, o, v, v), E(o, v, v, v), E(o, v, v, v)
+        self.t2x, self.ovA, self.ovB = E(o, o, v, v), E(o, vl, v, v), E(o, vl, v, v)
         if eng.model == 'CC2':
             self.T11 = eng.T11
             self.t1_0, self.t2_0, self.tau_0 = E(o, v), E(o, o, v, v), E(o, o, v, v)
@@ -145,7 +164,7 @@ class HbarEngine(object):
             self.plans[name] = []
             for s in st[name]:
                 names = set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s))
-                self.plans[name] += plan(s, {k: T[k] for k in names}, eng.dcode)
+                self.plans[name] += plan(s, {k: resolve(T, k, eng) for k in names}, eng.dcode)
 
     def tensors(self):
         eng = self.eng
@@ -161,7 +180,7 @@ class HbarEngine(object):
             F0 = eng.F0
             d.update(T11=eng.T11, F0oo=F0[:o, :o], F0ov=F0[:o, o:], F0vv=F0[o:, o:],
                      t1_0=self.t1_0, t2_0=self.t2_0, tau_0=self.tau_0)
-        return {k: TRef.of(t, k) for k, t in d.items()}
+        return d
 
     def snapshot(self):
         """CC2: remember the object's own amplitudes (the engine's current ones) for the terms of
@@ -196,8 +215,8 @@ class HbarEngine(object):
             self.be.permute4(self.t2x, eng.t2, 2.0, 0.0)
             self.be.permute4(self.t2x, eng.t2.permute(1, 0, 2, 3), -1.0, 1.0)
         if not self._ov_ready:       # integrals only: formed once
-            self.be.permute4(self.ovA, eng.ovvv_full.permute(0, 3, 2, 1))
-            self.be.permute4(self.ovB, eng.ovvv_full.permute(0, 2, 3, 1))
+            self.be.permute4(self.ovA, eng.ovvv_full.permute(0, 3, 2, 1).narrow(1, eng.vlo, eng.vl))
+            self.be.permute4(self.ovB, eng.ovvv_full.permute(0, 2, 3, 1).narrow(1, eng.vlo, eng.vl))
             self._ov_ready = True
         todo = self.ORDER if only is None else [n for n in self.ORDER if n == only or n in self.DEPS.get(only, ())]
         for name in todo:
@@ -216,26 +235,29 @@ class HbarEngine(object):
 class LambdaEngine(object):
     """Lambda residuals r_L1 / r_L2 (pycc/cclambda.py:450-543) for the HBAR held by ``hbar``."""
 
+    # r1 / r2 are zeroed first and every term accumulates into this rank's rows (A) or columns (B) of
+    # the result, so that the per-rank partial residuals add up under the allreduce.
     STATEMENTS = {
-        # build_Goo / build_Gvv (cclambda.py:450-457)
+        # build_Goo / build_Gvv (cclambda.py:450-457), replicated
         "G": ["Goo[mi] = t2[mjab]*l2[ijab]",
               "Gvv[ae] = -1.0*t2[ijeb]*l2[ijab]"],
-        # r_L1 (:460-493)
-        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hs[amef] - l2[mnae]*Hovoo[iemn]",
-                 "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
-                 "r1[ia] += Gvv[ef]*Hvovv[eiaf] - 2.0*Gvv[ef]*Hvovv[eifa]",
-                 "r1[ia] += Goo[mn]*Hooov[imna] - 2.0*Goo[mn]*Hooov[mina]"],
+        # r_L1 (:460-493); Hvvvo[efam] = Hs[amef]
+        "r_L1": ["r1_s1[iA] += 2.0*Hov_s1[iA] + l1[ie]*Hvv_s1[eA] - l1_s1[mA]*Hoo[im] + l2[imef]*Hs[Amef]"
+                 " - l2_s2[mnAe]*Hovoo[iemn]",
+                 "r1_s1[iA] += 2.0*l1[me]*Hovvo_s2[ieAm] - l1[me]*Hovov_s3[iemA]",
+                 "r1_s1[iA] += Gvv[ef]*Hvovv_s2[eiAf] - 2.0*Gvv[ef]*Hvovv_s3[eifA]",
+                 "r1_s1[iA] += Goo[mn]*Hooov_s3[imnA] - 2.0*Goo[mn]*Hooov_s3[minA]"],
         # r_L2 (:495-543), before the final r + r^T; Hvvvv[efab] = HvT[abef]
-        "r_L2": ["r2[ijab] = Loovv[ijab] + 2.0*l1[ia]*Hov[jb] - l1[ja]*Hov[ib]",
-                 "r2[ijab] += 2.0*l1[ie]*Hvovv[ejab] - l1[ie]*Hvovv[ejba]",
-                 "r2[ijab] += l1[mb]*Hooov[ijma] - 2.0*l1[mb]*Hooov[jima]",
-                 "r2[ijab] += l2[ijeb]*Hvv[ea] - l2[mjab]*Hoo[im]",
-                 "r2[ijab] += 0.5*l2[mnab]*Hoooo[ijmn]",
-                 "r2[ijab] += 0.5*l2[ijef]*HvT[abef]",
-                 "r2[ijab] += 2.0*l2[mjeb]*Hovvo[ieam] - l2[mjeb]*Hovov[iema]",
-                 "r2[ijab] -= l2[mibe]*Hovov[jema]",
-                 "r2[ijab] -= l2[mieb]*Hovvo[jeam]",
-                 "r2[ijab] += Gvv[ae]*Loovv[ijeb] - Goo[mi]*Loovv[mjab]"],
+        "r_L2": ["r2_s2[ijAb] += Loovv_s2[ijAb] + 2.0*l1_s1[iA]*Hov[jb] - l1_s1[jA]*Hov[ib]",
+                 "r2_s2[ijAb] += 2.0*l1[ie]*Hvovv_s2[ejAb] - l1[ie]*Hvovv_s3[ejbA]",
+                 "r2_s3[ijaB] += l1_s1[mB]*Hooov[ijma] - 2.0*l1_s1[mB]*Hooov[jima]",
+                 "r2_s2[ijAb] += l2[ijeb]*Hvv_s1[eA] - l2_s2[mjAb]*Hoo[im]",
+                 "r2_s2[ijAb] += 0.5*l2_s2[mnAb]*Hoooo[ijmn]",
+                 "r2_s2[ijAb] += 0.5*l2[ijef]*HvT[Abef]",
+                 "r2_s2[ijAb] += 2.0*l2[mjeb]*Hovvo_s2[ieAm] - l2[mjeb]*Hovov_s3[iemA]",
+                 "r2_s2[ijAb] -= l2[mibe]*Hovov_s3[jemA]",
+                 "r2_s2[ijAb] -= l2[mieb]*Hovvo_s2[jeAm]",
+                 "r2_s2[ijAb] += Gvv_s0[Ae]*Loovv[ijeb] - Goo[mi]*Loovv_s2[mjAb]"],
     }
 
     # CC2 (:481-486, 522-524): Goo / Gvv are built but not used; Fa / Fi are the t1-dressed Fock blocks.
@@ -243,12 +265,12 @@ class LambdaEngine(object):
     # self.ccwfn.t1 / .t2): F0.., t1_0, t2_0, tau_0 - identical to the arguments inside solve_lambda,
     # different when cclambda.residuals is called with other amplitudes (real-time propagation).
     STATEMENTS_CC2 = {
-        "r_L1": ["r1[ia] = 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hs[amef] - l2[mnae]*Hovoo[iemn]",
+        "r_L1": ["r1[ia] += 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hs[amef] - l2[mnae]*Hovoo[iemn]",
                  "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
                  "Ya[nf] = l1[me]*t2_0[nmfe]",
                  "Yb[nf] = l1[me]*tau_0[mnfe]",
                  "r1[ia] += 2.0*Ya[nf]*Loovv[inaf] - 2.0*Yb[nf]*oovv[inaf] + Yb[nf]*oovv[infa]"],
-        "r_L2": ["r2[ijab] = Loovv[ijab] + 2.0*l1[ia]*Hov[jb] - l1[ja]*Hov[ib]",
+        "r_L2": ["r2[ijab] += Loovv[ijab] + 2.0*l1[ia]*Hov[jb] - l1[ja]*Hov[ib]",
                  "r2[ijab] += 2.0*l1[ie]*Hvovv[ejab] - l1[ie]*Hvovv[ejba]",
                  "r2[ijab] += l1[mb]*Hooov[ijma] - 2.0*l1[mb]*Hooov[jima]",
                  "Fa[ea] = F0vv[ea] - F0ov[ma]*t1_0[me]",      # (F_vv - F_ov^T t1)[e,a], index order as the reference uses it
@@ -268,15 +290,17 @@ class LambdaEngine(object):
         st = dict(self.STATEMENTS)
         if eng.model == 'CC2':
             st.update(self.STATEMENTS_CC2)
+        if eng.model == 'CC2' and eng.comm.world > 1:
+            raise ValueError("CC2 Lambda runs on one GPU")
         T = hbar.tensors()
         for k in ("l1", "l2", "r1", "r2", "Goo", "Gvv", "Ya", "Yb", "Fa", "Fi"):
-            T[k] = TRef.of(getattr(self, k), k)
+            T[k] = getattr(self, k)
         self.plans = {}
         for name, stmts in st.items():
             self.plans[name] = []
             for s in stmts:
                 names = set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s))
-                for L in plan(s, {k: T[k] for k in names}, eng.dcode):
+                for L in plan(s, {k: resolve(T, k, eng) for k in names}, eng.dcode):
                     L.is_ladder = "HvT[" in s
                     self.plans[name].append(L)
         self.ladder_events = None
@@ -304,10 +328,18 @@ class LambdaEngine(object):
         self.be.bind_stream()
         if self.eng.model == 'CCD':
             self.l1.zero_()
-        if name == "r_L1" and self.eng.model == 'CCD':
-            self.r1.zero_()          # cclambda.py:462-466
-            return
+        if name == "r_L1":
+            self.r1.zero_()
+            if self.eng.model == 'CCD':
+                return               # cclambda.py:462-466
+        elif name == "r_L2":
+            self.r2.zero_()
         self._launch(name)
+        # the one exchange step: sum the per-rank partial residuals
+        if name == "r_L1":
+            self.eng.comm.allreduce_(self.r1)
+        elif name == "r_L2":
+            self.eng.comm.allreduce_(self.r2)
 
     def residuals(self, symmetrize=True):
         """r1, r2 for the amplitudes in self.l1 / self.l2 (the loop body of cclambda.py:146-151)."""

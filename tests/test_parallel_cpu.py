@@ -66,6 +66,69 @@ def _worker(rank, world, port, name, q):
         dist.destroy_process_group()
 
 
+def _lambda_worker(rank, world, port, name, model, q):
+    """HBAR + Lambda with the v^4 / o v^3 blocks sharded by rows over two ranks."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.interp_backend import InterpBackend
+        from tests import lambda_checks as lc
+        import pycc_b200
+        g, z = lc.load(name)
+        tag = model.lower()
+        t1 = np.zeros_like(g["gen_t1"]) if model == "CCD" else g["gen_t1"]
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model=model, group="world", full_ovvv=True,
+                                            _backend=InterpBackend())
+            w._load(None, t1, g["gen_t2"])
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+            r1, r2 = lam.residuals(g.F, t1, g["gen_t2"], z[tag + "_l1"], z[tag + "_l2"])
+            lo, hi = w.engine.vlo, w.engine.vhi
+            d_hvvvo = float(np.abs(hb.Hvvvo.numpy() - z[tag + "_Hvvvo"][:, :, lo:hi]).max())
+            out = dict(rank=rank, rows=int(hb.engine.HvT.shape[0]), d_hvvvo=d_hvvvo,
+                       d_r1=float(np.abs(r1.numpy() - z[tag + "_rl1"]).max()),
+                       d_r2=float(np.abs(r2.numpy() - z[tag + "_rl2"]).max()))
+            w._load(None, z[tag + "_solve_t1"], z[tag + "_solve_t2"])
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+            lecc = lam.solve_lambda(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+        out.update(niter=len(lam.iteration_log), d_e=abs(lecc - float(z[tag + "_solve_lecc"])),
+                   d_l2=float(np.abs(lam.l2.numpy() - z[tag + "_solve_l2"]).max()),
+                   niter_ref=int(z[tag + "_solve_niter"]))
+        q.put(out)
+    except Exception:
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name,model", [("o4v8", "CCSD"), ("o3v5_offdiag", "CCSD"), ("o4v8", "CCD")])
+def test_two_ranks_gloo_lambda(name, model):
+    from tests.conftest import Golden
+    g = Golden(name)
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_lambda_worker, args=(r, world, port, name, model, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for d in res:
+        assert "error" not in d, d.get("error")
+    assert sum(d["rows"] for d in res) == g.nv
+    for d in res:
+        assert d["d_hvvvo"] < 1e-12 and d["d_r1"] < 1e-12 and d["d_r2"] < 1e-12
+        assert d["niter"] == d["niter_ref"] and d["d_e"] < 1e-11 and d["d_l2"] < 1e-9
+
+
 @pytest.mark.parametrize("name", ["o4v8", "o5v19_offdiag"])
 def test_two_ranks_gloo(name):
     from tests.conftest import Golden
