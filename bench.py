@@ -207,7 +207,7 @@ def run_ours(args):
         w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD(T)" if want_t else "CCSD", group=group,
                                         precision=args.precision)
     eng, be = w.engine, w.backend
-    diis = helper_diis(w.t1, w.t2, 8, args.precision, backend=be)
+    diis = helper_diis(w.t1, w.t2, 8, args.precision, backend=be, comm=w.comm)
 
     def barrier():
         torch.cuda.synchronize()
@@ -473,7 +473,7 @@ def run_lambda(args):
     blocks = device_blocks(B, o, dev, vslice=virtual_slice(v, rank, world), keep_full_ovvv=True)
     with contextlib.redirect_stdout(io.StringIO()):
         w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD", group=group, full_ovvv=True)
-        d0 = helper_diis(w.t1, w.t2, 8, "DP", backend=w.backend)
+        d0 = helper_diis(w.t1, w.t2, 8, "DP", backend=w.backend, comm=w.comm)
         for it in range(6):                      # amplitudes a few DIIS iterations from the MP2 guess
             w._iteration(d0, it + 1, 1)
         del d0
@@ -503,7 +503,7 @@ def run_lambda(args):
     sync()
     hbar_ms = max_over_ranks(h0.elapsed_time(h1) / 3)
 
-    diis = helper_diis(lam.l1, lam.l2, 8, "DP", backend=be)
+    diis = helper_diis(lam.l1, lam.l2, 8, "DP", backend=be, comm=w.comm)
 
     def step(n):
         lecc, rms = lam._iteration()

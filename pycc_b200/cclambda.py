@@ -32,7 +32,8 @@ class cclambda(object):
         eng = self.engine
         lecc = eng.pseudoenergy()
         print("\nLCC Iter %3d: LCC PseudoE = %.15f  dE = % .5E" % (0, lecc, -lecc))
-        diis = helper_diis(self.l1, self.l2, max_diis, self.ccwfn.precision, backend=self.ccwfn.backend)
+        diis = helper_diis(self.l1, self.l2, max_diis, self.ccwfn.precision, backend=self.ccwfn.backend,
+                           comm=self.ccwfn.comm)
         self.iteration_log = []
         for niter in range(1, maxiter + 1):
             lecc_last = lecc

@@ -197,7 +197,8 @@ class ccwfn(object):
         eng.set_fock(eng.F0)
         ecc = eng.energy()
         print("CC Iter %3d: CC Ecorr = %.15f  dE = % .5E  MP2" % (0, ecc, -ecc))
-        diis = helper_diis(self.t1, self.t2, max_diis, self.precision, backend=self.backend)
+        diis = helper_diis(self.t1, self.t2, max_diis, self.precision, backend=self.backend, comm=self.comm)
+        self.diis = diis
         self.iteration_log = []
         for niter in range(1, maxiter + 1):
             ecc_last = ecc

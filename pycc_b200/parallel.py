@@ -79,6 +79,33 @@ class Comm(object):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return float(t.item())
 
+    def _device(self):
+        import torch.distributed as dist
+        return torch.device("cuda", torch.cuda.current_device()) if dist.get_backend(self.group) == "nccl" \
+            else torch.device("cpu")
+
+    def allreduce_scalars(self, xs):
+        """Sum a short list of host doubles over the ranks with ONE collective (the new Gram-matrix
+        entries of a DIIS step); every rank receives identical values."""
+        if self.world <= 1:
+            return [float(x) for x in xs]
+        import torch.distributed as dist
+        t = torch.tensor([float(x) for x in xs], dtype=torch.float64, device=self._device())
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        return t.tolist()
+
+    def allgather_into(self, full, chunk):
+        """full[r*len(chunk) : (r+1)*len(chunk)] = rank r's ``chunk`` on every rank (equal lengths)."""
+        if self.world <= 1:
+            full[:chunk.numel()].copy_(chunk)
+            return
+        import torch.distributed as dist
+        if dist.get_backend(self.group) == "nccl":
+            dist.all_gather_into_tensor(full, chunk, group=self.group)
+        else:
+            dist.all_gather(list(full.split(chunk.numel())), chunk, group=self.group)
+        self.bytes_gathered = getattr(self, "bytes_gathered", 0) + full.numel() * full.element_size()
+
     def barrier(self):
         if self.world > 1:
             import torch.distributed as dist

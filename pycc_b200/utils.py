@@ -24,9 +24,15 @@ class helper_diis(object):
     History vectors live in device memory; the Gram matrix entries are fixed-order FP64 dot
     products (``pccb_dot``), each computed once and cached; the (m+1)x(m+1) solve is done on the
     host in FP64 for both precisions (the reference's SP mode solves in float32, :104-105).
+
+    Several GPUs (``comm``, SURVEY.md 8(e) "DIIS" row): the history is SLICED - rank g keeps only
+    elements [g*chunk, (g+1)*chunk) of every amplitude / error vector (1/world of the memory and of
+    the axpby / dot / lincomb traffic).  The new Gram entries of an iteration are partial dot products,
+    summed by ONE allreduce of <= max_diis doubles; every rank then solves the same small system,
+    extrapolates its slice, and one allgather rebuilds the full (t1, t2) on every rank.
     """
 
-    def __init__(self, t1, t2, max_diis, precision='DP', backend=None):
+    def __init__(self, t1, t2, max_diis, precision='DP', backend=None, comm=None):
         if backend is None:
             raise _lib.EngineError("helper_diis needs the engine back end that owns t1/t2")
         self.be = backend
@@ -36,10 +42,22 @@ class helper_diis(object):
         self.shape1, self.shape2 = tuple(t1.shape), tuple(t2.shape)
         self.dtype = t2.dtype
         self.diis_size = 0
+        self.comm = comm if (comm is not None and comm.world > 1) else None
+        n = self.n1 + self.n2
+        if self.comm is None:
+            self.lo, self.hi, self.chunk = 0, n, n
+        else:
+            w = self.comm.world
+            self.chunk = ((n + w - 1) // w + 1) // 2 * 2        # even: slices stay 16-byte aligned
+            self.lo = min(n, self.comm.rank * self.chunk)
+            self.hi = min(n, self.lo + self.chunk)
+            # gathered extrapolated vector (world * chunk >= n; the tail is padding)
+            self._full = self.be.zeros((w * self.chunk,), self.dtype) if max_diis > 0 else None
         # every history vector the bookkeeping can hold at once (max_diis+2 amplitude vectors,
         # max_diis+1 error vectors, the extrapolated one) is allocated now and recycled, so no
-        # device allocation happens inside the iteration
-        self._pool = [self.be.empty((self.n1 + self.n2,), self.dtype) for _ in range(2 * max_diis + 4)] \
+        # device allocation happens inside the iteration.  Zero-filled: the padding of the last
+        # rank's slice must not contribute to the dot products.
+        self._pool = [self.be.zeros((self.chunk,), self.dtype) for _ in range(2 * max_diis + 4)] \
             if max_diis > 0 else []
         self.diis_vals = []
         self.old = None
@@ -53,16 +71,22 @@ class helper_diis(object):
         self._next_id = 0
 
     def _alloc(self):
-        return self._pool.pop() if self._pool else self.be.empty((self.n1 + self.n2,), self.dtype)
+        return self._pool.pop() if self._pool else self.be.zeros((self.chunk,), self.dtype)
 
     def _release(self, v):
         if v is not None and not any(v is x for x in self.diis_vals) and v is not self.old:
             self._pool.append(v)
 
     def _pack(self, t1, t2):
+        """This rank's slice [lo, hi) of the concatenated (t1, t2) vector."""
         v = self._alloc()
-        v[:self.n1].copy_(t1.reshape(-1))
-        v[self.n1:].copy_(t2.reshape(-1))
+        lo, hi, n1 = self.lo, self.hi, self.n1
+        if lo < n1:
+            e = min(hi, n1)
+            v[:e - lo].copy_(t1.reshape(-1)[lo:e])
+        if hi > n1:
+            b = max(lo, n1)
+            v[b - lo:hi - lo].copy_(t2.reshape(-1)[b - n1:hi - n1])
         return v
 
     def add_error_vector(self, t1, t2):
@@ -90,14 +114,18 @@ class helper_diis(object):
             self._gram = {k: v for k, v in self._gram.items() if dead not in k}
         self.diis_size = m = len(self.diis_errors)
         self.be.bind_stream()
+        # Gram entries not seen before (in steady state: the m products with the newest error vector)
+        missing = [(p, q) for p in range(m) for q in range(p, m) if (self._ids[p], self._ids[q]) not in self._gram]
+        vals = [self.be.dot(self.diis_errors[p], self.diis_errors[q]) for (p, q) in missing]
+        if self.comm is not None and vals:
+            vals = self.comm.allreduce_scalars(vals)      # partial dot products of the slices
+        for (p, q), x in zip(missing, vals):
+            self._gram[(self._ids[p], self._ids[q])] = x
         B = -np.ones((m + 1, m + 1))
         B[-1, -1] = 0.0
         for p in range(m):
             for q in range(p, m):
-                key = (self._ids[p], self._ids[q])
-                if key not in self._gram:
-                    self._gram[key] = self.be.dot(self.diis_errors[p], self.diis_errors[q])
-                B[p, q] = B[q, p] = self._gram[key]
+                B[p, q] = B[q, p] = self._gram[(self._ids[p], self._ids[q])]
         B[:-1, :-1] /= np.abs(B[:-1, :-1]).max()
         resid = np.zeros(m + 1)
         resid[-1] = -1.0
@@ -107,8 +135,13 @@ class helper_diis(object):
         prev, self.old = self.old, new
         self._release(prev)
         # the caller's amplitude tensors are updated in place (they are the engine's buffers)
-        t1.copy_(new[:self.n1].reshape(self.shape1))
-        t2.copy_(new[self.n1:].reshape(self.shape2))
+        if self.comm is None:
+            full = new
+        else:
+            self.comm.allgather_into(self._full, new)
+            full = self._full
+        t1.copy_(full[:self.n1].reshape(self.shape1))
+        t2.copy_(full[self.n1:self.n1 + self.n2].reshape(self.shape2))
         return t1, t2
 
 

@@ -57,7 +57,9 @@ def _worker(rank, world, port, name, q):
                    niter=len(w.iteration_log), d_e=abs(e - float(g["solve_eccsd_t_total"])),
                    d_t2=float(np.abs(w.t2.numpy() - g["solve_t2"]).max()),
                    vvvv_rows=int(w.engine.vvvv_loc.shape[0]), npairs=len(pycc_b200.cctriples._engine(w).my_pairs()),
-                   reduced=w.comm.bytes_reduced)
+                   reduced=w.comm.bytes_reduced, gathered=getattr(w.comm, 'bytes_gathered', 0),
+                   diis_chunk=w.diis.chunk, diis_n=w.diis.n1 + w.diis.n2,
+                   diis_pool=max(int(x.numel()) for x in w.diis.diis_vals + w.diis.diis_errors))
         q.put(out)
     except Exception as exc:      # surface the failure in the parent
         import traceback
@@ -155,6 +157,9 @@ def test_two_ranks_gloo(name):
         assert d["niter"] == g["solve_iter_log"].shape[0]
         assert d["d_e"] < 1e-11 and d["d_t2"] < 1e-10
         assert d["reduced"] > 0
+        # DIIS history is sliced over the ranks: half-length vectors, one allgather per step
+        assert d["diis_chunk"] * world >= d["diis_n"] and d["diis_chunk"] <= d["diis_n"] // 2 + 2
+        assert d["diis_pool"] == d["diis_chunk"] and d["gathered"] > 0
 
 
 def test_partition_helpers():
