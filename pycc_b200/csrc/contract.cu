@@ -715,6 +715,317 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     }   // tile loop
 }
 
+// ---- warp-specialised variant with an asynchronous epilogue ---------------------------------------
+// For short contractions (a few dozen k-tiles per output tile: the (T) / CC3 W build with
+// K = 2(v + o), r2 += Wmnij tau with K = o^2) the consumers' own epilogue - 8*MI strided stores per
+// thread, twice that with beta != 0 - is 15-30 % of the tile time and leaves the FP64 pipe idle
+// (ncu: 81 % / 70 % busy on the (T) launches).  Here the consumers only dump their accumulators
+// into a shared staging tile (STS) and go straight on to the next tile's k-loop; a fourth
+// warpgroup drains the staging tile to global memory (alpha / beta / gamma, compound output
+// strides) with the lanes laid along whichever output direction is contiguous, so the
+// read-modify-write of C is coalesced and overlaps the next tile's DMMAs.
+constexpr int NEPI = 128, NTHREADS_WSE = NCONS + NPROD + NEPI;
+constexpr int SPITCH = BN + 1;      // staging pitch (doubles): odd, so column reads are conflict free
+constexpr int WSE_MAX_KT = 64;      // beyond this the epilogue is < 5 % of the tile and the plain kernel has more stages
+template <int MI> constexpr int wse_stages() { return MI <= 5 ? 4 : 3; }
+
+template <int VEC, int MI>
+__global__ void __launch_bounds__(NTHREADS_WSE, 1) contract_f64_wse_kernel(const __grid_constant__ DParams p) {
+    constexpr int BM = 16 * MI;
+    constexpr int PMA = BM + 4, PMB = BN + 4;
+    constexpr int A_STAGE = (BM * PK > BK * PMA) ? BM * PK : BK * PMA;   // doubles
+    constexpr int B_STAGE = (BN * PK > BK * PMB) ? BN * PK : BK * PMB;
+    constexpr int S = (MI <= 5) ? 4 : 3;     // = wse_stages<MI>()
+
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double* sA = reinterpret_cast<double*>(smem_raw);
+    double* sB = sA + S * A_STAGE;
+    double* stg = sB + S * B_STAGE;                                      // [BM][SPITCH]
+    long long* rowA = reinterpret_cast<long long*>(stg + BM * SPITCH);
+    long long* rowB = rowA + BM;
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(rowB + BN);   // full[S], empty[S], staged, drained
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned gm = (p.M + BM - 1) / BM, gn = (p.N + BN - 1) / BN;
+    const long long ntiles = (long long)gm * gn * p.nz;     // splits == 1 (host): z is the batch index
+
+    const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
+    const unsigned sB_s = (unsigned)__cvta_generic_to_shared(sB);
+    const unsigned full_s = (unsigned)__cvta_generic_to_shared(bars);
+    const unsigned empty_s = full_s + 8 * S;
+    const unsigned staged_s = empty_s + 8 * S, drained_s = staged_s + 8;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            mbar_init(full_s + 8 * s, NPROD);
+            mbar_init(empty_s + 8 * s, NCONS / 32);
+        }
+        mbar_init(staged_s, NCONS / 32);
+        mbar_init(drained_s, NEPI / 32);
+    }
+    __syncthreads();
+
+    auto seg_of = [&](int kt) {
+        int s = 0;
+#pragma unroll
+        for (int q = 1; q < PCCB_MAX_SEGMENTS; ++q)
+            if (q < p.nseg && kt >= p.seg[q].kt_begin) s = q;
+        return s;
+    };
+
+    if (warp >= (NCONS + NPROD) / 32) {
+        // ================================ epilogue warps ================================
+        // (no D operand here: the host routes gamma * D contractions to the plain kernel)
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 88;\n");
+        const int ew = (tid - (NCONS + NPROD)) >> 5;
+        const bool use_beta = p.beta != 0.0;
+        const bool along_m = p.cm.s_lo == 1 && p.cn.s_lo != 1;     // lanes along the contiguous output direction
+        const double alpha = p.alpha, beta = p.beta;
+        unsigned lt = 0;
+#pragma unroll 1
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+            const unsigned mx = (unsigned)(tile % gm);
+            const long long rest = tile / gm;
+            const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+            const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
+            double* Cb = p.C + (rest / gn) * p.c_batch;
+            mbar_wait(staged_s, lt & 1);
+            if (!along_m) {
+                // a warp takes rows ew, ew+4, ...; its lanes cover the 128 columns in 4 passes
+                constexpr int CP = BN / 32, RU = 4;
+                long long co[CP];
+#pragma unroll
+                for (int q = 0; q < CP; ++q) {
+                    const int c = q * 32 + lane;
+                    co[q] = c < nlim ? didx_off(p.cn, n0 + c) : -1;
+                }
+                const double* sl = stg + lane;
+#pragma unroll 1
+                for (int r0 = ew; r0 < mlim; r0 += 4 * RU) {
+                    double v[RU][CP];
+                    double* crow[RU];
+#pragma unroll
+                    for (int u = 0; u < RU; ++u) {
+                        const int r = r0 + 4 * u;
+                        crow[u] = nullptr;
+                        if (r < mlim) {
+                            crow[u] = Cb + didx_off(p.cm, m0 + r);
+#pragma unroll
+                            for (int q = 0; q < CP; ++q) {
+                                double x = alpha * sl[r * SPITCH + q * 32];
+                                if (use_beta && co[q] >= 0) x += beta * crow[u][co[q]];
+                                v[u][q] = x;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < RU; ++u)
+                        if (crow[u]) {
+#pragma unroll
+                            for (int q = 0; q < CP; ++q)
+                                if (co[q] >= 0) crow[u][co[q]] = v[u][q];
+                        }
+                }
+            } else {
+                // a warp takes columns ew, ew+4, ...; its lanes cover the BM rows
+                constexpr int RP = (BM + 31) / 32, CU = 4;
+                long long ro[RP];
+#pragma unroll
+                for (int q = 0; q < RP; ++q) {
+                    const int r = q * 32 + lane;
+                    ro[q] = r < mlim ? didx_off(p.cm, m0 + r) : -1;
+                }
+                const double* sl = stg + lane * SPITCH;
+#pragma unroll 1
+                for (int c0 = ew; c0 < nlim; c0 += 4 * CU) {
+                    double v[CU][RP];
+                    double* ccol[CU];
+#pragma unroll
+                    for (int u = 0; u < CU; ++u) {
+                        const int c = c0 + 4 * u;
+                        ccol[u] = nullptr;
+                        if (c < nlim) {
+                            ccol[u] = Cb + didx_off(p.cn, n0 + c);
+#pragma unroll
+                            for (int q = 0; q < RP; ++q) {
+                                double x = 0.0;
+                                if (ro[q] >= 0) {
+                                    x = alpha * sl[q * 32 * SPITCH + c];
+                                    if (use_beta) x += beta * ccol[u][ro[q]];
+                                }
+                                v[u][q] = x;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < CU; ++u)
+                        if (ccol[u]) {
+#pragma unroll
+                            for (int q = 0; q < RP; ++q)
+                                if (ro[q] >= 0) ccol[u][ro[q]] = v[u][q];
+                        }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(drained_s);
+        }
+        return;
+    }
+
+    if (warp >= NCONS / 32) {
+        // ================================ producers ================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 56;\n");
+        const int ptid = tid - NCONS;
+        unsigned g = 0;     // k-tiles staged so far by this CTA (ring position)
+#pragma unroll 1
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+        const unsigned mx = (unsigned)(tile % gm);
+        const long long rest = tile / gm;
+        const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
+        const int batch = (int)(rest / gn);
+        const int nkt = p.total_kt;
+        const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
+        int cur_seg = -1;
+#pragma unroll 1
+        for (int it = 0; it < nkt; ++it, ++g) {
+            const int s = seg_of(it);
+            const DSeg& sg = p.seg[s];
+            if (s != cur_seg) {      // per-row offset tables of the segment (producer-private)
+                bar_sync_producers();
+                for (int r = ptid; r < BM + BN; r += NPROD) {
+                    if (r < BM) {
+                        const unsigned m = m0 + r;
+                        rowA[r] = (m < p.M) ? didx_off(sg.am, m) + (long long)batch * sg.a_batch : 0;
+                    } else {
+                        const unsigned n = n0 + (r - BM);
+                        rowB[r - BM] = (n < p.N) ? didx_off(sg.bn, n) + (long long)batch * sg.b_batch : 0;
+                    }
+                }
+                bar_sync_producers();
+                cur_seg = s;
+            }
+            const int st = g % S;
+            if (g >= S) mbar_wait_relaxed(empty_s + 8 * st, ((g - S) / S) & 1);
+            const unsigned k0 = (unsigned)(it - sg.kt_begin) * BK;
+            const unsigned ta = sA_s + st * (A_STAGE * 8), tb = sB_s + st * (B_STAGE * 8);
+            if (sg.a_mn_major) load_tile_mnmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);
+            else load_tile_kmajor<VEC, BM, NPROD>(ta, sg.A, rowA, mlim, sg.ak, k0, sg.K, ptid);
+            if (sg.b_mn_major) load_tile_mnmajor<VEC, BN, NPROD>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, ptid);
+            else load_tile_kmajor<VEC, BN, NPROD>(tb, sg.B, rowB, nlim, sg.bk, k0, sg.K, ptid);
+            cp_async_mbar_arrive(full_s + 8 * st);
+        }
+        }
+        asm volatile("cp.async.wait_all;\n" ::: "memory");
+        return;
+    }
+
+    // ================================ consumers ================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 184;\n");
+    const int wm = warp >> 2, wn = warp & 3;
+    const int frow = lane >> 2, fk = lane & 3;
+    unsigned g0 = 0;    // ring position of this tile's first k-tile
+    unsigned lt = 0;    // tiles finished by this CTA
+    const int nkt = p.total_kt;
+#pragma unroll 1
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+    double acc[MI][4][2];
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    struct FragPtr {
+        const double* ap;
+        const double* bp;
+        int a_rs, a_ks, b_rs, b_ks;
+    };
+    auto frag_ptr = [&](int it_) {
+        const DSeg& sg = p.seg[seg_of(it_)];
+        const int st = (g0 + it_) % S;
+        FragPtr f;
+        f.a_rs = sg.a_mn_major ? 1 : PK;
+        f.a_ks = sg.a_mn_major ? PMA : 1;
+        f.b_rs = sg.b_mn_major ? 1 : PK;
+        f.b_ks = sg.b_mn_major ? PMB : 1;
+        f.ap = sA + st * A_STAGE + (wm * (8 * MI) + frow) * f.a_rs + fk * f.a_ks;
+        f.bp = sB + st * B_STAGE + (wn * 32 + frow) * f.b_rs + fk * f.b_ks;
+        return f;
+    };
+
+    double a[MI], b[4], bnx[4];
+    mbar_wait(full_s + 8 * (g0 % S), (g0 / S) & 1);
+    FragPtr fp = frag_ptr(0);
+#pragma unroll
+    for (int i = 0; i < MI; ++i) a[i] = fp.ap[i * 8 * fp.a_rs];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) b[j] = fp.bp[j * 8 * fp.b_rs];
+
+    int seg_acc = -1;
+    double scale_acc = 1.0;
+#pragma unroll 1
+    for (int it = 0; it < nkt; ++it) {
+        const int st = (g0 + it) % S;
+        {
+            const int sgi = seg_of(it);
+            if (sgi != seg_acc) {
+                const double sc = p.seg[sgi].scale;
+                if (seg_acc >= 0 && sc != scale_acc) {
+                    const double r = scale_acc / sc;
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { acc[i][j][0] *= r; acc[i][j][1] *= r; }
+                }
+                seg_acc = sgi;
+                scale_acc = sc;
+            }
+        }
+        FragPtr fn = fp;
+#pragma unroll
+        for (int ks = 0; ks < BK / 4; ++ks) {
+            const int nks = (ks + 1) % (BK / 4);
+            // after the last k-tile the "next" fragments are re-read from the current stage (valid
+            // shared memory, values unused): the fragment loads stay unconditional, so the compiler
+            // has no reason to predicate / duplicate the DMMAs around them
+            if (ks == BK / 4 - 1 && it + 1 < nkt) {
+                mbar_wait(full_s + 8 * ((g0 + it + 1) % S), ((g0 + it + 1) / S) & 1);
+                fn = frag_ptr(it + 1);
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bnx[j] = fn.bp[j * 8 * fn.b_rs + nks * 4 * fn.b_ks];
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                a[i] = fn.ap[i * 8 * fn.a_rs + nks * 4 * fn.a_ks];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bnx[j];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_s + 8 * st);
+        fp = fn;
+    }
+    g0 += nkt;
+
+    // ---- hand the tile to the epilogue warps -------------------------------------------------
+    if (lt > 0) mbar_wait(drained_s, (lt - 1) & 1);      // the previous tile has left the staging buffer
+    {
+        double* sp = stg + (wm * (8 * MI) + frow) * SPITCH + wn * 32 + 2 * fk;
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                sp[i * 8 * SPITCH + j * 8] = scale_acc * acc[i][j][0];
+                sp[i * 8 * SPITCH + j * 8 + 1] = scale_acc * acc[i][j][1];
+            }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(staged_s);
+    }   // tile loop
+}
+
 // ---- TMA-staged variant (plain 2-D operands: the o^2 v^4 ladder, Wmnij, Zmbij) ------------------
 // When both operands of every segment are K-contiguous matrices with a uniform row stride, the
 // producer is ONE thread issuing two cp.async.bulk.tensor (TMA) copies per k-tile; completion is
@@ -1016,6 +1327,15 @@ constexpr size_t smem_bytes() {
            2 * STAGES * sizeof(unsigned long long) + 16;
 }
 
+template <int MI>
+constexpr size_t smem_bytes_wse() {
+    constexpr int BM = 16 * MI;
+    constexpr int A_STAGE = (BM * PK > BK * (BM + 4)) ? BM * PK : BK * (BM + 4);
+    constexpr int B_STAGE = (BN * PK > BK * (BN + 4)) ? BN * PK : BK * (BN + 4);
+    return ((size_t)wse_stages<MI>() * (A_STAGE + B_STAGE) + (size_t)BM * SPITCH) * sizeof(double) +
+           (BM + BN) * sizeof(long long) + (2 * wse_stages<MI>() + 2) * sizeof(unsigned long long) + 16;
+}
+
 bool even(long long x) { return (x & 1) == 0; }
 
 // Shared-memory layout of one operand of one segment and whether 16-byte copies are legal.
@@ -1053,6 +1373,25 @@ int launch_tile_kernel(pccb_ctx* ctx, const DParams& p, long long batch) {
     dim3 grid((unsigned)((p.M + BM - 1) / BM), (unsigned)((p.N + BN - 1) / BN), (unsigned)(batch * p.splits));
     // tuning hook: PCCB_WS=0 selects the non-specialised kernel (all 8 warps load and compute)
     static const bool use_ws = [] { const char* e = getenv("PCCB_WS"); return e ? atoi(e) != 0 : true; }();
+    // short contractions with many tiles per CTA: the variant with epilogue warps (PCCB_WSE=0 disables)
+    static const bool use_wse = [] { const char* e = getenv("PCCB_WSE"); return e ? atoi(e) != 0 : true; }();
+    if constexpr (MI >= 4 && MI <= 6) {
+        const long long ntiles = (long long)grid.x * grid.y * grid.z;
+        if (use_ws && use_wse && p.splits == 1 && !p.D && p.total_kt <= WSE_MAX_KT && ntiles >= 2ll * ctx->sm_count) {
+            constexpr size_t SMEM_E = smem_bytes_wse<MI>();
+            static bool attr_wse = false;
+            if (!attr_wse) {
+                PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_wse_kernel<VEC, MI>,
+                                                    cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_E));
+                attr_wse = true;
+            }
+            DParams q = p;
+            q.nz = (int)batch;
+            contract_f64_wse_kernel<VEC, MI><<<(unsigned)ctx->sm_count, NTHREADS_WSE, SMEM_E, ctx->stream>>>(q);
+            PCCB_CHECK_LAUNCH(ctx, "contract_f64_wse_kernel");
+            return PCCB_OK;
+        }
+    }
     if (use_ws && MI > 2) {
         static bool attr_ws = false;
         if (!attr_ws) {

@@ -42,6 +42,18 @@ CASES = [
     ("C[ijab] = A[ijef]*B[abef]", dict(A=(20, 20, 16, 16), B=(16, 16, 16, 16), C=(20, 20, 16, 16))),    # MI=5 tiles
     ("C[abc] = A[eab]*B[ce] + A2[eba]*B2[ce] - A3[mc]*B3[mab]",
      dict(A=(20, 20, 20), B=(20, 20), A2=(20, 20, 20), B2=(20, 20), A3=(6, 20), B3=(6, 20, 20), C=(20, 20, 20))),
+    # short K, >= 2 tiles per SM: the kernel with epilogue warps (MI = 5, 6, 4; outputs contiguous along
+    # M, along N and compound; the (T) W build at v = 150 in its three output orders)
+    ("C[abc] = A[eab]*B[ce] + A2[eba]*B2[ce] - A3[mc]*B3[mab]",
+     dict(A=(150, 150, 150), B=(150, 150), A2=(150, 150, 150), B2=(150, 150), A3=(7, 150), B3=(7, 150, 150),
+          C=(150, 150, 150))),
+    ("C[abc] = A[eac]*B[be] - A3[mb]*B3[mac]",
+     dict(A=(150, 150, 150), B=(150, 150), A3=(7, 150), B3=(7, 150, 150), C=(150, 150, 150))),
+    ("C[abc] = A[ebc]*B[ae] - A3[ma]*B3[mbc]",
+     dict(A=(150, 150, 150), B=(150, 150), A3=(7, 150), B3=(7, 150, 150), C=(150, 150, 150))),
+    ("C[mn] = A[mk]*B[nk]", dict(A=(90, 200), B=(38011, 200), C=(90, 38011))),
+    ("C[nm] = A[km]*B[kn]", dict(A=(100, 60), B=(100, 38002), C=(38002, 60))),
+    ("C[nm] = A[mk]*B[nk]", dict(A=(157, 300), B=(24000, 300), C=(24000, 157))),
 ]
 
 
