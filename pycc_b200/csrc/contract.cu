@@ -982,6 +982,15 @@ __global__ void __launch_bounds__(NTHREADS_WSE, 1) contract_f64_wse_kernel(const
             }
         }
         FragPtr fn = fp;
+        // k-steps (of 4) of this k-tile that hold data: the tail of a segment is zero-filled by the
+        // producers, and whole zero steps are skipped (K = o = 20 needs 5 steps, not 8)
+        int nsteps = BK / 4;
+        {
+            const DSeg& sg = p.seg[seg_acc];
+            const unsigned left = sg.K - (unsigned)(it - sg.kt_begin) * BK;
+            if (left < (unsigned)BK) nsteps = (int)((left + 3) >> 2);
+        }
+        if (nsteps == BK / 4) {
 #pragma unroll
         for (int ks = 0; ks < BK / 4; ++ks) {
             const int nks = (ks + 1) % (BK / 4);
@@ -1002,6 +1011,29 @@ __global__ void __launch_bounds__(NTHREADS_WSE, 1) contract_f64_wse_kernel(const
             }
 #pragma unroll
             for (int j = 0; j < 4; ++j) b[j] = bnx[j];
+        }
+        } else {
+            // partial k-tile (rare: the last one of a segment): plain step loop, then the hand-over to
+            // the next k-tile's first fragments
+#pragma unroll 1
+            for (int ks = 0; ks < nsteps; ++ks) {
+                const bool last = ks + 1 == nsteps;
+                if (last && it + 1 < nkt) {
+                    mbar_wait(full_s + 8 * ((g0 + it + 1) % S), ((g0 + it + 1) / S) & 1);
+                    fn = frag_ptr(it + 1);
+                }
+                const int nks = last ? 0 : ks + 1;
+#pragma unroll
+                for (int j = 0; j < 4; ++j) bnx[j] = fn.bp[j * 8 * fn.b_rs + nks * 4 * fn.b_ks];
+#pragma unroll
+                for (int i = 0; i < MI; ++i) {
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                    a[i] = fn.ap[i * 8 * fn.a_rs + nks * 4 * fn.a_ks];
+                }
+#pragma unroll
+                for (int j = 0; j < 4; ++j) b[j] = bnx[j];
+            }
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(empty_s + 8 * st);

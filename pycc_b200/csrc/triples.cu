@@ -53,9 +53,19 @@ __device__ __forceinline__ double brick_at(const double* s, int x, int y, int z)
     return s[(x * TB_ + y) * (TB_ + 1) + z];
 }
 
+// Shared-memory staging of the disconnected part: for the six v x v matrices
+//   m = 0..5 : <ij|..>, <ik|..>, <jk|..>, t2[ij], t2[ik], t2[jk]
+// the expression reads element (x,y) at every ordered pair of the three brick ranges, i.e. six 8x8
+// blocks per matrix: AB, BA (fixed for the CTA) and AC, CA, BC, CB (per c-tile).  Each block is
+// fetched once per CTA / c-tile with 64-byte runs (3 loads per thread per c-tile) instead of the 36
+// scattered global loads per element the direct evaluation needs.
+constexpr int GPITCH = TB_ + 1;
+constexpr int GBLK = TB_ * GPITCH;      // padded [8][9]
+
 template <typename T>
 __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_constant__ TriplesArgs<T> p) {
     __shared__ double sW[6][BRICK];
+    __shared__ double sG[36][GBLK];       // [matrix * 6 + pair type][8][9]
     __shared__ double sred[16];
     const int TBk = blockIdx.x, TAk = blockIdx.y, t = blockIdx.z;
     if (TBk > TAk) return;
@@ -65,18 +75,18 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
     const int i = p.ijk[3 * t], j = p.ijk[3 * t + 1], k = p.ijk[3 * t + 2];
     const T* W = p.W + (long long)t * nv * nv * nv;
     const long long nvv = (long long)nv * nv;
-    const T* g_ij = p.g + ((long long)i * no + j) * nvv;
-    const T* g_ik = p.g + ((long long)i * no + k) * nvv;
-    const T* g_jk = p.g + ((long long)j * no + k) * nvv;
-    const T* t_ij = p.t2 + ((long long)i * no + j) * nvv;
-    const T* t_ik = p.t2 + ((long long)i * no + k) * nvv;
-    const T* t_jk = p.t2 + ((long long)j * no + k) * nvv;
-    const T* t1i = p.t1 + (long long)i * nv;
-    const T* t1j = p.t1 + (long long)j * nv;
-    const T* t1k = p.t1 + (long long)k * nv;
-    const T* fi = p.fov + (long long)i * p.ld_fov;
-    const T* fj = p.fov + (long long)j * p.ld_fov;
-    const T* fk = p.fov + (long long)k * p.ld_fov;
+    // matrix m = 0..5 : <ij|..>, <ik|..>, <jk|..>, t2[ij], t2[ik], t2[jk];  vector m (its partner in the
+    // disconnected part): t1[k], t1[j], t1[i], f[k], f[j], f[i]
+    auto matp = [&](int m) -> const T* {
+        const int mm = m >= 3 ? m - 3 : m;
+        const int x = mm == 2 ? j : i, y = mm == 0 ? j : k;
+        return (m >= 3 ? p.t2 : p.g) + ((long long)x * no + y) * nvv;
+    };
+    auto vecp = [&](int m) -> const T* {
+        const int mm = m >= 3 ? m - 3 : m;
+        const int x = mm == 0 ? k : (mm == 1 ? j : i);
+        return m >= 3 ? p.fov + (long long)x * p.ld_fov : p.t1 + (long long)x * nv;
+    };
     const double eocc = (double)p.eps[i] + (double)p.eps[j] + (double)p.eps[k];
     const double occ = 2.0 - (double)((i == j) + (i == k) + (j == k));
 
@@ -84,10 +94,28 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
     const int a = A0 + la, b = B0 + lb;
     double esum = 0.0;
 
-    // the six permuted bricks of the NEXT c-tile are fetched into registers while the current
-    // one is being consumed from shared memory (hides the global-load latency of this
-    // HBM/L2-bound pass)
-    double nxt[6];
+    // one 8x8 block element of matrix m at (r0 + r, c0 + s), zero beyond nv
+    auto gfetch = [&](int m, int r0, int c0, int e) -> double {
+        const int r = r0 + (e >> 3), c = c0 + (e & 7);
+        return (r < nv && c < nv) ? (double)__ldg(matp(m) + (long long)r * nv + c) : 0.0;
+    };
+    // fixed blocks AB / BA: 12 blocks x 64 elements
+    for (int e = tid; e < 12 * 64; e += 512) {
+        const int q = e >> 6, m = q >> 1, pt = q & 1;
+        sG[m * 6 + pt][((e & 63) >> 3) * GPITCH + (e & 7)] = pt == 0 ? gfetch(m, A0, B0, e & 63) : gfetch(m, B0, A0, e & 63);
+    }
+    // per-thread vector values at a and b (position 0 and 1); the c values are read per c-tile
+    double va[6], vb[6];
+#pragma unroll
+    for (int m = 0; m < 6; ++m) {
+        va[m] = a < nv ? (double)vecp(m)[a] : 0.0;
+        vb[m] = b < nv ? (double)vecp(m)[b] : 0.0;
+    }
+    const double eab = (a < nv ? (double)p.eps[no + a] : 0.0) + (b < nv ? (double)p.eps[no + b] : 0.0);
+
+    // the six permuted bricks of W and the 24 c-dependent matrix blocks of the NEXT c-tile are fetched
+    // into registers while the current one is being consumed from shared memory
+    double nxt[6], gnx[3];
     auto fetch = [&](int C0) {
         nxt[0] = fetch_brick(W, nv, A0, B0, C0, tid);   // [a][b][c]
         nxt[1] = fetch_brick(W, nv, A0, C0, B0, tid);   // [a][c][b]
@@ -95,6 +123,12 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
         nxt[3] = fetch_brick(W, nv, B0, C0, A0, tid);   // [b][c][a]
         nxt[4] = fetch_brick(W, nv, C0, A0, B0, tid);   // [c][a][b]
         nxt[5] = fetch_brick(W, nv, C0, B0, A0, tid);   // [c][b][a]
+#pragma unroll
+        for (int u = 0; u < 3; ++u) {
+            const int e = tid + 512 * u, q = e >> 6, m = q >> 2, pt = q & 3;    // pt: AC, CA, BC, CB
+            const int r0 = pt == 0 ? A0 : (pt == 2 ? B0 : C0), c0 = pt == 1 ? A0 : (pt == 3 ? B0 : C0);
+            gnx[u] = gfetch(m, r0, c0, e & 63);
+        }
     };
     fetch(0);
     for (int TCk = 0; TCk <= TBk; ++TCk) {
@@ -103,6 +137,11 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
         __syncthreads();
 #pragma unroll
         for (int q = 0; q < 6; ++q) store_brick(sW[q], nxt[q], tid);
+#pragma unroll
+        for (int u = 0; u < 3; ++u) {
+            const int e = tid + 512 * u, q = e >> 6, m = q >> 2, pt = q & 3;
+            sG[m * 6 + 2 + pt][((e & 63) >> 3) * GPITCH + (e & 7)] = gnx[u];
+        }
         __syncthreads();
         if (TCk < TBk) fetch(C0 + TB_);
         if (a < nv && b < nv && c < nv && a >= b && b >= c) {
@@ -112,28 +151,34 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
             const double Wbca = brick_at(sW[3], lb, lc, la);
             const double Wcab = brick_at(sW[4], lc, la, lb);
             const double Wcba = brick_at(sW[5], lc, lb, la);
-            // disconnected part for an ordered triple (x,y,z) of virtual indices (cctriples.py:69-74)
-            auto dis = [&](int x, int y, int z) {
-                return (double)g_ij[(long long)x * nv + y] * (double)t1k[z] +
-                       (double)g_ik[(long long)x * nv + z] * (double)t1j[y] +
-                       (double)g_jk[(long long)y * nv + z] * (double)t1i[x] +
-                       (double)t_ij[(long long)x * nv + y] * (double)fk[z] +
-                       (double)t_ik[(long long)x * nv + z] * (double)fj[y] +
-                       (double)t_jk[(long long)y * nv + z] * (double)fi[x];
+            double vc[6];
+#pragma unroll
+            for (int m = 0; m < 6; ++m) vc[m] = (double)__ldg(vecp(m) + c);
+            // disconnected part for the virtual indices at positions (px,py,pz) of (a,b,c) (cctriples.py:69-74):
+            //   g_ij[x,y] t1k[z] + g_ik[x,z] t1j[y] + g_jk[y,z] t1i[x] + t_ij[x,y] fk[z] + t_ik[x,z] fj[y] + t_jk[y,z] fi[x]
+            auto blk = [&](int m, int px, int py) -> double {
+                const int pt = px == 0 ? (py == 1 ? 0 : 2) : (px == 1 ? (py == 0 ? 1 : 4) : (py == 0 ? 3 : 5));
+                return sG[m * 6 + pt][(px == 0 ? la : (px == 1 ? lb : lc)) * GPITCH + (py == 0 ? la : (py == 1 ? lb : lc))];
             };
-            const double sinv = 1.0 / (1.0 + (double)((a == b) + (a == c) + (b == c)));
-            const double Vabc = (Wabc + dis(a, b, c)) * sinv;
-            const double Vacb = (Wacb + dis(a, c, b)) * sinv;
-            const double Vbac = (Wbac + dis(b, a, c)) * sinv;
-            const double Vbca = (Wbca + dis(b, c, a)) * sinv;
-            const double Vcab = (Wcab + dis(c, a, b)) * sinv;
-            const double Vcba = (Wcba + dis(c, b, a)) * sinv;
+            auto vat = [&](int m, int pos) -> double { return pos == 0 ? va[m] : (pos == 1 ? vb[m] : vc[m]); };
+            auto dis = [&](int px, int py, int pz) -> double {
+                return blk(0, px, py) * vat(0, pz) + blk(1, px, pz) * vat(1, py) + blk(2, py, pz) * vat(2, px) +
+                       blk(3, px, py) * vat(3, pz) + blk(4, px, pz) * vat(4, py) + blk(5, py, pz) * vat(5, px);
+            };
+            const int ndel = (a == b) + (a == c) + (b == c);                  // 0, 1 or 3
+            const double sinv = ndel == 0 ? 1.0 : (ndel == 1 ? 0.5 : 0.25);    // 1 / (1 + ndel)
+            const double Vabc = (Wabc + dis(0, 1, 2)) * sinv;
+            const double Vacb = (Wacb + dis(0, 2, 1)) * sinv;
+            const double Vbac = (Wbac + dis(1, 0, 2)) * sinv;
+            const double Vbca = (Wbca + dis(1, 2, 0)) * sinv;
+            const double Vcab = (Wcab + dis(2, 0, 1)) * sinv;
+            const double Vcba = (Wcba + dis(2, 1, 0)) * sinv;
             const double X = Wabc * Vabc + Wacb * Vacb + Wbac * Vbac + Wbca * Vbca + Wcab * Vcab + Wcba * Vcba;
             const double Y = Vabc + Vbca + Vcab;
             const double Z = Vacb + Vbac + Vcba;
             const double Wc = Wabc + Wbca + Wcab;
             const double Wa = Wacb + Wbac + Wcba;
-            const double denom = eocc - (double)p.eps[no + a] - (double)p.eps[no + b] - (double)p.eps[no + c];
+            const double denom = eocc - eab - (double)p.eps[no + c];
             esum += ((Y - 2.0 * Z) * Wc + (Z - 2.0 * Y) * Wa + 3.0 * X) * occ / denom;
         }
     }
