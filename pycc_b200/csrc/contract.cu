@@ -727,6 +727,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
 constexpr int NEPI = 128, NTHREADS_WSE = NCONS + NPROD + NEPI;
 constexpr int SPITCH = BN + 1;      // staging pitch (doubles): odd, so column reads are conflict free
 constexpr int WSE_MAX_KT = 64;      // beyond this the epilogue is < 5 % of the tile and the plain kernel has more stages
+constexpr int WSE_MIN_KT = 8;       // below this the launch is a memory-bound read-modify-write of C: 8 storing warps beat 4
 template <int MI> constexpr int wse_stages() { return MI <= 5 ? 4 : 3; }
 
 template <int VEC, int MI>
@@ -1409,7 +1410,7 @@ int launch_tile_kernel(pccb_ctx* ctx, const DParams& p, long long batch) {
     static const bool use_wse = [] { const char* e = getenv("PCCB_WSE"); return e ? atoi(e) != 0 : true; }();
     if constexpr (MI >= 4 && MI <= 6) {
         const long long ntiles = (long long)grid.x * grid.y * grid.z;
-        if (use_ws && use_wse && p.splits == 1 && !p.D && p.total_kt <= WSE_MAX_KT && ntiles >= 2ll * ctx->sm_count) {
+        if (use_ws && use_wse && p.splits == 1 && !p.D && p.total_kt >= WSE_MIN_KT && p.total_kt <= WSE_MAX_KT && ntiles >= 2ll * ctx->sm_count) {
             constexpr size_t SMEM_E = smem_bytes_wse<MI>();
             static bool attr_wse = false;
             if (!attr_wse) {
@@ -1424,7 +1425,9 @@ int launch_tile_kernel(pccb_ctx* ctx, const DParams& p, long long batch) {
             return PCCB_OK;
         }
     }
-    if (use_ws && MI > 2) {
+    // skinny tiles (MI <= 2) normally run on the 2-CTA/SM kernel; a split-K reduction over a huge K with
+    // contiguous ranges (Fmi: 20 x 20 output, K = o v^2) is faster with dedicated producer warps (0.26 -> 0.15 ms)
+    if (use_ws && (MI > 2 || (p.splits > 1 && p.kchunk == 0))) {
         static bool attr_ws = false;
         if (!attr_ws) {
             PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_ws_kernel<VEC, MI>,

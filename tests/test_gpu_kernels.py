@@ -52,7 +52,7 @@ CASES = [
     ("C[abc] = A[ebc]*B[ae] - A3[ma]*B3[mbc]",
      dict(A=(150, 150, 150), B=(150, 150), A3=(7, 150), B3=(7, 150, 150), C=(150, 150, 150))),
     ("C[mn] = A[mk]*B[nk]", dict(A=(90, 200), B=(38011, 200), C=(90, 38011))),
-    ("C[nm] = A[km]*B[kn]", dict(A=(100, 60), B=(100, 38002), C=(38002, 60))),
+    ("C[nm] = A[km]*B[kn]", dict(A=(137, 60), B=(137, 38002), C=(38002, 60))),
     ("C[nm] = A[mk]*B[nk]", dict(A=(157, 300), B=(24000, 300), C=(24000, 157))),
 ]
 
