@@ -272,6 +272,49 @@ class ccwfn(object):
         eng.set_fock(eng.F0)
         return r1, r2
 
+    # ---- host <-> device transfer of the amplitudes, sharded over the ranks -------------------------
+    # (engine-only API)  With several GPUs the amplitude vector (t1, t2) lives in host memory ONCE: rank g
+    # holds elements [lo, hi) of the flattened concatenation.  Loading copies each shard over its own
+    # PCIe link and rebuilds the replicated (t1, t2) with one allgather over NVLink; storing writes back
+    # only the rank's shard.  On one GPU the shard is the whole vector.
+    def amplitude_shard(self):
+        """(lo, hi): this rank's range of the flattened (t1, t2) vector."""
+        from .parallel import flat_chunk
+        lo, hi, _ = flat_chunk(self.t1.numel() + self.t2.numel(), self.comm.rank, self.comm.world)
+        return lo, hi
+
+    def _shard_buffers(self):
+        if getattr(self, "_shard", None) is None:
+            from .parallel import flat_chunk
+            n = self.t1.numel() + self.t2.numel()
+            lo, hi, chunk = flat_chunk(n, self.comm.rank, self.comm.world)
+            dev = self.backend.zeros((chunk,), self.engine.dtype)
+            full = self.backend.zeros((chunk * self.comm.world,), self.engine.dtype) if self.comm.world > 1 else dev
+            self._shard = (lo, hi, dev, full)
+        return self._shard
+
+    def load_amplitude_shard(self, host_shard):
+        """(t1, t2) on every rank from the ranks' host shards (``host_shard``: this rank's elements
+        [lo, hi), ideally pinned).  Asynchronous on the current stream."""
+        lo, hi, dev, full = self._shard_buffers()
+        n1 = self.t1.numel()
+        dev[:hi - lo].copy_(host_shard, non_blocking=True)
+        self.comm.allgather_into(full, dev)
+        self.t1.copy_(full[:n1].reshape(self.t1.shape))
+        self.t2.copy_(full[n1:n1 + self.t2.numel()].reshape(self.t2.shape))
+
+    def store_amplitude_shard(self, host_shard):
+        """This rank's elements [lo, hi) of the current (t1, t2) into ``host_shard``.  Asynchronous."""
+        lo, hi, dev, _ = self._shard_buffers()
+        n1 = self.t1.numel()
+        if lo < n1:
+            e = min(hi, n1)
+            dev[:e - lo].copy_(self.t1.reshape(-1)[lo:e])
+        if hi > n1:
+            b = max(lo, n1)
+            dev[b - lo:hi - lo].copy_(self.t2.reshape(-1)[b - n1:hi - n1])
+        host_shard.copy_(dev[:hi - lo], non_blocking=True)
+
     def _complex(self):
         if getattr(self, "_cplx", None) is None:
             from .complex_engine import ComplexResiduals

@@ -28,6 +28,17 @@ def virtual_slice(nv, rank, world):
     return lo, hi
 
 
+def flat_chunk(n, rank, world):
+    """(lo, hi, chunk): the slice [lo, hi) of a flat n-vector owned by ``rank`` when it is cut into
+    ``world`` equal chunks (even length, so slices stay 16-byte aligned; the last one may be short).
+    Used for the DIIS history and for host <-> device shards of the amplitude vector."""
+    if world <= 1:
+        return 0, n, n
+    chunk = ((n + world - 1) // world + 1) // 2 * 2
+    lo = min(n, rank * chunk)
+    return lo, min(n, lo + chunk), chunk
+
+
 def deal_pairs(no, rank, world):
     """Occupied pairs (i >= j) for ``rank``: longest-processing-time-first by the cost j+1
     (number of triplets k <= j), ties broken by order, so every rank gets the same list."""

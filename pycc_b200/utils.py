@@ -44,13 +44,12 @@ class helper_diis(object):
         self.diis_size = 0
         self.comm = comm if (comm is not None and comm.world > 1) else None
         n = self.n1 + self.n2
+        from .parallel import flat_chunk
         if self.comm is None:
             self.lo, self.hi, self.chunk = 0, n, n
         else:
             w = self.comm.world
-            self.chunk = ((n + w - 1) // w + 1) // 2 * 2        # even: slices stay 16-byte aligned
-            self.lo = min(n, self.comm.rank * self.chunk)
-            self.hi = min(n, self.lo + self.chunk)
+            self.lo, self.hi, self.chunk = flat_chunk(n, self.comm.rank, w)
             # gathered extrapolated vector (world * chunk >= n; the tail is padding)
             self._full = self.be.zeros((w * self.chunk,), self.dtype) if max_diis > 0 else None
         # every history vector the bookkeeping can hold at once (max_diis+2 amplitude vectors,

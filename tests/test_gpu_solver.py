@@ -223,3 +223,22 @@ def test_cc3_model(name):
     assert abs(e - float(z["cc3_solve_ecc"])) < E_TOL
     assert np.abs(w.t1.cpu().numpy() - z["cc3_solve_t1"]).max() < T_TOL
     assert np.abs(w.t2.cpu().numpy() - z["cc3_solve_t2"]).max() < T_TOL
+
+
+def test_amplitude_shard_roundtrip(golden):
+    """Engine-only API used by bench.py's end-to-end leg: the amplitude vector goes to pinned host
+    memory and back (one GPU: the shard is the whole vector) without changing a bit."""
+    g = golden
+    w = _wfn(g.F, g.blocks, g.no, "CCSD")
+    w._load(None, g["gen_t1"], g["gen_t2"])
+    lo, hi = w.amplitude_shard()
+    assert (lo, hi) == (0, w.t1.numel() + w.t2.numel())
+    host = torch.empty(hi - lo, dtype=torch.float64).pin_memory()
+    w.store_amplitude_shard(host)
+    torch.cuda.synchronize()
+    assert np.array_equal(host[:w.t1.numel()].numpy().reshape(g.no, g.nv), g["gen_t1"])
+    w.t1.zero_()
+    w.t2.zero_()
+    w.load_amplitude_shard(host)
+    torch.cuda.synchronize()
+    assert np.array_equal(w.t2.cpu().numpy(), g["gen_t2"]) and np.array_equal(w.t1.cpu().numpy(), g["gen_t1"])

@@ -53,7 +53,17 @@ def _worker(rank, world, port, name, q):
             w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model="CCSD(T)", group="world",
                                             _backend=InterpBackend())
             e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
-        out = dict(rank=rank, vslice=(lo, hi), d_r1=d_r1, d_r2=d_r2, d_et_gen=d_et_gen,
+        # host <-> device amplitude shards: store this rank's slice, wipe, reload through the allgather
+        slo, shi = w.amplitude_shard()
+        hs = torch.empty(shi - slo, dtype=torch.float64)
+        w.store_amplitude_shard(hs)
+        keep1, keep2 = w.t1.clone(), w.t2.clone()
+        w.t1.zero_()
+        w.t2.zero_()
+        w.load_amplitude_shard(hs)
+        d_shard = float(max((w.t1 - keep1).abs().max(), (w.t2 - keep2).abs().max()))
+        out = dict(rank=rank, vslice=(lo, hi), d_r1=d_r1, d_r2=d_r2, d_et_gen=d_et_gen, d_shard=d_shard,
+                   shard=(slo, shi),
                    niter=len(w.iteration_log), d_e=abs(e - float(g["solve_eccsd_t_total"])),
                    d_t2=float(np.abs(w.t2.numpy() - g["solve_t2"]).max()),
                    vvvv_rows=int(w.engine.vvvv_loc.shape[0]), npairs=len(pycc_b200.cctriples._engine(w).my_pairs()),
@@ -150,6 +160,8 @@ def test_two_ranks_gloo(name):
         assert "error" not in d, d.get("error")
     assert res[0]["vslice"][1] == res[1]["vslice"][0] and res[1]["vslice"][1] == g.nv
     assert sum(d["vvvv_rows"] for d in res) == g.nv
+    assert res[0]["shard"][0] == 0 and res[0]["shard"][1] == res[1]["shard"][0] \
+        and res[1]["shard"][1] == g.no * g.nv + g.no ** 2 * g.nv ** 2
     assert sum(d["npairs"] for d in res) == g.no * (g.no + 1) // 2
     for d in res:
         assert d["d_r1"] < 1e-12 and d["d_r2"] < 1e-12
@@ -157,6 +169,7 @@ def test_two_ranks_gloo(name):
         assert d["niter"] == g["solve_iter_log"].shape[0]
         assert d["d_e"] < 1e-11 and d["d_t2"] < 1e-10
         assert d["reduced"] > 0
+        assert d["d_shard"] == 0.0
         # DIIS history is sliced over the ranks: half-length vectors, one allgather per step
         assert d["diis_chunk"] * world >= d["diis_n"] and d["diis_chunk"] <= d["diis_n"] // 2 + 2
         assert d["diis_pool"] == d["diis_chunk"] and d["gathered"] > 0
