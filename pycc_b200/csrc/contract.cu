@@ -449,7 +449,7 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
 // full/empty mbarrier hand-shake.  The consumers' instruction stream is then DMMA-dense, and the
 // producers run up to WS_STAGES k-tiles ahead.  Registers are re-balanced with setmaxnreg
 // (producers 56, consumers 216 per thread).
-constexpr int NCONS = 256, NPROD = 128, NTHREADS_WS = NCONS + NPROD, WS_STAGES = 4;
+constexpr int NCONS = 256, NPROD = 128, NTHREADS_WS = NCONS + NPROD, WS_STAGES = 4, WS_STAGES_SKINNY = 8;
 
 __device__ __forceinline__ void bar_sync_producers() {
     asm volatile("bar.sync 1, %0;\n" ::"n"(NPROD) : "memory");
@@ -461,7 +461,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
     constexpr int PMA = BM + 4, PMB = BN + 4;
     constexpr int A_STAGE = (BM * PK > BK * PMA) ? BM * PK : BK * PMA;   // doubles
     constexpr int B_STAGE = (BN * PK > BK * PMB) ? BN * PK : BK * PMB;
-    constexpr int S = WS_STAGES;
+    constexpr int S = (MI <= 2) ? WS_STAGES_SKINNY : WS_STAGES;   // skinny tiles are bandwidth-bound: deeper ring
 
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double* sA = reinterpret_cast<double*>(smem_raw);
@@ -1361,6 +1361,16 @@ constexpr size_t smem_bytes() {
 }
 
 template <int MI>
+constexpr size_t smem_bytes_ws() {
+    constexpr int BM = 16 * MI;
+    constexpr int A_STAGE = (BM * PK > BK * (BM + 4)) ? BM * PK : BK * (BM + 4);
+    constexpr int B_STAGE = (BN * PK > BK * (BN + 4)) ? BN * PK : BK * (BN + 4);
+    constexpr int S = (MI <= 2) ? WS_STAGES_SKINNY : WS_STAGES;
+    return (size_t)S * (A_STAGE + B_STAGE) * sizeof(double) + (BM + BN) * sizeof(long long) +
+           2 * S * sizeof(unsigned long long) + 16;
+}
+
+template <int MI>
 constexpr size_t smem_bytes_wse() {
     constexpr int BM = 16 * MI;
     constexpr int A_STAGE = (BM * PK > BK * (BM + 4)) ? BM * PK : BK * (BM + 4);
@@ -1426,19 +1436,24 @@ int launch_tile_kernel(pccb_ctx* ctx, const DParams& p, long long batch) {
         }
     }
     // skinny tiles (MI <= 2) normally run on the 2-CTA/SM kernel; a split-K reduction over a huge K with
-    // contiguous ranges (Fmi: 20 x 20 output, K = o v^2) is faster with dedicated producer warps (0.26 -> 0.15 ms)
-    if (use_ws && (MI > 2 || (p.splits > 1 && p.kchunk == 0))) {
+    // contiguous ranges (Fmi: 20 x 20 output, K = o v^2) is faster on the persistent kernel with its
+    // dedicated producer warps and an 8-stage ring (0.26 -> 0.15 ms).  Routing the other skinny launches
+    // (t1 x <mb|ef>: M = o padded to 32 rows, about as much DMMA time as HBM time) there was measured
+    // and is not faster (0.30 vs 0.29 ms).
+    const bool skinny_ws = MI <= 2 && p.kchunk == 0 && p.splits > 1;
+    if (use_ws && (MI > 2 || skinny_ws)) {
+        constexpr size_t SMEM_WS = smem_bytes_ws<MI>();
         static bool attr_ws = false;
         if (!attr_ws) {
             PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_ws_kernel<VEC, MI>,
-                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+                                                cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_WS));
             attr_ws = true;
         }
         DParams q = p;
         q.nz = (int)(batch * p.splits);
         const long long ntiles = (long long)grid.x * grid.y * grid.z;
         const unsigned nctas = (unsigned)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
-        contract_f64_ws_kernel<VEC, MI><<<nctas, NTHREADS_WS, SMEM, ctx->stream>>>(q);
+        contract_f64_ws_kernel<VEC, MI><<<nctas, NTHREADS_WS, SMEM_WS, ctx->stream>>>(q);
         PCCB_CHECK_LAUNCH(ctx, "contract_f64_ws_kernel");
         return PCCB_OK;
     }
