@@ -1675,11 +1675,17 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
     PCCB_REQUIRE(ctx, (long long)d->batch * splits <= 65535, "pccb_contract: batch*splits=%lld exceeds grid.z",
                  (long long)d->batch * splits);
     p.splits = splits;
-    // round-robin chunks pay off for a few skinny tiles with many operand rows and a huge K (Lambda's
-    // l2[imef] Hvvvo[efam]: 2.3 -> 0.8 ms at (20,150)); with few rows contiguous ranges are faster
+    // round-robin chunks pay off for a few skinny tiles with many operand rows and a huge K when those
+    // rows lie far apart (>= one 2 MB page each: Lambda's l2[imef] Hs[amef], rows 8 o v^2 bytes apart:
+    // 2.2 -> 0.8 ms at (20,150)).  With rows close together (r_T1's t2s[mief] <ma|ef>: 8 v^2 bytes) the
+    // contiguous ranges of the persistent kernel are faster (0.66 -> 0.32 ms), and so they are with few rows.
     {
         const long long rows = (d->M < bm ? d->M : bm) + (d->N < BN ? d->N : BN);
-        p.kchunk = (splits > 1 && mi <= 2 && tiles <= 4 && rows >= 96) ? 8 : 0;
+        long long kmax = 0, row_stride = 0;
+        for (int s = 0; s < ns; ++s)
+            if ((long long)p.seg[s].K > kmax) { kmax = p.seg[s].K; row_stride = p.seg[s].bn.s_lo; }
+        static const bool no_kchunk = [] { const char* e = getenv("PCCB_NO_KCHUNK"); return e ? atoi(e) != 0 : false; }();
+        p.kchunk = (!no_kchunk && splits > 1 && mi <= 2 && tiles <= 4 && rows >= 96 && row_stride * 8 >= (2ll << 20)) ? 8 : 0;
     }
 
     int rc = try_tma(ctx, p, d, mi);      // plain 2-D operands: TMA-staged kernel

@@ -185,6 +185,15 @@ def test_partition_helpers():
                 assert a[1] == b[0]
             if nv % 2 == 0 and nv // 2 >= world:
                 assert all(lo % 2 == 0 for lo, _ in edges)
+    from pycc_b200.parallel import flat_chunk
+    for n in (1, 2, 7, 1000, 9003000, 257123457):
+        for world in (1, 2, 3, 8):
+            cuts = [flat_chunk(n, r, world) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == n and len({c[2] for c in cuts}) == 1
+            assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:]))
+            assert all(hi - lo <= ch for lo, hi, ch in cuts) and cuts[0][2] * world >= n
+            if world > 1:
+                assert cuts[0][2] % 2 == 0
     for no in (1, 4, 20, 30):
         for world in (1, 2, 8):
             allp = sorted(p for r in range(world) for p in deal_pairs(no, r, world))
