@@ -1567,14 +1567,18 @@ int choose_mi(long long M) {
     // tuning hook for tools/bench_contract.py: PCCB_MI=<1|2|4|5|6|8> forces the tile height
     static const int forced = [] { const char* e = getenv("PCCB_MI"); return e ? atoi(e) : 0; }();
     if (forced == 1 || forced == 2 || forced == 4 || forced == 5 || forced == 6 || forced == 8) return forced;
+    // padded rows weighted by the measured relative rate of the tile height.  Per useful row the
+    // 64...128-row tiles run at nearly the same rate (ladder, M = 1600: 13 x 128 rows 33.1 TFLOP/s,
+    // 20 x 80 rows 35.2; M = 900: 10 x 96 32.5, 15 x 64 32.4, 8 x 128 29.8), so among them padding
+    // decides; the 16- and 32-row tiles have a quarter / half of the DMMAs per fragment load and run on
+    // the non-persistent kernel: only for outputs that are skinny anyway.
     static const int cand[] = {8, 6, 5, 4, 2, 1};
+    static const double eff[9] = {0.0, 0.35, 0.60, 0.0, 0.97, 0.985, 0.99, 0.0, 1.00};
     int best = 8;
-    long long best_cost = LLONG_MAX;
+    double best_cost = 1e300;
     for (int mi : cand) {
         const long long bm = 16 * mi;
-        long long padded = ((M + bm - 1) / bm) * bm;
-        // shorter tiles re-read the B operand more often: small penalty so that 128 wins near-ties
-        long long cost = padded * 64 + padded * (8 - mi);
+        const double cost = (double)(((M + bm - 1) / bm) * bm) / eff[mi];
         if (cost < best_cost) { best_cost = cost; best = mi; }
     }
     return best;
