@@ -99,6 +99,16 @@ int pccb_synchronize(pccb_ctx* ctx);
 /* ---- operator seam: cc_contract (pycc/utils.py:162-187) --------------------------------- */
 int pccb_contract(pccb_ctx* ctx, const pccb_contraction* desc);
 
+/* Mixed-precision mode (precision='SP', pycc/ccwfn.py:189-196), tcgen05 path: an FP32 operand tensor
+ * x can be given a residual plane lo = x - trunc_tf32(x) (pccb_split_lo writes it; same layout as x).
+ * Once both operands of a plain-matrix FP32 contraction have registered planes, pccb_contract runs it
+ * as 3xTF32 on the 5th-generation tensor cores (A B ~= A B + A_lo B + A B_lo, FP32 accumulation in
+ * tensor memory); otherwise the mma.sync 3xTF32 kernel is used.  Registration is by address range:
+ * views into a registered tensor are covered. */
+int pccb_split_lo(pccb_ctx* ctx, const void* x_dev, void* lo_dev, int64_t n);
+int pccb_register_lo_plane(pccb_ctx* ctx, const void* x_dev, const void* lo_dev, int64_t n);
+int pccb_clear_lo_planes(pccb_ctx* ctx);
+
 /* ---- solver seam: element-wise and reduction pieces ------------------------------------- */
 /* out[i,j,a,b] = c0*X[i,j,a,b] + c1*X[i,j,b,a] + c2*u[i,a]*w[j,b]   (u_dev/w_dev may be NULL)
  * build_tau (pycc/ccwfn.py:408-410), 2*t2 - t2.swapaxes(2,3) (:554,556), t2 - t2.swapaxes(2,3)

@@ -142,6 +142,15 @@ class CudaBackend(object):
                                                  t1.data_ptr(), t2.data_ptr(), oovv.data_ptr(), fov.data_ptr(),
                                                  ld_fov, eps.data_ptr(), no, nv, et_dev.data_ptr()))
 
+    # -- mixed-precision mode on the tcgen05 tensor cores -------------------------------------------
+    def split_lo(self, x, lo):
+        """lo = x - trunc_tf32(x) for an FP32 tensor (same layout)."""
+        self._check(self.lib.pccb_split_lo(self.h, x.data_ptr(), lo.data_ptr(), x.numel()))
+
+    def register_lo_plane(self, x, lo):
+        """From now on FP32 contractions whose operands are views of ``x`` may use ``lo`` as its residual plane."""
+        self._check(self.lib.pccb_register_lo_plane(self.h, x.data_ptr(), lo.data_ptr(), x.numel()))
+
     def t3_combine(self, W, nk, k0, i, j, eps, no, nv, A1, A2):
         """A1 / A2 combinations of t3 = W / D for the pair (i, j), k = k0 .. k0+nk-1 (CC3)."""
         self._check(self.lib.pccb_t3_combine(self.h, dtype_code(W), W.data_ptr(), nk, k0, i, j, eps.data_ptr(),

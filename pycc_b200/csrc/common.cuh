@@ -4,8 +4,16 @@
 #include <cstdint>
 #include <cstdio>
 #include <string>
+#include <vector>
 
 #include "../../include/pyccb200.h"
+
+// an FP32 tensor [base, base + bytes) whose TF32 residual plane lo = x - trunc_tf32(x) lives at `lo`
+struct pccb_lo_plane {
+    const char* base;
+    const char* lo;
+    size_t bytes;
+};
 
 struct pccb_ctx {
     int device = 0;
@@ -18,6 +26,7 @@ struct pccb_ctx {
     double* partial_dev = nullptr;   // small library-owned scratch for fixed-order reductions
     double* result_host = nullptr;   // pinned
     size_t partial_cap = 0;          // doubles
+    std::vector<pccb_lo_plane> lo_planes;   // registered by pccb_register_lo_plane (tcgen05 3xTF32 path)
     std::string err;
 };
 
@@ -101,3 +110,7 @@ int pccb_ensure_partials(pccb_ctx* ctx, size_t ndoubles);
 
 // FP32-operand contraction (contract_f32.cu); arguments already validated by pccb_contract
 int pccb_contract_f32(pccb_ctx* ctx, const pccb_contraction* desc);
+
+// tcgen05 / TMEM 3xTF32 kernel for plain-matrix FP32 contractions whose operands have registered lo planes
+// (contract_tc05.cu): 1 = launched, 0 = not eligible, < 0 = error
+int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* desc);

@@ -845,6 +845,11 @@ int pccb_contract_f32(pccb_ctx* ctx, const pccb_contraction* d) {
         PCCB_CHECK_LAUNCH(ctx, "contract_f32_naive_kernel");
         return PCCB_OK;
     }
+    {   // big plain-matrix contractions with registered lo planes: tcgen05 / TMEM kernel (contract_tc05.cu)
+        const int rc5 = pccb_contract_f32_tc05(ctx, d);
+        if (rc5 < 0) return rc5;
+        if (rc5 == 1) return PCCB_OK;
+    }
     const int mj = choose_mj(d->M);
     const long long bm = 32 * mj;
     const long long gm = (d->M + bm - 1) / bm, gn = (d->N + BN - 1) / BN;

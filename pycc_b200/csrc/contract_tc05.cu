@@ -1,0 +1,341 @@
+// pccb_contract, FP32 operands, 5th-generation tensor cores (tcgen05 + TMEM) - the path of the
+// big plain-matrix contractions of the mixed-precision mode (precision='SP'): the o^2 v^4 ladder
+// tau[ijef] <ab|ef>, Zmbij = <mb|ef> tau[ijef], Wmnij = <mn|ef> tau[ijef]  (pycc/ccwfn.py:473-482,
+// 537, 607 with pycc's precision='SP', ccwfn.py:189-196).
+//
+// Math: 3xTF32.  tcgen05.mma kind::tf32 reads FP32 words from shared memory and IGNORES the 13
+// low mantissa bits (measured: tools/tc05_test.cu, (1 + 2^-11 + 2^-12) * 1 -> 1.0), so an FP32
+// array is its own "hi" operand.  The caller registers, per operand tensor, a second array
+// lo = x - trunc_tf32(x) (pccb_split_lo / pccb_register_lo_plane); a product is then
+//     A B  ~=  A_hi B_hi + A_lo B_hi + A_hi B_lo
+// evaluated as three K-concatenated passes (A,B), (A_lo,B), (A,B_lo) into ONE FP32 accumulator
+// tile in tensor memory.  Same accuracy model as the mma.sync kernel of contract_f32.cu (the
+// lo*lo term, 2^-22 relative, is dropped), at the tcgen05 rate: a single TF32 pass runs at
+// ~800 TFLOP/s on the ladder shape (tools/tc05_test.cu), the mma.sync kernel tops out at 92/3.
+//
+// Kernel (one 128 x 256 output tile per CTA, 192 threads):
+//   warp 0, one lane : TMA producer - cp.async.bulk.tensor.2d, 128-byte swizzle, 4-stage ring of
+//                      (128 + 256) rows x 32 floats, completion counted in bytes on the stage's mbarrier;
+//   warp 1, one lane : issues tcgen05.mma.cta_group::1.kind::tf32 (M=128, N=256, K=8; 4 per stage)
+//                      from shared-memory matrix descriptors, tcgen05.commit -> the stage's "empty"
+//                      barrier, and after the last k-block -> the "accumulator full" barrier;
+//                      warp 1 also owns the 256-column TMEM allocation;
+//   warps 2-5        : epilogue - tcgen05.ld 32 lanes x 16 columns at a time, alpha / beta / gamma D
+//                      and the compound output strides of the descriptor, thread = output row.
+// Edges: TMA zero-fills rows >= M / N and k >= K; the epilogue masks rows and columns.
+#include <cuda.h>
+
+#include <cstdlib>
+#include <cstring>
+
+#include "common.cuh"
+
+namespace {
+
+constexpr int BM = 128, BN = 256, BKF = 32;            // 32 floats = one 128-byte swizzle row
+constexpr int STAGES = 4;
+constexpr int A_BYTES = BM * BKF * 4, B_BYTES = BN * BKF * 4, STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int NTHREADS = 192;
+constexpr int TMEM_COLS = 256;
+constexpr int MAXSEG = 2;
+
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    unsigned ok;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    } while (!ok);
+}
+__device__ __forceinline__ void mbar_expect_tx(unsigned bar, unsigned bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar) : "memory");
+}
+// shared-memory matrix descriptor (cute/arch/mma_sm100_desc.hpp layout): K-major tile, 128-byte
+// swizzle, 8-row groups 1024 bytes apart, descriptor version 1
+__device__ __forceinline__ uint64_t smem_desc(unsigned addr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)2 << 61;
+    return d;
+}
+__device__ __forceinline__ void umma_tf32(unsigned tmem_d, uint64_t adesc, uint64_t bdesc, unsigned idesc, unsigned accumulate) {
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n}\n"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void umma_commit(unsigned bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
+}
+
+struct alignas(64) TcMaps {
+    CUtensorMap a[MAXSEG], alo[MAXSEG], b[MAXSEG], blo[MAXSEG];
+};
+
+struct TcParams {
+    unsigned M, N;
+    int nseg;
+    int nkb[MAXSEG];          // k-blocks (of 32) per segment
+    float* C;
+    DIdx cm, cn;
+    const float* D;
+    DIdx dm, dn;
+    float alpha, beta, gamma;
+};
+
+__global__ void __launch_bounds__(NTHREADS, 1)
+contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const unsigned raw_s = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned pad = (1024u - (raw_s & 1023u)) & 1023u;
+    const unsigned ring_s = raw_s + pad;
+    const unsigned full_s = ring_s + STAGES * STAGE_BYTES, empty_s = full_s + 8 * STAGES, tfull_s = empty_s + 8 * STAGES,
+                   slot_s = tfull_s + 8;
+    volatile unsigned* slot = reinterpret_cast<volatile unsigned*>(smem_raw + pad + STAGES * STAGE_BYTES + 16 * STAGES + 8);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const unsigned m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    int total_kb = 0;
+    for (int s = 0; s < p.nseg; ++s) total_kb += 3 * p.nkb[s];
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_s + 8 * s, 1); mbar_init(empty_s + 8 * s, 1); }
+        mbar_init(tfull_s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(slot_s), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+    const unsigned tmem = *slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int g = 0;
+            for (int s = 0; s < p.nseg; ++s)
+                for (int pass = 0; pass < 3; ++pass) {          // (A,B), (A_lo,B), (A,B_lo)
+                    const CUtensorMap* ma = pass == 1 ? &maps.alo[s] : &maps.a[s];
+                    const CUtensorMap* mb = pass == 2 ? &maps.blo[s] : &maps.b[s];
+                    for (int kb = 0; kb < p.nkb[s]; ++kb, ++g) {
+                        const int st = g % STAGES;
+                        if (g >= STAGES) mbar_wait(empty_s + 8 * st, ((g / STAGES) - 1) & 1);
+                        const unsigned bar = full_s + 8 * st;
+                        mbar_expect_tx(bar, STAGE_BYTES);
+                        tma_load_2d(ring_s + st * STAGE_BYTES, ma, kb * BKF, (int)m0, bar);
+                        tma_load_2d(ring_s + st * STAGE_BYTES + A_BYTES, mb, kb * BKF, (int)n0, bar);
+                    }
+                }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 256, M = 128
+            const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(BN >> 3) << 17) | ((unsigned)(BM >> 4) << 24);
+            for (int g = 0; g < total_kb; ++g) {
+                const int st = g % STAGES;
+                mbar_wait(full_s + 8 * st, (g / STAGES) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+                const uint64_t ad = smem_desc(ring_s + st * STAGE_BYTES), bd = smem_desc(ring_s + st * STAGE_BYTES + A_BYTES);
+#pragma unroll
+                for (int k = 0; k < BKF / 8; ++k)          // UMMA_K = 8 tf32 = 32 bytes: start address + 2 (x16 bytes)
+                    umma_tf32(tmem, ad + 2 * k, bd + 2 * k, idesc, (g > 0 || k > 0) ? 1u : 0u);
+                umma_commit(empty_s + 8 * st);
+            }
+            umma_commit(tfull_s);
+        }
+    } else {
+        // epilogue: warp w may touch TMEM lanes 32 (w % 4) .. +31; thread = one output row
+        mbar_wait(tfull_s, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+        const unsigned lane_base = (warp & 3) * 32;
+        const unsigned row = m0 + lane_base + lane;
+        const bool row_ok = row < p.M;
+        const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
+        float* crow = p.C + (row_ok ? didx_off(p.cm, row) : 0);
+        const float* drow = use_d ? p.D + (row_ok ? didx_off(p.dm, row) : 0) : nullptr;
+        const bool c_flat = p.cn.flat && p.cn.s_lo == 1, d_flat = !use_d || (p.dn.flat && p.dn.s_lo == 1);
+#pragma unroll 1
+        for (unsigned c = 0; c < BN; c += 16) {
+            unsigned v[16];
+            const unsigned taddr = tmem + (lane_base << 16) + c;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                         : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+            if (!row_ok || n0 + c >= p.N) continue;
+            float add[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const unsigned col = n0 + c + q;
+                float x = 0.f;
+                if (col < p.N) {
+                    if (use_beta) x = p.beta * crow[c_flat ? (long long)col : didx_off(p.cn, col)];
+                    if (use_d) x += p.gamma * drow[d_flat ? (long long)col : didx_off(p.dn, col)];
+                }
+                add[q] = x;
+            }
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const unsigned col = n0 + c + q;
+                if (col < p.N) crow[c_flat ? (long long)col : didx_off(p.cn, col)] = p.alpha * __uint_as_float(v[q]) + add[q];
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+    __syncthreads();
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
+}
+
+// lo[i] = x[i] - trunc_tf32(x[i])   (exact in FP32; what the tensor core drops from an FP32 word)
+__global__ void split_lo_kernel(const float* __restrict__ x, float* __restrict__ lo, long long n) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+        const float v = x[i];
+        lo[i] = v - __uint_as_float(__float_as_uint(v) & 0xffffe000u);
+    }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) != cudaSuccess ||
+            q != cudaDriverEntryPointSuccess)
+            p = nullptr;
+        return reinterpret_cast<EncodeTiledFn>(p);
+    }();
+    return fn;
+}
+
+bool make_map(CUtensorMap* m, const float* base, long long rows, long long K, long long row_stride, int box_rows) {
+    EncodeTiledFn enc = encode_fn();
+    if (!enc || row_stride < K) return false;
+    const cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)row_stride * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)BKF, (cuuint32_t)box_rows};
+    const cuuint32_t estr[2] = {1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
+// operand = K-contiguous matrix with one uniform row stride, 16-byte aligned rows
+// stride of a flat compound index (same convention as to_didx in common.cuh)
+long long row_stride_of(const pccb_cidx& c, long long extent) { return (c.div == 1 && extent > 1) ? c.s_hi : c.s_lo; }
+
+bool operand_ok(const void* base, const pccb_cidx& mn, const pccb_cidx& k, long long rows, long long K) {
+    const bool k_flat = k.div <= 1 || k.div >= K, mn_flat = mn.div <= 1 || mn.div >= rows;
+    if (!k_flat || !mn_flat || row_stride_of(k, K) != 1) return false;
+    if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return false;
+    const long long rs = row_stride_of(mn, rows);
+    return rs > 0 && (rs & 3) == 0;
+}
+
+const float* lo_of(pccb_ctx* ctx, const void* ptr) {
+    const char* q = static_cast<const char*>(ptr);
+    for (const auto& e : ctx->lo_planes)
+        if (q >= e.base && q < e.base + e.bytes) return reinterpret_cast<const float*>(e.lo + (q - e.base));
+    return nullptr;
+}
+
+}  // namespace
+
+// returns 1 when the tcgen05 kernel was launched, 0 when the contraction is not eligible, < 0 on error
+int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
+    static const bool enabled = [] { const char* e = getenv("PCCB_TC05"); return e ? atoi(e) != 0 : true; }();
+    if (!enabled || ctx->lo_planes.empty() || d->batch != 1 || d->M < BM || d->N < BN) return 0;
+    int ns = 0;
+    const pccb_segment* segs[MAXSEG];
+    for (int s = 0; s < d->nseg; ++s) {
+        const pccb_segment& g = d->seg[s];
+        if (g.K == 0 || g.scale == 0.0) continue;
+        if (ns == MAXSEG) return 0;
+        segs[ns++] = &g;
+    }
+    if (ns == 0) return 0;
+    TcParams p;
+    memset(&p, 0, sizeof(p));
+    TcMaps maps;
+    memset(&maps, 0, sizeof(maps));
+    for (int s = 0; s < ns; ++s) {
+        const pccb_segment& g = *segs[s];
+        if (g.scale != segs[0]->scale || g.K < 256) return 0;
+        if (!operand_ok(g.A_dev, g.am, g.ak, d->M, g.K) || !operand_ok(g.B_dev, g.bn, g.bk, d->N, g.K)) return 0;
+        const float* alo = lo_of(ctx, g.A_dev);
+        const float* blo = lo_of(ctx, g.B_dev);
+        if (!alo || !blo) return 0;
+        const long long ars = row_stride_of(g.am, d->M), brs = row_stride_of(g.bn, d->N);
+        if (!make_map(&maps.a[s], static_cast<const float*>(g.A_dev), d->M, g.K, ars, BM) ||
+            !make_map(&maps.alo[s], alo, d->M, g.K, ars, BM) ||
+            !make_map(&maps.b[s], static_cast<const float*>(g.B_dev), d->N, g.K, brs, BN) ||
+            !make_map(&maps.blo[s], blo, d->N, g.K, brs, BN))
+            return 0;
+        p.nkb[s] = (int)((g.K + BKF - 1) / BKF);
+    }
+    p.M = (unsigned)d->M;
+    p.N = (unsigned)d->N;
+    p.nseg = ns;
+    p.C = static_cast<float*>(d->C_dev);
+    p.cm = to_didx(d->cm, d->M);
+    p.cn = to_didx(d->cn, d->N);
+    p.D = static_cast<const float*>(d->D_dev);
+    p.dm = to_didx(d->dm, d->M);
+    p.dn = to_didx(d->dn, d->N);
+    p.alpha = (float)(d->alpha * segs[0]->scale);
+    p.beta = (float)d->beta;
+    p.gamma = d->D_dev ? (float)d->gamma : 0.f;
+    const long long gm = (d->M + BM - 1) / BM, gn = (d->N + BN - 1) / BN;
+    if (gn > 65535) return 0;
+    constexpr size_t SMEM = STAGES * STAGE_BYTES + 16 * STAGES + 16 + 1024;
+    static bool attr_set = false;
+    if (!attr_set) {
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+        attr_set = true;
+    }
+    contract_tf32x3_tc05_kernel<<<dim3((unsigned)gm, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
+    PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_kernel");
+    return 1;
+}
+
+extern "C" int pccb_split_lo(pccb_ctx* ctx, const void* x_dev, void* lo_dev, int64_t n) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, x_dev && lo_dev && n > 0, "pccb_split_lo: bad arguments");
+    long long blocks = (n + 255) / 256;
+    if (blocks > 148 * 32) blocks = 148 * 32;
+    split_lo_kernel<<<(unsigned)blocks, 256, 0, ctx->stream>>>(static_cast<const float*>(x_dev), static_cast<float*>(lo_dev), n);
+    PCCB_CHECK_LAUNCH(ctx, "split_lo_kernel");
+    return PCCB_OK;
+}
+
+extern "C" int pccb_register_lo_plane(pccb_ctx* ctx, const void* x_dev, const void* lo_dev, int64_t n) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, x_dev && lo_dev && n > 0, "pccb_register_lo_plane: bad arguments");
+    for (auto& e : ctx->lo_planes)
+        if (e.base == static_cast<const char*>(x_dev)) {
+            e.lo = static_cast<const char*>(lo_dev);
+            e.bytes = (size_t)n * sizeof(float);
+            return PCCB_OK;
+        }
+    ctx->lo_planes.push_back({static_cast<const char*>(x_dev), static_cast<const char*>(lo_dev), (size_t)n * sizeof(float)});
+    return PCCB_OK;
+}
+
+extern "C" int pccb_clear_lo_planes(pccb_ctx* ctx) {
+    if (!ctx) return PCCB_ERR_ARG;
+    ctx->lo_planes.clear();
+    return PCCB_OK;
+}

@@ -94,6 +94,19 @@ class CCSDEngine(object):
         self.r1, self.r2 = E(o, v), E(o, o, v, v)
         if self.model == 'CC2':      # t1 t1 products and the two factorised intermediates of the CC2 r_T2
             self.T11, self.Yw, self.Xv = E(o, o, v, v), E(o, o, o, vl), E(vl, v, o, v)
+        # mixed-precision mode: residual planes lo = x - trunc_tf32(x) of the operands of the big
+        # plain-matrix contractions (ladder, Zmbij, Wmnij), which then run as 3xTF32 on the tcgen05
+        # tensor cores (csrc/contract_tc05.cu).  Constants are split once, tau every iteration.
+        self._lo = None
+        if dtype == torch.float32 and hasattr(be, "split_lo"):
+            self._lo = {}
+            for name, x in (("vvvv", self.vvvv_loc), ("ovvv", self.blk["ovvv"]), ("oovv", self.blk["oovv"])):
+                lo = be.empty(tuple(x.shape), dtype)
+                be.split_lo(x, lo)
+                be.register_lo_plane(x, lo)
+                self._lo[name] = lo
+            self._lo["tau"] = be.empty(tuple(self.tau.shape), dtype)
+            be.register_lo_plane(self.tau, self._lo["tau"])
         self.cc3 = None
         self.ladder_events = None    # bench.py: list that receives (start, end) CUDA events per ladder launch
         self._build_plans()
@@ -262,6 +275,8 @@ class CCSDEngine(object):
         """tau variants and the spin-adapted t2 (build_tau, pycc/ccwfn.py:408-410; :554)."""
         be, o, v = self.be, self.no, self.nv
         be.pair_combine(self.tau, self.t2, 1.0, 0.0, self.t1, self.t1, 1.0, o, v)
+        if self._lo is not None:
+            be.split_lo(self.tau, self._lo["tau"])
         be.pair_combine(self.tauh, self.t2, 1.0, 0.0, self.t1, self.t1, 0.5, o, v)
         be.pair_combine(self.tauW, self.t2, 0.5, 0.0, self.t1, self.t1, 1.0, o, v)
         be.pair_combine(self.t2s, self.t2, 2.0, -1.0, None, None, 0.0, o, v)

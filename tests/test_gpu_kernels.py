@@ -197,3 +197,60 @@ def test_residuals_golden(be, golden, tag, naive):
         assert abs(eng.energy() - float(g[tag + "_energy"])) < 1e-12
     finally:
         be.use_naive_contract(False)
+
+
+TC05_CASES = [
+    ("C[ijab] = 0.5*A[ijef]*B[abef]", dict(A=(12, 12, 16, 16), B=(16, 16, 16, 16), C=(12, 12, 16, 16))),
+    ("C[ijab] = 0.5*A[ijef]*B[abef]", dict(A=(13, 13, 18, 18), B=(18, 18, 18, 18), C=(13, 13, 18, 18))),   # ragged M, N, K
+    ("C[mn] = A[mk]*B[nk]", dict(A=(300, 1000), B=(520, 1000), C=(300, 520))),
+    ("C[nm] = A[mk]*B[nk]", dict(A=(260, 512), B=(300, 512), C=(300, 260))),                                # strided output
+    ("C[mn] = A[mk]*B[nk] + A2[mk]*B2[nk]", dict(A=(256, 260), B=(256, 260), A2=(256, 260), B2=(256, 260), C=(256, 256))),
+]
+
+
+@pytest.mark.parametrize("case", range(len(TC05_CASES)))
+def test_contract_f32_tcgen05_vs_einsum(be, case):
+    """FP32 plain-matrix contractions whose operands have registered residual planes run on the tcgen05 /
+    TMEM kernel (3xTF32 in tensor memory); compared with an FP64 einsum of the same FP32 inputs and with
+    the mma.sync 3xTF32 kernel (same accuracy model)."""
+    from pycc_b200.dsl import parse, plan
+    from pycc_b200 import _lib
+    stmt, shapes = TC05_CASES[case]
+    g = torch.Generator(device="cpu").manual_seed(300 + case)
+    T = {k: torch.randn(s, generator=g, dtype=torch.float32).to(be.device) for k, s in shapes.items()}
+    out_name, out_idx, acc, terms = parse(stmt)
+    ref = torch.zeros(shapes[out_name], dtype=torch.float64, device=be.device)
+    mag = torch.zeros_like(ref)
+    for coef, fac in terms:
+        spec = ",".join(f[1] for f in fac) + "->" + out_idx
+        ref += coef * torch.einsum(spec, *[T[f[0]].double() for f in fac])
+        mag += abs(coef) * torch.einsum(spec, *[T[f[0]].double().abs() for f in fac])
+    # the mma.sync kernel first (no planes registered for these tensors yet)
+    T[out_name].fill_(float("nan"))
+    for L in plan(stmt, T, _lib.F32):
+        be.contract(L.desc)
+    got_sync = T[out_name].double().clone()
+    los = {}
+    for k, t in T.items():
+        if k != out_name:
+            los[k] = torch.empty_like(t)
+            be.split_lo(t, los[k])
+            be.register_lo_plane(t, los[k])
+            hi = (t.view(torch.int32) & -8192).view(torch.float32)
+            assert torch.equal(los[k], t - hi)
+    n0 = be.launch_count()
+    T[out_name].fill_(float("nan"))
+    for L in plan(stmt, T, _lib.F32):
+        be.contract(L.desc)
+    got1 = T[out_name].double().clone()
+    C0 = torch.randn(shapes[out_name], generator=g, dtype=torch.float32).to(be.device)
+    T[out_name].copy_(C0)
+    for L in plan(stmt.replace(" = ", " += ", 1), T, _lib.F32):
+        be.contract(L.desc)
+    got2 = T[out_name].double().clone()
+    be._check(be.lib.pccb_clear_lo_planes(be.h))
+    tol = 4e-6 * mag + 1e-6
+    assert ((got1 - ref).abs() <= tol).all()
+    assert ((got2 - (ref + C0.double())).abs() <= tol).all()
+    assert ((got1 - got_sync).abs() <= tol).all()
+    assert be.launch_count() - n0 == 2          # one launch each: no split-K reduction, i.e. not the mma.sync path
