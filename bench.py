@@ -250,19 +250,23 @@ def run_ours(args):
     # ---- roofline of the dominant kernel (ladder launch on this rank) ------------------------
     peak, peak_src = dmma_peak()
     if sp:
+        # the SP ladder runs on the tcgen05 kernel: TF32 issues at half the dense bf16 rate, three TF32
+        # products per FP32-accurate product
         try:
-            peak = json.load(open(os.path.join(ROOT, "profiles", "r01_peaks.json")))["mma_sync_tf32_tflops"] / 3.0
+            mp = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+            peak = float(mp["bf16_tflops"]) / 2.0 / 3.0
+            peak_src = "MEASURED_PEAKS.json dense bf16 burst %.1f TFLOP/s / 2 (TF32) / 3 (3xTF32 split)" % float(mp["bf16_tflops"])
         except Exception:
-            peak = 92.5
-        peak_src = "measured mma.sync TF32 rate / 3 (3xTF32 split), profiles/r01_peaks.json"
+            peak = 1634.5 / 6.0
+            peak_src = "fallback: dense bf16 1634.5 TFLOP/s (this pool's B200, earlier MEASURED_PEAKS.json) / 2 (TF32) / 3 (3xTF32 split)"
     vl = vslice[1] - vslice[0]
     lad_flops = 2.0 * o * o * vl * v**3
     lad_ms = sum(ladder_ms) / max(len(ladder_ms), 1)
     lad_tf = lad_flops / (lad_ms * 1e-3) / 1e12 if lad_ms > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "contract_f%s_kernel (ladder r2 += 1/2 tau <ab|ef>)" % ("32" if sp else "64"),
+    roofline = {"bound": "tensor", "kernel": "%s (ladder r2 += 1/2 tau <ab|ef>)" % ("contract_tf32x3_tc05_kernel" if sp else "contract_f64_tma_kernel"),
                 "achieved": round(lad_tf, 3), "peak": peak, "unit": "TFLOP/s", "frac": round(lad_tf / peak, 4),
                 "traffic": None, "launch_ms": round(lad_ms, 4), "flops_per_launch": lad_flops,
-                "peak_source": peak_src + (" (cuBLAS SGEMM on the same box: 63.9 TFLOP/s)" if sp else
+                "peak_source": peak_src + (" (cuBLAS SGEMM on the same box: 63.9 TFLOP/s; the mma.sync 3xTF32 kernel this replaced: 66.7)" if sp else
                                            " (FP64 has no entry in MEASURED_PEAKS.json; cuBLAS DGEMM on the "
                                            "same box: 35.5 TFLOP/s)")}
 

@@ -33,8 +33,7 @@
 namespace {
 
 constexpr int BM = 128, BN = 256, BKF = 32;            // 32 floats = one 128-byte swizzle row
-constexpr int STAGES = 4;
-constexpr int A_BYTES = BM * BKF * 4, B_BYTES = BN * BKF * 4, STAGE_BYTES = A_BYTES + B_BYTES;
+constexpr int A_BYTES = BM * BKF * 4, B_BYTES = BN * BKF * 4;
 constexpr int NTHREADS = 192;
 constexpr int TMEM_COLS = 256;
 constexpr int MAXSEG = 2;
@@ -90,8 +89,14 @@ struct TcParams {
     float alpha, beta, gamma;
 };
 
+// FUSED = false: three K-concatenated passes (A,B), (A_lo,B), (A,B_lo), 4 stages of 48 KB.
+// FUSED = true : each stage holds A, A_lo, B, B_lo of one k-block (96 KB, 2 stages) and feeds all three
+//                products, so every operand byte crosses L2 -> shared memory once instead of 1.5 times.
+template <bool FUSED>
 __global__ void __launch_bounds__(NTHREADS, 1)
 contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
+    constexpr int STAGES = FUSED ? 2 : 4;
+    constexpr int STAGE_BYTES = FUSED ? 2 * (A_BYTES + B_BYTES) : (A_BYTES + B_BYTES);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const unsigned raw_s = (unsigned)__cvta_generic_to_shared(smem_raw);
     const unsigned pad = (1024u - (raw_s & 1023u)) & 1023u;
@@ -103,7 +108,7 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const unsigned m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
     int total_kb = 0;
-    for (int s = 0; s < p.nseg; ++s) total_kb += 3 * p.nkb[s];
+    for (int s = 0; s < p.nseg; ++s) total_kb += (FUSED ? 1 : 3) * p.nkb[s];
 
     if (tid == 0) {
         for (int s = 0; s < STAGES; ++s) { mbar_init(full_s + 8 * s, 1); mbar_init(empty_s + 8 * s, 1); }
@@ -124,16 +129,20 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
         if (lane == 0) {
             int g = 0;
             for (int s = 0; s < p.nseg; ++s)
-                for (int pass = 0; pass < 3; ++pass) {          // (A,B), (A_lo,B), (A,B_lo)
+                for (int pass = 0; pass < (FUSED ? 1 : 3); ++pass) {          // (A,B), (A_lo,B), (A,B_lo)
                     const CUtensorMap* ma = pass == 1 ? &maps.alo[s] : &maps.a[s];
                     const CUtensorMap* mb = pass == 2 ? &maps.blo[s] : &maps.b[s];
                     for (int kb = 0; kb < p.nkb[s]; ++kb, ++g) {
                         const int st = g % STAGES;
                         if (g >= STAGES) mbar_wait(empty_s + 8 * st, ((g / STAGES) - 1) & 1);
-                        const unsigned bar = full_s + 8 * st;
+                        const unsigned bar = full_s + 8 * st, base = ring_s + st * STAGE_BYTES;
                         mbar_expect_tx(bar, STAGE_BYTES);
-                        tma_load_2d(ring_s + st * STAGE_BYTES, ma, kb * BKF, (int)m0, bar);
-                        tma_load_2d(ring_s + st * STAGE_BYTES + A_BYTES, mb, kb * BKF, (int)n0, bar);
+                        tma_load_2d(base, ma, kb * BKF, (int)m0, bar);
+                        tma_load_2d(base + A_BYTES, mb, kb * BKF, (int)n0, bar);
+                        if (FUSED) {
+                            tma_load_2d(base + A_BYTES + B_BYTES, &maps.alo[s], kb * BKF, (int)m0, bar);
+                            tma_load_2d(base + 2 * A_BYTES + B_BYTES, &maps.blo[s], kb * BKF, (int)n0, bar);
+                        }
                     }
                 }
         }
@@ -145,10 +154,17 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
                 const int st = g % STAGES;
                 mbar_wait(full_s + 8 * st, (g / STAGES) & 1);
                 asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
-                const uint64_t ad = smem_desc(ring_s + st * STAGE_BYTES), bd = smem_desc(ring_s + st * STAGE_BYTES + A_BYTES);
+                const unsigned base = ring_s + st * STAGE_BYTES;
+                const uint64_t ad = smem_desc(base), bd = smem_desc(base + A_BYTES);
 #pragma unroll
-                for (int k = 0; k < BKF / 8; ++k)          // UMMA_K = 8 tf32 = 32 bytes: start address + 2 (x16 bytes)
+                for (int k = 0; k < BKF / 8; ++k) {        // UMMA_K = 8 tf32 = 32 bytes: start address + 2 (x16 bytes)
                     umma_tf32(tmem, ad + 2 * k, bd + 2 * k, idesc, (g > 0 || k > 0) ? 1u : 0u);
+                    if (FUSED) {
+                        const uint64_t al = smem_desc(base + A_BYTES + B_BYTES), bl = smem_desc(base + 2 * A_BYTES + B_BYTES);
+                        umma_tf32(tmem, al + 2 * k, bd + 2 * k, idesc, 1u);
+                        umma_tf32(tmem, ad + 2 * k, bl + 2 * k, idesc, 1u);
+                    }
+                }
                 umma_commit(empty_s + 8 * st);
             }
             umma_commit(tfull_s);
@@ -267,47 +283,80 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
         segs[ns++] = &g;
     }
     if (ns == 0) return 0;
-    TcParams p;
-    memset(&p, 0, sizeof(p));
-    TcMaps maps;
-    memset(&maps, 0, sizeof(maps));
+    // K panels: with one segment and an A operand (both planes) larger than a slice of L2, the contraction
+    // is run panel by panel over K, accumulating into C (beta = 1 after the first panel).  The A panel then
+    // stays L2-resident while the big B operand streams once per panel; without this the CTAs that share
+    // operand tiles drift apart and the ladder at (40,300) read 511 GB from DRAM for 65 GB of operands.
+    static const long long panel_bytes = [] { const char* e = getenv("PCCB_TC05_PANEL_MB"); return (long long)(e ? atoi(e) : 128) << 20; }();
+    long long kpanel = 0;
+    if (ns == 1 && panel_bytes > 0) {
+        const long long a_bytes = 8ll * d->M * segs[0]->K;          // two FP32 planes
+        if (a_bytes > panel_bytes) {
+            kpanel = panel_bytes / (8ll * d->M) / BKF * BKF;
+            if (kpanel < 512) kpanel = 512;
+        }
+    }
     for (int s = 0; s < ns; ++s) {
         const pccb_segment& g = *segs[s];
         if (g.scale != segs[0]->scale || g.K < 256) return 0;
         if (!operand_ok(g.A_dev, g.am, g.ak, d->M, g.K) || !operand_ok(g.B_dev, g.bn, g.bk, d->N, g.K)) return 0;
-        const float* alo = lo_of(ctx, g.A_dev);
-        const float* blo = lo_of(ctx, g.B_dev);
-        if (!alo || !blo) return 0;
-        const long long ars = row_stride_of(g.am, d->M), brs = row_stride_of(g.bn, d->N);
-        if (!make_map(&maps.a[s], static_cast<const float*>(g.A_dev), d->M, g.K, ars, BM) ||
-            !make_map(&maps.alo[s], alo, d->M, g.K, ars, BM) ||
-            !make_map(&maps.b[s], static_cast<const float*>(g.B_dev), d->N, g.K, brs, BN) ||
-            !make_map(&maps.blo[s], blo, d->N, g.K, brs, BN))
-            return 0;
-        p.nkb[s] = (int)((g.K + BKF - 1) / BKF);
+        if (!lo_of(ctx, g.A_dev) || !lo_of(ctx, g.B_dev)) return 0;
     }
-    p.M = (unsigned)d->M;
-    p.N = (unsigned)d->N;
-    p.nseg = ns;
-    p.C = static_cast<float*>(d->C_dev);
-    p.cm = to_didx(d->cm, d->M);
-    p.cn = to_didx(d->cn, d->N);
-    p.D = static_cast<const float*>(d->D_dev);
-    p.dm = to_didx(d->dm, d->M);
-    p.dn = to_didx(d->dn, d->N);
-    p.alpha = (float)(d->alpha * segs[0]->scale);
-    p.beta = (float)d->beta;
-    p.gamma = d->D_dev ? (float)d->gamma : 0.f;
     const long long gm = (d->M + BM - 1) / BM, gn = (d->N + BN - 1) / BN;
     if (gn > 65535) return 0;
-    constexpr size_t SMEM = STAGES * STAGE_BYTES + 16 * STAGES + 16 + 1024;
+    constexpr size_t SMEM = 4 * (A_BYTES + B_BYTES) + 16 * 4 + 16 + 1024;       // both variants: 192 KB of ring
+    static const bool fused = [] { const char* e = getenv("PCCB_TC05_FUSED"); return e ? atoi(e) != 0 : true; }();
     static bool attr_set = false;
     if (!attr_set) {
-        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
         attr_set = true;
     }
-    contract_tf32x3_tc05_kernel<<<dim3((unsigned)gm, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
-    PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_kernel");
+    const long long Ktot = segs[0]->K;
+    const long long step = kpanel > 0 ? kpanel : Ktot;
+    for (long long k0 = 0; k0 < (kpanel > 0 ? Ktot : 1); k0 += step) {
+        TcParams p;
+        memset(&p, 0, sizeof(p));
+        TcMaps maps;
+        memset(&maps, 0, sizeof(maps));
+        for (int s = 0; s < ns; ++s) {
+            const pccb_segment& g = *segs[s];
+            const long long koff = kpanel > 0 ? k0 : 0;
+            const long long Kp = kpanel > 0 ? (Ktot - k0 < step ? Ktot - k0 : step) : g.K;
+            const float* a = static_cast<const float*>(g.A_dev) + koff;
+            const float* b = static_cast<const float*>(g.B_dev) + koff;
+            const float* alo = lo_of(ctx, g.A_dev) + koff;
+            const float* blo = lo_of(ctx, g.B_dev) + koff;
+            const long long ars = row_stride_of(g.am, d->M), brs = row_stride_of(g.bn, d->N);
+            if (!make_map(&maps.a[s], a, d->M, Kp, ars, BM) || !make_map(&maps.alo[s], alo, d->M, Kp, ars, BM) ||
+                !make_map(&maps.b[s], b, d->N, Kp, brs, BN) || !make_map(&maps.blo[s], blo, d->N, Kp, brs, BN)) {
+                if (k0 == 0) return 0;
+                PCCB_FAIL(ctx, PCCB_ERR_ARG, "pccb_contract (tcgen05): tensor map of K panel %lld failed", (long long)k0);
+            }
+            p.nkb[s] = (int)((Kp + BKF - 1) / BKF);
+        }
+        p.M = (unsigned)d->M;
+        p.N = (unsigned)d->N;
+        p.nseg = ns;
+        p.C = static_cast<float*>(d->C_dev);
+        p.cm = to_didx(d->cm, d->M);
+        p.cn = to_didx(d->cn, d->N);
+        p.alpha = (float)(d->alpha * segs[0]->scale);
+        if (k0 == 0) {
+            p.D = static_cast<const float*>(d->D_dev);
+            p.dm = to_didx(d->dm, d->M);
+            p.dn = to_didx(d->dn, d->N);
+            p.beta = (float)d->beta;
+            p.gamma = d->D_dev ? (float)d->gamma : 0.f;
+        } else {
+            p.beta = 1.f;
+        }
+        if (fused)
+            contract_tf32x3_tc05_kernel<true><<<dim3((unsigned)gm, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
+        else
+            contract_tf32x3_tc05_kernel<false><<<dim3((unsigned)gm, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
+        PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_kernel");
+    }
     return 1;
 }
 
