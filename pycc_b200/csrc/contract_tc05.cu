@@ -8,15 +8,16 @@
 // array is its own "hi" operand.  The caller registers, per operand tensor, a second array
 // lo = x - trunc_tf32(x) (pccb_split_lo / pccb_register_lo_plane); a product is then
 //     A B  ~=  A_hi B_hi + A_lo B_hi + A_hi B_lo
-// evaluated as three K-concatenated passes (A,B), (A_lo,B), (A,B_lo) into ONE FP32 accumulator
-// tile in tensor memory.  Same accuracy model as the mma.sync kernel of contract_f32.cu (the
+// with all three products accumulated into ONE FP32 accumulator tile in tensor memory (default:
+// every stage holds A, A_lo, B, B_lo of a k-block and feeds the three products; PCCB_TC05_FUSED=0
+// selects three K-concatenated passes instead).  Same accuracy model as the mma.sync kernel of contract_f32.cu (the
 // lo*lo term, 2^-22 relative, is dropped), at the tcgen05 rate: a single TF32 pass runs at
 // ~800 TFLOP/s on the ladder shape (tools/tc05_test.cu), the mma.sync kernel tops out at 92/3.
 //
 // Kernel (one 128 x 256 output tile per CTA, 192 threads):
-//   warp 0, one lane : TMA producer - cp.async.bulk.tensor.2d, 128-byte swizzle, 4-stage ring of
-//                      (128 + 256) rows x 32 floats, completion counted in bytes on the stage's mbarrier;
-//   warp 1, one lane : issues tcgen05.mma.cta_group::1.kind::tf32 (M=128, N=256, K=8; 4 per stage)
+//   warp 0, one lane : TMA producer - cp.async.bulk.tensor.2d, 128-byte swizzle, 2-stage ring of
+//                      2 x (128 + 256) rows x 32 floats, completion counted in bytes on the stage's mbarrier;
+//   warp 1, one lane : issues tcgen05.mma.cta_group::1.kind::tf32 (M=128, N=256, K=8; 12 per stage)
 //                      from shared-memory matrix descriptors, tcgen05.commit -> the stage's "empty"
 //                      barrier, and after the last k-block -> the "accumulator full" barrier;
 //                      warp 1 also owns the 256-column TMEM allocation;
