@@ -251,12 +251,14 @@ bool make_map(CUtensorMap* m, const float* base, long long rows, long long K, lo
 }
 
 // operand = K-contiguous matrix with one uniform row stride, 16-byte aligned rows
-// stride of a flat compound index (same convention as to_didx in common.cuh)
+// A compound index is a plain matrix dimension when it is flat (same convention as to_didx in
+// common.cuh) or when its two levels happen to be contiguous (s_hi == div * s_lo: the planner emits
+// one div per index group, e.g. (j,B) of Wr1[jBme] next to the strided (j,B) of <mj|eB>).
+bool is_flat(const pccb_cidx& c, long long extent) { return c.div <= 1 || c.div >= extent || c.s_hi == c.div * c.s_lo; }
 long long row_stride_of(const pccb_cidx& c, long long extent) { return (c.div == 1 && extent > 1) ? c.s_hi : c.s_lo; }
 
 bool operand_ok(const void* base, const pccb_cidx& mn, const pccb_cidx& k, long long rows, long long K) {
-    const bool k_flat = k.div <= 1 || k.div >= K, mn_flat = mn.div <= 1 || mn.div >= rows;
-    if (!k_flat || !mn_flat || row_stride_of(k, K) != 1) return false;
+    if (!is_flat(k, K) || !is_flat(mn, rows) || row_stride_of(k, K) != 1) return false;
     if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return false;
     const long long rs = row_stride_of(mn, rows);
     return rs > 0 && (rs & 3) == 0;

@@ -112,9 +112,12 @@ def _view(ref, idx, ext):
     return v
 
 
-def _flatten(group, views, ext, prefer_inner):
+def _flatten(group, views, ext, prefer_inner, prefer_flat=False):
     """Order the letters of one index group so that it is a <=2-level compound index in every
-    view.  Returns (total_extent, inner_extent_or_FLAT, [(s_hi, s_lo) per view])."""
+    view.  Returns (total_extent, inner_extent_or_FLAT, [(s_hi, s_lo) per view]).
+    ``prefer_flat``: among otherwise equal orders take the one whose level break is a real break in the
+    fewest views, i.e. that leaves the most operands plain matrices (the FP32 tcgen05 kernel takes
+    plain-matrix operands only; without it ties fall to the alphabetical order)."""
     letters = sorted(x for x in group if ext[x] > 1)
     total = 1
     for x in group:
@@ -123,15 +126,17 @@ def _flatten(group, views, ext, prefer_inner):
         return total, FLAT, [(0, 0) for _ in views]
     best = None
     for perm in itertools.permutations(letters):
-        breaks = []
+        breaks, nbroken = [], 0
         for q in range(len(perm) - 1):
             x, y = perm[q], perm[q + 1]
-            if not all(v.get(x, 0) == v.get(y, 0) * ext[y] for v in views):
+            bad = sum(1 for v in views if v.get(x, 0) != v.get(y, 0) * ext[y])
+            if bad:
                 breaks.append(q)
+                nbroken += bad
         if len(breaks) > 1:
             continue
         rank = prefer_inner.index(perm[-1]) if perm[-1] in prefer_inner else len(prefer_inner)
-        score = (len(breaks), rank, perm)
+        score = (len(breaks), rank, nbroken if prefer_flat else 0, perm)
         if best is None or score < best[0]:
             best = (score, perm, breaks)
     if best is None:
@@ -265,8 +270,8 @@ def plan(stmt, tensors, dtype=_lib.F64):
         bviews = [s[2] for s in segs] + [s[4] for s in segs] + [cv] + ([dv] if dv else [])
 
         def flatten_all(Ms, Ns, Bs):
-            Mt, md, ms_ = _flatten(Ms, mviews, ext, pref_m)
-            Nt, nd, ns_ = _flatten(Ns, nviews, ext, pref_n)
+            Mt, md, ms_ = _flatten(Ms, mviews, ext, pref_m, dtype == _lib.F32)
+            Nt, nd, ns_ = _flatten(Ns, nviews, ext, pref_n, dtype == _lib.F32)
             Bt, bd, bs_ = _flatten(Bs, bviews, ext, [])
             if bd != FLAT:
                 raise PlanError("batch indices %r do not flatten to one stride" % (sorted(Bs),))

@@ -94,19 +94,36 @@ class CCSDEngine(object):
         self.r1, self.r2 = E(o, v), E(o, o, v, v)
         if self.model == 'CC2':      # t1 t1 products and the two factorised intermediates of the CC2 r_T2
             self.T11, self.Yw, self.Xv = E(o, o, v, v), E(o, o, o, vl), E(vl, v, o, v)
-        # mixed-precision mode: residual planes lo = x - trunc_tf32(x) of the operands of the big
-        # plain-matrix contractions (ladder, Zmbij, Wmnij), which then run as 3xTF32 on the tcgen05
-        # tensor cores (csrc/contract_tc05.cu).  Constants are split once, tau every iteration.
+        # Mixed-precision mode.  (i) The ring-term operands are kept in PLAIN-MATRIX layouts as well
+        # (permuted o^2 v^2 copies: constants once, amplitudes every iteration), so that the five
+        # o^3 v^3 contractions are K-contiguous 2-D GEMMs like the ladder.  (ii) Every operand of those
+        # GEMMs has a residual plane lo = x - trunc_tf32(x); the plain-matrix contractions then run as
+        # 3xTF32 on the tcgen05 tensor cores (csrc/contract_tc05.cu), everything else on the mma.sync kernel.
+        import os
+        self.sp_plain = dtype == torch.float32 and self.model != 'CC2' and os.environ.get("PCCB_SP_PLAIN", "1") != "0"
         self._lo = None
+        if self.sp_plain:
+            self.oovvP, self.oovvX, self.LoovvP = E(o, v, o, v), E(o, v, o, v), E(o, v, o, v)      # [m,e,n,f]
+            be.permute4(self.oovvP, self.blk["oovv"].permute(0, 2, 1, 3))       # <mn|ef>
+            be.permute4(self.oovvX, self.blk["oovv"].permute(0, 3, 1, 2))       # <mn|fe>
+            be.permute4(self.LoovvP, self.Loovv.permute(0, 2, 1, 3))
+            self.t2sP, self.t2P, self.t2Q = E(o, v, o, v), E(o, v, o, v), E(o, v, o, v)            # [i,a,m,e]
+            self.tauWPn, self.t2Rh = E(o, vl, o, v), E(o, vl, o, v)                                # [j,B,n,f]
         if dtype == torch.float32 and hasattr(be, "split_lo"):
             self._lo = {}
-            for name, x in (("vvvv", self.vvvv_loc), ("ovvv", self.blk["ovvv"]), ("oovv", self.blk["oovv"])):
+            const = [("vvvv", self.vvvv_loc), ("ovvv", self.blk["ovvv"]), ("oovv", self.blk["oovv"])]
+            if self.sp_plain:
+                const += [("oovvP", self.oovvP), ("oovvX", self.oovvX), ("LoovvP", self.LoovvP)]
+            for name, x in const:
                 lo = be.empty(tuple(x.shape), dtype)
                 be.split_lo(x, lo)
                 be.register_lo_plane(x, lo)
                 self._lo[name] = lo
-            self._lo["tau"] = be.empty(tuple(self.tau.shape), dtype)
-            be.register_lo_plane(self.tau, self._lo["tau"])
+            varying = ["tau"] + (["t2sP", "t2P", "t2Q", "tauWPn", "t2Rh", "Wr1", "Wr2"] if self.sp_plain else [])
+            for name in varying:
+                x = getattr(self, name)
+                self._lo[name] = be.empty(tuple(x.shape), dtype)
+                be.register_lo_plane(x, self._lo[name])
         self.cc3 = None
         self.ladder_events = None    # bench.py: list that receives (start, end) CUDA events per ladder launch
         self._build_plans()
@@ -124,6 +141,9 @@ class CCSDEngine(object):
                  Wr1=self.Wr1, Wr2=self.Wr2, Zr=self.Zr, Y1=self.Y1, Y2=self.Y2, r1=self.r1, r2=self.r2)
         if self.model == 'CC2':
             d.update(T11=self.T11, Yw=self.Yw, Xv=self.Xv)
+        if self.sp_plain:
+            d.update(oovvP=self.oovvP, oovvX=self.oovvX, LoovvP=self.LoovvP, t2sP=self.t2sP, t2P=self.t2P, t2Q=self.t2Q,
+                     tauWPn=self.tauWPn, t2Rh=self.t2Rh)
         out = {}
         for nm in names:
             if nm == "vvvv_s0":
@@ -218,6 +238,21 @@ class CCSDEngine(object):
                  "r2_s2[ijAb] -= t1_s1[mA]*ooov[ijmb]"],
     }
 
+    # Mixed-precision mode: the ring terms over plain-matrix copies (see __init__), same algebra:
+    #   oovvP[menf] = <mn|ef>, oovvX[menf] = <mn|fe>, LoovvP[menf] = Loovv[mnef],
+    #   t2sP[iame] = t2s[imae], t2P[iame] = t2[imae], t2Q[jame] = t2[mjae],
+    #   tauWPn[jBnf] = -tauW[jnfB], t2Rh[jBnf] = 0.5 t2[njfB]   (factors folded in: one scale per launch)
+    STATEMENTS_SP = {
+        "Wmbej": ["Wr1[jBme] = oovv_s3[mjeB] + tauWPn[jBnf]*oovvP[menf] + t2Rh[jBnf]*LoovvP[menf]",
+                  "Wr1[jBme] += t1[jf]*ovvv_s1[mBef]",
+                  "Wr1[jBme] -= t1_s1[nB]*ooov[nmje]"],
+        "Wmbje": ["Wr2[jBme] = -1.0*ovov_s1[mBje] - tauWPn[jBnf]*oovvX[menf]",
+                  "Wr2[jBme] -= t1[jf]*ovvv_s1[mBfe]",
+                  "Wr2[jBme] += t1_s1[nB]*ooov[mnje]"],
+    }
+    R_T2_SP = {"r2_s3[ijaB] += t2s[imae]*Wr1[jBme] + t2[imae]*Wr2[jBme]": "r2_s3[ijaB] += t2sP[iame]*Wr1[jBme] + t2P[iame]*Wr2[jBme]",
+               "r2_s3[ijaB] += t2[mjae]*Wr2[iBme]": "r2_s3[ijaB] += t2Q[jame]*Wr2[iBme]"}
+
     def builder_order(self):
         """Builders run by residuals(), in the reference's order (pycc/ccwfn.py:357-366).
         CCD (:415-420, 434-439, 466-471, 488-496, 511-518, 563-573) is the CCSD algebra with
@@ -233,6 +268,9 @@ class CCSDEngine(object):
         if self.model == 'CC2':
             st.update(self.STATEMENTS_CC2)
             del st["Wmbej"], st["Wmbje"]
+        elif self.sp_plain:
+            st.update(self.STATEMENTS_SP)
+            st["r_T2"] = [self.R_T2_SP.get(x, x) for x in st["r_T2"]]
         return st
 
     def _build_plans(self):
@@ -252,6 +290,9 @@ class CCSDEngine(object):
             self.r1.zero_()
         elif name == "r_T2":
             self.r2.zero_()
+            if self._lo is not None and self.sp_plain:      # the ring intermediates are operands now
+                self.be.split_lo(self.Wr1, self._lo["Wr1"])
+                self.be.split_lo(self.Wr2, self._lo["Wr2"])
         self._launch(name)
         # the one exchange step of the iteration: sum the per-rank partial residuals
         if name == "r_T1":
@@ -275,13 +316,21 @@ class CCSDEngine(object):
         """tau variants and the spin-adapted t2 (build_tau, pycc/ccwfn.py:408-410; :554)."""
         be, o, v = self.be, self.no, self.nv
         be.pair_combine(self.tau, self.t2, 1.0, 0.0, self.t1, self.t1, 1.0, o, v)
-        if self._lo is not None:
-            be.split_lo(self.tau, self._lo["tau"])
         be.pair_combine(self.tauh, self.t2, 1.0, 0.0, self.t1, self.t1, 0.5, o, v)
         be.pair_combine(self.tauW, self.t2, 0.5, 0.0, self.t1, self.t1, 1.0, o, v)
         be.pair_combine(self.t2s, self.t2, 2.0, -1.0, None, None, 0.0, o, v)
         if self.model == 'CC2':
             be.pair_combine(self.T11, self.t2, 0.0, 0.0, self.t1, self.t1, 1.0, o, v)
+        if self.sp_plain:
+            sl = slice(self.vlo, self.vhi)
+            be.permute4(self.t2sP, self.t2s.permute(0, 2, 1, 3))
+            be.permute4(self.t2P, self.t2.permute(0, 2, 1, 3))
+            be.permute4(self.t2Q, self.t2.permute(1, 2, 0, 3))
+            be.permute4(self.tauWPn, self.tauW.permute(0, 3, 1, 2)[:, sl], -1.0)
+            be.permute4(self.t2Rh, self.t2.permute(1, 3, 0, 2)[:, sl], 0.5)
+        if self._lo is not None:
+            for name in ["tau"] + (["t2sP", "t2P", "t2Q", "tauWPn", "t2Rh"] if self.sp_plain else []):
+                be.split_lo(getattr(self, name), self._lo[name])
 
     def set_amplitudes(self, t1, t2):
         self.t1.copy_(torch.as_tensor(t1).to(self.t1.device, self.dtype))

@@ -149,6 +149,13 @@ class InterpBackend(object):
             term = ((Y - 2.0 * Z) * Wc + (Z - 2.0 * Y) * Wa + 3.0 * X) * occ / den
             et_dev[t] = float(term[(a >= b) & (b >= c)].sum())
 
+    def split_lo(self, x, lo):
+        hi = (x.view(torch.int32) & -8192).view(torch.float32)
+        lo.copy_(x - hi)
+
+    def register_lo_plane(self, x, lo):
+        pass          # the interpreter contracts the full FP32 values
+
     def t3_combine(self, W, nk, k0, i, j, eps, no, nv, A1, A2):
         e = eps.double()
         ev = e[no:]

@@ -127,3 +127,20 @@ def test_sp_mode_host_logic(golden):
     assert w.t2.dtype == torch.float32 and w.precision == "SP"
     assert abs(e - float(g["solve_eccsd"])) < 1e-6
     assert abs(e - float(g["solve_sp_ecc"])) < 5e-6
+
+
+@pytest.mark.parametrize("model", ["CCSD", "CCD"])
+def test_sp_mode_plain_matrix_ring_terms(golden, model):
+    """precision='SP' keeps the ring-term operands in plain-matrix layouts (permuted copies, factors folded
+    in; engine.STATEMENTS_SP) so that they can run on the tcgen05 kernel: same residual as the FP64
+    statements on unsymmetric amplitudes, to FP32 rounding."""
+    g = golden
+    t1 = np.zeros_like(g["gen_t1"]) if model == "CCD" else g["gen_t1"]
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, precision="SP", model=model, _backend=InterpBackend())
+        wd = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model=model, _backend=InterpBackend())
+        r1, r2 = w.residuals(g.F, t1, g["gen_t2"])
+        d1, d2 = wd.residuals(g.F, t1, g["gen_t2"])
+    assert w.engine.sp_plain and any("t2sP" in L.text for L in w.engine.plans["r_T2"])
+    assert np.abs(r2.double().numpy() - d2.numpy()).max() < 2e-6 * max(1.0, np.abs(d2.numpy()).max())
+    assert np.abs(r1.double().numpy() - d1.numpy()).max() < 2e-6
