@@ -78,6 +78,50 @@ def _worker(rank, world, port, name, q):
         dist.destroy_process_group()
 
 
+def _sp_worker(rank, world, port, name, q):
+    """Mixed-precision mode on two ranks: the plain-matrix ring-term statements with the sliced index."""
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.conftest import Golden
+        from tests.interp_backend import InterpBackend
+        import pycc_b200
+        g = Golden(name)
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, precision="SP", group="world", _backend=InterpBackend())
+            r1, r2 = w.residuals(g.F, g["gen_t1"], g["gen_t2"])
+        q.put(dict(rank=rank, plain=bool(w.engine.sp_plain), rows=int(w.engine.tauWPn.shape[1]),
+                   d_r1=float(np.abs(r1.double().numpy() - g["gen_r1"]).max()),
+                   d_r2=float(np.abs(r2.double().numpy() - g["gen_r2"]).max())))
+    except Exception:
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_ranks_gloo_mixed_precision():
+    from tests.conftest import Golden
+    g = Golden("o6v13")
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sp_worker, args=(r, world, port, "o6v13", q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for d in res:
+        assert "error" not in d, d.get("error")
+        assert d["plain"] and d["d_r1"] < 2e-6 and d["d_r2"] < 2e-6
+    assert sum(d["rows"] for d in res) == g.nv
+
+
 def _lambda_worker(rank, world, port, name, model, q):
     """HBAR + Lambda with the v^4 / o v^3 blocks sharded by rows over two ranks."""
     sys.path.insert(0, ROOT)
