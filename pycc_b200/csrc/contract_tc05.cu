@@ -292,7 +292,10 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
     // operand tiles drift apart and the ladder at (40,300) read 511 GB from DRAM for 65 GB of operands.
     static const long long panel_bytes = [] { const char* e = getenv("PCCB_TC05_PANEL_MB"); return (long long)(e ? atoi(e) : 128) << 20; }();
     long long kpanel = 0;
-    if (ns == 1 && panel_bytes > 0) {
+    // (only when B is the big streaming operand, N >> M: the ladder; for square-ish products such as the ring
+    //  terms the extra read-modify-write passes over C cost more than the panels save)
+    static const long long panel_ratio = [] { const char* e = getenv("PCCB_TC05_PANEL_RATIO"); return (long long)(e ? atoi(e) : 8); }();
+    if (ns == 1 && panel_bytes > 0 && d->N >= panel_ratio * d->M) {
         const long long a_bytes = 8ll * d->M * segs[0]->K;          // two FP32 planes
         if (a_bytes > panel_bytes) {
             kpanel = panel_bytes / (8ll * d->M) / BKF * BKF;
