@@ -191,7 +191,7 @@ class ComplexResiduals(object):
             shapes.update(T11=(o, o, v, v), Yw=(o, o, o, v), Xv=(v, v, o, v))
         for k, s in shapes.items():
             P.add_complex(k, s)
-        st = eng._statements()
+        st = eng._statements(plain=False)
         self.prep = P.compile(self.PREP + (["T11[ijab] = t1[ia]*t1[jb]"] if eng.model == 'CC2' else []))
         self.progs = {name: P.compile(st[name], _strip) for name in eng.builder_order()}
         self._lam = None

@@ -1492,8 +1492,12 @@ EncodeTiledFn encode_tiled_fn() {
 }
 
 // operand = K-contiguous matrix with one uniform, 16-byte-aligned row stride
+// (a two-level index whose levels happen to be contiguous, s_hi == div * s_lo, is a plain dimension too:
+//  the planner emits one div per index group)
+bool plain_dim(const DIdx& c) { return c.flat || c.s_hi == (long long)c.div * c.s_lo; }
+
 bool tma_operand_ok(const void* base, const DIdx& mn, const DIdx& k, long long rows) {
-    if (!(k.flat && k.s_lo == 1 && mn.flat)) return false;
+    if (!(plain_dim(k) && k.s_lo == 1 && plain_dim(mn))) return false;
     if ((reinterpret_cast<uintptr_t>(base) & 15) != 0) return false;
     if (rows > 1 && (mn.s_lo <= 0 || (mn.s_lo & 1))) return false;     // stride in doubles, must be even
     return true;

@@ -173,10 +173,12 @@ def _roles(fx, fy, out_set):
     return M, N, K, batch, stray
 
 
-def plan(stmt, tensors, dtype=_lib.F64):
+def plan(stmt, tensors, dtype=_lib.F64, prefer_flat=None):
     """Plan one statement into a list of Launch objects (usually one).
     ``tensors`` maps names to TRef (or torch tensors)."""
     out_name, out_idx, accumulate, terms = parse(stmt)
+    if prefer_flat is None:
+        prefer_flat = dtype == _lib.F32
 
     def ref(name):
         if name not in tensors:
@@ -270,8 +272,8 @@ def plan(stmt, tensors, dtype=_lib.F64):
         bviews = [s[2] for s in segs] + [s[4] for s in segs] + [cv] + ([dv] if dv else [])
 
         def flatten_all(Ms, Ns, Bs):
-            Mt, md, ms_ = _flatten(Ms, mviews, ext, pref_m, dtype == _lib.F32)
-            Nt, nd, ns_ = _flatten(Ns, nviews, ext, pref_n, dtype == _lib.F32)
+            Mt, md, ms_ = _flatten(Ms, mviews, ext, pref_m, prefer_flat)
+            Nt, nd, ns_ = _flatten(Ns, nviews, ext, pref_n, prefer_flat)
             Bt, bd, bs_ = _flatten(Bs, bviews, ext, [])
             if bd != FLAT:
                 raise PlanError("batch indices %r do not flatten to one stride" % (sorted(Bs),))

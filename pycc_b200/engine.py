@@ -100,7 +100,11 @@ class CCSDEngine(object):
         # GEMMs has a residual plane lo = x - trunc_tf32(x); the plain-matrix contractions then run as
         # 3xTF32 on the tcgen05 tensor cores (csrc/contract_tc05.cu), everything else on the mma.sync kernel.
         import os
-        self.sp_plain = dtype == torch.float32 and self.model != 'CC2' and os.environ.get("PCCB_SP_PLAIN", "1") != "0"
+        # (FP64: the same plain-matrix copies make the ring terms eligible for the TMA-staged kernel:
+        #  28.35 -> 28.01 ms at (20,150), 0.4295 -> 0.4209 s at (30,250); PCCB_PLAIN_RING=0 disables)
+        self.sp_plain = self.model != 'CC2' and (
+            (dtype == torch.float32 and os.environ.get("PCCB_SP_PLAIN", "1") != "0") or
+            (dtype == torch.float64 and os.environ.get("PCCB_PLAIN_RING", "1") != "0"))
         self._lo = None
         if self.sp_plain:
             self.oovvP, self.oovvX, self.LoovvP = E(o, v, o, v), E(o, v, o, v), E(o, v, o, v)      # [m,e,n,f]
@@ -263,12 +267,14 @@ class CCSDEngine(object):
             return ("Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij", "r_T2")
         return ("Fae", "Fmi", "Fme", "Wmnij", "Wmbej", "Wmbje", "Zmbij", "r_T1", "r_T2")
 
-    def _statements(self):
+    def _statements(self, plain=None):
+        """``plain=False``: the layout-independent statement set (complex_engine expands that one)."""
+        plain = self.sp_plain if plain is None else plain
         st = dict(self.STATEMENTS)
         if self.model == 'CC2':
             st.update(self.STATEMENTS_CC2)
             del st["Wmbej"], st["Wmbje"]
-        elif self.sp_plain:
+        elif plain:
             st.update(self.STATEMENTS_SP)
             st["r_T2"] = [self.R_T2_SP.get(x, x) for x in st["r_T2"]]
         return st
@@ -280,7 +286,7 @@ class CCSDEngine(object):
             launches = []
             for s in stmts:
                 T = self._tensors(set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s)))
-                for L in plan(s, T, self.dcode):
+                for L in plan(s, T, self.dcode, prefer_flat=True if self.sp_plain else None):
                     L.is_ladder = "vvvv_s0" in s
                     launches.append(L)
             self.plans[name] = launches
