@@ -12,14 +12,19 @@
 //   * CTA tile (16*MI) x 128 x 16 with MI in {1,2,4,5,6,8} chosen per launch to minimise padded
 //     rows (o^2 = 400 -> five 80-row tiles); 8 DMMA warps as 2(M) x 4(N), warp tile (8*MI) x 32:
 //     4*MI DMMA per MI+4 LDS.64, so the tensor pipe, not shared memory, is the limiter.
-//   * three kernels behind the one entry point (all persistent over output tiles):
-//       contract_f64_tma_kernel  plain 2-D operands (o^2 v^4 ladder, Wmnij, Zmbij): one producer
+//   * four kernels behind the one entry point (the first three persistent over output tiles):
+//       contract_f64_tma_kernel  plain 2-D operands (o^2 v^4 ladder, Wmnij, Zmbij, and the ring terms over
+//                                the engine's plain-matrix copies of the o^2 v^2 operands): one producer
 //                                thread issues cp.async.bulk.tensor (TMA) copies, 128-byte swizzle,
 //                                fragment rows permuted so that LDS.64 stays conflict free
 //                                (35.1 TFLOP/s = 0.95 of peak on the ladder);
 //       contract_f64_ws_kernel   compound (gathered) operands: 4 producer warps do the index
 //                                arithmetic + cp.async (LDGSTS, zero-fill at the edges), 8 consumer
 //                                warps run DMMA + LDS only (30.5-32.9 TFLOP/s);
+//       contract_f64_wse_kernel  the same plus a fourth warpgroup that owns the epilogue, for short
+//                                contractions (8..64 k-tiles: the (T) / CC3 W build): consumers dump
+//                                their accumulators to a staging tile and start the next tile at once;
+//                                zero-filled k-steps of segment tails are skipped;
 //       contract_f64_kernel      MI <= 2 (skinny, memory-bound launches): all warps load and
 //                                compute, two CTAs per SM.
 //     Stages are guarded by full/empty mbarriers; registers are re-balanced with setmaxnreg.
@@ -32,7 +37,9 @@
 //     are rescaled once when the k-loop crosses a segment boundary.
 //   * small outputs (Fae, Fmi, Wmnij ...) use deterministic split-K (wave-aware split count)
 //     through a caller-owned workspace, reduced in fixed order with the alpha/beta/gamma epilogue.
-//   * FP32 operands (precision='SP') are routed to contract_f32.cu (3xTF32 tensor-core kernel).
+//   * FP32 operands (precision='SP') are routed to contract_f32.cu: plain-matrix contractions with
+//     registered residual planes to the tcgen05 / TMEM 3xTF32 kernel (contract_tc05.cu), the rest to the
+//     mma.sync 3xTF32 kernel.
 #include <climits>
 #include <cstdlib>
 #include <cstring>
