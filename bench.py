@@ -6,7 +6,9 @@ bench.py - the driver-facing benchmark of the pycc_b200 hot path.
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 Metric (BASELINE.json): CCSD seconds per iteration (+ (T) seconds and FP64 tensor TFLOP/s vs peak)
-on synthetic, symmetry-correct RHF integrals; default workload = configs[1], o=20 v=150 FP64.
+on synthetic, symmetry-correct RHF integrals; default workload = BASELINE configs[2], CCSD(T) at
+o=30 v=250 FP64 - the largest named FP64 configuration whose <ab|ef> block (31 GB) fits one GPU, and
+the one named for 1 and 8 GPUs (configs[1], o=20 v=150, is ``--workload 20,150``).
 One "step" = one pass of the solve_cc loop body (pycc/ccwfn.py:274-329): residuals, amplitude
 update + norm, energy, DIIS push + extrapolation.  Prints ONE JSON line (rank 0).
 
@@ -42,7 +44,7 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="20,150", help="o,v (default: BASELINE.json configs[1])")
+    ap.add_argument("--workload", default="30,250", help="o,v (default: BASELINE.json configs[2], CCSD(T) o=30 v=250)")
     ap.add_argument("--seed", type=int, default=0)
     ap.add_argument("--precision", default="DP", choices=["DP", "SP"],
                     help="SP = mixed mode: FP32 contractions (3xTF32), FP64 energy/norm/DIIS")
@@ -173,6 +175,63 @@ def oracle_iteration(F, blocks, t1, t2):
     return r1, r2, t1n, t2n, oc.cc_energy(F, blk, t1n, t2n), rms
 
 
+
+def workload_config(o, v, sp, world, seed, scale):
+    """The ``config`` object of the JSON line - identical in both arms (``--impl ours|reference``)."""
+    from pycc_b200.parallel import virtual_slice
+    vl = max(hi - lo for lo, hi in (virtual_slice(v, r, world) for r in range(world)))
+    return {"workload": "RHF-CCSD(T): CCSD iteration + (T), o=%d v=%d %s" % (o, v, "FP32 contractions / FP64 energy+DIIS" if sp else "FP64"),
+            "o": o, "v": v,
+            "parallelism": ("virtual-index sharding x%d: allgather(r2 slabs) -> sliced update/energy/DIIS -> allgather(t2); "
+                            "(T) pairs dealt over ranks" % world) if world > 1 else "1 GPU",
+            "l2": "inputs larger than L2 (vvvv rows %.2f GB per rank)" % (vl * v**3 * (4 if sp else 8) / 1e9),
+            "seed": seed, "eri_scale": round(scale, 6), "diis": 8}
+
+
+ORACLE_FITS_V = 160      # NumPy oracle on the host: full <ab|ef> block up to v = 160 (5.2 GB)
+TRIPLET_SAMPLE = lambda o: [(o - 1, o // 2, 0), (o - 1, o - 1, o - 2), (o // 2, 1, 1), (3, 2, 1)]
+
+
+class FactorChecker(object):
+    """Independent full-size checker (SURVEY.md 8(d) "Correctness gates run with every timing"): the
+    reference's formulas (oracle/torch_oracle.py, pinned to the golden vectors) evaluated with
+    torch.einsum = cuBLAS FP64 on the device, on integrals REGENERATED from the seeded factor B row by
+    row - neither the engine's kernels nor its stored blocks are involved.  With several ranks each one
+    checks the ladder rows it owns (the pieces are summed), everything else is evaluated on every rank."""
+
+    def __init__(self, B, F, o, dev, vslice):
+        import torch
+        from oracle import torch_oracle as to
+        self.to, self.torch = to, torch
+        Bd = torch.as_tensor(B).to(device=dev, dtype=torch.float64)
+        n = Bd.shape[1]
+        v = n - o
+        Bo, Bv = Bd[:, :o, :], Bd[:, o:, :]
+        self.Boo, self.Bov, self.Bvv = Bo[:, :, :o].contiguous(), Bo[:, :, o:].contiguous(), Bv[:, :, o:].contiguous()
+        ein = torch.einsum
+        small = {"oooo": ein('Qmi,Qnj->mnij', self.Boo, self.Boo), "ooov": ein('Qmi,Qne->mnie', self.Boo, self.Bov),
+                 "oovv": ein('Qia,Qjb->ijab', self.Bov, self.Bov), "ovov": ein('Qmj,Qbe->mbje', self.Boo, self.Bvv),
+                 "ovvv": lambda m: ein('Qe,Qbf->bef', self.Bov[:, m, :], self.Bvv),
+                 "vvvv": lambda lo, hi: ein('Qae,Qbf->abef', self.Bvv[:, lo:hi, :], self.Bvv)}
+        chunk = max(1, int((3 << 30) // (8 * v**3)))          # <= 3 GB of regenerated <ab|ef> rows at a time
+        self.blk = to.Blocks(small, device=dev, vv_rows=vslice, chunk=chunk)
+        self.F = torch.as_tensor(F).to(device=dev, dtype=torch.float64)
+
+    def residuals(self, t1, t2, comm):
+        """(r1, r2) of the reference algorithm, identical on every rank."""
+        torch, to = self.torch, self.to
+        r1, rest = to.residuals(self.F, self.blk, t1, t2, skip_ladder=True)
+        _, lad = to.residuals(self.F, self.blk, t1, t2, ladder_only=True)
+        comm.allreduce_(lad)
+        return r1, rest + lad + lad.permute(1, 0, 3, 2)
+
+    def energy(self, t1, t2):
+        return self.to.cc_energy(self.F, self.blk, t1, t2)
+
+    def et_triplet(self, t1, t2, i, j, k):
+        return self.to.et_triplet(self.F, self.blk, t1, t2, i, j, k)
+
+
 def run_ours(args):
     import numpy as np
     import torch
@@ -192,6 +251,7 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=dev)
         group = "world"
     import pycc_b200
+    import pycc_b200.cctriples as cct
     from pycc_b200.parallel import virtual_slice
     from pycc_b200.synthetic import device_blocks
     from pycc_b200.utils import helper_diis
@@ -323,7 +383,6 @@ def run_ours(args):
     # ---- (T): timed once after the CCSD steps (all ranks; max over ranks) ---------------------
     triples = None
     if want_t:
-        import pycc_b200.cctriples as cct
         tri = cct._engine(w)
         tri.energy(tri.my_pairs()[:1])                 # warm-up: one occupied pair
         barrier()
@@ -338,40 +397,89 @@ def run_ours(args):
                    "tflops": round(flops_triples(o, v) / tsec / 1e12, 3),
                    "frac_of_peak": round(flops_triples(o, v) / tsec / 1e12 / (peak * world), 4)}
 
-    # ---- CPU baseline (rank 0, N=1 only): the oracle on the host cores + parity of the step -----
-    cpu_baseline, parity = None, None
+    # ---- parity of the timed engine, every workload and every N (gate: no parity, no number) ---------
+    # amplitudes pushed off the fixed point (at convergence every residual is ~0 and the check is void)
+    t1h = (1.1 * w.t1.double() + 0.01)
+    t2h = 1.1 * w.t2.double()
+    r1g, r2g = w.residuals(F, t1h, t2h)               # the engine's answer (all ranks take part)
+    e_eng = eng.energy()
+    chk = FactorChecker(B, F, o, dev, vslice)
+    r1c, r2c = chk.residuals(t1h, t2h, w.comm)
+    tol_r = 2e-5 if sp else 1e-10
+    parity = {"max_abs_dr1": float((r1g.double() - r1c).abs().max()), "max_abs_dr2": float((r2g.double() - r2c).abs().max()),
+              "max_abs_r2": float(r2c.abs().max()),
+              "abs_dE_same_amplitudes": abs(e_eng - chk.energy(w.t1, w.t2)),
+              "tolerance": tol_r,
+              "checked": "residuals() of the timed engine on perturbed (t1, t2) and its energy, o=%d v=%d, %d GPU(s), against "
+                         "oracle/torch_oracle.py (reference formulas, torch.einsum/cuBLAS FP64 on the device) on integrals "
+                         "regenerated from the factor B; each rank checks the <ab|ef> rows it owns" % (o, v, world)}
+    del r1c, r2c, r1g, r2g
+    if want_t:
+        tri = cct._engine(w)
+        sample = [t for t in TRIPLET_SAMPLE(o) if t[0] < o and t[1] <= t[0] and t[2] <= t[1]]
+        pairs = sorted(set((i, j) for (i, j, k) in sample))
+        _, per, trip = tri.energy(pairs)
+        got = dict(zip(trip, per.tolist()))
+        dev_t = [abs(got[t] - chk.et_triplet(w.t1.double(), w.t2.double(), *t)) for t in sample]
+        parity["max_abs_dE_T_triplet"] = max(dev_t)
+        parity["triplets_checked"] = sample
+        parity["tolerance_triplet"] = 1e-7 if sp else 1e-12
+    ok = parity["max_abs_dr1"] <= tol_r and parity["max_abs_dr2"] <= tol_r and parity["abs_dE_same_amplitudes"] <= (1e-6 if sp else 1e-10)
+    if want_t:
+        ok = ok and parity["max_abs_dE_T_triplet"] <= parity["tolerance_triplet"]
+    parity["passed"] = bool(ok)
+    del chk
+    torch.cuda.empty_cache()
+
+    # ---- CPU baseline (rank 0, N=1 only): the NumPy oracle on the host cores, a bounded sample ----------
+    cpu_baseline = None
     if world == 1 and not args.no_cpu_baseline:
         from oracle import ccsd_oracle as oc
         cores = set_host_threads()
-        hb = {k: t.double().cpu().numpy() for k, t in w.H.blocks.items()}
-        # amplitudes pushed off the fixed point (at convergence every residual is ~0 and the check is void)
-        t1h = 1.1 * w.t1.double().cpu().numpy() + 0.01
-        t2h = 1.1 * w.t2.double().cpu().numpy()
-        # the GPU's answer for the same amplitudes
-        r1g, r2g = w.residuals(F, t1h, t2h)
-        blk = oc.Blocks(hb)
+        t1n, t2n = t1h.cpu().numpy(), t2h.cpu().numpy()
+        hb = {k: t.double().cpu().numpy() for k, t in w.H.blocks.items() if k != "vvvv"}
         warm_numpy()
-        t0 = time.perf_counter()
-        r1c, r2c, _, _, ecpu, _ = oracle_iteration(F, blk, t1h, t2h)
-        cpu_s = time.perf_counter() - t0
-        parity = {"max_abs_dr1": float(np.abs(r1g.double().cpu().numpy() - r1c).max()),
-                  "max_abs_dr2": float(np.abs(r2g.double().cpu().numpy() - r2c).max()),
-                  "max_abs_r2": float(np.abs(r2c).max()),
-                  "checked": "residuals() of the timed engine vs the oracle on the same perturbed (t1, t2), o=%d v=%d" % (o, v)}
+        if v <= ORACLE_FITS_V:
+            hb["vvvv"] = w.H.blocks["vvvv"].double().cpu().numpy()
+            blk = oc.Blocks(hb)
+            t0 = time.perf_counter()
+            r1c, r2c, _, _, ecpu, _ = oracle_iteration(F, blk, t1n, t2n)
+            cpu_s = time.perf_counter() - t0
+            r1g, r2g = w.residuals(F, t1h, t2h)
+            parity["numpy_oracle_max_abs_dr2"] = float(np.abs(r2g.double().cpu().numpy() - r2c).max())
+            sample_txt = ("1 full CCSD iteration (residuals + update + energy) of the NumPy oracle "
+                          "(port of pycc/ccwfn.py:331-366) at o=%d v=%d, after a tiny warm-up" % (o, v))
+            extrap = False
+        else:
+            # bounded: every builder except the ladder at full size + the ladder einsum on a slice of rows
+            hb["vvvv"] = None
+            blk = oc.Blocks(hb)
+            t0 = time.perf_counter()
+            oracle_iteration(F, blk, t1n, t2n)
+            rest_s = time.perf_counter() - t0
+            c = max(2, min(v, int(8e11 / (2.0 * o * o * v**3))))          # ~0.8 TFLOP of ladder work
+            rows = eng.vvvv_loc[:c].double().cpu().numpy()
+            tt = oc.tau(t1n, t2n)
+            t0 = time.perf_counter()
+            oc._ein('ijef,abef->ijab', tt, rows)
+            lad_s = (time.perf_counter() - t0) * v / c
+            cpu_s = rest_s + lad_s
+            sample_txt = ("NumPy oracle at o=%d v=%d: all builders, update and energy at full size (%.1f s) + the o^2 v^4 "
+                          "ladder einsum on %d of %d <ab|ef> rows, scaled by %d/%d (%.1f s)" % (o, v, rest_s, c, v, v, c, lad_s))
+            extrap = True
         cpu_baseline = {"value": round(cpu_s, 4), "unit": "s/iteration", "cores": cores, "kind": "port",
-                        "sample": "1 full CCSD iteration (residuals + update + energy) of the NumPy oracle "
-                                  "(port of pycc/ccwfn.py:331-366) at o=%d v=%d, after a tiny warm-up" % (o, v)}
+                        "extrapolated": extrap, "sample": sample_txt}
         if want_t:
             from oracle import triples_oracle as ot
-            ns = 4
-            trip = [(o - 1, o // 2, 0), (o - 1, o - 1, o - 2), (o // 2, 1, 1), (3, 2, 1)][:ns]
+            sample = [t for t in TRIPLET_SAMPLE(o) if t[0] < o and t[1] <= t[0] and t[2] <= t[1]]
+            t1o, t2o = w.t1.double().cpu().numpy(), w.t2.double().cpu().numpy()
             t0 = time.perf_counter()
-            for (i, j, k) in trip:
-                ot.et_triplet(F, blk, t1h, t2h, i, j, k)
-            per = (time.perf_counter() - t0) / ns
+            ecpu_t = [ot.et_triplet(F, blk, t1o, t2o, i, j, k) for (i, j, k) in sample]
+            per = (time.perf_counter() - t0) / len(sample)
             ntrip = o * (o + 1) * (o + 2) // 6
             cpu_baseline["triples"] = {"value": round(per * ntrip, 2), "unit": "s", "extrapolated": True,
-                                       "sample": "%d triplets timed (vectorised t_tjl body), x %d triplets" % (ns, ntrip)}
+                                       "sample": "%d triplets timed (vectorised t_tjl body, NumPy), x %d triplets" % (len(sample), ntrip)}
+            parity["numpy_oracle_max_abs_dE_T_triplet"] = max(abs(a - got[t]) for a, t in zip(ecpu_t, sample))
 
     if rank == 0:
         fl = flops_ccsd_iteration(o, v)
@@ -379,10 +487,7 @@ def run_ours(args):
                "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(ms_step, 4),
                "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f32" if sp else "f64",
                "data": "synthetic (seeded factorised 8-fold-symmetric ERIs, diagonal Fock; SURVEY.md 8(d))",
-               "config": {"workload": "RHF-CCSD iteration o=%d v=%d %s" % (o, v, "FP32 contractions / FP64 energy+DIIS" if sp else "FP64"),
-                          "o": o, "v": v, "parallelism": "virtual-index sharding x%d + allreduce(r1,r2)" % world if world > 1 else "1 GPU",
-                          "l2": "inputs larger than L2 (vvvv rows %.2f GB per rank)" % (vl * v**3 * 8 / 1e9),
-                          "seed": args.seed, "eri_scale": round(scale, 6), "diis": 8},
+               "config": workload_config(o, v, sp, world, args.seed, scale),
                "tflops": round(fl / (ms_step * 1e-3) / 1e12, 3),
                "tflops_frac_of_peak": round(fl / (ms_step * 1e-3) / 1e12 / (peak * world), 4),
                "flops_per_iteration": fl, "flops_issued": flops_issued,
@@ -391,16 +496,23 @@ def run_ours(args):
                "energy": last[0] if last else None, "rms": last[1] if last else None,
                "gpu_launches": int(launches), "clocks": clk, "roofline": roofline, "e2e": e2e,
                "triples": triples, "cpu_baseline": cpu_baseline, "parity": parity}
+        if not parity["passed"]:
+            # a number without a green parity check is not a number: print the evidence, not the metric
+            out = {"error": "parity check failed - timing withheld", "parity": parity, "config": out["config"]}
         emit(out)
     if world > 1:
         dist.destroy_process_group()
+    if not parity["passed"]:
+        sys.exit(3)
 
 
 def run_reference(args):
-    """The reference's CPU algorithm for the same workload, on all host cores.  The reference
-    itself (pure Python + psi4 + opt_einsum) is not importable on the GPU box, so this is the
-    oracle port (kind='port'); each step is one full CCSD iteration incl. DIIS, and the number of
-    steps is cut down when the first one shows that K+W of them would not finish in ~4 minutes."""
+    """The reference's CPU algorithm for the same workload, on all host cores.  The reference itself
+    (pure Python + psi4 + opt_einsum) is not importable on the GPU box, so this is the oracle port
+    (kind='port').  Each step is one full CCSD iteration incl. DIIS; the number of steps is cut down when
+    the first one shows that K+W of them would not finish in ~4 minutes.  Shapes whose <ab|ef> block does
+    not fit the host (v > 160) run the o^2 v^4 ladder chunk by chunk over rows manufactured from the factor
+    on the fly - the same einsum per chunk; the seconds spent manufacturing rows are set-up and not timed."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
@@ -408,11 +520,18 @@ def run_reference(args):
     from oracle import ccsd_oracle as oc
     from pycc_b200.synthetic import _blk
     o, v = [int(x) for x in args.workload.split(",")]
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     cores = set_host_threads()
     B, F, scale = make_factor(o, v, args.seed)
     oo, vv = slice(0, o), slice(o, o + v)
     blocks = {"oooo": _blk(B, oo, oo, oo, oo), "ooov": _blk(B, oo, oo, oo, vv), "oovv": _blk(B, oo, oo, vv, vv),
-              "ovov": _blk(B, oo, vv, oo, vv), "ovvv": _blk(B, oo, vv, vv, vv), "vvvv": _blk(B, vv, vv, vv, vv)}
+              "ovov": _blk(B, oo, vv, oo, vv), "ovvv": _blk(B, oo, vv, vv, vv)}
+    streamed = v > ORACLE_FITS_V
+    if streamed:
+        blocks["vvvv"] = lambda lo, hi: _blk(B, slice(o + lo, o + hi), vv, vv, vv)
+        blocks["vvvv_chunk"] = max(1, int((2 << 30) // (8 * v**3)))
+    else:
+        blocks["vvvv"] = _blk(B, vv, vv, vv, vv)
     blk = oc.Blocks(blocks)
     Dia, Dijab = oc.denominators(F, o)
     t1 = np.zeros((o, v))
@@ -421,34 +540,39 @@ def run_reference(args):
     warm_numpy()
 
     def step(t1, t2):
+        """Returns (t1, t2, energy, timed seconds of this step)."""
+        g0 = blk.gen_seconds
+        t0 = time.perf_counter()
         _, _, t1, t2, e, rms = oracle_iteration(F, blk, t1, t2)
         diis.add_error_vector(t1, t2)
         t1, t2 = diis.extrapolate(t1, t2)
-        return t1, t2, e
+        return t1, t2, e, (time.perf_counter() - t0) - (blk.gen_seconds - g0)
 
-    t0 = time.perf_counter()
-    t1, t2, e = step(t1, t2)                      # first (warm-up) step, also the calibration
-    first = time.perf_counter() - t0
+    w0 = time.perf_counter()
+    t1, t2, e, first = step(t1, t2)               # first (warm-up) step, also the calibration
+    wall_first = time.perf_counter() - w0
     budget = 240.0
-    warm = max(min(args.warmup - 1, int((0.25 * budget) / max(first, 1e-3))), 0)
+    warm = max(min(args.warmup - 1, int((0.25 * budget) / max(wall_first, 1e-3))), 0)
     for _ in range(warm):
-        t1, t2, e = step(t1, t2)
-    steps = max(min(args.steps, int((budget - (1 + warm) * first) / max(first, 1e-3))), 1)
-    t0 = time.perf_counter()
+        t1, t2, e, _s = step(t1, t2)
+    steps = max(min(args.steps, int((budget - (1 + warm) * wall_first) / max(wall_first, 1e-3))), 1)
+    tot = 0.0
     for _ in range(steps):
-        t1, t2, e = step(t1, t2)
-    sec = (time.perf_counter() - t0) / steps
+        t1, t2, e, dt = step(t1, t2)
+        tot += dt
+    sec = tot / steps
     fl = flops_ccsd_iteration(o, v)
     out = {"impl": "reference", "metric": "ccsd_seconds_per_iteration", "value": round(sec, 4), "unit": "s/iteration",
-           "n_gpus": int(os.environ.get("WORLD_SIZE", "1")), "steps": steps, "warmup": 1 + warm,
+           "n_gpus": world, "steps": steps, "warmup": 1 + warm,
            "ms_per_step": round(sec * 1e3, 2), "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
            "dtype": "f64", "data": "synthetic (same seeded system as the GPU arm)",
-           "config": {"workload": "RHF-CCSD iteration o=%d v=%d FP64" % (o, v), "o": o, "v": v, "seed": args.seed,
-                      "eri_scale": round(scale, 6), "diis": 8},
+           "config": workload_config(o, v, args.precision == "SP", world, args.seed, scale),
            "tflops": round(fl / sec / 1e12, 4), "energy": float(e), "gpu_launches": 0,
            "cpu_baseline": {"value": round(sec, 4), "unit": "s/iteration", "cores": cores, "kind": "port",
                             "sample": "%d full CCSD iterations (residuals + update + energy + DIIS) of the NumPy "
-                                      "oracle at o=%d v=%d (requested %d; bounded to ~4 min)" % (steps, o, v, args.steps)},
+                                      "oracle at o=%d v=%d (requested %d; bounded to ~4 min)%s"
+                                      % (steps, o, v, args.steps,
+                                         "; <ab|ef> rows manufactured chunk by chunk from the factor, untimed" if streamed else "")},
            "e2e": {"value": round(sec, 4), "unit": "s/iteration", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(out)
 

@@ -108,6 +108,8 @@ int pccb_contract(pccb_ctx* ctx, const pccb_contraction* desc);
 int pccb_split_lo(pccb_ctx* ctx, const void* x_dev, void* lo_dev, int64_t n);
 int pccb_register_lo_plane(pccb_ctx* ctx, const void* x_dev, const void* lo_dev, int64_t n);
 int pccb_clear_lo_planes(pccb_ctx* ctx);
+/* forget the plane registered for the tensor whose base address is x_dev (no-op when there is none) */
+int pccb_unregister_lo_plane(pccb_ctx* ctx, const void* x_dev);
 
 /* ---- solver seam: element-wise and reduction pieces ------------------------------------- */
 /* out[i,j,a,b] = c0*X[i,j,a,b] + c1*X[i,j,b,a] + c2*u[i,a]*w[j,b]   (u_dev/w_dev may be NULL)

@@ -39,6 +39,11 @@ class Blocks(object):
         self.vvvv = blocks.get("vvvv")
         self.no = self.oovv.shape[0]
         self.nv = self.oovv.shape[2]
+        # bench.py, shapes whose <ab|ef> block does not fit the host: ``vvvv`` may be a callable
+        # (lo, hi) -> rows a in [lo, hi); the ladder then runs chunk by chunk (same einsum per chunk) and
+        # the seconds spent manufacturing the rows are kept apart in ``gen_seconds`` (they are set-up)
+        self.vvvv_chunk = blocks.get("vvvv_chunk", 16)
+        self.gen_seconds = 0.0
 
     # ERI slices in the reference's index order
     def oovo(self):  # <mn|ej>
@@ -153,6 +158,24 @@ def r_T1(F, blk, t1, t2, Fae, Fme, Fmi):
     return r
 
 
+def ladder(blk, tt):
+    """sum_ef tau[ijef] <ab|ef> (pycc/ccwfn.py:607), one einsum - or, with provided rows, one per chunk."""
+    if blk.vvvv is None:          # bench.py's bounded CPU sample times the ladder separately, on a slice
+        return 0.0
+    if not callable(blk.vvvv):
+        return _ein('ijef,abef->ijab', tt, blk.vvvv)
+    import time
+    out = np.empty_like(tt)
+    for lo in range(0, blk.nv, blk.vvvv_chunk):
+        hi = min(blk.nv, lo + blk.vvvv_chunk)
+        t0 = time.perf_counter()
+        rows = blk.vvvv(lo, hi)
+        blk.gen_seconds += time.perf_counter() - t0
+        out[:, :, lo:hi, :] = _ein('ijef,abef->ijab', tt, rows)
+        del rows
+    return out
+
+
 def r_T2(F, blk, t1, t2, Fae, Fme, Fmi, Wmnij, Wmbej, Wmbje, Zmbij):
     """pycc/ccwfn.py:596-621 (CCSD branch, including the final pair symmetrisation)."""
     tt = tau(t1, t2)
@@ -162,7 +185,7 @@ def r_T2(F, blk, t1, t2, Fae, Fme, Fmi, Wmnij, Wmbej, Wmbje, Zmbij):
     r = r - _ein('imab,mj->ijab', t2, Fmi)
     r = r - 0.5 * _ein('imab,jm->ijab', t2, _ein('je,me->jm', t1, Fme))
     r = r + 0.5 * _ein('mnab,mnij->ijab', tt, Wmnij)
-    r = r + 0.5 * _ein('ijef,abef->ijab', tt, blk.vvvv)
+    r = r + 0.5 * ladder(blk, tt)
     r = r - _ein('ma,mbij->ijab', t1, Zmbij)
     r = r + _ein('imae,mbej->ijab', t2 - t2.transpose(0, 1, 3, 2), Wmbej)
     r = r + _ein('imae,mbej->ijab', t2, Wmbej + Wmbje.transpose(0, 1, 3, 2))

@@ -23,6 +23,7 @@ EXPORTS = (
     "pccb_synchronize", "pccb_contract", "pccb_pair_combine", "pccb_pair_symmetrize", "pccb_permute4",
     "pccb_update_amplitudes", "pccb_cc_energy", "pccb_dot", "pccb_axpby", "pccb_lincomb",
     "pccb_triples_energy", "pccb_t3_combine", "pccb_split_lo", "pccb_register_lo_plane", "pccb_clear_lo_planes",
+    "pccb_unregister_lo_plane",
 )
 
 
@@ -88,6 +89,7 @@ def load():
     lib.pccb_split_lo.argtypes = [vp, vp, vp, i64]
     lib.pccb_register_lo_plane.argtypes = [vp, vp, vp, i64]
     lib.pccb_clear_lo_planes.argtypes = [vp]
+    lib.pccb_unregister_lo_plane.argtypes = [vp, vp]
     lib.pccb_t3_combine.argtypes = [vp, i32, vp, i32, i32, i32, i32, vp, i64, i64, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)

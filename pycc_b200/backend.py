@@ -151,6 +151,10 @@ class CudaBackend(object):
         """From now on FP32 contractions whose operands are views of ``x`` may use ``lo`` as its residual plane."""
         self._check(self.lib.pccb_register_lo_plane(self.h, x.data_ptr(), lo.data_ptr(), x.numel()))
 
+    def unregister_lo_plane(self, x_ptr):
+        """Forget the residual plane registered for the tensor whose base address is ``x_ptr``."""
+        self._check(self.lib.pccb_unregister_lo_plane(self.h, x_ptr))
+
     def t3_combine(self, W, nk, k0, i, j, eps, no, nv, A1, A2):
         """A1 / A2 combinations of t3 = W / D for the pair (i, j), k = k0 .. k0+nk-1 (CC3)."""
         self._check(self.lib.pccb_t3_combine(self.h, dtype_code(W), W.data_ptr(), nk, k0, i, j, eps.data_ptr(),

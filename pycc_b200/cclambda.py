@@ -29,6 +29,7 @@ class cclambda(object):
         """Solve the Lambda equations (pycc/cclambda.py:60-274).  Returns the pseudoenergy, or None
         when not converged in ``maxiter`` iterations."""
         lambda_tstart = time.time()
+        self._ensure_hbar()
         eng = self.engine
         lecc = eng.pseudoenergy()
         print("\nLCC Iter %3d: LCC PseudoE = %.15f  dE = % .5E" % (0, lecc, -lecc))
@@ -51,6 +52,7 @@ class cclambda(object):
     def _iteration(self):
         """Residuals, l += r/D (the r2 + r2^T of :542 folded into the update), increment norm and
         pseudoenergy (cclambda.py:141-151, 244-254).  Returns (lecc, rms)."""
+        self._ensure_hbar()
         eng = self.engine
         eng.residuals(symmetrize=False)
         rms = np.sqrt(eng.update(symmetrize_on_the_fly=True))
@@ -90,7 +92,21 @@ class cclambda(object):
             le.l1.copy_(kl1)
             le.l2.copy_(kl2)
         eng.set_fock(eng.F0)
+        # the HBAR blocks now hold the values of THIS call; the reference's hbar.H* are never touched
+        # by residuals(): rebuild them from the object's own (F0, t1, t2) before the next use
+        foreign_F = F is not None and F is not eng.F0 and F is not eng.F
+        if not own_t or foreign_F:
+            self._hbar_dirty = True
         return r1, r2
+
+    def _ensure_hbar(self):
+        """HBAR of the object's own amplitudes (rebuilt after a residuals() call on other inputs)."""
+        if getattr(self, "_hbar_dirty", False):
+            eng = self.ccwfn.engine
+            eng.set_fock(eng.F0)
+            self.hbar.engine.snapshot()
+            self.hbar.engine.build()
+            self._hbar_dirty = False
 
     def build_Goo(self, t2, l2):
         self.ccwfn._load(None, self.ccwfn.engine.t1, t2)

@@ -242,6 +242,9 @@ class ccwfn(object):
 
     def _load(self, F, t1, t2):
         eng = self.engine
+        if _is_complex(F) or _is_complex(t1) or _is_complex(t2):
+            raise Exception("complex amplitudes / Fock matrices go through ccwfn.residuals() only "
+                            "(two real planes); the builders of the B200 engine are real.")
         if F is None:
             F = eng.F0                   # the Hamiltonian's own Fock matrix
         if F is not eng.F:
@@ -251,6 +254,29 @@ class ccwfn(object):
         if t2 is not eng.t2:
             eng.t2.copy_(torch.as_tensor(t2).to(eng.t2.device, eng.dtype))
 
+    class _Pure(object):
+        """Context manager that makes a public builder pure, like the reference's: the object's own
+        amplitudes and Fock matrix are put back when the call used other ones (the engine's
+        intermediates keep the values of the call)."""
+
+        def __init__(self, w, t1, t2):
+            self.eng = w.engine
+            e = self.eng
+            self.k1 = None if (t1 is None or t1 is e.t1) else e.t1.clone()
+            self.k2 = None if (t2 is None or t2 is e.t2) else e.t2.clone()
+
+        def __enter__(self):
+            return self
+
+        def __exit__(self, *exc):
+            e = self.eng
+            if self.k1 is not None:
+                e.t1.copy_(self.k1)
+            if self.k2 is not None:
+                e.t2.copy_(self.k2)
+            e.set_fock(e.F0)
+            return False
+
     def residuals(self, F, t1, t2, real_time=False):
         """r1, r2 = <mu|HBAR|0> for the given Fock operator and amplitudes (pycc/ccwfn.py:331-406).
         Pure, like the reference's: the object's amplitudes and ``H.F`` are unchanged afterwards
@@ -259,17 +285,14 @@ class ccwfn(object):
         if _is_complex(F) or _is_complex(t1) or _is_complex(t2):
             # complex amplitudes (real-time propagation, pycc/rt/rtcc.py:125): two real planes
             return self._complex().residuals(F, t1, t2)
+        if real_time and self.model == 'CC3':
+            # the reference adds t3_pert_ijk terms built from the field-dressed F (pycc/ccwfn.py:378-386)
+            raise NotImplementedError("real_time=True with model CC3 (t3_pert_ijk) is outside the B200 engine")
         eng = self.engine
-        own = t1 is eng.t1 and t2 is eng.t2
-        if not own:                      # pure: the object's amplitudes are put back afterwards
-            keep1, keep2 = eng.t1.clone(), eng.t2.clone()
-        self._load(F, t1, t2)
-        r1, r2 = eng.residuals(symmetrize=True)
-        r1, r2 = r1.clone(), r2.clone()
-        if not own:
-            eng.t1.copy_(keep1)
-            eng.t2.copy_(keep2)
-        eng.set_fock(eng.F0)
+        with self._Pure(self, t1, t2):   # pure: the object's amplitudes and H.F are put back afterwards
+            self._load(F, t1, t2)
+            r1, r2 = eng.residuals(symmetrize=True)
+            r1, r2 = r1.clone(), r2.clone()
         return r1, r2
 
     # ---- host <-> device transfer of the amplitudes, sharded over the ranks -------------------------
@@ -337,8 +360,9 @@ class ccwfn(object):
         if name not in self.engine.plans or name not in self.engine.builder_order() or \
                 (self.model == 'CCD' and name in ('Fme', 'Zmbij')):
             return False
-        self._load(F, t1, t2)
-        self.engine.run_builder(name)
+        with self._Pure(self, t1, t2):
+            self._load(F, t1, t2)
+            self.engine.run_builder(name)
         return True
 
     def build_Fae(self, o, v, F, L, t1, t2):
@@ -378,32 +402,38 @@ class ccwfn(object):
 
     def r_T1(self, o, v, F, ERI, L, t1, t2, Fae, Fme, Fmi):
         eng = self.engine
-        self._load(F, t1, t2)
-        eng.be.bind_stream()
-        eng.prepare()
-        eng.Fae.copy_(torch.as_tensor(Fae).to(eng.Fae.device, eng.dtype))
-        eng.Fme.copy_(torch.as_tensor(Fme).to(eng.Fme.device, eng.dtype))
-        eng.Fmi.copy_(torch.as_tensor(Fmi).to(eng.Fmi.device, eng.dtype))
-        eng._run("r_T1")
-        return eng.r1.clone()
+        with self._Pure(self, t1, t2):
+            self._load(F, t1, t2)
+            eng.be.bind_stream()
+            eng.prepare()
+            eng.Fae.copy_(torch.as_tensor(Fae).to(eng.Fae.device, eng.dtype))
+            eng.Fme.copy_(torch.as_tensor(Fme).to(eng.Fme.device, eng.dtype))
+            eng.Fmi.copy_(torch.as_tensor(Fmi).to(eng.Fmi.device, eng.dtype))
+            eng._run("r_T1")
+            out = eng.r1.clone()
+        return out
 
     def r_T2(self, o, v, F, ERI, L, t1, t2, Fae, Fme, Fmi, Wmnij, Wmbej, Wmbje, Zmbij):
         eng = self.engine
-        self._load(F, t1, t2)
-        eng.be.bind_stream()
-        eng.prepare()
-        dev = lambda x: torch.as_tensor(x).to(eng.t2.device, eng.dtype)
-        eng.Fae.copy_(dev(Fae))
-        eng.Fme.copy_(dev(Fme))
-        eng.Fmi.copy_(dev(Fmi))
-        eng.Wmnij.copy_(dev(Wmnij))
-        eng.Wmbej_view().copy_(dev(Wmbej))
-        eng.Wmbje_view().copy_(dev(Wmbje))
-        eng.Zmbij_view().copy_(dev(Zmbij))
-        eng._run("r_T2")
-        eng.be.pair_symmetrize(eng.r2, self.no, self.nv)
-        return eng.r2.clone()
+        with self._Pure(self, t1, t2):
+            self._load(F, t1, t2)
+            eng.be.bind_stream()
+            eng.prepare()
+            dev = lambda x: torch.as_tensor(x).to(eng.t2.device, eng.dtype)
+            eng.Fae.copy_(dev(Fae))
+            eng.Fme.copy_(dev(Fme))
+            eng.Fmi.copy_(dev(Fmi))
+            eng.Wmnij.copy_(dev(Wmnij))
+            eng.Wmbej_view().copy_(dev(Wmbej))
+            eng.Wmbje_view().copy_(dev(Wmbje))
+            eng.Zmbij_view().copy_(dev(Zmbij))
+            eng._run("r_T2")
+            eng.be.pair_symmetrize(eng.r2, self.no, self.nv)
+            out = eng.r2.clone()
+        return out
 
     def cc_energy(self, o, v, F, L, t1, t2):
-        self._load(F, t1, t2)
-        return self.engine.energy()
+        with self._Pure(self, t1, t2):
+            self._load(F, t1, t2)
+            e = self.engine.energy()
+        return e

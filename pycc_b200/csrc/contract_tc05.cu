@@ -290,11 +290,12 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
     // is run panel by panel over K, accumulating into C (beta = 1 after the first panel).  The A panel then
     // stays L2-resident while the big B operand streams once per panel; without this the CTAs that share
     // operand tiles drift apart and the ladder at (40,300) read 511 GB from DRAM for 65 GB of operands.
-    static const long long panel_bytes = [] { const char* e = getenv("PCCB_TC05_PANEL_MB"); return (long long)(e ? atoi(e) : 128) << 20; }();
+    // (the two knobs are read on every call - a getenv is nothing next to a launch - so that a test can lower them)
+    const long long panel_bytes = [] { const char* e = getenv("PCCB_TC05_PANEL_MB"); return (long long)(e ? atoi(e) : 128) << 20; }();
     long long kpanel = 0;
     // (only when B is the big streaming operand, N >> M: the ladder; for square-ish products such as the ring
     //  terms the extra read-modify-write passes over C cost more than the panels save)
-    static const long long panel_ratio = [] { const char* e = getenv("PCCB_TC05_PANEL_RATIO"); return (long long)(e ? atoi(e) : 8); }();
+    const long long panel_ratio = [] { const char* e = getenv("PCCB_TC05_PANEL_RATIO"); return (long long)(e ? atoi(e) : 8); }();
     if (ns == 1 && panel_bytes > 0 && d->N >= panel_ratio * d->M) {
         const long long a_bytes = 8ll * d->M * segs[0]->K;          // two FP32 planes
         if (a_bytes > panel_bytes) {
@@ -379,13 +380,26 @@ extern "C" int pccb_split_lo(pccb_ctx* ctx, const void* x_dev, void* lo_dev, int
 extern "C" int pccb_register_lo_plane(pccb_ctx* ctx, const void* x_dev, const void* lo_dev, int64_t n) {
     if (!ctx) return PCCB_ERR_ARG;
     PCCB_REQUIRE(ctx, x_dev && lo_dev && n > 0, "pccb_register_lo_plane: bad arguments");
-    for (auto& e : ctx->lo_planes)
-        if (e.base == static_cast<const char*>(x_dev)) {
-            e.lo = static_cast<const char*>(lo_dev);
-            e.bytes = (size_t)n * sizeof(float);
-            return PCCB_OK;
-        }
-    ctx->lo_planes.push_back({static_cast<const char*>(x_dev), static_cast<const char*>(lo_dev), (size_t)n * sizeof(float)});
+    // a new registration replaces every entry whose address range overlaps it (same base re-registered, or
+    // memory recycled by the caller's allocator after the tensor that owned the old entry was freed)
+    const char* b = static_cast<const char*>(x_dev);
+    const size_t bytes = (size_t)n * sizeof(float);
+    auto& v = ctx->lo_planes;
+    for (size_t q = 0; q < v.size();) {
+        if (b < v[q].base + v[q].bytes && v[q].base < b + bytes) v.erase(v.begin() + q);
+        else ++q;
+    }
+    v.push_back({b, static_cast<const char*>(lo_dev), bytes});
+    return PCCB_OK;
+}
+
+extern "C" int pccb_unregister_lo_plane(pccb_ctx* ctx, const void* x_dev) {
+    if (!ctx) return PCCB_ERR_ARG;
+    auto& v = ctx->lo_planes;
+    for (size_t q = 0; q < v.size();) {
+        if (v[q].base == static_cast<const char*>(x_dev)) v.erase(v.begin() + q);
+        else ++q;
+    }
     return PCCB_OK;
 }
 

@@ -31,6 +31,15 @@ from .dsl import TRef, plan
 from .parallel import Comm, virtual_slice
 
 
+def _unregister_lo(be, ptrs):
+    try:
+        if getattr(be, "h", None):
+            for p in ptrs:
+                be.unregister_lo_plane(p)
+    except Exception:
+        pass
+
+
 class CCSDEngine(object):
     def __init__(self, backend, F, blocks, no, nv, dtype=torch.float64, comm=None, keep_full_ovvv=True,
                  model='CCSD'):
@@ -128,6 +137,14 @@ class CCSDEngine(object):
                 x = getattr(self, name)
                 self._lo[name] = be.empty(tuple(x.shape), dtype)
                 be.register_lo_plane(x, self._lo[name])
+        if self._lo is not None:
+            # the registry maps raw address ranges to lo planes: drop this engine's ranges when it dies, so
+            # that memory the caching allocator recycles can never match a stale entry
+            import weakref
+            ranges = [x.data_ptr() for x in
+                      [self.vvvv_loc, self.blk["ovvv"], self.blk["oovv"]] + [getattr(self, n) for n in self._lo
+                                                                            if hasattr(self, n)]]
+            weakref.finalize(self, _unregister_lo, be, sorted(set(ranges)))
         self.cc3 = None
         self.ladder_events = None    # bench.py: list that receives (start, end) CUDA events per ladder launch
         self._build_plans()
@@ -350,10 +367,10 @@ class CCSDEngine(object):
     def residuals(self, symmetrize=True):
         """r1, r2 for the amplitudes held in self.t1 / self.t2 (pycc/ccwfn.py:357-366)."""
         self.be.bind_stream()
-        self.prepare()
         if self.model == 'CCD':
-            self.t1.zero_()          # CCD carries no singles (ccwfn.py:543-546)
+            self.t1.zero_()          # CCD carries no singles (ccwfn.py:543-546): before tau is formed
             self.r1.zero_()
+        self.prepare()
         for name in self.builder_order():
             self._run(name)
         if self.model == 'CC3':      # triples contributions X1, X2 (pycc/ccwfn.py:371-401)

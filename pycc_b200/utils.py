@@ -129,8 +129,20 @@ class helper_diis(object):
         resid = np.zeros(m + 1)
         resid[-1] = -1.0
         ci = np.linalg.solve(B, resid)
+        # sum_k c_k vals[k+1]; pccb_lincomb takes at most 16 vectors per launch, so a longer history
+        # (max_diis > 16, or a late start_diis) is accumulated in groups: the running sum enters the
+        # next group as one more vector with coefficient 1
         new = self._alloc()
-        self.be.lincomb(new, [self.diis_vals[k + 1] for k in range(m)], [ci[k] for k in range(m)])
+        G = 16
+        self.be.lincomb(new, [self.diis_vals[k + 1] for k in range(min(m, G))], [ci[k] for k in range(min(m, G))])
+        k0 = G
+        while k0 < m:
+            k1 = min(m, k0 + G - 1)
+            nxt = self._alloc()
+            self.be.lincomb(nxt, [new] + [self.diis_vals[k + 1] for k in range(k0, k1)],
+                            [1.0] + [ci[k] for k in range(k0, k1)])
+            self._pool.append(new)
+            new, k0 = nxt, k1
         prev, self.old = self.old, new
         self._release(prev)
         # the caller's amplitude tensors are updated in place (they are the engine's buffers)

@@ -54,6 +54,9 @@ CASES = [
     ("C[mn] = A[mk]*B[nk]", dict(A=(90, 200), B=(38011, 200), C=(90, 38011))),
     ("C[nm] = A[km]*B[kn]", dict(A=(137, 60), B=(137, 38002), C=(38002, 60))),
     ("C[nm] = A[mk]*B[nk]", dict(A=(157, 300), B=(24000, 300), C=(24000, 157))),
+    # plain K-contiguous matrices with M = 256 / 1024: the 128-row TMA-staged kernel, contract_f64_tma_kernel<8>
+    ("C[mn] = A[mk]*B[nk]", dict(A=(256, 520), B=(390, 520), C=(256, 390))),
+    ("C[mn] = A[mk]*B[nk] + A2[mk]*B2[nk]", dict(A=(1024, 200), B=(2100, 200), A2=(1024, 72), B2=(2100, 72), C=(1024, 2100))),
 ]
 
 
@@ -206,6 +209,40 @@ TC05_CASES = [
     ("C[nm] = A[mk]*B[nk]", dict(A=(260, 512), B=(300, 512), C=(300, 260))),                                # strided output
     ("C[mn] = A[mk]*B[nk] + A2[mk]*B2[nk]", dict(A=(256, 260), B=(256, 260), A2=(256, 260), B2=(256, 260), C=(256, 256))),
 ]
+
+
+def test_contract_f32_tcgen05_k_panels(be, monkeypatch):
+    """The K-panel loop of the tcgen05 path (one segment, N >= 8 M, A planes larger than the panel budget:
+    the SP ladder at (40,300)) with the budget lowered to 1 MB so that a small shape runs it: three panels
+    of 1024 + 1024 + 952 k, the last one ragged against the 32-float k-block, beta = 1 from the second on."""
+    from pycc_b200.dsl import plan
+    from pycc_b200 import _lib
+    monkeypatch.setenv("PCCB_TC05_PANEL_MB", "1")
+    g = torch.Generator(device="cpu").manual_seed(77)
+    M, N, K = 128, 1100, 3000
+    A = torch.randn(M, K, generator=g, dtype=torch.float32).to(be.device)
+    B = torch.randn(N, K, generator=g, dtype=torch.float32).to(be.device)
+    C0 = torch.randn(M, N, generator=g, dtype=torch.float32).to(be.device)
+    los = []
+    for t in (A, B):
+        lo = torch.empty_like(t)
+        be.split_lo(t, lo)
+        be.register_lo_plane(t, lo)
+        los.append(lo)
+    ref = A.double() @ B.double().T
+    mag = A.double().abs() @ B.double().abs().T
+    tol = 4e-6 * mag + 1e-6
+    try:
+        for stmt, base in (("C[mn] = A[mk]*B[nk]", None), ("C[mn] += 0.5*A[mk]*B[nk]", C0)):
+            C = torch.full((M, N), float("nan"), dtype=torch.float32, device=be.device) if base is None else base.clone()
+            n0 = be.launch_count()
+            for L in plan(stmt, dict(A=A, B=B, C=C), _lib.F32):
+                be.contract(L.desc)
+            assert be.launch_count() - n0 == 3          # three K panels, tcgen05 kernel each
+            want = ref if base is None else base.double() + 0.5 * ref
+            assert ((C.double() - want).abs() <= tol).all()
+    finally:
+        be._check(be.lib.pccb_clear_lo_planes(be.h))
 
 
 @pytest.mark.parametrize("case", range(len(TC05_CASES)))

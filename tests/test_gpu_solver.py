@@ -104,6 +104,40 @@ def test_seeded_systems_vs_oracle(no, nv, offdiag):
     assert abs(et_all - (et_a + et_b)) < 1e-13
 
 
+def test_config2_o20_v150_converged_solve_vs_oracle():
+    """BASELINE.json configs[1] ("synthetic RHF-CCSD o=20 v=150 FP64 on 1xB200 ... correctness vs CPU
+    reference"), the bench's own seeded system: converged solve against the pinned NumPy oracle -
+    same iteration count, |dE| <= 1e-10 Eh, max|dT1|, max|dT2| <= 1e-9 - and E(T) per triplet on a seeded
+    sample against the oracle's t_tjl body.  About a minute of host time for the oracle."""
+    import pycc_b200
+    from pycc_b200.synthetic import SyntheticSystem
+    from oracle import ccsd_oracle as oc, triples_oracle as ot
+    no, nv = 20, 150
+    s = SyntheticSystem(no, nv, seed=0)
+    w = _wfn(s.F, s.blocks, no, "CCSD(T)")
+    with contextlib.redirect_stdout(io.StringIO()):
+        e = w.solve_cc(e_conv=1e-10, r_conv=1e-10, maxiter=60)
+    et_gpu = e - w.iteration_log[-1][1]
+    eo, t1, t2, niter = oc.solve_cc(s.F, s.blocks, 1e-10, 1e-10, maxiter=60)
+    assert eo is not None and len(w.iteration_log) == niter
+    assert abs(w.iteration_log[-1][1] - eo) < E_TOL
+    assert np.abs(w.t1.cpu().numpy() - t1).max() < T_TOL
+    assert np.abs(w.t2.cpu().numpy() - t2).max() < T_TOL
+    tri = pycc_b200.cctriples._engine(w)
+    rng = np.random.default_rng(20150)
+    pairs = tri.pairs()
+    sample = [pairs[q] for q in sorted(rng.choice(len(pairs), size=3, replace=False))]
+    _, per, trip = tri.energy(sample)
+    blk = oc.Blocks(s.blocks)
+    pick = sorted(rng.choice(len(trip), size=min(6, len(trip)), replace=False))
+    for q in pick:
+        i, j, k = trip[q]
+        assert abs(per[q].item() - ot.et_triplet(s.F, blk, t1, t2, i, j, k)) < 1e-12
+    # the full (T) sum is bit-reproducible and additive over any partition of the pairs
+    half = len(pairs) // 2
+    assert abs(et_gpu - (tri.energy(pairs[:half])[0] + tri.energy(pairs[half:])[0])) < 1e-12
+
+
 def test_residual_properties_at_scale():
     """(16, 100): no CPU oracle in the test budget -> size-independent properties.
     (1) pair symmetry r2[ijab] = r2[jiba]; (2) the ladder term equals the factorised checker

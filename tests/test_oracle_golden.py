@@ -83,3 +83,43 @@ def test_lambda_oracle_against_reference_vectors(golden):
     H = ol.build_hbar(g.F, blk, ts1, ts2)
     n1, n2, lecc, rms = ol.lambda_iteration(g.F, blk, H, ts2, z["ccsd_solve_l1"], z["ccsd_solve_l2"])
     assert rms < 1e-10 and abs(lecc - float(z["ccsd_solve_lecc"])) < 1e-11
+
+
+# ---- the torch restatement (oracle/torch_oracle.py): same formulas on torch tensors, used by bench.py as
+# the full-size checker on the GPU box (cuBLAS FP64); pinned here, on the CPU, to the same golden vectors
+@pytest.mark.parametrize("tag", ["sym", "gen"])
+def test_torch_oracle_residuals_and_energy(golden, tag):
+    from oracle import torch_oracle as to
+    g = golden
+    blk = to.Blocks(g.blocks)
+    t1, t2 = g[tag + "_t1"], g[tag + "_t2"]
+    r1, r2 = to.residuals(g.F, blk, t1, t2)
+    assert np.abs(r1.numpy() - g[tag + "_r1"]).max() < TOL
+    assert np.abs(r2.numpy() - g[tag + "_r2"]).max() < TOL
+    assert abs(to.cc_energy(g.F, blk, t1, t2) - float(g[tag + "_energy"])) < TOL
+    # sharded ladder: rows [lo, hi) of <ab|ef> on each "rank"; pieces + the rest = the whole
+    nv = g.nv
+    cut = nv // 2
+    _, rest = to.residuals(g.F, blk, t1, t2, skip_ladder=True)
+    lad = 0.0
+    for lo, hi in ((0, cut), (cut, nv)):
+        sub = dict(g.blocks)
+        sub["vvvv"] = g.blocks["vvvv"][lo:hi]
+        _, piece = to.residuals(g.F, to.Blocks(sub, vv_rows=(lo, hi)), t1, t2, ladder_only=True)
+        lad = lad + piece
+    lad = lad + lad.permute(1, 0, 3, 2)
+    assert np.abs((rest + lad).numpy() - g[tag + "_r2"]).max() < TOL
+
+
+def test_torch_oracle_triplets(golden):
+    from oracle import torch_oracle as to
+    g = golden
+    blk, tblk = oc.Blocks(g.blocks), to.Blocks(g.blocks)
+    t1, t2 = g["gen_t1"], g["gen_t2"]
+    no = g.no
+    tot = 0.0
+    for (i, j, k) in [(i, j, k) for i in range(no) for j in range(i + 1) for k in range(j + 1)]:
+        e = to.et_triplet(g.F, tblk, t1, t2, i, j, k)
+        assert abs(e - ot.et_triplet(g.F, blk, t1, t2, i, j, k)) < 1e-13
+        tot += e
+    assert abs(tot - float(g["gen_et_tjl"])) < TOL
