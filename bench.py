@@ -267,7 +267,7 @@ def run_ours(args):
         w = pycc_b200.ccwfn.from_arrays(F, blocks, o, model="CCSD(T)" if want_t else "CCSD", group=group,
                                         precision=args.precision)
     eng, be = w.engine, w.backend
-    diis = helper_diis(w.t1, w.t2, 8, args.precision, backend=be, comm=w.comm)
+    diis = w.make_diis(8)
 
     def barrier():
         torch.cuda.synchronize()

@@ -134,6 +134,27 @@ int pccb_update_amplitudes(pccb_ctx* ctx, int dtype, void* t1_dev, void* t2_dev,
                            const void* r2_dev, const void* eps_dev, int64_t no, int64_t nv, int symmetrize,
                            double* rms2_host);
 
+/* Fused form of the two calls around this comment, for the (i,j) blocks ij = i*no+j in [ij_lo, ij_hi)
+ * of t2 (the whole range on one GPU; one rank's share when the update is split over ranks):
+ * t1 += r1/Dia (always, all of it), t2[ij] += (r2[ijab] (+ r2[jiba])) / Dijab, and the energy of the NEW
+ * amplitudes over those blocks.  out_host[0] = sum of squared increments, out_host[1] = energy part;
+ * the t1 increment norm and the singles energy 2 sum F_ia t_ia are included only when count_t1 != 0, so
+ * that the ranks' results add up to pycc/ccwfn.py:287-296.  Host-returning. */
+int pccb_update_energy(pccb_ctx* ctx, int dtype, void* t1_dev, void* t2_dev, const void* r1_dev, const void* r2_dev,
+                       const void* eps_dev, const void* fov_dev, int64_t ld_fov, const void* oovv_dev, int64_t no,
+                       int64_t nv, int symmetrize, int64_t ij_lo, int64_t ij_hi, int count_t1, double* out_host);
+
+/* One pass over t2 that writes every amplitude-dependent o^2 v^2 operand of the planned contractions
+ * (any pointer may be NULL): tau = t2 + t1 t1, tauh = t2 + t1 t1 / 2, tauW = t2 / 2 + t1 t1
+ * (build_tau, pycc/ccwfn.py:408-410), t2s = 2 t2 - t2.swapaxes(2,3) (:554), t11 = t1 t1 (CC2), and the
+ * plain-matrix layouts t2sP[i,a,m,e] = t2s[i,m,a,e], t2P[i,a,m,e] = t2[i,m,a,e], t2Q[j,a,m,e] = t2[m,j,a,e],
+ * tauWPn[j,B,n,f] = -tauW[j,n,f,B], t2Rh[j,B,n,f] = t2[n,j,f,B] / 2 with B restricted to [vlo, vlo+vl). */
+typedef struct pccb_prepare_outputs {
+    void *tau, *tauh, *tauW, *t2s, *t11, *t2sP, *t2P, *t2Q, *tauWPn, *t2Rh;
+} pccb_prepare_outputs;
+int pccb_prepare_amplitudes(pccb_ctx* ctx, int dtype, const void* t1_dev, const void* t2_dev, int64_t no, int64_t nv,
+                            int64_t vlo, int64_t vl, const pccb_prepare_outputs* out);
+
 /* E = 2 sum F_ia t_ia + sum (t2_ijab + t_ia t_jb) (2<ij|ab> - <ij|ba>)  (pycc/ccwfn.py:717-718).
  * fov_dev is the (no,nv) occupied-virtual Fock block, row stride ld_fov.  Host-returning. */
 int pccb_cc_energy(pccb_ctx* ctx, int dtype, const void* fov_dev, int64_t ld_fov, const void* t1_dev,

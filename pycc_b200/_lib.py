@@ -23,7 +23,7 @@ EXPORTS = (
     "pccb_synchronize", "pccb_contract", "pccb_pair_combine", "pccb_pair_symmetrize", "pccb_permute4",
     "pccb_update_amplitudes", "pccb_cc_energy", "pccb_dot", "pccb_axpby", "pccb_lincomb",
     "pccb_triples_energy", "pccb_t3_combine", "pccb_split_lo", "pccb_register_lo_plane", "pccb_clear_lo_planes",
-    "pccb_unregister_lo_plane",
+    "pccb_unregister_lo_plane", "pccb_update_energy", "pccb_prepare_amplitudes",
 )
 
 
@@ -45,6 +45,10 @@ class Contraction(C.Structure):
                 ("C_dev", C.c_void_p), ("cm", CIdx), ("cn", CIdx), ("c_batch", C.c_int64),
                 ("D_dev", C.c_void_p), ("dm", CIdx), ("dn", CIdx), ("d_batch", C.c_int64),
                 ("alpha", C.c_double), ("beta", C.c_double), ("gamma", C.c_double)]
+
+
+class PrepareOutputs(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ("tau", "tauh", "tauW", "t2s", "t11", "t2sP", "t2P", "t2Q", "tauWPn", "t2Rh")]
 
 
 class EngineError(RuntimeError):
@@ -81,6 +85,8 @@ def load():
     lib.pccb_pair_symmetrize.argtypes = [vp, i32, vp, i64, i64]
     lib.pccb_permute4.argtypes = [vp, i32, vp, vp, C.POINTER(i64), C.POINTER(i64), dbl, dbl]
     lib.pccb_update_amplitudes.argtypes = [vp, i32, vp, vp, vp, vp, vp, i64, i64, i32, pd]
+    lib.pccb_update_energy.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, i64, vp, i64, i64, i32, i64, i64, i32, pd]
+    lib.pccb_prepare_amplitudes.argtypes = [vp, i32, vp, vp, i64, i64, i64, i64, C.POINTER(PrepareOutputs)]
     lib.pccb_cc_energy.argtypes = [vp, i32, vp, i64, vp, vp, vp, i64, i64, pd]
     lib.pccb_dot.argtypes = [vp, i32, vp, vp, i64, pd]
     lib.pccb_axpby.argtypes = [vp, i32, vp, dbl, vp, dbl, vp, i64]

@@ -114,6 +114,25 @@ class CudaBackend(object):
                                                     1 if symmetrize else 0, C.byref(out)))
         return out.value
 
+    def update_energy(self, t1, t2, r1, r2, eps, fov, ld_fov, oovv, no, nv, symmetrize, ij_lo, ij_hi, count_t1):
+        """Fused t += r/D, increment norm and energy of the new amplitudes for the (i,j) blocks
+        [ij_lo, ij_hi) of t2 (t1 is always updated in full).  Returns (rms2 part, energy part)."""
+        out = (C.c_double * 2)()
+        self._check(self.lib.pccb_update_energy(self.h, dtype_code(t2), t1.data_ptr(), t2.data_ptr(), r1.data_ptr(),
+                                                r2.data_ptr(), eps.data_ptr(), fov.data_ptr(), ld_fov, oovv.data_ptr(),
+                                                no, nv, 1 if symmetrize else 0, ij_lo, ij_hi, 1 if count_t1 else 0, out))
+        return out[0], out[1]
+
+    def prepare_amplitudes(self, t1, t2, no, nv, vlo, vl, **outs):
+        """One pass over t2 writing the amplitude-dependent operands named in ``outs`` (tau, tauh, tauW, t2s,
+        t11, t2sP, t2P, t2Q, tauWPn, t2Rh; see pccb_prepare_amplitudes)."""
+        o = _lib.PrepareOutputs()
+        for k, t in outs.items():
+            if t is not None:
+                setattr(o, k, t.data_ptr())
+        self._check(self.lib.pccb_prepare_amplitudes(self.h, dtype_code(t2), t1.data_ptr(), t2.data_ptr(), no, nv,
+                                                     vlo, vl, C.byref(o)))
+
     def cc_energy(self, fov, ld_fov, t1, t2, oovv, no, nv):
         out = C.c_double()
         self._check(self.lib.pccb_cc_energy(self.h, dtype_code(t2), fov.data_ptr(), ld_fov, t1.data_ptr(),

@@ -197,7 +197,7 @@ class ccwfn(object):
         eng.set_fock(eng.F0)
         ecc = eng.energy()
         print("CC Iter %3d: CC Ecorr = %.15f  dE = % .5E  MP2" % (0, ecc, -ecc))
-        diis = helper_diis(self.t1, self.t2, max_diis, self.precision, backend=self.backend, comm=self.comm)
+        diis = self.make_diis(max_diis)
         self.diis = diis
         self.iteration_log = []
         for niter in range(1, maxiter + 1):
@@ -207,6 +207,7 @@ class ccwfn(object):
             print("CC Iter %3d: CC Ecorr = %.15f  dE = % .5E  rms = % .5E" % (niter, ecc, ediff, rms))
             self.iteration_log.append((niter, ecc, ediff, rms))
             if (abs(ediff) < e_conv) and abs(rms) < r_conv:
+                eng.sync_amplitudes()
                 print("\nCCWFN converged in %.3f seconds.\n" % (time.time() - ccsd_tstart))
                 print("E(REF)  = %20.15f" % self.eref)
                 if self.model == 'CCSD(T)':
@@ -221,6 +222,15 @@ class ccwfn(object):
                 print("E(TOT)  = %20.15f" % (ecc + self.eref))
                 return ecc
             self._diis_step(diis, niter, start_diis)
+        eng.sync_amplitudes()
+
+    def make_diis(self, max_diis=8):
+        """helper_diis over this object's amplitudes; with several GPUs its history is sliced by the same
+        (i,j) blocks of t2 that each rank updates."""
+        eng = self.engine
+        blocks = (eng._t2_store, self.nv * self.nv, eng.chunk_pairs) if self.comm.world > 1 else None
+        return helper_diis(self.t1, self.t2, max_diis, self.precision, backend=self.backend, comm=self.comm,
+                           blocks=blocks)
 
     def _iteration(self, diis, niter, start_diis, extrapolate=True):
         """One pass of the solve_cc loop body (pycc/ccwfn.py:274-296, 327-329): residuals, t += r/D
@@ -228,17 +238,27 @@ class ccwfn(object):
         energy and (``extrapolate``) the DIIS step.  Returns (ecc, rms).  This is the unit bench.py
         times as one step."""
         eng = self.engine
+        eng.sync_amplitudes()
         eng.residuals(symmetrize=False)
-        rms = np.sqrt(eng.update(symmetrize_on_the_fly=True))
-        ecc = eng.energy()
+        rms2, ecc = eng.update_energy()          # one fused pass; split over the ranks by (i,j) blocks
+        rms = np.sqrt(rms2)
         if extrapolate:
             self._diis_step(diis, niter, start_diis)
         return ecc, rms
 
     def _diis_step(self, diis, niter, start_diis):
+        """DIIS push + extrapolation.  After a split update each rank's history slice is exactly the blocks it
+        updated, and the allgather of the extrapolated chunks completes t2; without an extrapolation the
+        updated chunks themselves are gathered."""
+        eng = self.engine
+        if diis.blocks is None:
+            eng.sync_amplitudes()        # a flat-chunk history packs slices of the COMPLETE vector
         diis.add_error_vector(self.t1, self.t2)
-        if niter >= start_diis:
+        if niter >= start_diis and diis.max_diis > 0:
             self.t1, self.t2 = diis.extrapolate(self.t1, self.t2)
+            if diis.blocks is not None:
+                eng.t2_stale = False     # the allgather of the extrapolated chunks completed t2
+        eng.sync_amplitudes()
 
     def _load(self, F, t1, t2):
         eng = self.engine

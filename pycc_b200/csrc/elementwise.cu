@@ -147,45 +147,6 @@ __global__ void permute4_kernel(T* __restrict__ out, const T* __restrict__ in, l
     }
 }
 
-// ---- amplitude update + squared norm of the increment ------------------------------------------
-template <typename T>
-__global__ void update_t2_kernel(T* __restrict__ t2, const T* __restrict__ r2, const T* __restrict__ eps, int no,
-                                 int nv, int symmetrize, double* __restrict__ partials) {
-    const long long nvv = (long long)nv * nv, total = (long long)no * no * nvv;
-    double acc = 0.0;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-         idx += (long long)gridDim.x * blockDim.x) {
-        const long long ij = idx / nvv, ab = idx - ij * nvv;
-        const int i = (int)(ij / no), j = (int)(ij - (long long)i * no);
-        const int a = (int)(ab / nv), b = (int)(ab - (long long)a * nv);
-        double r = (double)r2[idx];
-        if (symmetrize) r += (double)r2[((long long)j * no + i) * nvv + (long long)b * nv + a];
-        const double d = (double)eps[i] + (double)eps[j] - (double)eps[no + a] - (double)eps[no + b];
-        const double inc = (double)(T)(r / d);
-        t2[idx] = (T)((double)t2[idx] + inc);
-        acc += inc * inc;
-    }
-    acc = block_sum(acc);
-    if (threadIdx.x == 0) partials[blockIdx.x] = acc;
-}
-
-template <typename T>
-__global__ void update_t1_kernel(T* __restrict__ t1, const T* __restrict__ r1, const T* __restrict__ eps, int no,
-                                 int nv, double* __restrict__ partials) {
-    const long long total = (long long)no * nv;
-    double acc = 0.0;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
-         idx += (long long)gridDim.x * blockDim.x) {
-        const int i = (int)(idx / nv), a = (int)(idx - (long long)i * nv);
-        const double d = (double)eps[i] - (double)eps[no + a];
-        const double inc = (double)(T)((double)r1[idx] / d);
-        t1[idx] = (T)((double)t1[idx] + inc);
-        acc += inc * inc;
-    }
-    acc = block_sum(acc);
-    if (threadIdx.x == 0) partials[blockIdx.x] = acc;
-}
-
 // ---- energy --------------------------------------------------------------------------------------
 // One CTA per 32x32 (a,b) tile of one (i,j): E += (t2[ijab] + t1[ia] t1[jb]) (2 g[ijab] - g[ijba])
 template <typename T>
@@ -224,27 +185,6 @@ __global__ void energy_kernel(const T* __restrict__ fov, long long ld_fov, const
 }
 
 // ---- DIIS vector algebra ---------------------------------------------------------------------
-template <typename T>
-__global__ void dot_kernel(const T* __restrict__ x, const T* __restrict__ y, long long n, double* __restrict__ partials) {
-    double acc = 0.0;
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n;
-         idx += (long long)gridDim.x * blockDim.x)
-        acc += (double)x[idx] * (double)y[idx];
-    acc = block_sum(acc);
-    if (threadIdx.x == 0) partials[blockIdx.x] = acc;
-}
-
-template <typename T>
-__global__ void axpby_kernel(T* __restrict__ out, double a, const T* __restrict__ x, double b, const T* __restrict__ y,
-                             long long n) {
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n;
-         idx += (long long)gridDim.x * blockDim.x) {
-        double v = a * (double)x[idx];
-        if (y != nullptr) v += b * (double)y[idx];
-        out[idx] = (T)v;
-    }
-}
-
 constexpr int MAX_LINCOMB = 16;
 template <typename T>
 struct LincombArgs {
@@ -253,13 +193,296 @@ struct LincombArgs {
     int n;
 };
 
-template <typename T>
-__global__ void lincomb_kernel(T* __restrict__ out, const __grid_constant__ LincombArgs<T> args, long long n) {
-    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n;
-         idx += (long long)gridDim.x * blockDim.x) {
+
+// ---- 16-byte vectorised streaming kernels (DIIS algebra) ---------------------------------------------
+// VEC elements of T make one 16-byte access (2 doubles / 4 floats); the host picks VEC = 1 when a pointer
+// is not 16-byte aligned.  The tail (n % VEC) is handled by scalar accesses of the last threads.
+template <typename T, int VEC> struct alignas(sizeof(T) * VEC) Pack { T v[VEC]; };
+
+template <typename T, int VEC>
+__global__ void dot_vec_kernel(const T* __restrict__ x, const T* __restrict__ y, long long n, double* __restrict__ partials) {
+    using P = Pack<T, VEC>;
+    const long long nvec = n / VEC, stride = (long long)gridDim.x * blockDim.x;
+    double acc = 0.0;
+    const P* xp = reinterpret_cast<const P*>(x);
+    const P* yp = reinterpret_cast<const P*>(y);
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) {
+        const P a = xp[q], b = yp[q];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) acc += (double)a.v[e] * (double)b.v[e];
+    }
+    for (long long idx = nvec * VEC + (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride)
+        acc += (double)x[idx] * (double)y[idx];
+    acc = block_sum(acc);
+    if (threadIdx.x == 0) partials[blockIdx.x] = acc;
+}
+
+template <typename T, int VEC>
+__global__ void axpby_vec_kernel(T* __restrict__ out, double a, const T* __restrict__ x, double b, const T* __restrict__ y,
+                                 long long n) {
+    using P = Pack<T, VEC>;
+    const long long nvec = n / VEC, stride = (long long)gridDim.x * blockDim.x;
+    const P* xp = reinterpret_cast<const P*>(x);
+    const P* yp = reinterpret_cast<const P*>(y);
+    P* op = reinterpret_cast<P*>(out);
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) {
+        const P u = xp[q];
+        P r;
+        if (y != nullptr) {
+            const P w = yp[q];
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) r.v[e] = (T)(a * (double)u.v[e] + b * (double)w.v[e]);
+        } else {
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) r.v[e] = (T)(a * (double)u.v[e]);
+        }
+        op[q] = r;
+    }
+    for (long long idx = nvec * VEC + (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
+        double v = a * (double)x[idx];
+        if (y != nullptr) v += b * (double)y[idx];
+        out[idx] = (T)v;
+    }
+}
+
+template <typename T, int VEC>
+__global__ void lincomb_vec_kernel(T* __restrict__ out, const __grid_constant__ LincombArgs<T> args, long long n) {
+    using P = Pack<T, VEC>;
+    const long long nvec = n / VEC, stride = (long long)gridDim.x * blockDim.x;
+    P* op = reinterpret_cast<P*>(out);
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) {
+        double acc[VEC];
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) acc[e] = 0.0;
+        for (int k = 0; k < args.n; ++k) {
+            const P u = reinterpret_cast<const P*>(args.v[k])[q];
+#pragma unroll
+            for (int e = 0; e < VEC; ++e) acc[e] += args.c[k] * (double)u.v[e];
+        }
+        P r;
+#pragma unroll
+        for (int e = 0; e < VEC; ++e) r.v[e] = (T)acc[e];
+        op[q] = r;
+    }
+    for (long long idx = nvec * VEC + (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride) {
         double v = 0.0;
         for (int k = 0; k < args.n; ++k) v += args.c[k] * (double)args.v[k][idx];
         out[idx] = (T)v;
+    }
+}
+
+__host__ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+// ---- fused amplitude update + increment norm + energy ----------------------------------------------
+// One CTA per 32x32 (a,b) tile of one (i,j) block, for the blocks ij in [ij_lo, ij_hi) (a rank's share of
+// the update when several GPUs split it; the whole range on one GPU):
+//     r      = r2[ijab] (+ r2[jiba] when `symmetrize`: the partner tile is read coalesced and transposed
+//              through shared memory, ccwfn.py:621)
+//     t2    += r / D_ijab,  D from the Fock diagonal                                  (ccwfn.py:288)
+//     rms2  += (r / D)^2                                                              (ccwfn.py:289-290)
+//     E     += (t2_new[ijab] + t1[ia] t1[jb]) (2 <ij|ab> - <ij|ba>)   when `g` is given (ccwfn.py:717-718)
+// t2 is in registers when the energy needs it, so fusing saves one full read of t2 per iteration.  All
+// global accesses are two-element vectors along b (16 bytes in FP64), 256-byte runs per tile row.
+template <typename T>
+__global__ void __launch_bounds__(256) update_energy_kernel(T* __restrict__ t2, const T* __restrict__ r2,
+                                                            const T* __restrict__ eps, const T* __restrict__ t1,
+                                                            const T* __restrict__ g, int no, int nv, int tiles_per_dim,
+                                                            int ij_lo, int symmetrize, double* __restrict__ part_rms,
+                                                            double* __restrict__ part_e) {
+    __shared__ T tr[32][33];      // r2[ji] tile, [b][a]
+    __shared__ T tg[32][33];      // g[ij] tile at (b, a)
+    const int ij = ij_lo + blockIdx.y;
+    const int i = ij / no, j = ij - i * no;
+    const int ta = blockIdx.x / tiles_per_dim, tb = blockIdx.x % tiles_per_dim;
+    const long long nvv = (long long)nv * nv;
+    const long long Pb = (long long)ij * nvv, Qb = ((long long)j * no + i) * nvv;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;       // 16 x 16, two columns per thread
+    const bool vec = (nv & 1) == 0;
+    const bool want_e = g != nullptr;
+    // transposed inputs: rows b of the tile (tb), columns a (ta)
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int b = tb * 32 + ty + 16 * p, a0 = ta * 32 + 2 * tx;
+        T x0 = T(0), x1 = T(0), y0 = T(0), y1 = T(0);
+        if (b < nv && a0 < nv) {
+            const long long off = (long long)b * nv + a0;
+            if (vec) {
+                if (symmetrize) { const Pack<T, 2> q = *reinterpret_cast<const Pack<T, 2>*>(r2 + Qb + off); x0 = q.v[0]; x1 = q.v[1]; }
+                if (want_e) { const Pack<T, 2> q = *reinterpret_cast<const Pack<T, 2>*>(g + Pb + off); y0 = q.v[0]; y1 = q.v[1]; }
+            } else {
+                if (symmetrize) { x0 = r2[Qb + off]; if (a0 + 1 < nv) x1 = r2[Qb + off + 1]; }
+                if (want_e) { y0 = g[Pb + off]; if (a0 + 1 < nv) y1 = g[Pb + off + 1]; }
+            }
+        }
+        tr[ty + 16 * p][2 * tx] = x0; tr[ty + 16 * p][2 * tx + 1] = x1;
+        tg[ty + 16 * p][2 * tx] = y0; tg[ty + 16 * p][2 * tx + 1] = y1;
+    }
+    __syncthreads();
+    const double ei = (double)eps[i] + (double)eps[j];
+    double acc_r = 0.0, acc_e = 0.0;
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int al = ty + 16 * p, a = ta * 32 + al, b0 = tb * 32 + 2 * tx;
+        if (a < nv && b0 < nv) {
+            const long long off = (long long)a * nv + b0;
+            const bool two = b0 + 1 < nv;
+            T rr[2] = {T(0), T(0)}, tt[2] = {T(0), T(0)}, gg[2] = {T(0), T(0)};
+            if (vec) {
+                const Pack<T, 2> q = *reinterpret_cast<const Pack<T, 2>*>(r2 + Pb + off); rr[0] = q.v[0]; rr[1] = q.v[1];
+                const Pack<T, 2> u = *reinterpret_cast<const Pack<T, 2>*>(t2 + Pb + off); tt[0] = u.v[0]; tt[1] = u.v[1];
+                if (want_e) { const Pack<T, 2> w = *reinterpret_cast<const Pack<T, 2>*>(g + Pb + off); gg[0] = w.v[0]; gg[1] = w.v[1]; }
+            } else {
+                rr[0] = r2[Pb + off]; tt[0] = t2[Pb + off];
+                if (want_e) gg[0] = g[Pb + off];
+                if (two) { rr[1] = r2[Pb + off + 1]; tt[1] = t2[Pb + off + 1]; if (want_e) gg[1] = g[Pb + off + 1]; }
+            }
+            const double ea = ei - (double)eps[no + a];
+            const double t1a = want_e ? (double)t1[(long long)i * nv + a] : 0.0;
+            T out[2];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int b = b0 + e;
+                double r = (double)rr[e] + (double)tr[2 * tx + e][al];
+                const double d = ea - (double)eps[no + (b < nv ? b : 0)];
+                const double inc = (double)(T)(r / d);
+                const double tn = (double)tt[e] + inc;
+                out[e] = (T)tn;
+                if (b < nv) {
+                    acc_r += inc * inc;
+                    if (want_e)
+                        acc_e += ((double)out[e] + t1a * (double)t1[(long long)j * nv + b]) *
+                                 (2.0 * (double)gg[e] - (double)tg[2 * tx + e][al]);
+                }
+            }
+            if (vec) {
+                Pack<T, 2> q; q.v[0] = out[0]; q.v[1] = out[1];
+                *reinterpret_cast<Pack<T, 2>*>(t2 + Pb + off) = q;
+            } else {
+                t2[Pb + off] = out[0];
+                if (two) t2[Pb + off + 1] = out[1];
+            }
+        }
+    }
+    const long long slot = (long long)blockIdx.y * gridDim.x + blockIdx.x;
+    acc_r = block_sum(acc_r);
+    if (threadIdx.x == 0) part_rms[slot] = acc_r;
+    acc_e = block_sum(acc_e);
+    if (threadIdx.x == 0) part_e[slot] = acc_e;
+}
+
+// singles: t1 += r1/D, increment norm and 2 sum F_ia t_ia of the NEW t1 (one small block grid)
+template <typename T>
+__global__ void update_t1_energy_kernel(T* __restrict__ t1, const T* __restrict__ r1, const T* __restrict__ eps,
+                                        const T* __restrict__ fov, long long ld_fov, int no, int nv,
+                                        double* __restrict__ part_rms, double* __restrict__ part_e) {
+    const long long total = (long long)no * nv;
+    double acc = 0.0, ace = 0.0;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const int i = (int)(idx / nv), a = (int)(idx - (long long)i * nv);
+        const double d = (double)eps[i] - (double)eps[no + a];
+        const double inc = (double)(T)((double)r1[idx] / d);
+        const T tn = (T)((double)t1[idx] + inc);
+        t1[idx] = tn;
+        acc += inc * inc;
+        if (fov != nullptr) ace += 2.0 * (double)fov[(long long)i * ld_fov + a] * (double)tn;
+    }
+    acc = block_sum(acc);
+    if (threadIdx.x == 0) part_rms[blockIdx.x] = acc;
+    ace = block_sum(ace);
+    if (threadIdx.x == 0) part_e[blockIdx.x] = ace;
+}
+
+// ---- fused per-iteration preparation of the amplitude-dependent operands ---------------------------
+// One pass over t2 (each tile and its (a,b)-transposed partner) writes every o^2 v^2 operand the planned
+// contractions read: the three tau variants and 2 t2 - t2^T (build_tau, ccwfn.py:408-410, :554), t1 x t1
+// (CC2), and the plain-matrix layouts of the ring-term operands (engine.STATEMENTS_SP):
+//     t2sP[i,a,m,e] = (2 t2 - t2^T)[i,m,a,e]    t2P[i,a,m,e] = t2[i,m,a,e]    t2Q[j,a,m,e] = t2[m,j,a,e]
+//     tauWPn[j,B,n,f] = -(t2/2 + t1 t1)[j,n,f,B]   t2Rh[j,B,n,f] = t2[n,j,f,B] / 2     (B in [vlo, vlo+vl))
+// 11 tensor passes instead of the 22 of four pair_combine + five permute4 launches.
+struct PrepareOut {
+    void *tau, *tauh, *tauW, *t2s, *t11, *t2sP, *t2P, *t2Q, *tauWPn, *t2Rh;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) prepare_kernel(const T* __restrict__ t1, const T* __restrict__ t2, int no, int nv,
+                                                      int vlo, int vl, int tiles_per_dim, const __grid_constant__ PrepareOut o) {
+    __shared__ T tile[32][33];
+    __shared__ T tile2[32][33];
+    const int ij = blockIdx.y, i = ij / no, j = ij - i * no;
+    const int ta = blockIdx.x / tiles_per_dim, tb = blockIdx.x % tiles_per_dim;
+    const long long nvv = (long long)nv * nv, Pb = (long long)ij * nvv;
+    const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;
+    const bool vec = (nv & 1) == 0;
+    const bool need_t = o.t2s != nullptr || o.t2sP != nullptr;
+    if (need_t) {       // tile[b_local][a_local] = t2[ij][b][a]
+#pragma unroll
+        for (int p = 0; p < 2; ++p) {
+            const int b = tb * 32 + ty + 16 * p, a0 = ta * 32 + 2 * tx;
+            T x0 = T(0), x1 = T(0);
+            if (b < nv && a0 < nv) {
+                const long long off = Pb + (long long)b * nv + a0;
+                if (vec) { const Pack<T, 2> q = *reinterpret_cast<const Pack<T, 2>*>(t2 + off); x0 = q.v[0]; x1 = q.v[1]; }
+                else { x0 = t2[off]; if (a0 + 1 < nv) x1 = t2[off + 1]; }
+            }
+            tile[ty + 16 * p][2 * tx] = x0; tile[ty + 16 * p][2 * tx + 1] = x1;
+        }
+        __syncthreads();
+    }
+    auto put2 = [&](void* base, long long off, double v0, double v1, bool two) {
+        T* q = static_cast<T*>(base) + off;
+        if (vec) { Pack<T, 2> w; w.v[0] = (T)v0; w.v[1] = (T)v1; *reinterpret_cast<Pack<T, 2>*>(q) = w; }
+        else { q[0] = (T)v0; if (two) q[1] = (T)v1; }
+    };
+    double xw[2][2], xx[2][2];     // tauW and t2 of this thread's elements, kept for the transposed writes
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {
+        const int al = ty + 16 * p, a = ta * 32 + al, b0 = tb * 32 + 2 * tx;
+        xw[p][0] = xw[p][1] = xx[p][0] = xx[p][1] = 0.0;
+        if (a < nv && b0 < nv) {
+            const bool two = b0 + 1 < nv;
+            const long long off = Pb + (long long)a * nv + b0;
+            double x[2] = {0.0, 0.0};
+            if (vec) { const Pack<T, 2> q = *reinterpret_cast<const Pack<T, 2>*>(t2 + off); x[0] = (double)q.v[0]; x[1] = (double)q.v[1]; }
+            else { x[0] = (double)t2[off]; if (two) x[1] = (double)t2[off + 1]; }
+            const double ua = (double)t1[(long long)i * nv + a];
+            const double pr[2] = {ua * (double)t1[(long long)j * nv + b0], two ? ua * (double)t1[(long long)j * nv + b0 + 1] : 0.0};
+            const double s[2] = {2.0 * x[0] - (need_t ? (double)tile[2 * tx][al] : 0.0),
+                                 2.0 * x[1] - (need_t ? (double)tile[2 * tx + 1][al] : 0.0)};
+            if (o.tau) put2(o.tau, off, x[0] + pr[0], x[1] + pr[1], two);
+            if (o.tauh) put2(o.tauh, off, x[0] + 0.5 * pr[0], x[1] + 0.5 * pr[1], two);
+            if (o.tauW) put2(o.tauW, off, 0.5 * x[0] + pr[0], 0.5 * x[1] + pr[1], two);
+            if (o.t2s) put2(o.t2s, off, s[0], s[1], two);
+            if (o.t11) put2(o.t11, off, pr[0], pr[1], two);
+            // row-permuted copies: the run along b stays contiguous
+            const long long offP = (((long long)i * nv + a) * no + j) * nv + b0;       // [i][a][j][b]
+            if (o.t2sP) put2(o.t2sP, offP, s[0], s[1], two);
+            if (o.t2P) put2(o.t2P, offP, x[0], x[1], two);
+            if (o.t2Q) put2(o.t2Q, (((long long)j * nv + a) * no + i) * nv + b0, x[0], x[1], two);   // [j][a][i][b]
+            xw[p][0] = 0.5 * x[0] + pr[0]; xw[p][1] = 0.5 * x[1] + pr[1];
+            xx[p][0] = x[0]; xx[p][1] = x[1];
+        }
+    }
+    if (o.tauWPn == nullptr && o.t2Rh == nullptr) return;
+    if (tb * 32 >= vlo + vl || tb * 32 + 32 <= vlo) return;      // no column B of this tile is in the slice
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {       // tile[a_local][b_local] = tauW, tile2 = t2
+        tile[ty + 16 * p][2 * tx] = (T)xw[p][0]; tile[ty + 16 * p][2 * tx + 1] = (T)xw[p][1];
+        tile2[ty + 16 * p][2 * tx] = (T)xx[p][0]; tile2[ty + 16 * p][2 * tx + 1] = (T)xx[p][1];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int p = 0; p < 2; ++p) {       // rows b (slice only), two columns a per thread
+        const int bl = ty + 16 * p, b = tb * 32 + bl, a0 = ta * 32 + 2 * tx;
+        if (b < nv && b >= vlo && b < vlo + vl && a0 < nv) {
+            const bool two = a0 + 1 < nv;
+            // tauWPn[i][B][j][a] = -tauW[i,j,a,B];  t2Rh[j][B][i][a] = t2[i,j,a,B] / 2
+            if (o.tauWPn) put2(o.tauWPn, (((long long)i * vl + (b - vlo)) * no + j) * nv + a0,
+                               -(double)tile[2 * tx][bl], -(double)tile[2 * tx + 1][bl], two);
+            if (o.t2Rh) put2(o.t2Rh, (((long long)j * vl + (b - vlo)) * no + i) * nv + a0,
+                             0.5 * (double)tile2[2 * tx][bl], 0.5 * (double)tile2[2 * tx + 1][bl], two);
+        }
     }
 }
 
@@ -293,20 +516,40 @@ int pair_combine_t(pccb_ctx* ctx, void* out, const void* X, double c0, double c1
     return PCCB_OK;
 }
 
+// t1 / t2 update (+ optional fused energy) for the (i,j) blocks [ij_lo, ij_hi); out_host[0] = squared
+// increment norm, out_host[1] = energy of the new amplitudes over those blocks (0 without `g`).  `with_t1`:
+// also update t1 and count its norm / singles energy (one rank does when the blocks are split over ranks).
 template <typename T>
-int update_t(pccb_ctx* ctx, void* t1, void* t2, const void* r1, const void* r2, const void* eps, int64_t no,
-             int64_t nv, int symmetrize, double* rms2_host) {
-    const long long n2 = no * no * nv * nv, n1 = no * nv;
-    const int g2 = grid_for(n2, RED_THREADS, MAX_RED_BLOCKS), g1 = grid_for(n1, RED_THREADS, 64);
-    int rc = pccb_ensure_partials(ctx, (size_t)g1 + g2 + 64);
+int update_energy_t(pccb_ctx* ctx, void* t1, void* t2, const void* r1, const void* r2, const void* eps, const void* fov,
+                    int64_t ld_fov, const void* g, int64_t no, int64_t nv, int symmetrize, int64_t ij_lo, int64_t ij_hi,
+                    int with_t1, int count_t1, double* out_host) {
+    const int tpd = (int)((nv + 31) / 32);
+    const long long nblk = ij_hi - ij_lo;
+    const long long g2 = nblk * tpd * tpd;
+    const int g1 = with_t1 ? grid_for(no * nv, RED_THREADS, 64) : 0;
+    const long long n = g2 + g1;
+    int rc = pccb_ensure_partials(ctx, (size_t)(2 * n) + 64);
     if (rc) return rc;
-    update_t2_kernel<T><<<g2, RED_THREADS, 0, ctx->stream>>>((T*)t2, (const T*)r2, (const T*)eps, (int)no, (int)nv,
-                                                             symmetrize, ctx->partial_dev);
-    PCCB_CHECK_LAUNCH(ctx, "update_t2_kernel");
-    update_t1_kernel<T><<<g1, RED_THREADS, 0, ctx->stream>>>((T*)t1, (const T*)r1, (const T*)eps, (int)no, (int)nv,
-                                                             ctx->partial_dev + g2);
-    PCCB_CHECK_LAUNCH(ctx, "update_t1_kernel");
-    return finish_reduction(ctx, g1 + g2, 1, rms2_host);
+    double* prms = ctx->partial_dev;
+    double* pe = ctx->partial_dev + n;
+    if (with_t1) {
+        // t1 first: the doubles energy reads the NEW singles
+        update_t1_energy_kernel<T><<<g1, RED_THREADS, 0, ctx->stream>>>((T*)t1, (const T*)r1, (const T*)eps,
+                                                                        g ? (const T*)fov : nullptr, ld_fov, (int)no, (int)nv,
+                                                                        prms + g2, pe + g2);
+        PCCB_CHECK_LAUNCH(ctx, "update_t1_energy_kernel");
+        if (!count_t1) PCCB_CUDA(ctx, cudaMemsetAsync(prms + g2, 0, sizeof(double) * g1, ctx->stream));
+        if (!count_t1) PCCB_CUDA(ctx, cudaMemsetAsync(pe + g2, 0, sizeof(double) * g1, ctx->stream));
+    }
+    if (nblk > 0) {
+        dim3 grid((unsigned)(tpd * tpd), (unsigned)nblk);
+        update_energy_kernel<T><<<grid, 256, 0, ctx->stream>>>((T*)t2, (const T*)r2, (const T*)eps, (const T*)t1,
+                                                               (const T*)g, (int)no, (int)nv, tpd, (int)ij_lo, symmetrize,
+                                                               prms, pe);
+        PCCB_CHECK_LAUNCH(ctx, "update_energy_kernel");
+    }
+    if (n == 0) { out_host[0] = out_host[1] = 0.0; return PCCB_OK; }
+    return finish_reduction(ctx, (int)n, 2, out_host);
 }
 
 template <typename T>
@@ -394,11 +637,57 @@ extern "C" int pccb_update_amplitudes(pccb_ctx* ctx, int dtype, void* t1_dev, vo
                                       const void* r2_dev, const void* eps_dev, int64_t no, int64_t nv,
                                       int symmetrize, double* rms2_host) {
     if (!ctx) return PCCB_ERR_ARG;
-    PCCB_REQUIRE(ctx, t1_dev && t2_dev && r1_dev && r2_dev && eps_dev && rms2_host && no > 0 && nv > 0,
+    PCCB_REQUIRE(ctx, t1_dev && t2_dev && r1_dev && r2_dev && eps_dev && rms2_host && no > 0 && nv > 0 && no * no <= 65535,
                  "pccb_update_amplitudes: bad arguments");
+    double out[2] = {0.0, 0.0};
+    int rc;
+    if (dtype == PCCB_F64)
+        rc = update_energy_t<double>(ctx, t1_dev, t2_dev, r1_dev, r2_dev, eps_dev, nullptr, 0, nullptr, no, nv, symmetrize, 0,
+                                     no * no, 1, 1, out);
+    else if (dtype == PCCB_F32)
+        rc = update_energy_t<float>(ctx, t1_dev, t2_dev, r1_dev, r2_dev, eps_dev, nullptr, 0, nullptr, no, nv, symmetrize, 0,
+                                    no * no, 1, 1, out);
+    else
+        PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
+    *rms2_host = out[0];
+    return rc;
+}
+
+extern "C" int pccb_update_energy(pccb_ctx* ctx, int dtype, void* t1_dev, void* t2_dev, const void* r1_dev,
+                                  const void* r2_dev, const void* eps_dev, const void* fov_dev, int64_t ld_fov,
+                                  const void* oovv_dev, int64_t no, int64_t nv, int symmetrize, int64_t ij_lo,
+                                  int64_t ij_hi, int count_t1, double* out_host) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, t1_dev && t2_dev && r1_dev && r2_dev && eps_dev && fov_dev && oovv_dev && out_host && no > 0 && nv > 0 &&
+                          no * no <= 65535 && ij_lo >= 0 && ij_lo <= ij_hi && ij_hi <= no * no,
+                 "pccb_update_energy: bad arguments");
     DISPATCH_DTYPE(ctx, dtype,
-                   update_t<double>(ctx, t1_dev, t2_dev, r1_dev, r2_dev, eps_dev, no, nv, symmetrize, rms2_host),
-                   update_t<float>(ctx, t1_dev, t2_dev, r1_dev, r2_dev, eps_dev, no, nv, symmetrize, rms2_host));
+                   update_energy_t<double>(ctx, t1_dev, t2_dev, r1_dev, r2_dev, eps_dev, fov_dev, ld_fov, oovv_dev, no, nv,
+                                           symmetrize, ij_lo, ij_hi, 1, count_t1, out_host),
+                   update_energy_t<float>(ctx, t1_dev, t2_dev, r1_dev, r2_dev, eps_dev, fov_dev, ld_fov, oovv_dev, no, nv,
+                                          symmetrize, ij_lo, ij_hi, 1, count_t1, out_host));
+}
+
+extern "C" int pccb_prepare_amplitudes(pccb_ctx* ctx, int dtype, const void* t1_dev, const void* t2_dev, int64_t no,
+                                       int64_t nv, int64_t vlo, int64_t vl, const pccb_prepare_outputs* out) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, t1_dev && t2_dev && out && no > 0 && nv > 0 && no * no <= 65535 && vlo >= 0 && vl >= 0 && vlo + vl <= nv,
+                 "pccb_prepare_amplitudes: bad arguments");
+    PrepareOut o;
+    o.tau = out->tau; o.tauh = out->tauh; o.tauW = out->tauW; o.t2s = out->t2s; o.t11 = out->t11;
+    o.t2sP = out->t2sP; o.t2P = out->t2P; o.t2Q = out->t2Q; o.tauWPn = out->tauWPn; o.t2Rh = out->t2Rh;
+    const int tpd = (int)((nv + 31) / 32);
+    dim3 grid((unsigned)(tpd * tpd), (unsigned)(no * no));
+    if (dtype == PCCB_F64)
+        prepare_kernel<double><<<grid, 256, 0, ctx->stream>>>((const double*)t1_dev, (const double*)t2_dev, (int)no, (int)nv,
+                                                              (int)vlo, (int)vl, tpd, o);
+    else if (dtype == PCCB_F32)
+        prepare_kernel<float><<<grid, 256, 0, ctx->stream>>>((const float*)t1_dev, (const float*)t2_dev, (int)no, (int)nv,
+                                                             (int)vlo, (int)vl, tpd, o);
+    else
+        PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
+    PCCB_CHECK_LAUNCH(ctx, "prepare_kernel");
+    return PCCB_OK;
 }
 
 extern "C" int pccb_cc_energy(pccb_ctx* ctx, int dtype, const void* fov_dev, int64_t ld_fov, const void* t1_dev,
@@ -410,39 +699,58 @@ extern "C" int pccb_cc_energy(pccb_ctx* ctx, int dtype, const void* fov_dev, int
                    energy_t<float>(ctx, fov_dev, ld_fov, t1_dev, t2_dev, oovv_dev, no, nv, e_host));
 }
 
+template <typename T>
+int dot_t(pccb_ctx* ctx, const void* x, const void* y, int64_t n, double* out_host) {
+    constexpr int V = 16 / sizeof(T);
+    const int g = grid_for((n + V - 1) / V, RED_THREADS, MAX_RED_BLOCKS);
+    int rc = pccb_ensure_partials(ctx, (size_t)g + 64);
+    if (rc) return rc;
+    if (aligned16(x) && aligned16(y))
+        dot_vec_kernel<T, V><<<g, RED_THREADS, 0, ctx->stream>>>((const T*)x, (const T*)y, n, ctx->partial_dev);
+    else
+        dot_vec_kernel<T, 1><<<g, RED_THREADS, 0, ctx->stream>>>((const T*)x, (const T*)y, n, ctx->partial_dev);
+    PCCB_CHECK_LAUNCH(ctx, "dot_kernel");
+    return finish_reduction(ctx, g, 1, out_host);
+}
+
+template <typename T>
+int axpby_t(pccb_ctx* ctx, void* out, double a, const void* x, double b, const void* y, int64_t n) {
+    constexpr int V = 16 / sizeof(T);
+    const int g = grid_for((n + V - 1) / V, 256, 148 * 8);
+    if (aligned16(out) && aligned16(x) && aligned16(y))
+        axpby_vec_kernel<T, V><<<g, 256, 0, ctx->stream>>>((T*)out, a, (const T*)x, b, (const T*)y, n);
+    else
+        axpby_vec_kernel<T, 1><<<g, 256, 0, ctx->stream>>>((T*)out, a, (const T*)x, b, (const T*)y, n);
+    PCCB_CHECK_LAUNCH(ctx, "axpby_kernel");
+    return PCCB_OK;
+}
+
+template <typename T>
+int lincomb_t(pccb_ctx* ctx, void* out, const void* const* vecs, const double* coef, int nvec, int64_t n) {
+    constexpr int V = 16 / sizeof(T);
+    LincombArgs<T> a;
+    a.n = nvec;
+    bool al = aligned16(out);
+    for (int k = 0; k < nvec; ++k) { a.v[k] = (const T*)vecs[k]; a.c[k] = coef[k]; al = al && aligned16(vecs[k]); }
+    const int g = grid_for((n + V - 1) / V, 256, 148 * 8);
+    if (al) lincomb_vec_kernel<T, V><<<g, 256, 0, ctx->stream>>>((T*)out, a, n);
+    else lincomb_vec_kernel<T, 1><<<g, 256, 0, ctx->stream>>>((T*)out, a, n);
+    PCCB_CHECK_LAUNCH(ctx, "lincomb_kernel");
+    return PCCB_OK;
+}
+
 extern "C" int pccb_dot(pccb_ctx* ctx, int dtype, const void* x_dev, const void* y_dev, int64_t n, double* out_host) {
     if (!ctx) return PCCB_ERR_ARG;
     PCCB_REQUIRE(ctx, x_dev && y_dev && out_host && n > 0, "pccb_dot: bad arguments");
-    const int g = grid_for(n, RED_THREADS, MAX_RED_BLOCKS);
-    int rc = pccb_ensure_partials(ctx, (size_t)g + 64);
-    if (rc) return rc;
-    if (dtype == PCCB_F64)
-        dot_kernel<double><<<g, RED_THREADS, 0, ctx->stream>>>((const double*)x_dev, (const double*)y_dev, n,
-                                                               ctx->partial_dev);
-    else if (dtype == PCCB_F32)
-        dot_kernel<float><<<g, RED_THREADS, 0, ctx->stream>>>((const float*)x_dev, (const float*)y_dev, n,
-                                                              ctx->partial_dev);
-    else
-        PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
-    PCCB_CHECK_LAUNCH(ctx, "dot_kernel");
-    return finish_reduction(ctx, g, 1, out_host);
+    DISPATCH_DTYPE(ctx, dtype, dot_t<double>(ctx, x_dev, y_dev, n, out_host), dot_t<float>(ctx, x_dev, y_dev, n, out_host));
 }
 
 extern "C" int pccb_axpby(pccb_ctx* ctx, int dtype, void* out_dev, double a, const void* x_dev, double b,
                           const void* y_dev, int64_t n) {
     if (!ctx) return PCCB_ERR_ARG;
     PCCB_REQUIRE(ctx, out_dev && x_dev && n > 0, "pccb_axpby: bad arguments");
-    const int g = grid_for(n, 256, 148 * 16);
-    if (dtype == PCCB_F64)
-        axpby_kernel<double><<<g, 256, 0, ctx->stream>>>((double*)out_dev, a, (const double*)x_dev, b,
-                                                         (const double*)y_dev, n);
-    else if (dtype == PCCB_F32)
-        axpby_kernel<float><<<g, 256, 0, ctx->stream>>>((float*)out_dev, a, (const float*)x_dev, b,
-                                                        (const float*)y_dev, n);
-    else
-        PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
-    PCCB_CHECK_LAUNCH(ctx, "axpby_kernel");
-    return PCCB_OK;
+    DISPATCH_DTYPE(ctx, dtype, axpby_t<double>(ctx, out_dev, a, x_dev, b, y_dev, n),
+                   axpby_t<float>(ctx, out_dev, a, x_dev, b, y_dev, n));
 }
 
 extern "C" int pccb_lincomb(pccb_ctx* ctx, int dtype, void* out_dev, const void* const* vecs, const double* coef,
@@ -450,20 +758,6 @@ extern "C" int pccb_lincomb(pccb_ctx* ctx, int dtype, void* out_dev, const void*
     if (!ctx) return PCCB_ERR_ARG;
     PCCB_REQUIRE(ctx, out_dev && vecs && coef && nvec >= 1 && nvec <= MAX_LINCOMB && n > 0,
                  "pccb_lincomb: bad arguments (nvec=%d)", nvec);
-    const int g = grid_for(n, 256, 148 * 16);
-    if (dtype == PCCB_F64) {
-        LincombArgs<double> a;
-        a.n = nvec;
-        for (int k = 0; k < nvec; ++k) { a.v[k] = (const double*)vecs[k]; a.c[k] = coef[k]; }
-        lincomb_kernel<double><<<g, 256, 0, ctx->stream>>>((double*)out_dev, a, n);
-    } else if (dtype == PCCB_F32) {
-        LincombArgs<float> a;
-        a.n = nvec;
-        for (int k = 0; k < nvec; ++k) { a.v[k] = (const float*)vecs[k]; a.c[k] = coef[k]; }
-        lincomb_kernel<float><<<g, 256, 0, ctx->stream>>>((float*)out_dev, a, n);
-    } else {
-        PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
-    }
-    PCCB_CHECK_LAUNCH(ctx, "lincomb_kernel");
-    return PCCB_OK;
+    DISPATCH_DTYPE(ctx, dtype, lincomb_t<double>(ctx, out_dev, vecs, coef, nvec, n),
+                   lincomb_t<float>(ctx, out_dev, vecs, coef, nvec, n));
 }

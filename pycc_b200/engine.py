@@ -92,11 +92,21 @@ class CCSDEngine(object):
         be.permute4(self.Looov, self.blk["ooov"].permute(1, 0, 2, 3), -1.0, 1.0)
         # amplitudes and per-iteration buffers (intermediates carrying the sliced index are local-sized)
         E = lambda *s: be.zeros(s, dtype)
-        self.t1, self.t2 = E(o, v), E(o, o, v, v)
+        # Several GPUs: the amplitude update is split over the ranks by (i,j) blocks of t2 - rank g owns the
+        # blocks [ij_lo, ij_hi), chunk_pairs = ceil(o^2 / world) of them - and the updated / extrapolated
+        # chunks are allgathered IN PLACE: t2 is a view of a buffer padded to world * chunk_pairs blocks.
+        W = self.comm.world
+        self.chunk_pairs = -(-(o * o) // W)
+        self.ij_lo = min(o * o, self.comm.rank * self.chunk_pairs)
+        self.ij_hi = min(o * o, self.ij_lo + self.chunk_pairs)
+        self._t2_store = be.zeros((W * self.chunk_pairs * v * v,), dtype)
+        self.t1, self.t2 = E(o, v), self._t2_store[:o * o * v * v].view(o, o, v, v)
+        self.t2_stale = False          # True between a split update and the allgather that completes t2
         self.tau, self.tauh, self.tauW, self.t2s = E(o, o, v, v), E(o, o, v, v), E(o, o, v, v), E(o, o, v, v)
-        self.Fae, self.Fmi, self.Fme = E(vl, v), E(o, o), E(o, v)
+        self._small = E(o * o + o ** 4)                      # [Fmi | Wmnij]: summed over the ranks in one allreduce
+        self.Fae, self.Fmi, self.Fme = E(vl, v), self._small[:o * o].view(o, o), E(o, v)
         self.Fae2, self.Fmi2 = E(vl, v), E(o, o)
-        self.Wmnij = E(o, o, o, o)
+        self.Wmnij = self._small[o * o:].view(o, o, o, o)
         self.Wr1, self.Wr2 = E(o, vl, o, v), E(o, vl, o, v)      # [j,b,m,e]
         self.Zr = E(o, o, o, vl)                                 # [m,i,j,b]
         self.Y1, self.Y2 = E(o, o, o, vl), E(o, o, vl, o)        # [i,m,j,b], [i,m,a,j]
@@ -231,6 +241,20 @@ class CCSDEngine(object):
                  "r2_s2[ijAb] -= t1_s1[mA]*ooov[ijmb]"],
     }
 
+    # Several GPUs: the two builders every rank would otherwise compute in full (2 o^4 v^2 + 2 o^3 v^2 flops,
+    # 3 ms of a 54 ms rank share at (30,250) x 8) are sliced over the CONTRACTED virtual index E instead; the
+    # partial sums share one buffer and one small allreduce, then the cheap unsliced terms are added.
+    SLICED_K = {
+        "Fmi": (["Fmi[mi] = Loovv_s2[mnEf]*tauh_s2[inEf]"],
+                ["Fmi[mi] += Foo[mi] + 0.5*Fov[me]*t1[ie]", "Fmi[mi] += t1[ne]*Looov[mnie]"]),
+        "Wmnij": (["Wmnij[mnij] = oovv_s2[mnEf]*tau_s2[ijEf]"],
+                  ["Wmnij[mnij] += oooo[mnij] + ooov[mnie]*t1[je]", "Wmnij[mnij] += ooov[nmje]*t1[ie]"]),
+    }
+    SLICED_K_CC2 = {
+        "Wmnij": (["Wmnij[mnij] = oovv_s2[mnEf]*T11_s2[ijEf]"],
+                  ["Wmnij[mnij] += oooo[mnij] + ooov[mnie]*t1[je]", "Wmnij[mnij] += ooov[nmje]*t1[ie]"]),
+    }
+
     # CC2 branch of the same builders (pycc/ccwfn.py:478-479, 495-496, 517-518, 534-535, 575-592):
     # Fae / Fmi / Fme / r_T1 as in CCSD; Wmnij and Zmbij with t1 t1 in place of tau; no Wmbej / Wmbje;
     # r_T2 with bare Fock matrices and the doubles-into-doubles terms dropped.  T11[ijef] = t1[ie] t1[jf].
@@ -296,19 +320,42 @@ class CCSDEngine(object):
             st["r_T2"] = [self.R_T2_SP.get(x, x) for x in st["r_T2"]]
         return st
 
-    def _build_plans(self):
+    def _plan_list(self, stmts):
         import re
+        launches = []
+        for s in stmts:
+            T = self._tensors(set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s)))
+            for L in plan(s, T, self.dcode, prefer_flat=True if self.sp_plain else None):
+                L.is_ladder = "vvvv_s0" in s
+                launches.append(L)
+        return launches
+
+    def _build_plans(self):
         self.plans = {}
+        self.pre_plans = {}         # world > 1: K-sliced partial sums that precede the small allreduce
         for name, stmts in self._statements().items():
-            launches = []
-            for s in stmts:
-                T = self._tensors(set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s)))
-                for L in plan(s, T, self.dcode, prefer_flat=True if self.sp_plain else None):
-                    L.is_ladder = "vvvv_s0" in s
-                    launches.append(L)
-            self.plans[name] = launches
+            self.plans[name] = self._plan_list(stmts)
+        if self.comm.world > 1:
+            sk = dict(self.SLICED_K)
+            if self.model == 'CC2':
+                sk.update(self.SLICED_K_CC2)
+            for name, (pre, post) in sk.items():
+                self.pre_plans[name] = self._plan_list(pre)
+                self.plans[name] = self._plan_list(post)
+
+    def _run_small(self, names):
+        """Fmi / Wmnij on several GPUs: partial sums over this rank's slice of the contracted index, ONE
+        allreduce of the shared buffer, then the unsliced terms."""
+        for name in names:
+            for L in self.pre_plans[name]:
+                self.be.contract(L.desc)
+        self.comm.allreduce_(self._small)
+        for name in names:
+            self._launch(name)
 
     def _run(self, name):
+        if name in self.pre_plans:
+            return self._run_small([name])
         if name == "r_T1":
             self.r1.zero_()
         elif name == "r_T2":
@@ -336,21 +383,15 @@ class CCSDEngine(object):
 
     # ---- amplitude-dependent element-wise preparations ---------------------------------------
     def prepare(self):
-        """tau variants and the spin-adapted t2 (build_tau, pycc/ccwfn.py:408-410; :554)."""
+        """tau variants, the spin-adapted t2 (build_tau, pycc/ccwfn.py:408-410; :554) and the plain-matrix
+        layouts of the ring-term operands: ONE pass over t2 (pccb_prepare_amplitudes)."""
         be, o, v = self.be, self.no, self.nv
-        be.pair_combine(self.tau, self.t2, 1.0, 0.0, self.t1, self.t1, 1.0, o, v)
-        be.pair_combine(self.tauh, self.t2, 1.0, 0.0, self.t1, self.t1, 0.5, o, v)
-        be.pair_combine(self.tauW, self.t2, 0.5, 0.0, self.t1, self.t1, 1.0, o, v)
-        be.pair_combine(self.t2s, self.t2, 2.0, -1.0, None, None, 0.0, o, v)
+        outs = dict(tau=self.tau, tauh=self.tauh, tauW=self.tauW, t2s=self.t2s)
         if self.model == 'CC2':
-            be.pair_combine(self.T11, self.t2, 0.0, 0.0, self.t1, self.t1, 1.0, o, v)
+            outs["t11"] = self.T11
         if self.sp_plain:
-            sl = slice(self.vlo, self.vhi)
-            be.permute4(self.t2sP, self.t2s.permute(0, 2, 1, 3))
-            be.permute4(self.t2P, self.t2.permute(0, 2, 1, 3))
-            be.permute4(self.t2Q, self.t2.permute(1, 2, 0, 3))
-            be.permute4(self.tauWPn, self.tauW.permute(0, 3, 1, 2)[:, sl], -1.0)
-            be.permute4(self.t2Rh, self.t2.permute(1, 3, 0, 2)[:, sl], 0.5)
+            outs.update(t2sP=self.t2sP, t2P=self.t2P, t2Q=self.t2Q, tauWPn=self.tauWPn, t2Rh=self.t2Rh)
+        be.prepare_amplitudes(self.t1, self.t2, o, v, self.vlo, self.vl, **outs)
         if self._lo is not None:
             for name in ["tau"] + (["t2sP", "t2P", "t2Q", "tauWPn", "t2Rh"] if self.sp_plain else []):
                 be.split_lo(getattr(self, name), self._lo[name])
@@ -371,7 +412,11 @@ class CCSDEngine(object):
             self.t1.zero_()          # CCD carries no singles (ccwfn.py:543-546): before tau is formed
             self.r1.zero_()
         self.prepare()
-        for name in self.builder_order():
+        order = list(self.builder_order())
+        if self.pre_plans:
+            self._run_small([n for n in order if n in self.pre_plans])
+            order = [n for n in order if n not in self.pre_plans]
+        for name in order:
             self._run(name)
         if self.model == 'CC3':      # triples contributions X1, X2 (pycc/ccwfn.py:371-401)
             if self.cc3 is None:
@@ -415,10 +460,35 @@ class CCSDEngine(object):
         return self.be.update_amplitudes(self.t1, self.t2, self.r1, self.r2, self.eps, self.no, self.nv,
                                          symmetrize_on_the_fly)
 
+    def update_energy(self):
+        """t += r/D (the pair symmetrisation of r2, ccwfn.py:621, on the fly), the increment norm and the
+        energy of the new amplitudes in ONE pass (pccb_update_energy).  Several GPUs: each rank updates the
+        (i,j) blocks it owns (t1: all of it, every rank holds the summed r1), the two scalars are summed
+        over the ranks, and t2 stays incomplete until ``sync_amplitudes`` or the DIIS allgather.
+        Returns (squared increment norm, energy)."""
+        self.be.bind_stream()
+        o = self.no
+        fov = self.F[:o, o:]
+        rms2, e = self.be.update_energy(self.t1, self.t2, self.r1, self.r2, self.eps, fov, self.F.stride(0),
+                                        self.blk["oovv"], o, self.nv, True, self.ij_lo, self.ij_hi,
+                                        self.comm.rank == 0)
+        if self.comm.world > 1:
+            rms2, e = self.comm.allreduce_scalars([rms2, e])
+            self.t2_stale = True
+        return rms2, e
+
+    def sync_amplitudes(self):
+        """Complete t2 on every rank after a split update (in-place allgather of the ranks' chunks)."""
+        if self.t2_stale:
+            n = self.chunk_pairs * self.nv * self.nv
+            self.comm.allgather_into(self._t2_store, self._t2_store[self.comm.rank * n:(self.comm.rank + 1) * n],
+                                     in_place=True)
+            self.t2_stale = False
+
     def flops_issued(self):
         """Flops the planned launches actually issue per residuals() call (2*M*N*K summed)."""
         tot = 0
-        for launches in self.plans.values():
+        for launches in list(self.plans.values()) + list(self.pre_plans.values()):
             for L in launches:
                 d = L.desc
                 for q in range(d.nseg):

@@ -105,16 +105,18 @@ class Comm(object):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
         return t.tolist()
 
-    def allgather_into(self, full, chunk):
-        """full[r*len(chunk) : (r+1)*len(chunk)] = rank r's ``chunk`` on every rank (equal lengths)."""
+    def allgather_into(self, full, chunk, in_place=False):
+        """full[r*len(chunk) : (r+1)*len(chunk)] = rank r's ``chunk`` on every rank (equal lengths).
+        ``in_place``: ``chunk`` IS this rank's slice of ``full`` (NCCL gathers in place; gloo gets a copy)."""
         if self.world <= 1:
-            full[:chunk.numel()].copy_(chunk)
+            if not in_place:
+                full[:chunk.numel()].copy_(chunk)
             return
         import torch.distributed as dist
         if dist.get_backend(self.group) == "nccl":
             dist.all_gather_into_tensor(full, chunk, group=self.group)
         else:
-            dist.all_gather(list(full.split(chunk.numel())), chunk, group=self.group)
+            dist.all_gather(list(full.split(chunk.numel())), chunk.clone() if in_place else chunk, group=self.group)
         self.bytes_gathered = getattr(self, "bytes_gathered", 0) + full.numel() * full.element_size()
 
     def barrier(self):

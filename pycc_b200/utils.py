@@ -32,7 +32,12 @@ class helper_diis(object):
     extrapolates its slice, and one allgather rebuilds the full (t1, t2) on every rank.
     """
 
-    def __init__(self, t1, t2, max_diis, precision='DP', backend=None, comm=None):
+    def __init__(self, t1, t2, max_diis, precision='DP', backend=None, comm=None, blocks=None):
+        """``blocks`` = (t2_store, block_len, nblock_per_rank) (several GPUs, CCSD engine): slice the history by
+        whole (i,j) BLOCKS of t2 instead of flat chunks - rank g keeps the blocks it also updates
+        (engine.update_energy) followed by t1 (real on rank 0, zeros elsewhere, so that the summed partial dot
+        products count it once) - and gather the extrapolated chunks straight into ``t2_store``, the padded
+        buffer t2 is a view of: no staging copy of the amplitude vector."""
         if backend is None:
             raise _lib.EngineError("helper_diis needs the engine back end that owns t1/t2")
         self.be = backend
@@ -43,10 +48,18 @@ class helper_diis(object):
         self.dtype = t2.dtype
         self.diis_size = 0
         self.comm = comm if (comm is not None and comm.world > 1) else None
+        self.blocks = blocks if self.comm is not None else None
         n = self.n1 + self.n2
         from .parallel import flat_chunk
         if self.comm is None:
             self.lo, self.hi, self.chunk = 0, n, n
+        elif self.blocks is not None:
+            store, blen, nper = self.blocks
+            self.t2_chunk = blen * nper                        # elements of t2 per rank (padded)
+            self.lo = min(self.n2, self.comm.rank * self.t2_chunk)
+            self.hi = min(self.n2, self.lo + self.t2_chunk)
+            self.chunk = self.t2_chunk + self.n1
+            self._full = None
         else:
             w = self.comm.world
             self.lo, self.hi, self.chunk = flat_chunk(n, self.comm.rank, w)
@@ -80,6 +93,11 @@ class helper_diis(object):
         """This rank's slice [lo, hi) of the concatenated (t1, t2) vector."""
         v = self._alloc()
         lo, hi, n1 = self.lo, self.hi, self.n1
+        if self.blocks is not None:      # [ this rank's (i,j) blocks of t2 (zero padding) | t1 on rank 0 ]
+            v[:hi - lo].copy_(t2.reshape(-1)[lo:hi])
+            if self.comm.rank == 0:
+                v[self.t2_chunk:].copy_(t1.reshape(-1))
+            return v
         if lo < n1:
             e = min(hi, n1)
             v[:e - lo].copy_(t1.reshape(-1)[lo:e])
@@ -146,6 +164,13 @@ class helper_diis(object):
         prev, self.old = self.old, new
         self._release(prev)
         # the caller's amplitude tensors are updated in place (they are the engine's buffers)
+        if self.blocks is not None:
+            # chunks of t2 gathered straight into the padded buffer behind t2; t1 lives on rank 0's vector
+            # (zeros elsewhere): a sum over the ranks hands it to everybody
+            self.comm.allgather_into(self.blocks[0], new[:self.t2_chunk])
+            t1.copy_(new[self.t2_chunk:].reshape(self.shape1))
+            self.comm.allreduce_(t1)
+            return t1, t2
         if self.comm is None:
             full = new
         else:

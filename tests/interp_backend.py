@@ -104,6 +104,38 @@ class InterpBackend(object):
         t2 += i2
         return float((i1.double() ** 2).sum() + (i2.double() ** 2).sum())
 
+    def update_energy(self, t1, t2, r1, r2, eps, fov, ld_fov, oovv, no, nv, symmetrize, ij_lo, ij_hi, count_t1):
+        eo, ev = eps[:no], eps[no:]
+        Dia = eo[:, None] - ev[None, :]
+        Dijab = eo[:, None, None, None] + eo[None, :, None, None] - ev[None, None, :, None] - ev[None, None, None, :]
+        rr = r2 + r2.permute(1, 0, 3, 2) if symmetrize else r2
+        i1 = r1 / Dia
+        t1 += i1
+        sel = torch.zeros(no * no, dtype=torch.bool)
+        sel[ij_lo:ij_hi] = True
+        sel = sel.reshape(no, no)
+        i2 = (rr / Dijab) * sel[:, :, None, None].to(rr.dtype)
+        t2 += i2
+        tau = t2 + t1[:, None, :, None] * t1[None, :, None, :]
+        L = 2.0 * oovv - oovv.transpose(2, 3)
+        e2 = float(((tau * L).double() * sel[:, :, None, None]).sum())
+        rms2 = float((i2.double() ** 2).sum())
+        if count_t1:
+            rms2 += float((i1.double() ** 2).sum())
+            e2 += float(2.0 * (fov * t1).double().sum())
+        return rms2, e2
+
+    def prepare_amplitudes(self, t1, t2, no, nv, vlo, vl, **outs):
+        pr = t1[:, None, :, None] * t1[None, :, None, :]
+        t2s = 2.0 * t2 - t2.transpose(2, 3)
+        tauW = 0.5 * t2 + pr
+        val = dict(tau=t2 + pr, tauh=t2 + 0.5 * pr, tauW=tauW, t2s=t2s, t11=pr,
+                   t2sP=t2s.permute(0, 2, 1, 3), t2P=t2.permute(0, 2, 1, 3), t2Q=t2.permute(1, 2, 0, 3),
+                   tauWPn=-tauW.permute(0, 3, 1, 2)[:, vlo:vlo + vl], t2Rh=0.5 * t2.permute(1, 3, 0, 2)[:, vlo:vlo + vl])
+        for k, out in outs.items():
+            if out is not None:
+                out.copy_(val[k])
+
     def cc_energy(self, fov, ld_fov, t1, t2, oovv, no, nv):
         tau = t2 + t1[:, None, :, None] * t1[None, :, None, :]
         L = 2.0 * oovv - oovv.transpose(2, 3)
