@@ -56,7 +56,7 @@ CASES = [
     ("C[nm] = A[mk]*B[nk]", dict(A=(157, 300), B=(24000, 300), C=(24000, 157))),
     # plain K-contiguous matrices with M = 256 / 1024: the 128-row TMA-staged kernel, contract_f64_tma_kernel<8>
     ("C[mn] = A[mk]*B[nk]", dict(A=(256, 520), B=(390, 520), C=(256, 390))),
-    ("C[mn] = A[mk]*B[nk] + A2[mk]*B2[nk]", dict(A=(1024, 200), B=(2100, 200), A2=(1024, 72), B2=(2100, 72), C=(1024, 2100))),
+    ("C[mn] = A[mk]*B[nk] + A2[ml]*B2[nl]", dict(A=(1024, 200), B=(2100, 200), A2=(1024, 72), B2=(2100, 72), C=(1024, 2100))),
 ]
 
 
