@@ -214,12 +214,13 @@ TC05_CASES = [
 def test_contract_f32_tcgen05_k_panels(be, monkeypatch):
     """The K-panel loop of the tcgen05 path (one segment, N >= 8 M, A planes larger than the panel budget:
     the SP ladder at (40,300)) with the budget lowered to 1 MB so that a small shape runs it: three panels
-    of 1024 + 1024 + 952 k, the last one ragged against the 32-float k-block, beta = 1 from the second on."""
+    of 512 + 512 + 376 k, the last one ragged against the 32-float k-block, beta = 1 from the second on.
+    (M = 256, N = 2304: both whole tiles, so the planner keeps m on M and the launch stays tcgen05-eligible.)"""
     from pycc_b200.dsl import plan
     from pycc_b200 import _lib
     monkeypatch.setenv("PCCB_TC05_PANEL_MB", "1")
     g = torch.Generator(device="cpu").manual_seed(77)
-    M, N, K = 128, 1100, 3000
+    M, N, K = 256, 2304, 1400
     A = torch.randn(M, K, generator=g, dtype=torch.float32).to(be.device)
     B = torch.randn(N, K, generator=g, dtype=torch.float32).to(be.device)
     C0 = torch.randn(M, N, generator=g, dtype=torch.float32).to(be.device)

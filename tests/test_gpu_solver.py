@@ -61,6 +61,10 @@ def test_golden_builder_api_and_operator(golden):
     r1, r2 = w.residuals(F, t1, t2)
     assert np.abs(r1.cpu().numpy() - g["gen_r1"]).max() < 1e-12
     assert np.abs(r2.cpu().numpy() - g["gen_r2"]).max() < 1e-12
+    assert float(w.t1.abs().max()) == 0.0 and torch.equal(w.H.F, w.engine.F)      # MP2 guess and H.F untouched
+    # the builders above are pure (the object's own amplitudes were put back): the operator checks below want
+    # the test amplitudes on the device
+    w._load(None, t1, t2)
     c = w.contract
     x = c('ijef,abef->ijab', w.t2, H.ERI[v, v, v, v])
     assert np.abs(x.cpu().numpy() - np.einsum('ijef,abef->ijab', t2, g.blocks["vvvv"])).max() < 1e-12
