@@ -160,6 +160,22 @@ int pccb_prepare_amplitudes(pccb_ctx* ctx, int dtype, const void* t1_dev, const 
 int pccb_cc_energy(pccb_ctx* ctx, int dtype, const void* fov_dev, int64_t ld_fov, const void* t1_dev,
                    const void* t2_dev, const void* oovv_dev, int64_t no, int64_t nv, double* e_host);
 
+/* pccb_cc_energy without any allocation.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA-graph capture, tight serving
+ * loops, harnesses that forbid it).  Same arithmetic and summation order as pccb_cc_energy, but
+ *   - the per-CTA partial sums live in a file-scope static __device__ array of
+ *     pccb_cc_energy_static_max_partials() = 131072 doubles (1 MiB; every GPU that loads the library holds
+ *     it until the process exits); problems with ceil(nv/32)^2 * no^2 above that are rejected with
+ *     PCCB_ERR_ARG and a message (e.g. no=30 nv=250 needs 57600, no=40 nv=400 needs 270400: too large);
+ *   - the energy is written to e_dev, a DEVICE double the caller owns; the call is asynchronous on the
+ *     ctx stream and calls no cudaMalloc / cudaFree / cudaMallocHost and no allocating library routine.
+ * Every call shares the one array: calls that overlap on the GPU (two streams, concurrent graph branches,
+ * two contexts on one device) race on it; serialise them.  Nothing needs clearing between calls (each call
+ * overwrites every slot it sums). */
+int64_t pccb_cc_energy_static_max_partials(void);
+int pccb_cc_energy_static(pccb_ctx* ctx, int dtype, const void* fov_dev, int64_t ld_fov, const void* t1_dev,
+                          const void* t2_dev, const void* oovv_dev, int64_t no, int64_t nv, double* e_dev);
+
 /* DIIS building blocks (pycc/utils.py:26-46, 108-133); accumulation is FP64 for both dtypes. */
 int pccb_dot(pccb_ctx* ctx, int dtype, const void* x_dev, const void* y_dev, int64_t n, double* out_host);
 int pccb_axpby(pccb_ctx* ctx, int dtype, void* out_dev, double a, const void* x_dev, double b, const void* y_dev,

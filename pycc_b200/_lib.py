@@ -24,6 +24,7 @@ EXPORTS = (
     "pccb_update_amplitudes", "pccb_cc_energy", "pccb_dot", "pccb_axpby", "pccb_lincomb",
     "pccb_triples_energy", "pccb_t3_combine", "pccb_split_lo", "pccb_register_lo_plane", "pccb_clear_lo_planes",
     "pccb_unregister_lo_plane", "pccb_update_energy", "pccb_prepare_amplitudes",
+    "pccb_cc_energy_static", "pccb_cc_energy_static_max_partials",
 )
 
 
@@ -87,6 +88,7 @@ def load():
     lib.pccb_update_amplitudes.argtypes = [vp, i32, vp, vp, vp, vp, vp, i64, i64, i32, pd]
     lib.pccb_update_energy.argtypes = [vp, i32, vp, vp, vp, vp, vp, vp, i64, vp, i64, i64, i32, i64, i64, i32, pd]
     lib.pccb_prepare_amplitudes.argtypes = [vp, i32, vp, vp, i64, i64, i64, i64, C.POINTER(PrepareOutputs)]
+    lib.pccb_cc_energy_static.argtypes = [vp, i32, vp, i64, vp, vp, vp, i64, i64, vp]
     lib.pccb_cc_energy.argtypes = [vp, i32, vp, i64, vp, vp, vp, i64, i64, pd]
     lib.pccb_dot.argtypes = [vp, i32, vp, vp, i64, pd]
     lib.pccb_axpby.argtypes = [vp, i32, vp, dbl, vp, dbl, vp, i64]
@@ -99,7 +101,9 @@ def load():
     lib.pccb_t3_combine.argtypes = [vp, i32, vp, i32, i32, i32, i32, vp, i64, i64, vp, vp]
     for name in EXPORTS:
         fn = getattr(lib, name)
-        if name not in ("pccb_last_error",):
+        if name == "pccb_cc_energy_static_max_partials":
+            fn.restype = i64
+        elif name not in ("pccb_last_error",):
             fn.restype = i32
     if lib.pccb_abi_version() != ABI_VERSION:
         raise EngineError("libpyccb200.so ABI version mismatch")

@@ -761,3 +761,82 @@ extern "C" int pccb_lincomb(pccb_ctx* ctx, int dtype, void* out_dev, const void*
     DISPATCH_DTYPE(ctx, dtype, lincomb_t<double>(ctx, out_dev, vecs, coef, nvec, n),
                    lincomb_t<float>(ctx, out_dev, vecs, coef, nvec, n));
 }
+
+// ---- pccb_cc_energy_static: the energy reduction with NO allocation anywhere --------------------------
+// (No counterpart in the reference; added for callers that cannot
+//  call cudaMalloc: CUDA-graph capture, tight serving loops, harnesses that forbid it.)
+// pccb_cc_energy keeps its per-CTA partial sums in ctx->partial_dev, which pccb_ensure_partials
+// cudaMalloc's / cudaFree's on demand, and returns through a pinned host slot after a stream
+// synchronise.  This variant runs the SAME two kernels (energy_kernel, final_sum_kernel) but
+//   * the partial sums live in the file-scope array below: PCCB_STATIC_SCRATCH_DOUBLES doubles = 1 MiB,
+//     held by every GPU that loads the library until the process exits;
+//   * the result goes to a caller-supplied DEVICE double: no host copy, no synchronise.
+// In host code `g_static_scratch` is a host-side stand-in, not a device address: its device address is
+// looked up once per device with cudaGetSymbolAddress (that device current) and that pointer is what
+// the kernels receive.  Every call shares the array and it keeps the previous call's contents; a call
+// overwrites every slot it later sums (one per CTA), so nothing needs clearing, but two calls that
+// overlap on the GPU (different streams, or concurrent graph branches) race on it.
+constexpr size_t PCCB_STATIC_SCRATCH_DOUBLES = size_t(1) << 17;
+static __device__ __align__(256) double g_static_scratch[PCCB_STATIC_SCRATCH_DOUBLES];
+
+namespace {
+
+constexpr int MAX_STATIC_DEVICES = 64;
+double* g_static_scratch_ptr[MAX_STATIC_DEVICES] = {};     // device address of g_static_scratch, per device
+
+// set-up, once per device: the device address of the scratch array (never an allocation)
+int static_scratch_for(pccb_ctx* ctx, double** out) {
+    const int dev = ctx->device;
+    PCCB_REQUIRE(ctx, dev >= 0 && dev < MAX_STATIC_DEVICES, "pccb_cc_energy_static: device index %d out of range", dev);
+    if (!g_static_scratch_ptr[dev]) {
+        int cur = -1;
+        PCCB_CUDA(ctx, cudaGetDevice(&cur));
+        if (cur != dev) PCCB_CUDA(ctx, cudaSetDevice(dev));
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_static_scratch);
+        if (cur != dev && cur >= 0) cudaSetDevice(cur);
+        if (e != cudaSuccess || !p)
+            PCCB_FAIL(ctx, PCCB_ERR_CUDA, "cudaGetSymbolAddress(g_static_scratch) failed on device %d: %s", dev,
+                      cudaGetErrorString(e));
+        g_static_scratch_ptr[dev] = static_cast<double*>(p);
+    }
+    *out = g_static_scratch_ptr[dev];
+    return PCCB_OK;
+}
+
+template <typename T>
+int energy_static_t(pccb_ctx* ctx, const void* fov, int64_t ld_fov, const void* t1, const void* t2, const void* g,
+                    int64_t no, int64_t nv, double* scratch, double* e_dev) {
+    const int tpd = (int)((nv + 31) / 32);
+    dim3 grid(tpd * tpd, (unsigned)(no * no));
+    const size_t nb = (size_t)grid.x * grid.y;
+    energy_kernel<T><<<grid, 256, 0, ctx->stream>>>((const T*)fov, ld_fov, (const T*)t1, (const T*)t2, (const T*)g,
+                                                    (int)no, (int)nv, tpd, scratch);
+    PCCB_CHECK_LAUNCH(ctx, "energy_kernel");
+    final_sum_kernel<<<1, RED_THREADS, 0, ctx->stream>>>(scratch, (int)nb, 1, e_dev);
+    PCCB_CHECK_LAUNCH(ctx, "final_sum_kernel");
+    return PCCB_OK;
+}
+
+}  // namespace
+
+extern "C" int64_t pccb_cc_energy_static_max_partials(void) { return (int64_t)PCCB_STATIC_SCRATCH_DOUBLES; }
+
+extern "C" int pccb_cc_energy_static(pccb_ctx* ctx, int dtype, const void* fov_dev, int64_t ld_fov, const void* t1_dev,
+                                     const void* t2_dev, const void* oovv_dev, int64_t no, int64_t nv, double* e_dev) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, fov_dev && t1_dev && t2_dev && oovv_dev && e_dev && no > 0 && nv > 0 && no * no <= 65535,
+                 "pccb_cc_energy_static: bad arguments");
+    const int64_t tpd = (nv + 31) / 32;
+    const int64_t need = tpd * tpd * no * no;
+    PCCB_REQUIRE(ctx, need <= (int64_t)PCCB_STATIC_SCRATCH_DOUBLES,
+                 "pccb_cc_energy_static: no=%lld nv=%lld needs %lld partial sums, the static scratch holds %lld "
+                 "(ceil(nv/32)^2 * no^2 must not exceed it); use pccb_cc_energy",
+                 (long long)no, (long long)nv, (long long)need, (long long)PCCB_STATIC_SCRATCH_DOUBLES);
+    double* scratch = nullptr;
+    int rc = static_scratch_for(ctx, &scratch);
+    if (rc) return rc;
+    DISPATCH_DTYPE(ctx, dtype,
+                   energy_static_t<double>(ctx, fov_dev, ld_fov, t1_dev, t2_dev, oovv_dev, no, nv, scratch, e_dev),
+                   energy_static_t<float>(ctx, fov_dev, ld_fov, t1_dev, t2_dev, oovv_dev, no, nv, scratch, e_dev));
+}
