@@ -413,7 +413,32 @@ def run_ours(args):
               "checked": "residuals() of the timed engine on perturbed (t1, t2) and its energy, o=%d v=%d, %d GPU(s), against "
                          "oracle/torch_oracle.py (reference formulas, torch.einsum/cuBLAS FP64 on the device) on integrals "
                          "regenerated from the factor B; each rank checks the <ab|ef> rows it owns" % (o, v, world)}
-    del r1c, r2c, r1g, r2g
+    # the ITERATION path (reduce-scatter of r2 -> update of this rank's (i,j) blocks -> fused energy -> allgather):
+    # one solver step from the same perturbed amplitudes must give t + r/D, its norm and the energy of the
+    # checker's residuals (pycc/ccwfn.py:287-296)
+    keep1, keep2 = w.t1.clone(), w.t2.clone()
+    w._load(F, t1h, t2h)
+    e_it, rms_it = w._iteration(None, 0, 1, extrapolate=False)
+    eng.sync_amplitudes()
+    epsd = chk.F.diagonal()
+    eo, ev = epsd[:o], epsd[o:]
+    i1 = r1c / (eo[:, None] - ev[None, :])
+    r2c /= (eo[:, None, None, None] + eo[None, :, None, None] - ev[None, None, :, None] - ev[None, None, None, :])
+    rms_c = float(torch.sqrt((i1 * i1).sum() + (r2c * r2c).sum()))
+    i1 += t1h
+    r2c += t2h                                           # r2c now holds the expected new t2
+    parity["iteration_max_abs_dt1"] = float((w.t1.double() - i1).abs().max())
+    parity["iteration_max_abs_dt2"] = float((w.t2.double() - r2c).abs().max())
+    parity["iteration_abs_dE"] = abs(e_it - chk.energy(i1, r2c))
+    parity["iteration_rel_drms"] = abs(rms_it - rms_c) / max(rms_c, 1e-300)
+    parity["tolerance_iteration"] = {"dt": 1e-5 if sp else 1e-9, "dE": 1e-6 if sp else 1e-10, "rel_rms": 1e-5 if sp else 1e-9}
+    it_ok = (max(parity["iteration_max_abs_dt1"], parity["iteration_max_abs_dt2"]) <= parity["tolerance_iteration"]["dt"]
+             and parity["iteration_abs_dE"] <= parity["tolerance_iteration"]["dE"]
+             and parity["iteration_rel_drms"] <= parity["tolerance_iteration"]["rel_rms"])
+    w.t1.copy_(keep1)
+    w.t2.copy_(keep2)
+    eng.set_fock(eng.F0)
+    del r1c, r2c, r1g, r2g, i1, keep1, keep2
     if want_t:
         tri = cct._engine(w)
         sample = [t for t in TRIPLET_SAMPLE(o) if t[0] < o and t[1] <= t[0] and t[2] <= t[1]]
@@ -425,6 +450,7 @@ def run_ours(args):
         parity["triplets_checked"] = sample
         parity["tolerance_triplet"] = 1e-7 if sp else 1e-12
     ok = parity["max_abs_dr1"] <= tol_r and parity["max_abs_dr2"] <= tol_r and parity["abs_dE_same_amplitudes"] <= (1e-6 if sp else 1e-10)
+    ok = ok and it_ok
     if want_t:
         ok = ok and parity["max_abs_dE_T_triplet"] <= parity["tolerance_triplet"]
     parity["passed"] = bool(ok)

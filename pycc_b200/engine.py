@@ -110,7 +110,12 @@ class CCSDEngine(object):
         self.Wr1, self.Wr2 = E(o, vl, o, v), E(o, vl, o, v)      # [j,b,m,e]
         self.Zr = E(o, o, o, vl)                                 # [m,i,j,b]
         self.Y1, self.Y2 = E(o, o, o, vl), E(o, o, vl, o)        # [i,m,j,b], [i,m,a,j]
-        self.r1, self.r2 = E(o, v), E(o, o, v, v)
+        # r2 is padded like t2: the iteration's exchange step is an in-place reduce-scatter over the same
+        # (i,j)-block chunks, which leaves on each rank the finished residual of the blocks it updates
+        self._r2_store = be.zeros((W * self.chunk_pairs * v * v,), dtype)
+        self.r1, self.r2 = E(o, v), self._r2_store[:o * o * v * v].view(o, o, v, v)
+        self._scatter_r2 = False       # set by residuals(symmetrize=False) on several GPUs
+        self.r2_scattered = False      # True: r2 holds the symmetrised, summed residual of this rank's blocks only
         if self.model == 'CC2':      # t1 t1 products and the two factorised intermediates of the CC2 r_T2
             self.T11, self.Yw, self.Xv = E(o, o, v, v), E(o, o, o, vl), E(vl, v, o, v)
         # Mixed-precision mode.  (i) The ring-term operands are kept in PLAIN-MATRIX layouts as well
@@ -368,7 +373,16 @@ class CCSDEngine(object):
         if name == "r_T1":
             self.comm.allreduce_(self.r1)
         elif name == "r_T2":
-            self.comm.allreduce_(self.r2)
+            if self._scatter_r2:
+                # r2 + r2^T (ccwfn.py:621) is linear: symmetrise the partial sums locally, then reduce-scatter
+                # by (i,j) blocks - half the bytes of an allreduce, and no partner read in the update
+                self.be.pair_symmetrize(self.r2, self.no, self.nv)
+                n = self.chunk_pairs * self.nv * self.nv
+                self.comm.reduce_scatter_(self._r2_store, self.comm.rank * n, n)
+                self.r2_scattered = True
+            else:
+                self.comm.allreduce_(self.r2)
+                self.r2_scattered = False
 
     def _launch(self, name):
         for L in self.plans[name]:
@@ -412,6 +426,9 @@ class CCSDEngine(object):
             self.t1.zero_()          # CCD carries no singles (ccwfn.py:543-546): before tau is formed
             self.r1.zero_()
         self.prepare()
+        # the solver's iteration (symmetrize=False) may leave r2 scattered over the ranks; callers that want the
+        # whole residual get the allreduce.  CC3 adds its triples terms after the builders: allreduce there.
+        self._scatter_r2 = (not symmetrize) and self.comm.world > 1 and self.model != 'CC3'
         order = list(self.builder_order())
         if self.pre_plans:
             self._run_small([n for n in order if n in self.pre_plans])
@@ -423,6 +440,7 @@ class CCSDEngine(object):
                 from .cc3_engine import CC3Engine
                 self.cc3 = CC3Engine(self)
             self.cc3.contribute()
+        self._scatter_r2 = False
         if symmetrize:
             self.be.pair_symmetrize(self.r2, self.no, self.nv)       # ccwfn.py:621
         return self.r1, self.r2
@@ -463,14 +481,15 @@ class CCSDEngine(object):
     def update_energy(self):
         """t += r/D (the pair symmetrisation of r2, ccwfn.py:621, on the fly), the increment norm and the
         energy of the new amplitudes in ONE pass (pccb_update_energy).  Several GPUs: each rank updates the
-        (i,j) blocks it owns (t1: all of it, every rank holds the summed r1), the two scalars are summed
-        over the ranks, and t2 stays incomplete until ``sync_amplitudes`` or the DIIS allgather.
+        (i,j) blocks it owns - whose residual the reduce-scatter of residuals(symmetrize=False) delivered
+        already summed and symmetrised - (t1: all of it, every rank holds the summed r1), the two scalars are
+        summed over the ranks, and t2 stays incomplete until ``sync_amplitudes`` or the DIIS allgather.
         Returns (squared increment norm, energy)."""
         self.be.bind_stream()
         o = self.no
         fov = self.F[:o, o:]
         rms2, e = self.be.update_energy(self.t1, self.t2, self.r1, self.r2, self.eps, fov, self.F.stride(0),
-                                        self.blk["oovv"], o, self.nv, True, self.ij_lo, self.ij_hi,
+                                        self.blk["oovv"], o, self.nv, not self.r2_scattered, self.ij_lo, self.ij_hi,
                                         self.comm.rank == 0)
         if self.comm.world > 1:
             rms2, e = self.comm.allreduce_scalars([rms2, e])

@@ -80,6 +80,20 @@ class Comm(object):
             dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
             self.bytes_reduced += t.numel() * t.element_size()
 
+    def reduce_scatter_(self, full, lo, n):
+        """Sum ``full`` (world * n elements) over the ranks, leaving full[lo : lo + n] (lo = rank * n) complete
+        on this rank; the rest of ``full`` is unspecified afterwards.  In place: NCCL's reduce-scatter with
+        recvbuff = sendbuff + rank * n.  gloo has no reduce-scatter: an allreduce does (host-logic tests)."""
+        if self.world <= 1:
+            return
+        import torch.distributed as dist
+        if dist.get_backend(self.group) == "nccl":
+            dist.reduce_scatter_tensor(full[lo:lo + n], full, op=dist.ReduceOp.SUM, group=self.group)
+            self.bytes_reduced += n * full.element_size()
+        else:
+            dist.all_reduce(full, op=dist.ReduceOp.SUM, group=self.group)
+            self.bytes_reduced += full.numel() * full.element_size()
+
     def allreduce_scalar(self, x):
         if self.world <= 1:
             return float(x)
