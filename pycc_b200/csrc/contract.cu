@@ -9,7 +9,7 @@
 //   * FP64 has no tcgen05/TMEM path on Blackwell; the FP64 tensor instruction is the
 //     warp-synchronous DMMA.8x8x4 (PTX mma.sync.m8n8k4.f64), one issue per 16 cycles per SM
 //     sub-partition = 37.0 TFLOP/s per GPU; cuBLAS DGEMM reaches 35.5.
-//   * CTA tile (16*MI) x 128 x 16 with MI in {1,2,4,5,6,8} chosen per launch to minimise padded
+//   * CTA tile (16*MI) x 128 x 16 with MI in {1,2,3,4,5,6,8} chosen per launch to minimise padded
 //     rows (o^2 = 400 -> five 80-row tiles); 8 DMMA warps as 2(M) x 4(N), warp tile (8*MI) x 32:
 //     4*MI DMMA per MI+4 LDS.64, so the tensor pipe, not shared memory, is the limiter.
 //   * four kernels behind the one entry point (the first three persistent over output tiles):
@@ -64,7 +64,7 @@ struct DSeg {
     int kt_begin;          // first global k-tile of this segment
     int a_mn_major;        // A tile in shared memory: 0 = [row][k], 1 = [k][row]
     int b_mn_major;
-    int pad_;
+    int bz;                // TMA kernel, batched launch: bit 0 / 1 = A / B carries the batch index (3-D tensor map)
 };
 
 struct DParams {
@@ -1092,7 +1092,17 @@ __device__ __forceinline__ void tma_load_2d(unsigned dst, const CUtensorMap* map
         : "memory");
 }
 
-template <int MI>
+__device__ __forceinline__ void tma_load_3d(unsigned dst, const CUtensorMap* map, int c0, int c1, int c2, unsigned bar) {
+    asm volatile(
+        "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3, %4}], [%5];\n"
+        ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(c2), "r"(bar)
+        : "memory");
+}
+
+// BATCHED: the operands are 3-D tensors (k, row, batch) - the (T) / CC3 W build over plain-matrix operands, one
+// launch for all k of an occupied pair; an operand that does not depend on the batch index has a batch
+// dimension of extent 1 and is always read at batch coordinate 0.
+template <int MI, bool BATCHED>
 __global__ void __launch_bounds__(TMA_THREADS, 1)
 contract_f64_tma_kernel(const __grid_constant__ DParams p, const __grid_constant__ TmaMaps maps) {
     constexpr int BM = 16 * MI;
@@ -1146,7 +1156,7 @@ contract_f64_tma_kernel(const __grid_constant__ DParams p, const __grid_constant
                 const long long rest = tile / gm;
                 const unsigned m0 = mx * BM, n0 = (unsigned)(rest % gn) * BN;
                 const int z = (int)(rest / gn);
-                const int split = z % p.splits;
+                const int split = z % p.splits, batch = z / p.splits;
                 const int kt_lo = (int)(((long long)p.total_kt * split) / p.splits);
                 const int nkt = (int)(((long long)p.total_kt * (split + 1)) / p.splits) - kt_lo;
 #pragma unroll 1
@@ -1157,8 +1167,14 @@ contract_f64_tma_kernel(const __grid_constant__ DParams p, const __grid_constant
                     const int k0 = (kt_lo + it - p.seg[s].kt_begin) * BK;
                     const unsigned bar = full_s + 8 * st;
                     mbar_expect_tx(bar, (unsigned)((A_STAGE + B_STAGE) * sizeof(double)));
-                    tma_load_2d(sA_s + st * (A_STAGE * 8), &maps.a[s], k0, (int)m0, bar);
-                    tma_load_2d(sB_s + st * (B_STAGE * 8), &maps.b[s], k0, (int)n0, bar);
+                    if (BATCHED) {
+                        const int bz = p.seg[s].bz;
+                        tma_load_3d(sA_s + st * (A_STAGE * 8), &maps.a[s], k0, (int)m0, (bz & 1) ? batch : 0, bar);
+                        tma_load_3d(sB_s + st * (B_STAGE * 8), &maps.b[s], k0, (int)n0, (bz & 2) ? batch : 0, bar);
+                    } else {
+                        tma_load_2d(sA_s + st * (A_STAGE * 8), &maps.a[s], k0, (int)m0, bar);
+                        tma_load_2d(sB_s + st * (B_STAGE * 8), &maps.b[s], k0, (int)n0, bar);
+                    }
                 }
             }
         }
@@ -1474,6 +1490,7 @@ int dispatch_mi(pccb_ctx* ctx, const DParams& p, long long batch, int mi) {
     switch (mi) {
         case 1: return launch_tile_kernel<VEC, 1>(ctx, p, batch);
         case 2: return launch_tile_kernel<VEC, 2>(ctx, p, batch);
+        case 3: return launch_tile_kernel<VEC, 3>(ctx, p, batch);
         case 4: return launch_tile_kernel<VEC, 4>(ctx, p, batch);
         case 5: return launch_tile_kernel<VEC, 5>(ctx, p, batch);
         case 6: return launch_tile_kernel<VEC, 6>(ctx, p, batch);
@@ -1524,18 +1541,36 @@ bool make_map(CUtensorMap* m, const void* base, long long rows, long long K, lon
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
+// batched operand: (k, row, batch); an operand without a batch stride gets a batch dimension of extent 1
+bool make_map3(CUtensorMap* m, const void* base, long long rows, long long K, long long row_stride, int box_rows,
+               long long nbatch, long long batch_stride) {
+    EncodeTiledFn enc = encode_tiled_fn();
+    if (!enc) return false;
+    if (rows <= 1) row_stride = ((K + 1) / 2) * 2;
+    if (row_stride < K) return false;
+    if (batch_stride <= 0) { nbatch = 1; batch_stride = row_stride * (rows > 0 ? rows : 1); }
+    if (batch_stride & 1) return false;
+    const cuuint64_t dims[3] = {(cuuint64_t)K, (cuuint64_t)rows, (cuuint64_t)nbatch};
+    const cuuint64_t strides[2] = {(cuuint64_t)row_stride * sizeof(double), (cuuint64_t)batch_stride * sizeof(double)};
+    const cuuint32_t box[3] = {(cuuint32_t)BK, (cuuint32_t)box_rows, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 3, const_cast<void*>(base), dims, strides, box, estr,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <int MI>
 constexpr size_t smem_bytes_tma() {
     return (size_t)TMA_STAGES * (16 * MI + BN) * BK * sizeof(double) + 2 * TMA_STAGES * sizeof(unsigned long long) + 1024;
 }
 
-template <int MI>
+template <int MI, bool BATCHED>
 int launch_tma_kernel(pccb_ctx* ctx, const DParams& p, const TmaMaps& maps, long long batch) {
     constexpr int BM = 16 * MI;
     constexpr size_t SMEM = smem_bytes_tma<MI>();
     static bool attr_set = false;
     if (!attr_set) {
-        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_tma_kernel<MI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_tma_kernel<MI, BATCHED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                             (int)SMEM));
         attr_set = true;
     }
@@ -1543,32 +1578,54 @@ int launch_tma_kernel(pccb_ctx* ctx, const DParams& p, const TmaMaps& maps, long
     q.nz = (int)(batch * p.splits);
     const long long ntiles = (long long)((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * q.nz;
     const unsigned nctas = (unsigned)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
-    contract_f64_tma_kernel<MI><<<nctas, TMA_THREADS, SMEM, ctx->stream>>>(q, maps);
+    contract_f64_tma_kernel<MI, BATCHED><<<nctas, TMA_THREADS, SMEM, ctx->stream>>>(q, maps);
     PCCB_CHECK_LAUNCH(ctx, "contract_f64_tma_kernel");
     return PCCB_OK;
 }
 
 // returns 1 when the TMA kernel was launched, 0 when the contraction is not eligible, < 0 on error
-int try_tma(pccb_ctx* ctx, const DParams& p, const pccb_contraction* d, int mi) {
+int try_tma(pccb_ctx* ctx, const DParams& p_in, const pccb_contraction* d, int mi) {
     static const bool use_tma = [] { const char* e = getenv("PCCB_TMA"); return e ? atoi(e) != 0 : true; }();
-    if (!use_tma || mi <= 2 || d->batch != 1 || p.nseg < 1) return 0;
+    static const bool use_tma_batched = [] { const char* e = getenv("PCCB_TMA_BATCHED"); return e ? atoi(e) != 0 : true; }();
+    if (!use_tma || mi <= 2 || p_in.nseg < 1) return 0;
+    const bool batched = d->batch != 1;
+    if (batched && (!use_tma_batched || p_in.splits != 1)) return 0;
+    DParams p = p_in;
     for (int s = 0; s < p.nseg; ++s) {
-        const DSeg& g = p.seg[s];
+        DSeg& g = p.seg[s];
         if (!tma_operand_ok(g.A, g.am, g.ak, p.M) || !tma_operand_ok(g.B, g.bn, g.bk, p.N)) return 0;
+        if (batched && (g.a_batch < 0 || g.b_batch < 0 || (g.a_batch & 1) || (g.b_batch & 1))) return 0;
+        g.bz = (g.a_batch > 0 ? 1 : 0) | (g.b_batch > 0 ? 2 : 0);
     }
     TmaMaps maps;
     memset(&maps, 0, sizeof(maps));
     for (int s = 0; s < p.nseg; ++s) {
         const DSeg& g = p.seg[s];
-        if (!make_map(&maps.a[s], g.A, p.M, g.K, g.am.s_lo, 16 * mi)) return 0;
-        if (!make_map(&maps.b[s], g.B, p.N, g.K, g.bn.s_lo, BN)) return 0;
+        if (batched) {
+            if (!make_map3(&maps.a[s], g.A, p.M, g.K, g.am.s_lo, 16 * mi, d->batch, g.a_batch)) return 0;
+            if (!make_map3(&maps.b[s], g.B, p.N, g.K, g.bn.s_lo, BN, d->batch, g.b_batch)) return 0;
+        } else {
+            if (!make_map(&maps.a[s], g.A, p.M, g.K, g.am.s_lo, 16 * mi)) return 0;
+            if (!make_map(&maps.b[s], g.B, p.N, g.K, g.bn.s_lo, BN)) return 0;
+        }
     }
     int rc;
-    switch (mi) {
-        case 4: rc = launch_tma_kernel<4>(ctx, p, maps, d->batch); break;
-        case 5: rc = launch_tma_kernel<5>(ctx, p, maps, d->batch); break;
-        case 6: rc = launch_tma_kernel<6>(ctx, p, maps, d->batch); break;
-        default: rc = launch_tma_kernel<8>(ctx, p, maps, d->batch); break;
+    if (batched) {
+        switch (mi) {
+            case 3: rc = launch_tma_kernel<3, true>(ctx, p, maps, d->batch); break;
+            case 4: rc = launch_tma_kernel<4, true>(ctx, p, maps, d->batch); break;
+            case 5: rc = launch_tma_kernel<5, true>(ctx, p, maps, d->batch); break;
+            case 6: rc = launch_tma_kernel<6, true>(ctx, p, maps, d->batch); break;
+            default: rc = launch_tma_kernel<8, true>(ctx, p, maps, d->batch); break;
+        }
+    } else {
+        switch (mi) {
+            case 3: rc = launch_tma_kernel<3, false>(ctx, p, maps, d->batch); break;
+            case 4: rc = launch_tma_kernel<4, false>(ctx, p, maps, d->batch); break;
+            case 5: rc = launch_tma_kernel<5, false>(ctx, p, maps, d->batch); break;
+            case 6: rc = launch_tma_kernel<6, false>(ctx, p, maps, d->batch); break;
+            default: rc = launch_tma_kernel<8, false>(ctx, p, maps, d->batch); break;
+        }
     }
     return rc == PCCB_OK ? 1 : rc;
 }
@@ -1577,14 +1634,16 @@ int try_tma(pccb_ctx* ctx, const DParams& p, const pccb_contraction* d, int mi) 
 int choose_mi(long long M) {
     // tuning hook for tools/bench_contract.py: PCCB_MI=<1|2|4|5|6|8> forces the tile height
     static const int forced = [] { const char* e = getenv("PCCB_MI"); return e ? atoi(e) : 0; }();
-    if (forced == 1 || forced == 2 || forced == 4 || forced == 5 || forced == 6 || forced == 8) return forced;
+    if (forced == 1 || forced == 2 || forced == 3 || forced == 4 || forced == 5 || forced == 6 || forced == 8) return forced;
     // padded rows weighted by the measured relative rate of the tile height.  Per useful row the
     // 64...128-row tiles run at nearly the same rate (ladder, M = 1600: 13 x 128 rows 33.1 TFLOP/s,
     // 20 x 80 rows 35.2; M = 900: 10 x 96 32.5, 15 x 64 32.4, 8 x 128 29.8), so among them padding
     // decides; the 16- and 32-row tiles have a quarter / half of the DMMAs per fragment load and run on
     // the non-persistent kernel: only for outputs that are skinny anyway.
-    static const int cand[] = {8, 6, 5, 4, 2, 1};
-    static const double eff[9] = {0.0, 0.35, 0.60, 0.0, 0.97, 0.985, 0.99, 0.0, 1.00};
+    // (48-row tiles: M = o^2 = 900 pads to 912 rows instead of 960 - the ladder at o = 30; weighted a little below
+    //  the 64-row tile, so that it is taken only when it saves more than ~1.5 % of padded rows)
+    static const int cand[] = {8, 6, 5, 4, 3, 2, 1};
+    static const double eff[9] = {0.0, 0.35, 0.60, 0.955, 0.97, 0.985, 0.99, 0.0, 1.00};
     int best = 8;
     double best_cost = 1e300;
     for (int mi : cand) {
@@ -1664,7 +1723,7 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
         return PCCB_OK;
     }
 
-    const int mi = choose_mi(d->M);
+    int mi = choose_mi(d->M);
     const long long bm = 16 * mi;
     const long long gm = (d->M + bm - 1) / bm, gn = (d->N + BN - 1) / BN;
     PCCB_REQUIRE(ctx, gn <= 65535, "pccb_contract: N=%lld needs more than 65535 column tiles", (long long)d->N);
@@ -1706,6 +1765,21 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
     int rc = try_tma(ctx, p, d, mi);      // plain 2-D operands: TMA-staged kernel
     if (rc < 0) return rc;
     if (rc == 0) {
+        // Short contractions (8..64 k-tiles) with many tiles per SM - the (T) / CC3 W build, M = v^2 - spend
+        // 12-20 % of a tile in the epilogue; the kernel with epilogue warps exists for 64/80/96-row tiles only, and
+        // choose_mi prefers 128 rows for a large M (v = 250: 128-row tiles ran at 0.88 / 0.79 of the DMMA rate with
+        // beta = 0 / 1, profiles/r02_ncu_triples_w_o30v250.txt).  Take the best of the three heights instead.
+        static const bool wse_mi = [] { const char* e = getenv("PCCB_WSE_MI"); return e ? atoi(e) != 0 : true; }();
+        if (wse_mi && (mi == 8 || mi == 3) && splits == 1 && !p.D && kt >= WSE_MIN_KT && kt <= WSE_MAX_KT) {
+            int best = 0;
+            long long best_rows = 0;
+            for (int c : {6, 5, 4}) {
+                const long long b = 16 * c, rows = ((d->M + b - 1) / b) * b;
+                if (!best || rows < best_rows) { best = c; best_rows = rows; }
+            }
+            const long long t2 = ((d->M + 16 * best - 1) / (16 * best)) * gn * d->batch;
+            if (t2 >= 2ll * ctx->sm_count) mi = best;
+        }
         rc = vec2 ? dispatch_mi<2>(ctx, p, d->batch, mi) : dispatch_mi<1>(ctx, p, d->batch, mi);
         if (rc != PCCB_OK) return rc;
     }

@@ -32,6 +32,18 @@ _STATEMENTS = (
     "W[abc] += Vk[bce]*tij[ae] + Vj[cbe]*tik[ae] - tTk[mbc]*Oji[ma] - tj[mbc]*Oki[ma]",
 )
 
+# FP64: the same twelve terms over PLAIN K-contiguous matrices, so that all three launches run on the TMA-staged
+# kernel (batched 3-D tensor maps) instead of the cp.async kernels, whose four producer warps of compound-index
+# address arithmetic hold the 80-row tile at 81 % tensor-pipe activity (profiles/r02_ncu_triples_wse_o30v250.txt).
+# Four helper copies, made once per (T) call (once per iteration in CC3, where V and O are dressed):
+#   VT[i][y][x][e] = V[i][x][y][e]            tM[i][a][b][m]  = t2[i][m][a][b]
+#   OT[j][k][c][m] = O[j][k][m][c]            tMT[j][a][b][m] = t2[j][m][b][a]
+_STATEMENTS_PLAIN = (
+    "W[abc] = VTi[abe]*tkj[ce] + Vj[abe]*tki[ce] - tMi[abm]*OTjk[cm] - tMTj[abm]*OTik[cm]",
+    "W[abc] += VTi[ace]*tjk[be] + Vk[ace]*tji[be] - tMi[acm]*OTkj[bm] - tMTk[acm]*OTij[bm]",
+    "W[abc] += Vk[bce]*tij[ae] + VTj[bce]*tik[ae] - tMTk[bcm]*OTji[am] - tMj[bcm]*OTki[am]",
+)
+
 
 def _ptr_fields(desc):
     """(getter, setter) pairs for every device pointer of a descriptor."""
@@ -68,24 +80,42 @@ class TriplesEngine(object):
             raise ValueError("(T) needs the full <mb|ef> block on every rank (only this rank's slice was given)")
         self.V = V if V is not None else eng.ovvv_full
         self.O = O if O is not None else eng.blk["ooov"]
-        self.t2T = self.be.empty((o, o, v, v), eng.dtype)
+        import os
+        self.plain = eng.dtype == torch.float64 and os.environ.get("PCCB_T_PLAIN", "1") != "0"
+        self.statements = _STATEMENTS_PLAIN if self.plain else _STATEMENTS
+        if self.plain:
+            self.VT = self.be.empty((o, v, v, v), eng.dtype)
+            self.OT = self.be.empty((o, o, v, o), eng.dtype)
+            self.tM = self.be.empty((o, v, v, o), eng.dtype)
+            self.tMT = self.be.empty((o, v, v, o), eng.dtype)
+            self.t2T = None
+        else:
+            self.t2T = self.be.empty((o, o, v, v), eng.dtype)
         self.W = self.be.empty((o, v, v, v), eng.dtype)          # batch over k
         self._plan()
 
     def _tensors(self, i, j, k):
         e = self.eng
-        t2, tT, V, O = e.t2, self.t2T, self.V, self.O
+        t2, V, O = e.t2, self.V, self.O
         d = dict(W=self.W[k], Vi=V[i], Vj=V[j], Vk=V[k],
-                 tij=t2[i, j], tik=t2[i, k], tji=t2[j, i], tjk=t2[j, k], tki=t2[k, i], tkj=t2[k, j],
-                 ti=t2[i], tj=t2[j], tTj=tT[j], tTk=tT[k],
-                 Oij=O[i, j], Oik=O[i, k], Oji=O[j, i], Ojk=O[j, k], Oki=O[k, i], Okj=O[k, j])
+                 tij=t2[i, j], tik=t2[i, k], tji=t2[j, i], tjk=t2[j, k], tki=t2[k, i], tkj=t2[k, j])
+        if self.plain:
+            VT, OT, tM, tMT = self.VT, self.OT, self.tM, self.tMT
+            d.update(VTi=VT[i], VTj=VT[j], tMi=tM[i], tMj=tM[j], tMTj=tMT[j], tMTk=tMT[k],
+                     OTij=OT[i, j], OTik=OT[i, k], OTji=OT[j, i], OTjk=OT[j, k], OTki=OT[k, i], OTkj=OT[k, j])
+        else:
+            tT = self.t2T
+            d.update(ti=t2[i], tj=t2[j], tTj=tT[j], tTk=tT[k],
+                     Oij=O[i, j], Oik=O[i, k], Oji=O[j, i], Ojk=O[j, k], Oki=O[k, i], Okj=O[k, j])
         return {n: TRef.of(t, n) for n, t in d.items()}
 
     def _plan(self):
         """Plan at (0,0,0) and difference the pointers at unit steps of i, j, k."""
         o = self.eng.no
         dcode = self.eng.dcode
-        base = [plan(s, self._tensors(0, 0, 0), dcode) for s in _STATEMENTS]
+        stm = self.statements
+        pf = True if self.plain else None
+        base = [plan(s, self._tensors(0, 0, 0), dcode, prefer_flat=pf) for s in stm]
         for L in base:
             if len(L) != 1 or L[0].desc.batch != 1:
                 raise RuntimeError("unexpected (T) plan structure")
@@ -93,7 +123,7 @@ class TriplesEngine(object):
         step = 1 if o > 1 else 0
         shifted = []
         for unit in ((step, 0, 0), (0, step, 0), (0, 0, step)):
-            shifted.append([plan(s, self._tensors(*unit), dcode)[0].desc for s in _STATEMENTS])
+            shifted.append([plan(s, self._tensors(*unit), dcode, prefer_flat=pf)[0].desc for s in stm])
         for n, L in enumerate(base):
             d0 = L[0].desc
             fields = _ptr_fields(d0)
@@ -105,9 +135,19 @@ class TriplesEngine(object):
         self._keep = base
         self.itemsize = self.eng.t2.element_size()
 
-    def refresh_t2T(self):
-        o, v = self.eng.no, self.eng.nv
-        self.be.pair_combine(self.t2T, self.eng.t2, 0.0, 1.0, None, None, 0.0, o, v)
+    def refresh(self):
+        """The amplitude- (and, for CC3, intermediate-) dependent helper layouts of the W build."""
+        e, be = self.eng, self.be
+        o, v = e.no, e.nv
+        if self.plain:
+            be.permute4(self.VT, self.V.permute(0, 2, 1, 3))
+            be.permute4(self.OT, self.O.permute(0, 1, 3, 2))
+            be.permute4(self.tM, e.t2.permute(0, 2, 3, 1))
+            be.permute4(self.tMT, e.t2.permute(0, 3, 2, 1))
+        else:
+            be.pair_combine(self.t2T, e.t2, 0.0, 1.0, None, None, 0.0, o, v)
+
+    refresh_t2T = refresh
 
     def _launch_pair(self, i, j, nk=None):
         """W[k] for k = 0..nk-1 (default: 0..j) of the pair (i, j): three batched contractions."""
@@ -155,7 +195,7 @@ class TriplesEngine(object):
             return 0.0, torch.zeros(0, dtype=torch.float64), trip
         ijk = torch.tensor(trip, dtype=torch.int32).reshape(-1).to(be.device)
         et = be.zeros((len(trip),), torch.float64)
-        be.pair_combine(self.t2T, eng.t2, 0.0, 1.0, None, None, 0.0, o, v)
+        self.refresh()
         fov = eng.F[:o, o:]
         pos = 0
         for (i, j) in pairs:

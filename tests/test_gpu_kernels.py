@@ -57,6 +57,17 @@ CASES = [
     # plain K-contiguous matrices with M = 256 / 1024: the 128-row TMA-staged kernel, contract_f64_tma_kernel<8>
     ("C[mn] = A[mk]*B[nk]", dict(A=(256, 520), B=(390, 520), C=(256, 390))),
     ("C[mn] = A[mk]*B[nk] + A2[ml]*B2[nl]", dict(A=(1024, 200), B=(2100, 200), A2=(1024, 72), B2=(2100, 72), C=(1024, 2100))),
+    # M = 900 (= o^2 at o = 30): the 48-row tile, TMA-staged kernel <3> and the cp.async kernel <.,3> (row-contiguous operands)
+    ("C[mn] = A[mk]*B[nk]", dict(A=(900, 300), B=(520, 300), C=(900, 520))),
+    ("C[mn] = A[km]*B[kn]", dict(A=(2000, 900), B=(2000, 260), C=(900, 260))),
+    # batched plain matrices (batch index on A, B and C; on A and C only): the TMA kernel with 3-D tensor maps,
+    # ragged K (70 = 4 k-tiles + 6: partial last k-tile, zero k-steps skipped), two segments
+    ("C[kmn] = A[kmp]*B[knp]", dict(A=(5, 300, 70), B=(5, 260, 70), C=(5, 300, 260))),
+    ("C[kmn] = A[kmp]*B[knp] - 0.5*A2[kmq]*B2[nq]",
+     dict(A=(3, 320, 150), B=(3, 130, 150), A2=(3, 320, 30), B2=(130, 30), C=(3, 320, 130))),
+    # short K, M = v^2 with v = 250 rows (128-row tiles by padding): rerouted to the kernel with epilogue warps
+    ("C[abc] = A[eab]*B[ce] - A3[mc]*B3[mab]",
+     dict(A=(250, 250, 250), B=(250, 250), A3=(9, 250), B3=(9, 250, 250), C=(250, 250, 250))),
 ]
 
 
