@@ -1331,6 +1331,325 @@ contract_f64_tma_kernel(const __grid_constant__ DParams p, const __grid_constant
     }   // tile loop
 }
 
+// ---- TMA-staged variant with an asynchronous epilogue ------------------------------------------------
+// contract_f64_tma_kernel plus the fourth warpgroup of contract_f64_wse_kernel: one TMA producer thread, 8 DMMA
+// consumer warps, 4 epilogue warps.  For short contractions over plain matrices with many tiles per SM - the (T) /
+// CC3 W build over the helper layouts of triples_engine.py: K = 2(v + o), three launches of which two accumulate
+// into W (beta = 1, strided output) - the consumers' own epilogue left the tensor pipe idle 11 % (beta = 0) to
+// 22 % (beta = 1) of the launch (15.9 / 18.2 ms per launch at v = 250).  The consumers dump scale * acc into a
+// staging tile and start the next tile at once; the epilogue warps apply alpha / beta with their lanes along the
+// contiguous output direction.  64 / 80 / 96-row tiles only (the staging tile of 128 rows does not fit next to
+// the ring); 4 stages; no split-K, no D operand.
+// fire-and-forget FP64 add in L2 (each output element receives one add per launch: the result is deterministic)
+__device__ __forceinline__ void red_add_f64(double* addr, double v) {
+    asm volatile("red.global.add.f64 [%0], %1;\n" ::"l"(addr), "d"(v) : "memory");
+}
+
+constexpr int TMAE_THREADS = NCONS + 128 + NEPI, TMAE_STAGES = 4;
+
+template <int MI, bool BATCHED>
+__global__ void __launch_bounds__(TMAE_THREADS, 1)
+contract_f64_tmae_kernel(const __grid_constant__ DParams p, const __grid_constant__ TmaMaps maps) {
+    constexpr int BM = 16 * MI;
+    constexpr int A_STAGE = BM * BK, B_STAGE = BN * BK;       // doubles; rows of 128 bytes
+    constexpr int S = TMAE_STAGES;
+
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const unsigned raw_s = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned pad = (1024u - (raw_s & 1023u)) & 1023u;
+    double* sA = reinterpret_cast<double*>(smem_raw + pad);
+    double* sB = sA + S * A_STAGE;
+    double* stg = sB + S * B_STAGE;                                                       // [BM][SPITCH]
+    unsigned long long* bars = reinterpret_cast<unsigned long long*>(stg + BM * SPITCH);  // full[S], empty[S], staged, drained
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned gm = (p.M + BM - 1) / BM, gn = (p.N + BN - 1) / BN;
+    const long long ntiles = (long long)gm * gn * p.nz;       // splits == 1 (host): z is the batch index
+    const int nkt = p.total_kt;
+
+    const unsigned sA_s = (unsigned)__cvta_generic_to_shared(sA);
+    const unsigned sB_s = (unsigned)__cvta_generic_to_shared(sB);
+    const unsigned full_s = (unsigned)__cvta_generic_to_shared(bars);
+    const unsigned empty_s = full_s + 8 * S;
+    const unsigned staged_s = empty_s + 8 * S, drained_s = staged_s + 8;
+
+    if (tid == 0) {
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+            mbar_init(full_s + 8 * s, 1);
+            mbar_init(empty_s + 8 * s, NCONS / 32);
+        }
+        mbar_init(staged_s, NCONS / 32);
+        mbar_init(drained_s, NEPI / 32);
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    }
+    __syncthreads();
+
+    auto seg_of = [&](int kt) {
+        int s = 0;
+#pragma unroll
+        for (int q = 1; q < PCCB_MAX_SEGMENTS; ++q)
+            if (q < p.nseg && kt >= p.seg[q].kt_begin) s = q;
+        return s;
+    };
+
+    // Tile order: groups of gridDim.x consecutive m-tiles outermost; inside a group n, then the batch index, vary
+    // while every persistent CTA keeps ITS m-tile.  The A rows of a group (148 x 96 rows x K: tens of MB) stay in
+    // L2 - and a CTA's own A tile mostly in its L1 - across the gn * batch tiles that share them.  With m fastest
+    // over the whole M (the order of the other kernels) the (T) W build re-streamed its k-independent A operands
+    // from DRAM for every (n, k): 16.9 GB read per launch for 0.25 GB of operands.
+    const long long per_group = (long long)gridDim.x * gn * p.nz;
+    auto decode = [&](long long tile, unsigned& mx, unsigned& nx, int& z) {
+        const long long mg = tile / per_group, rem = tile - mg * per_group;
+        const long long left = (long long)gm - mg * gridDim.x;
+        const long long gsz = left < (long long)gridDim.x ? left : (long long)gridDim.x;
+        mx = (unsigned)(mg * gridDim.x + rem % gsz);
+        const long long rest = rem / gsz;
+        nx = (unsigned)(rest % gn);
+        z = (int)(rest / gn);
+    };
+
+    if (warp >= (NCONS + 128) / 32) {
+        // ================================ epilogue warps ================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 104;\n");     // 256 x 184 + 128 x 40 + 128 x 104 = 64 K registers
+        const int ew = (tid - (NCONS + 128)) >> 5;
+        // The FP64 pipe belongs to the consumers' DMMAs (94 % busy): an epilogue warp that has to squeeze a DMUL /
+        // DFMA per element into its gaps drains a tile more slowly than the consumers produce one (beta = 1 launches
+        // ran at 79 % tensor activity).  So alpha is folded into the staged values by the consumers, beta = 0 is a plain
+        // copy and beta = 1 an L2 add (red.global.add.f64); only a general beta does arithmetic here.
+        const int mode = p.beta == 0.0 ? 0 : (p.beta == 1.0 ? 1 : 2);
+        const bool along_m = p.cm.s_lo == 1 && p.cn.s_lo != 1;     // lanes along the contiguous output direction
+        const double beta = p.beta;
+        unsigned lt = 0;
+#pragma unroll 1
+        for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+            unsigned mx, nx;
+            int z;
+            decode(tile, mx, nx, z);
+            const unsigned m0 = mx * BM, n0 = nx * BN;
+            const int mlim = (int)min((unsigned)BM, p.M - m0), nlim = (int)min((unsigned)BN, p.N - n0);
+            double* Cb = p.C + (long long)z * p.c_batch;
+            mbar_wait(staged_s, lt & 1);
+            if (!along_m) {
+                constexpr int CP = BN / 32, RU = 4;
+                long long co[CP];
+#pragma unroll
+                for (int q = 0; q < CP; ++q) {
+                    const int c = q * 32 + lane;
+                    co[q] = c < nlim ? didx_off(p.cn, n0 + c) : -1;
+                }
+                const double* sl = stg + lane;
+#pragma unroll 1
+                for (int r0 = ew; r0 < mlim; r0 += 4 * RU) {
+                    double v[RU][CP];
+                    double* crow[RU];
+#pragma unroll
+                    for (int u = 0; u < RU; ++u) {
+                        const int r = r0 + 4 * u;
+                        crow[u] = nullptr;
+                        if (r < mlim) {
+                            crow[u] = Cb + didx_off(p.cm, m0 + r);
+#pragma unroll
+                            for (int q = 0; q < CP; ++q) {
+                                double x = sl[r * SPITCH + q * 32];
+                                if (mode == 2 && co[q] >= 0) x += beta * crow[u][co[q]];
+                                v[u][q] = x;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < RU; ++u)
+                        if (crow[u]) {
+#pragma unroll
+                            for (int q = 0; q < CP; ++q)
+                                if (co[q] >= 0) {
+                                    if (mode == 1) red_add_f64(crow[u] + co[q], v[u][q]);
+                                    else crow[u][co[q]] = v[u][q];
+                                }
+                        }
+                }
+            } else {
+                constexpr int RP = (BM + 31) / 32, CU = 4;
+                long long ro[RP];
+#pragma unroll
+                for (int q = 0; q < RP; ++q) {
+                    const int r = q * 32 + lane;
+                    ro[q] = r < mlim ? didx_off(p.cm, m0 + r) : -1;
+                }
+                const double* sl = stg + lane * SPITCH;
+#pragma unroll 1
+                for (int c0 = ew; c0 < nlim; c0 += 4 * CU) {
+                    double v[CU][RP];
+                    double* ccol[CU];
+#pragma unroll
+                    for (int u = 0; u < CU; ++u) {
+                        const int c = c0 + 4 * u;
+                        ccol[u] = nullptr;
+                        if (c < nlim) {
+                            ccol[u] = Cb + didx_off(p.cn, n0 + c);
+#pragma unroll
+                            for (int q = 0; q < RP; ++q) {
+                                double x = 0.0;
+                                if (ro[q] >= 0) {
+                                    x = sl[q * 32 * SPITCH + c];
+                                    if (mode == 2) x += beta * ccol[u][ro[q]];
+                                }
+                                v[u][q] = x;
+                            }
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < CU; ++u)
+                        if (ccol[u]) {
+#pragma unroll
+                            for (int q = 0; q < RP; ++q)
+                                if (ro[q] >= 0) {
+                                    if (mode == 1) red_add_f64(ccol[u] + ro[q], v[u][q]);
+                                    else ccol[u][ro[q]] = v[u][q];
+                                }
+                        }
+                }
+            }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(drained_s);
+        }
+        return;
+    }
+
+    if (warp >= NCONS / 32) {
+        // ================================ TMA producer (one thread) ================================
+        asm volatile("setmaxnreg.dec.sync.aligned.u32 40;\n");
+        if (warp == NCONS / 32 && lane == 0) {
+            unsigned g = 0;
+#pragma unroll 1
+            for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
+                unsigned mx, nx;
+                int batch;
+                decode(tile, mx, nx, batch);
+                const unsigned m0 = mx * BM, n0 = nx * BN;
+#pragma unroll 1
+                for (int it = 0; it < nkt; ++it, ++g) {
+                    const int s = seg_of(it);
+                    const int st = g % S;
+                    if (g >= S) mbar_wait_relaxed(empty_s + 8 * st, ((g - S) / S) & 1);
+                    const int k0 = (it - p.seg[s].kt_begin) * BK;
+                    const unsigned bar = full_s + 8 * st;
+                    mbar_expect_tx(bar, (unsigned)((A_STAGE + B_STAGE) * sizeof(double)));
+                    if (BATCHED) {
+                        const int bz = p.seg[s].bz;
+                        tma_load_3d(sA_s + st * (A_STAGE * 8), &maps.a[s], k0, (int)m0, (bz & 1) ? batch : 0, bar);
+                        tma_load_3d(sB_s + st * (B_STAGE * 8), &maps.b[s], k0, (int)n0, (bz & 2) ? batch : 0, bar);
+                    } else {
+                        tma_load_2d(sA_s + st * (A_STAGE * 8), &maps.a[s], k0, (int)m0, bar);
+                        tma_load_2d(sB_s + st * (B_STAGE * 8), &maps.b[s], k0, (int)n0, bar);
+                    }
+                }
+            }
+        }
+        return;
+    }
+
+    // ================================ consumers ================================
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 184;\n");
+    const int wm = warp >> 2, wn = warp & 3;
+    const int frow = lane >> 2, fk = lane & 3;
+    const int pf = ((frow & 3) << 1) | (frow >> 2);          // tile row (within its 8-row group) of fragment row frow
+    int koff[BK / 4];
+#pragma unroll
+    for (int ks = 0; ks < BK / 4; ++ks) koff[ks] = ((((2 * ks) + (fk >> 1)) ^ pf) << 1) | (fk & 1);
+    const int arow = (wm * (8 * MI) + pf) * BK, brow = (wn * 32 + pf) * BK;
+    // accumulator (frow, 2 fk + e) of an 8x8 block is tile element (perm(frow), perm(2 fk + e))
+    const int pc0 = (((2 * fk) & 3) << 1) | ((2 * fk) >> 2), pc1 = (((2 * fk + 1) & 3) << 1) | ((2 * fk + 1) >> 2);
+
+    unsigned g0 = 0, lt = 0;
+#pragma unroll 1
+    for (long long tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++lt) {
+    double acc[MI][4][2];
+#pragma unroll
+    for (int i = 0; i < MI; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j][0] = acc[i][j][1] = 0.0;
+
+    double a[MI], b[4], bnx[4];
+    mbar_wait(full_s + 8 * (g0 % S), (g0 / S) & 1);
+    const double* ap = sA + (g0 % S) * A_STAGE + arow;
+    const double* bp = sB + (g0 % S) * B_STAGE + brow;
+#pragma unroll
+    for (int i = 0; i < MI; ++i) a[i] = ap[i * 8 * BK + koff[0]];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) b[j] = bp[j * 8 * BK + koff[0]];
+
+    int seg_acc = -1;
+    double scale_acc = 1.0;
+#pragma unroll 1
+    for (int it = 0; it < nkt; ++it) {
+        const int st = (g0 + it) % S;
+        {
+            const int sgi = seg_of(it);
+            if (sgi != seg_acc) {
+                const double sc = p.seg[sgi].scale;
+                if (seg_acc >= 0 && sc != scale_acc) {
+                    const double r = scale_acc / sc;
+#pragma unroll
+                    for (int i = 0; i < MI; ++i)
+#pragma unroll
+                        for (int j = 0; j < 4; ++j) { acc[i][j][0] *= r; acc[i][j][1] *= r; }
+                }
+                seg_acc = sgi;
+                scale_acc = sc;
+            }
+        }
+        const double* an = ap;
+        const double* bn = bp;
+#pragma unroll
+        for (int ks = 0; ks < BK / 4; ++ks) {
+            const int nks = (ks + 1) % (BK / 4);
+            // after the last k-tile the "next" fragments are re-read from the current stage (valid shared memory,
+            // values unused): the fragment loads stay unconditional, so ptxas has no reason to predicate /
+            // duplicate the DMMAs around them (it did: 116 DMMAs per k-tile instead of 96, +50 % time)
+            if (ks == BK / 4 - 1 && it + 1 < nkt) {
+                const unsigned gn1 = g0 + it + 1;
+                mbar_wait(full_s + 8 * (gn1 % S), (gn1 / S) & 1);
+                an = sA + (gn1 % S) * A_STAGE + arow;
+                bn = sB + (gn1 % S) * B_STAGE + brow;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) bnx[j] = bn[j * 8 * BK + koff[nks]];
+#pragma unroll
+            for (int i = 0; i < MI; ++i) {
+#pragma unroll
+                for (int j = 0; j < 4; ++j) dmma884(acc[i][j][0], acc[i][j][1], a[i], b[j]);
+                a[i] = an[i * 8 * BK + koff[nks]];
+            }
+#pragma unroll
+            for (int j = 0; j < 4; ++j) b[j] = bnx[j];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(empty_s + 8 * st);
+        ap = an;
+        bp = bn;
+    }
+    g0 += nkt;
+
+    // ---- hand the tile to the epilogue warps -------------------------------------------------
+    if (lt > 0) mbar_wait(drained_s, (lt - 1) & 1);      // the previous tile has left the staging buffer
+    {
+        const double stage_scale = p.alpha * scale_acc;      // alpha applied here, on the consumers' own pipe slots
+        double* sp = stg + (wm * (8 * MI) + pf) * SPITCH + wn * 32;
+#pragma unroll
+        for (int i = 0; i < MI; ++i)
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                sp[i * 8 * SPITCH + j * 8 + pc0] = stage_scale * acc[i][j][0];
+                sp[i * 8 * SPITCH + j * 8 + pc1] = stage_scale * acc[i][j][1];
+            }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(staged_s);
+    }   // tile loop
+}
+
 // fixed-order reduction of the split-K partial tiles + epilogue
 __global__ void splitk_reduce_kernel(const __grid_constant__ DParams p, long long total) {
     const long long MN = (long long)p.M * p.N;
@@ -1583,6 +1902,34 @@ int launch_tma_kernel(pccb_ctx* ctx, const DParams& p, const TmaMaps& maps, long
     return PCCB_OK;
 }
 
+int choose_mi_epi(long long M);
+
+template <int MI>
+constexpr size_t smem_bytes_tmae() {
+    return (size_t)TMAE_STAGES * (16 * MI + BN) * BK * sizeof(double) + (size_t)(16 * MI) * SPITCH * sizeof(double) +
+           (2 * TMAE_STAGES + 2) * sizeof(unsigned long long) + 1024;
+}
+
+template <int MI, bool BATCHED>
+int launch_tmae_kernel(pccb_ctx* ctx, const DParams& p, const TmaMaps& maps, long long batch) {
+    constexpr int BM = 16 * MI;
+    constexpr size_t SMEM = smem_bytes_tmae<MI>();
+    static_assert(SMEM <= 232448, "staging tile + ring exceed the shared memory of an SM");
+    static bool attr_set = false;
+    if (!attr_set) {
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_f64_tmae_kernel<MI, BATCHED>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                            (int)SMEM));
+        attr_set = true;
+    }
+    DParams q = p;
+    q.nz = (int)batch;
+    const long long ntiles = (long long)((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN) * q.nz;
+    const unsigned nctas = (unsigned)(ntiles < ctx->sm_count ? ntiles : ctx->sm_count);
+    contract_f64_tmae_kernel<MI, BATCHED><<<nctas, TMAE_THREADS, SMEM, ctx->stream>>>(q, maps);
+    PCCB_CHECK_LAUNCH(ctx, "contract_f64_tmae_kernel");
+    return PCCB_OK;
+}
+
 // returns 1 when the TMA kernel was launched, 0 when the contraction is not eligible, < 0 on error
 int try_tma(pccb_ctx* ctx, const DParams& p_in, const pccb_contraction* d, int mi) {
     static const bool use_tma = [] { const char* e = getenv("PCCB_TMA"); return e ? atoi(e) != 0 : true; }();
@@ -1597,6 +1944,15 @@ int try_tma(pccb_ctx* ctx, const DParams& p_in, const pccb_contraction* d, int m
         if (batched && (g.a_batch < 0 || g.b_batch < 0 || (g.a_batch & 1) || (g.b_batch & 1))) return 0;
         g.bz = (g.a_batch > 0 ? 1 : 0) | (g.b_batch > 0 ? 2 : 0);
     }
+    // short contractions (8..64 k-tiles) with many tiles per SM: the variant with epilogue warps and the
+    // L2-friendly tile order, on the best of the 64 / 80 / 96-row tiles (PCCB_TMAE=0 disables)
+    static const bool use_tmae = [] { const char* e = getenv("PCCB_TMAE"); return e ? atoi(e) != 0 : true; }();
+    bool epi = false;
+    if (use_tmae && mi >= 4 && p.splits == 1 && !p.D && p.total_kt >= WSE_MIN_KT && p.total_kt <= WSE_MAX_KT) {
+        const int best = choose_mi_epi(p.M);
+        const long long t2 = (((long long)p.M + 16 * best - 1) / (16 * best)) * (((long long)p.N + BN - 1) / BN) * d->batch;
+        if (t2 >= 2ll * ctx->sm_count) { mi = best; epi = true; }
+    }
     TmaMaps maps;
     memset(&maps, 0, sizeof(maps));
     for (int s = 0; s < p.nseg; ++s) {
@@ -1610,7 +1966,21 @@ int try_tma(pccb_ctx* ctx, const DParams& p_in, const pccb_contraction* d, int m
         }
     }
     int rc;
-    if (batched) {
+    if (epi) {
+        if (batched) {
+            switch (mi) {
+                case 4: rc = launch_tmae_kernel<4, true>(ctx, p, maps, d->batch); break;
+                case 5: rc = launch_tmae_kernel<5, true>(ctx, p, maps, d->batch); break;
+                default: rc = launch_tmae_kernel<6, true>(ctx, p, maps, d->batch); break;
+            }
+        } else {
+            switch (mi) {
+                case 4: rc = launch_tmae_kernel<4, false>(ctx, p, maps, d->batch); break;
+                case 5: rc = launch_tmae_kernel<5, false>(ctx, p, maps, d->batch); break;
+                default: rc = launch_tmae_kernel<6, false>(ctx, p, maps, d->batch); break;
+            }
+        }
+    } else if (batched) {
         switch (mi) {
             case 3: rc = launch_tma_kernel<3, true>(ctx, p, maps, d->batch); break;
             case 4: rc = launch_tma_kernel<4, true>(ctx, p, maps, d->batch); break;
@@ -1628,6 +1998,23 @@ int try_tma(pccb_ctx* ctx, const DParams& p_in, const pccb_contraction* d, int m
         }
     }
     return rc == PCCB_OK ? 1 : rc;
+}
+
+// tile height for the kernels with epilogue warps (64 / 80 / 96 rows): padded rows weighted like choose_mi
+int choose_mi_epi(long long M) {
+    // tuning hook: PCCB_EPI_MI=<4|5|6> forces the height
+    static const int forced = [] { const char* e = getenv("PCCB_EPI_MI"); return e ? atoi(e) : 0; }();
+    if (forced >= 4 && forced <= 6) return forced;
+    static const int cand[] = {6, 5, 4};
+    static const double eff[7] = {0, 0, 0, 0, 0.97, 0.985, 0.99};
+    int best = 6;
+    double best_cost = 1e300;
+    for (int c : cand) {
+        const long long b = 16 * c;
+        const double cost = (double)(((M + b - 1) / b) * b) / eff[c];
+        if (cost < best_cost) { best_cost = cost; best = c; }
+    }
+    return best;
 }
 
 // rows per CTA tile: minimise padded rows, prefer the taller tile on ties (more operand reuse)
@@ -1771,12 +2158,7 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
         // beta = 0 / 1, profiles/r02_ncu_triples_w_o30v250.txt).  Take the best of the three heights instead.
         static const bool wse_mi = [] { const char* e = getenv("PCCB_WSE_MI"); return e ? atoi(e) != 0 : true; }();
         if (wse_mi && (mi == 8 || mi == 3) && splits == 1 && !p.D && kt >= WSE_MIN_KT && kt <= WSE_MAX_KT) {
-            int best = 0;
-            long long best_rows = 0;
-            for (int c : {6, 5, 4}) {
-                const long long b = 16 * c, rows = ((d->M + b - 1) / b) * b;
-                if (!best || rows < best_rows) { best = c; best_rows = rows; }
-            }
+            const int best = choose_mi_epi(d->M);
             const long long t2 = ((d->M + 16 * best - 1) / (16 * best)) * gn * d->batch;
             if (t2 >= 2ll * ctx->sm_count) mi = best;
         }
