@@ -238,12 +238,18 @@ class ccwfn(object):
         energy and (``extrapolate``) the DIIS step.  Returns (ecc, rms).  This is the unit bench.py
         times as one step."""
         eng = self.engine
+        ev = getattr(self, "phase_events", None)     # bench.py: list receiving 4 CUDA events per step
+        mark = (lambda: None) if ev is None else (lambda: (ev.append(torch.cuda.Event(enable_timing=True)), ev[-1].record()))
+        mark()
         eng.sync_amplitudes()
         eng.residuals(symmetrize=False)
+        mark()
         rms2, ecc = eng.update_energy()          # one fused pass; split over the ranks by (i,j) blocks
         rms = np.sqrt(rms2)
+        mark()
         if extrapolate:
             self._diis_step(diis, niter, start_diis)
+        mark()
         return ecc, rms
 
     def _diis_step(self, diis, niter, start_diis):
