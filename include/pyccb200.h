@@ -178,6 +178,10 @@ int pccb_cc_energy_static(pccb_ctx* ctx, int dtype, const void* fov_dev, int64_t
 
 /* DIIS building blocks (pycc/utils.py:26-46, 108-133); accumulation is FP64 for both dtypes. */
 int pccb_dot(pccb_ctx* ctx, int dtype, const void* x_dev, const void* y_dev, int64_t n, double* out_host);
+/* out_host[k] = <x, ys[k]>, k < m <= 16, in ONE pass over x and one host synchronisation: the new row of the DIIS
+ * Gram matrix (pycc/utils.py:108-112 fills B[a,b] with one np.dot per entry). */
+int pccb_dot_many(pccb_ctx* ctx, int dtype, const void* x_dev, const void* const* ys_dev_hostarray, int m, int64_t n,
+                  double* out_host);
 int pccb_axpby(pccb_ctx* ctx, int dtype, void* out_dev, double a, const void* x_dev, double b, const void* y_dev,
                int64_t n); /* out = a*x + b*y (y_dev may be NULL) */
 int pccb_lincomb(pccb_ctx* ctx, int dtype, void* out_dev, const void* const* vecs_dev_hostarray,

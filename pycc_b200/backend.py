@@ -144,6 +144,18 @@ class CudaBackend(object):
         self._check(self.lib.pccb_dot(self.h, dtype_code(x), x.data_ptr(), y.data_ptr(), x.numel(), C.byref(out)))
         return out.value
 
+    def dot_many(self, x, ys):
+        """[<x, y> for y in ys] in one pass over x (at most 16 vectors per launch)."""
+        out = []
+        for k0 in range(0, len(ys), 16):
+            grp = ys[k0:k0 + 16]
+            m = len(grp)
+            ptrs = (C.c_void_p * m)(*[y.data_ptr() for y in grp])
+            res = (C.c_double * m)()
+            self._check(self.lib.pccb_dot_many(self.h, dtype_code(x), x.data_ptr(), ptrs, m, x.numel(), res))
+            out += [res[k] for k in range(m)]
+        return out
+
     def axpby(self, out, a, x, b=0.0, y=None):
         self._check(self.lib.pccb_axpby(self.h, dtype_code(out), out.data_ptr(), a, x.data_ptr(), b,
                                         None if y is None else y.data_ptr(), out.numel()))

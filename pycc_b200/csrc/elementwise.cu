@@ -271,6 +271,39 @@ __global__ void lincomb_vec_kernel(T* __restrict__ out, const __grid_constant__ 
     }
 }
 
+// m dot products <x, y_k> in one pass: x is read once, partials[k * gridDim.x + block] (DIIS: the new row of the
+// Gram matrix, utils.py:108-112, in one launch and one host synchronisation instead of m)
+template <typename T, int VEC>
+__global__ void dot_many_kernel(const T* __restrict__ x, const __grid_constant__ LincombArgs<T> ys, long long n,
+                                double* __restrict__ partials) {
+    using P = Pack<T, VEC>;
+    const long long nvec = n / VEC, stride = (long long)gridDim.x * blockDim.x;
+    double acc[MAX_LINCOMB];
+#pragma unroll
+    for (int k = 0; k < MAX_LINCOMB; ++k) acc[k] = 0.0;
+    const P* xp = reinterpret_cast<const P*>(x);
+    for (long long q = (long long)blockIdx.x * blockDim.x + threadIdx.x; q < nvec; q += stride) {
+        const P a = xp[q];
+#pragma unroll
+        for (int k = 0; k < MAX_LINCOMB; ++k)
+            if (k < ys.n) {
+                const P b = reinterpret_cast<const P*>(ys.v[k])[q];
+#pragma unroll
+                for (int e = 0; e < VEC; ++e) acc[k] += (double)a.v[e] * (double)b.v[e];
+            }
+    }
+    for (long long idx = nvec * VEC + (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < n; idx += stride)
+#pragma unroll
+        for (int k = 0; k < MAX_LINCOMB; ++k)
+            if (k < ys.n) acc[k] += (double)x[idx] * (double)ys.v[k][idx];
+#pragma unroll
+    for (int k = 0; k < MAX_LINCOMB; ++k)
+        if (k < ys.n) {          // uniform over the block
+            const double r = block_sum(acc[k]);
+            if (threadIdx.x == 0) partials[(size_t)k * gridDim.x + blockIdx.x] = r;
+        }
+}
+
 __host__ bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 // ---- fused amplitude update + increment norm + energy ----------------------------------------------
@@ -737,6 +770,31 @@ int lincomb_t(pccb_ctx* ctx, void* out, const void* const* vecs, const double* c
     else lincomb_vec_kernel<T, 1><<<g, 256, 0, ctx->stream>>>((T*)out, a, n);
     PCCB_CHECK_LAUNCH(ctx, "lincomb_kernel");
     return PCCB_OK;
+}
+
+template <typename T>
+int dot_many_t(pccb_ctx* ctx, const void* x, const void* const* ys, int m, int64_t n, double* out_host) {
+    constexpr int V = 16 / sizeof(T);
+    const int g = grid_for((n + V - 1) / V, RED_THREADS, 148 * 4);
+    int rc = pccb_ensure_partials(ctx, (size_t)g * m + 64);
+    if (rc) return rc;
+    LincombArgs<T> a;
+    a.n = m;
+    bool al = aligned16(x);
+    for (int k = 0; k < m; ++k) { a.v[k] = (const T*)ys[k]; a.c[k] = 0.0; al = al && aligned16(ys[k]); }
+    if (al) dot_many_kernel<T, V><<<g, RED_THREADS, 0, ctx->stream>>>((const T*)x, a, n, ctx->partial_dev);
+    else dot_many_kernel<T, 1><<<g, RED_THREADS, 0, ctx->stream>>>((const T*)x, a, n, ctx->partial_dev);
+    PCCB_CHECK_LAUNCH(ctx, "dot_many_kernel");
+    return finish_reduction(ctx, g, m, out_host);
+}
+
+extern "C" int pccb_dot_many(pccb_ctx* ctx, int dtype, const void* x_dev, const void* const* ys_dev_hostarray, int m,
+                             int64_t n, double* out_host) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, x_dev && ys_dev_hostarray && out_host && m >= 1 && m <= MAX_LINCOMB && n > 0,
+                 "pccb_dot_many: bad arguments (m=%d)", m);
+    DISPATCH_DTYPE(ctx, dtype, dot_many_t<double>(ctx, x_dev, ys_dev_hostarray, m, n, out_host),
+                   dot_many_t<float>(ctx, x_dev, ys_dev_hostarray, m, n, out_host));
 }
 
 extern "C" int pccb_dot(pccb_ctx* ctx, int dtype, const void* x_dev, const void* y_dev, int64_t n, double* out_host) {

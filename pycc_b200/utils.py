@@ -133,7 +133,14 @@ class helper_diis(object):
         self.be.bind_stream()
         # Gram entries not seen before (in steady state: the m products with the newest error vector)
         missing = [(p, q) for p in range(m) for q in range(p, m) if (self._ids[p], self._ids[q]) not in self._gram]
-        vals = [self.be.dot(self.diis_errors[p], self.diis_errors[q]) for (p, q) in missing]
+        # grouped by their second vector: in steady state ALL missing entries pair the newest error vector with the
+        # others, i.e. one pccb_dot_many launch and one host synchronisation per DIIS step
+        vals_by = {}
+        for q in sorted(set(q for (_, q) in missing)):
+            ps = [p for (p, qq) in missing if qq == q]
+            for p, x in zip(ps, self.be.dot_many(self.diis_errors[q], [self.diis_errors[p] for p in ps])):
+                vals_by[(p, q)] = x
+        vals = [vals_by[pq] for pq in missing]
         if self.comm is not None and vals:
             vals = self.comm.allreduce_scalars(vals)      # partial dot products of the slices
         for (p, q), x in zip(missing, vals):

@@ -144,6 +144,9 @@ class InterpBackend(object):
     def dot(self, x, y):
         return float((x.double().reshape(-1) * y.double().reshape(-1)).sum())
 
+    def dot_many(self, x, ys):
+        return [self.dot(x, y) for y in ys]
+
     def axpby(self, out, a, x, b=0.0, y=None):
         out.copy_(a * x if y is None else a * x + b * y)
 

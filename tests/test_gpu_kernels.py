@@ -303,3 +303,20 @@ def test_contract_f32_tcgen05_vs_einsum(be, case):
     assert ((got2 - (ref + C0.double())).abs() <= tol).all()
     assert ((got1 - got_sync).abs() <= tol).all()
     assert be.launch_count() - n0 == 2          # one launch each: no split-K reduction, i.e. not the mma.sync path
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_dot_many_vs_dot(be, dtype):
+    """pccb_dot_many (one pass, one synchronisation: the new DIIS Gram row) against pccb_dot entry by entry and
+    an FP64 torch dot; odd length (scalar tail) and an unaligned view (VEC = 1 path)."""
+    g = torch.Generator(device="cpu").manual_seed(5)
+    n = 1_000_003
+    x = torch.randn(n + 1, generator=g, dtype=torch.float64).to(dtype).to(be.device)
+    ys = [torch.randn(n + 1, generator=g, dtype=torch.float64).to(dtype).to(be.device) for _ in range(9)]
+    for off in (0, 1):
+        xv, yv = x[off:off + n], [y[off:off + n] for y in ys]
+        got = be.dot_many(xv, yv)
+        for k, y in enumerate(yv):
+            ref = float((xv.double() * y.double()).sum())
+            assert abs(got[k] - ref) <= 1e-9 * n ** 0.5
+            assert abs(got[k] - be.dot(xv, y)) <= 1e-9 * n ** 0.5
