@@ -71,6 +71,28 @@ class ccwfn(object):
                     time_init=time.time())
         return self
 
+    @classmethod
+    def from_factor(cls, F, B, no, eref=0.0, **kwargs):
+        """psi4-free constructor from a density-fitting / Cholesky factor B[Q,n,n] in the MO basis,
+        (pq|rs) = sum_Q B[Q,p,q] B[Q,r,s]: every rank forms the six blocks - its own rows of <ab|ef> / <mb|ef> only -
+        on the device (hamiltonian.blocks_from_factor); no n^4 array exists anywhere."""
+        self = object.__new__(cls)
+        n = F.shape[0]
+        self._setup(F, ("factor", B), int(no), int(n - no), kwargs, eref=eref, nfzc=0, ref=None, C=None,
+                    time_init=time.time())
+        return self
+
+    @classmethod
+    def from_ao(cls, Fao, ao_eri, C, no, eref=0.0, **kwargs):
+        """psi4-free constructor from AO-basis integrals: Fock matrix Fao[mu,nu], two-electron integrals in
+        chemists' order ao_eri[mu,nu,la,si] = (mu nu|la si), MO coefficients C[mu,p] (pycc/hamiltonian.py:32-38
+        without MintsHelper: hamiltonian.mo_transform, four pccb_contract launches)."""
+        self = object.__new__(cls)
+        nmo = C.shape[1]
+        self._setup(None, ("ao", Fao, ao_eri, C), int(no), int(nmo - no), kwargs, eref=eref, nfzc=0, ref=None, C=C,
+                    time_init=time.time())
+        return self
+
     # -----------------------------------------------------------------------------------------
     def _setup(self, F, ERI, no, nv, kwargs, eref, nfzc, ref, C, time_init):
         model = kwargs.pop('model', 'CCSD').upper()
@@ -153,7 +175,11 @@ class ccwfn(object):
         # engine-only kwarg: keep every row of <mb|ef> on each rank (needed by HBAR / Lambda with group=...)
         full_ovvv = bool(kwargs.pop('full_ovvv', False))
         keep_ovvv = model in ('CCSD(T)', 'CC3') or self.comm.world == 1 or full_ovvv
-        if isinstance(ERI, dict):
+        if isinstance(ERI, tuple) and ERI[0] == "factor":
+            self.H = Hamiltonian.from_factor(F, ERI[1], no, backend, dtype, vslice, keep_ovvv)
+        elif isinstance(ERI, tuple) and ERI[0] == "ao":
+            self.H = Hamiltonian.from_ao(ERI[1], ERI[2], ERI[3], no, backend, dtype, vslice, keep_ovvv)
+        elif isinstance(ERI, dict):
             self.H = Hamiltonian.from_blocks(F, ERI, no, backend.device, dtype, vslice, keep_ovvv)
         else:
             if tuple(ERI.shape) != (no + nv,) * 4:

@@ -129,3 +129,94 @@ class Hamiltonian(object):
     @classmethod
     def from_full(cls, F, ERI, no, device, dtype=torch.float64, vslice=None, keep_full_ovvv=True):
         return cls.from_blocks(F, blocks_from_full(ERI, no), no, device, dtype, vslice, keep_full_ovvv)
+
+
+# ---- integral front end without psi4 ------------------------------------------
+# The reference builds  F = C^T Fa C  and  ERI = mo_eri(C, C, C, C).swapaxes(1, 2)  through psi4's MintsHelper
+# (pycc/hamiltonian.py:32-38).  Without psi4 the same arrays come from (a) AO-basis integrals and the MO
+# coefficients, by the O(n^5) quarter transformations, or (b) a density-fitting / Cholesky factor
+# B[Q,p,q], (pq|rs) = sum_Q B[Q,p,q] B[Q,r,s]; both run on the device as pccb_contract launches, and (b)
+# never forms an n^4 array: each rank manufactures only the blocks (and <ab|ef> / <mb|ef> rows) it owns.
+def _run(backend, stmt, tensors, dtype):
+    from . import _lib
+    from .dsl import TRef, plan
+    backend.bind_stream()
+    T = {k: TRef.of(t, k) for k, t in tensors.items()}
+    for L in plan(stmt, T, _lib.F64 if dtype == torch.float64 else _lib.F32):
+        backend.contract(L.desc)
+
+
+def blocks_from_factor(backend, B, no, dtype=torch.float64, vslice=None, keep_full_ovvv=True, row_chunk=None):
+    """The six stored Dirac blocks <pq|rs> = (pr|qs) = sum_Q B[Q,p,r] B[Q,q,s] from a factor B[Q,n,n] (symmetric
+    in its orbital indices), each as one pccb_contract launch per chunk of leading rows (``row_chunk`` bounds
+    nothing but the launch size: the blocks are written in place, no temporary).  ``vslice`` as in from_blocks."""
+    Bd = B.to(device=backend.device, dtype=dtype).contiguous() if isinstance(B, torch.Tensor) else \
+        torch.as_tensor(np.ascontiguousarray(B), dtype=dtype).to(backend.device)
+    n = Bd.shape[1]
+    nv = n - no
+    lo, hi = (0, nv) if vslice is None else vslice
+    sp = {"o": (0, no), "v": (no, n)}
+
+    def build(pattern, p_rng=None, q_rng=None):
+        rng = [sp[c] for c in pattern]
+        if p_rng is not None:
+            rng[0] = p_rng
+        if q_rng is not None:
+            rng[1] = q_rng
+        (p0, p1), (q0, q1), (r0, r1), (s0, s1) = rng
+        out = torch.empty((p1 - p0, q1 - q0, r1 - r0, s1 - s0), dtype=dtype, device=backend.device)
+        step = row_chunk or (p1 - p0)
+        for a in range(p0, p1, max(step, 1)):
+            b = min(p1, a + step)
+            _run(backend, "X[pqrs] = Y[Qpr]*Z[Qqs]",
+                 dict(X=out[a - p0:b - p0], Y=Bd[:, a:b, r0:r1], Z=Bd[:, q0:q1, s0:s1]), dtype)
+        return out
+
+    return {"oooo": build("oooo"), "ooov": build("ooov"), "oovv": build("oovv"), "ovov": build("ovov"),
+            "ovvv": build("ovvv", q_rng=None if keep_full_ovvv else (no + lo, no + hi)),
+            "vvvv": build("vvvv", p_rng=(no + lo, no + hi), )}
+
+
+def mo_transform(backend, Fao, ao_eri, C, dtype=torch.float64):
+    """F = C^T Fa C and the Dirac array ERI[p,q,r,s] = <pq|rs> = (pr|qs) from AO-basis integrals in chemists'
+    order ao_eri[mu,nu,la,si] = (mu nu|la si) and MO coefficients C[mu,p]: what MintsHelper.mo_eri(C,C,C,C)
+    .swapaxes(1,2) returns (pycc/hamiltonian.py:36-38), as four quarter transformations = four pccb_contract
+    launches.  The result is a permuted VIEW of the chemists'-order MO tensor, like the reference's."""
+    dev = backend.device
+    to = lambda x: (x if isinstance(x, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(x))).to(device=dev, dtype=dtype).contiguous()
+    Fao, g, C = to(Fao), to(ao_eri), to(C)
+    nao, nmo = C.shape
+    E = lambda *s: torch.empty(s, dtype=dtype, device=dev)
+    h = E(nao, nmo)
+    F = E(nmo, nmo)
+    _run(backend, "h[mq] = Fa[mn]*C[nq]", dict(h=h, Fa=Fao, C=C), dtype)
+    _run(backend, "F[pq] = C[mp]*h[mq]", dict(F=F, C=C, h=h), dtype)
+    t1, t2 = E(nmo, nao, nao, nao), E(nmo, nmo, nao, nao)
+    _run(backend, "t[pnls] = C[mp]*g[mnls]", dict(t=t1, C=C, g=g), dtype)
+    _run(backend, "t[pqls] = C[nq]*u[pnls]", dict(t=t2, C=C, u=t1), dtype)
+    del t1
+    t3 = E(nmo, nmo, nmo, nao)
+    _run(backend, "t[pqrs] = C[lr]*u[pqls]", dict(t=t3, C=C, u=t2), dtype)
+    del t2
+    mo = E(nmo, nmo, nmo, nmo)
+    _run(backend, "t[pqrs] = C[ms]*u[pqrm]", dict(t=mo, C=C, u=t3), dtype)
+    return F, mo.permute(0, 2, 1, 3)            # (pq|rs) chemists' -> <pr|qs>: ERI[p,q,r,s] = mo[p,r,q,s]
+
+
+def _from_factor(cls, F, B, no, backend, dtype=torch.float64, vslice=None, keep_full_ovvv=True):
+    """Hamiltonian from a DF / Cholesky factor B[Q,n,n] in the MO basis (never an n^4 array)."""
+    blocks = blocks_from_factor(backend, B, no, dtype, vslice, keep_full_ovvv, row_chunk=8)
+    n = blocks["oovv"].shape[2] + no
+    H = cls(cls._to_dev(F, backend.device, dtype), blocks, no, n - no, backend.device, dtype)
+    H.vslice = tuple(vslice) if vslice is not None else (0, n - no)
+    return H
+
+
+def _from_ao(cls, Fao, ao_eri, C, no, backend, dtype=torch.float64, vslice=None, keep_full_ovvv=True):
+    """Hamiltonian from AO-basis Fock / two-electron integrals and MO coefficients (small systems: n^4)."""
+    F, ERI = mo_transform(backend, Fao, ao_eri, C, dtype)
+    return cls.from_full(F, ERI, no, backend.device, dtype, vslice, keep_full_ovvv)
+
+
+Hamiltonian.from_factor = classmethod(_from_factor)
+Hamiltonian.from_ao = classmethod(_from_ao)

@@ -73,6 +73,12 @@ def test_golden_builder_api_and_operator(golden):
     from oracle import triples_oracle as ot
     from oracle.ccsd_oracle import Blocks
     assert np.abs(W.cpu().numpy() - ot.w_connected(Blocks(g.blocks), t2, g.no - 1, 1, 0)).max() < 1e-12
+    from pycc_b200.cctriples import t3d_ijk
+    D = t3d_ijk(o, v, g.no - 1, 1, 0, w.t1, w.t2, H.ERI[o, o, v, v], H.F, c, False)
+    assert np.abs(D.cpu().numpy() - ot.v_disconnected(F, Blocks(g.blocks), t1, t2, g.no - 1, 1, 0)).max() < 1e-12
+    Dd = t3d_ijk(o, v, g.no - 1, 1, 0, w.t1, w.t2, H.ERI[o, o, v, v], H.F, c, True)
+    den = ot.triples_denominator(F, g.no, g.no - 1, 1, 0)
+    assert np.abs(Dd.cpu().numpy() - ot.v_disconnected(F, Blocks(g.blocks), t1, t2, g.no - 1, 1, 0) / den).max() < 1e-11
 
 
 @pytest.mark.parametrize("no,nv,offdiag", [(8, 30, True), (10, 44, False), (7, 51, True)])
@@ -280,3 +286,13 @@ def test_amplitude_shard_roundtrip(golden):
     w.load_amplitude_shard(host)
     torch.cuda.synchronize()
     assert np.array_equal(w.t2.cpu().numpy(), g["gen_t2"]) and np.array_equal(w.t1.cpu().numpy(), g["gen_t1"])
+
+
+def test_integral_front_end():
+    """Hamiltonian.from_factor (DF block provider, per-rank rows) and from_ao (AO -> MO quarter transformations) on
+    the device, against numpy and the oracle (pycc/hamiltonian.py:26-39 without psi4)."""
+    from pycc_b200.backend import CudaBackend
+    from tests import frontend_checks as fc
+    be = CudaBackend()
+    fc.check_factor_blocks(be)
+    fc.check_ao_transform(be)

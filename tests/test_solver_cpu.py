@@ -144,3 +144,11 @@ def test_sp_mode_plain_matrix_ring_terms(golden, model):
     assert w.engine.sp_plain and any("t2sP" in L.text for L in w.engine.plans["r_T2"])
     assert np.abs(r2.double().numpy() - d2.numpy()).max() < 2e-6 * max(1.0, np.abs(d2.numpy()).max())
     assert np.abs(r1.double().numpy() - d1.numpy()).max() < 2e-6
+
+
+def test_integral_front_end_host_logic():
+    """from_factor / from_ao through the NumPy interpreter of the C-ABI descriptors."""
+    from tests.interp_backend import InterpBackend
+    from tests import frontend_checks as fc
+    fc.check_factor_blocks(InterpBackend())
+    fc.check_ao_transform(InterpBackend())
