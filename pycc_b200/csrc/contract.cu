@@ -12,7 +12,7 @@
 //   * CTA tile (16*MI) x 128 x 16 with MI in {1,2,3,4,5,6,8} chosen per launch to minimise padded
 //     rows (o^2 = 400 -> five 80-row tiles); 8 DMMA warps as 2(M) x 4(N), warp tile (8*MI) x 32:
 //     4*MI DMMA per MI+4 LDS.64, so the tensor pipe, not shared memory, is the limiter.
-//   * four kernels behind the one entry point (the first three persistent over output tiles):
+//   * five kernels behind the one entry point (all but the last persistent over output tiles):
 //       contract_f64_tma_kernel  plain 2-D operands (o^2 v^4 ladder, Wmnij, Zmbij, and the ring terms over
 //                                the engine's plain-matrix copies of the o^2 v^2 operands): one producer
 //                                thread issues cp.async.bulk.tensor (TMA) copies, 128-byte swizzle,
@@ -25,6 +25,10 @@
 //                                contractions (8..64 k-tiles: the (T) / CC3 W build): consumers dump
 //                                their accumulators to a staging tile and start the next tile at once;
 //                                zero-filled k-steps of segment tails are skipped;
+//       contract_f64_tmae_kernel plain operands, short K, optionally batched (3-D tensor maps): TMA producer + DMMA
+//                                consumers + epilogue warps, L2-friendly tile order (m-tile groups outermost); the
+//                                (T) / CC3 W build over the helper layouts of triples_engine.py: 94.5 % tensor activity
+//                                on all three launches (beta = 1 as red.global.add.f64);
 //       contract_f64_kernel      MI <= 2 (skinny, memory-bound launches): all warps load and
 //                                compute, two CTAs per SM.
 //     Stages are guarded by full/empty mbarriers; registers are re-balanced with setmaxnreg.
