@@ -67,11 +67,8 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
     __shared__ double sW[6][BRICK];
     __shared__ double sG[36][GBLK];       // [matrix * 6 + pair type][8][9]
     __shared__ double sred[16];
-    // blockIdx.x enumerates the canonical brick pairs TA >= TB: p = TA (TA + 1) / 2 + TB
-    int TAk = (int)((sqrt(8.0 * (double)blockIdx.x + 1.0) - 1.0) * 0.5);
-    while (TAk * (TAk + 1) / 2 > (int)blockIdx.x) --TAk;
-    while ((TAk + 1) * (TAk + 2) / 2 <= (int)blockIdx.x) ++TAk;
-    const int TBk = (int)blockIdx.x - TAk * (TAk + 1) / 2, t = blockIdx.y;
+    const int TBk = blockIdx.x, TAk = blockIdx.y, t = blockIdx.z;
+    if (TBk > TAk) return;
     const int tid = threadIdx.x;
     const int lc = tid & 7, lb = (tid >> 3) & 7, la = tid >> 6;
     const int nv = p.nv, no = p.no;
@@ -115,15 +112,6 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
         vb[m] = b < nv ? (double)vecp(m)[b] : 0.0;
     }
     const double eab = (a < nv ? (double)p.eps[no + a] : 0.0) + (b < nv ? (double)p.eps[no + b] : 0.0);
-    // the AB / BA blocks do not depend on the c-tile: this thread's 12 values live in registers for the whole loop
-    // (36 -> 24 shared loads per element for the disconnected part)
-    __syncthreads();
-    double gAB[6], gBA[6];
-#pragma unroll
-    for (int m = 0; m < 6; ++m) {
-        gAB[m] = sG[m * 6 + 0][la * GPITCH + lb];
-        gBA[m] = sG[m * 6 + 1][lb * GPITCH + la];
-    }
 
     // the six permuted bricks of W and the 24 c-dependent matrix blocks of the NEXT c-tile are fetched
     // into registers while the current one is being consumed from shared memory
@@ -170,8 +158,6 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
             //   g_ij[x,y] t1k[z] + g_ik[x,z] t1j[y] + g_jk[y,z] t1i[x] + t_ij[x,y] fk[z] + t_ik[x,z] fj[y] + t_jk[y,z] fi[x]
             auto blk = [&](int m, int px, int py) -> double {
                 const int pt = px == 0 ? (py == 1 ? 0 : 2) : (px == 1 ? (py == 0 ? 1 : 4) : (py == 0 ? 3 : 5));
-                if (pt == 0) return gAB[m];
-                if (pt == 1) return gBA[m];
                 return sG[m * 6 + pt][(px == 0 ? la : (px == 1 ? lb : lc)) * GPITCH + (py == 0 ? la : (py == 1 ? lb : lc))];
             };
             auto vat = [&](int m, int pos) -> double { return pos == 0 ? va[m] : (pos == 1 ? vb[m] : vc[m]); };
@@ -204,7 +190,7 @@ __global__ void __launch_bounds__(512) triples_energy_kernel(const __grid_consta
 #pragma unroll
         for (int w = 0; w < 16; ++w) r += sred[w];
         const int npair = p.nb * (p.nb + 1) / 2;
-        p.partials[(long long)t * npair + blockIdx.x] = r;
+        p.partials[(long long)t * npair + TAk * (TAk + 1) / 2 + TBk] = r;
     }
 }
 
@@ -263,7 +249,8 @@ int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_dev, i
     a.W = (const T*)w_dev; a.ijk = ijk_dev; a.t1 = (const T*)t1; a.t2 = (const T*)t2; a.g = (const T*)g;
     a.fov = (const T*)fov; a.eps = (const T*)eps; a.ld_fov = ld_fov; a.no = (int)no; a.nv = (int)nv; a.nb = nb;
     a.ntrip = ntrip; a.partials = partials;
-    dim3 grid(npair, ntrip);          // canonical brick pairs only
+    // non-canonical CTAs (TB > TA) exit at once, so only their partial slots stay unused
+    dim3 grid(nb, nb, ntrip);
     triples_energy_kernel<T><<<grid, 512, 0, ctx->stream>>>(a);
     PCCB_CHECK_LAUNCH(ctx, "triples_energy_kernel");
     sum_rows_kernel<<<ntrip, 256, 0, ctx->stream>>>(partials, npair, et_dev);
