@@ -206,6 +206,16 @@ int pccb_triples_energy(pccb_ctx* ctx, int dtype, const void* w_dev, const int32
 int pccb_t3_combine(pccb_ctx* ctx, int dtype, const void* w_dev, int nk, int k0, int i, int j, const void* eps_dev,
                     int64_t no, int64_t nv, void* a1_dev, void* a2_dev);
 
+/* ---- (T) contributions to the Lambda equations and densities (next row; pycc/ccwfn.py:721-801
+ * t3_density): for the occupied pair (i, j) and k = k0 .. k0+nk-1, from the connected w_dev[k][a][b][c] and the
+ * disconnected dd_dev[k][a][b][c] triples (both without denominator; pycc/cctriples.py:8-35, 68-83), the seven
+ * combinations the density / Lambda contractions consume, out7 = {M, A1, A2, B1, Z3, P, Q} (any may be NULL):
+ *   M = W/D, N = Dd/D, X(T) = 8T - 4T[bac] - 4T[acb] - 4T[cba] + 2T[cab] + 2T[bca],
+ *   A1 = M - M[cba], A2 = 2M - M[acb] - M[cba], B1 = 2(M - M[bac]), Z3 = 2(M - M[acb]) - (M[bac] - M[bca]),
+ *   P = 2X(M) + X(N), Q = X(M) + X(N).  Asynchronous. */
+int pccb_t3_density_combine(pccb_ctx* ctx, int dtype, const void* w_dev, const void* dd_dev, int nk, int k0, int i, int j,
+                            const void* eps_dev, int64_t no, int64_t nv, void* const* out7_dev_hostarray);
+
 #ifdef __cplusplus
 }
 #endif

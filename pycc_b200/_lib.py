@@ -24,7 +24,7 @@ EXPORTS = (
     "pccb_update_amplitudes", "pccb_cc_energy", "pccb_dot", "pccb_axpby", "pccb_lincomb",
     "pccb_triples_energy", "pccb_t3_combine", "pccb_split_lo", "pccb_register_lo_plane", "pccb_clear_lo_planes",
     "pccb_unregister_lo_plane", "pccb_update_energy", "pccb_prepare_amplitudes",
-    "pccb_cc_energy_static", "pccb_cc_energy_static_max_partials", "pccb_dot_many",
+    "pccb_cc_energy_static", "pccb_cc_energy_static_max_partials", "pccb_dot_many", "pccb_t3_density_combine",
 )
 
 
@@ -91,6 +91,7 @@ def load():
     lib.pccb_cc_energy_static.argtypes = [vp, i32, vp, i64, vp, vp, vp, i64, i64, vp]
     lib.pccb_cc_energy.argtypes = [vp, i32, vp, i64, vp, vp, vp, i64, i64, pd]
     lib.pccb_dot.argtypes = [vp, i32, vp, vp, i64, pd]
+    lib.pccb_t3_density_combine.argtypes = [vp, i32, vp, vp, i32, i32, i32, i32, vp, i64, i64, C.POINTER(vp)]
     lib.pccb_dot_many.argtypes = [vp, i32, vp, C.POINTER(vp), i32, i64, pd]
     lib.pccb_axpby.argtypes = [vp, i32, vp, dbl, vp, dbl, vp, i64]
     lib.pccb_lincomb.argtypes = [vp, i32, vp, C.POINTER(vp), pd, i32, i64]

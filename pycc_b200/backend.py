@@ -186,6 +186,13 @@ class CudaBackend(object):
         """Forget the residual plane registered for the tensor whose base address is ``x_ptr``."""
         self._check(self.lib.pccb_unregister_lo_plane(self.h, x_ptr))
 
+    def t3_density_combine(self, W, Dd, nk, k0, i, j, eps, no, nv, outs):
+        """outs: dict with any of M, A1, A2, B1, Z3, P, Q (tensors [nk, nv, nv, nv]); see pccb_t3_density_combine."""
+        ptrs = (C.c_void_p * 7)(*[(outs[k].data_ptr() if outs.get(k) is not None else None)
+                                  for k in ("M", "A1", "A2", "B1", "Z3", "P", "Q")])
+        self._check(self.lib.pccb_t3_density_combine(self.h, dtype_code(W), W.data_ptr(), Dd.data_ptr(), nk, k0, i, j,
+                                                     eps.data_ptr(), no, nv, ptrs))
+
     def t3_combine(self, W, nk, k0, i, j, eps, no, nv, A1, A2):
         """A1 / A2 combinations of t3 = W / D for the pair (i, j), k = k0 .. k0+nk-1 (CC3)."""
         self._check(self.lib.pccb_t3_combine(self.h, dtype_code(W), W.data_ptr(), nk, k0, i, j, eps.data_ptr(),

@@ -1,6 +1,6 @@
 """
 cclambda.py: Lambda-amplitude solver, API-compatible with ``pycc/cclambda.py`` (class cclambda
-:16-581) for the models CCD, CC2 and CCSD, executing on the B200 engine
+:16-581) for the models CCD, CC2, CCSD and CCSD(T), executing on the B200 engine
 (``hbar_engine.LambdaEngine``).
 
     hbar = pycc_b200.cchbar(cc)
@@ -22,6 +22,15 @@ class cclambda(object):
         self.hbar = hbar
         self.contract = ccwfn.contract
         self.engine = LambdaEngine(hbar.engine)
+        if ccwfn.model == 'CCSD(T)':
+            # the reference reads ccwfn.S1 / ccwfn.S2 (cclambda.py:474-475, 519-520): they must exist
+            # (solve_cc(..., make_t3_density=True) or ccwfn.t3_density())
+            if not hasattr(ccwfn, "S1") or not hasattr(ccwfn, "S2"):
+                raise Exception("CCSD(T) Lambda needs the (T) source terms: construct ccwfn with make_t3_density=True "
+                                "or call ccwfn.t3_density() first.")
+            if ccwfn.comm.world > 1:
+                raise Exception("CCSD(T) Lambda runs on one GPU for now.")
+            self.engine.t3_source = (ccwfn.S1, ccwfn.S2)
         self.engine.guess()                       # l1 = 2 t1, l2 = 2 (2 t2 - t2^T)  (cclambda.py:57-58)
         self.l1, self.l2 = self.engine.l1, self.engine.l2
 

@@ -104,8 +104,6 @@ class ccwfn(object):
         self.need_singles = ['CCSD', 'CCSD(T)', 'CC2', 'CC3']
         self.need_t1_transform = ['CC3']
         self.make_t3_density = kwargs.pop('make_t3_density', False)
-        if self.make_t3_density:
-            raise Exception("make_t3_density (Lambda/(T) densities) is outside the B200 engine's scope.")
         self.real_time = kwargs.pop('real_time', False)
 
         valid_local_models = [None, 'PNO', 'PAO', 'CPNO++', 'PNO++']
@@ -238,8 +236,11 @@ class ccwfn(object):
                 print("E(REF)  = %20.15f" % self.eref)
                 if self.model == 'CCSD(T)':
                     print("E(CCSD) = %20.15f" % ecc)
-                    from .cctriples import t_tjl
-                    et = t_tjl(self)
+                    if self.make_t3_density is True:
+                        et = self.t3_density()
+                    else:
+                        from .cctriples import t_tjl
+                        et = t_tjl(self)
                     print("E(T)    = %20.15f" % et)
                     ecc = ecc + et
                 else:
@@ -249,6 +250,20 @@ class ccwfn(object):
                 return ecc
             self._diis_step(diis, niter, start_diis)
         eng.sync_amplitudes()
+
+    def t3_density(self):
+        """(T) contributions to the Lambda equations and the densities (pycc/ccwfn.py:721-855): sets S1, S2, Dvv, Doo,
+        Dov, Goovv, Gooov, Gvvvo (device tensors in the reference's index order) and returns E(T)."""
+        if getattr(self, "_t3d", None) is None:
+            from .t3density_engine import T3DensityEngine
+            self._t3d = T3DensityEngine(self.engine)
+        self.engine.sync_amplitudes()
+        d = self._t3d
+        et = d.run()
+        self.S1, self.S2 = d.S1, d.S2
+        self.Dvv, self.Doo, self.Dov = d.Dvv, d.Doo, d.Dov
+        self.Goovv, self.Gooov, self.Gvvvo = d.Goovv, d.Gooov, d.Gvvvo
+        return et
 
     def make_diis(self, max_diis=8):
         """helper_diis over this object's amplitudes; with several GPUs its history is sliced by the same

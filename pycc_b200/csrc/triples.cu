@@ -234,6 +234,47 @@ __global__ void t3_combine_kernel(const T* __restrict__ W, int nk, int k0, int i
     }
 }
 
+// ---- (T) densities / Lambda source terms (pycc/ccwfn.py:721-801, t3_density): for the occupied pair (i, j) and
+// k = k0 .. k0+nk-1, from the connected W[k][abc] and disconnected Dd[k][abc] (both WITHOUT denominator):
+//   M = W / D,  N = Dd / D                                            (t3c_ijk / t3d_ijk with WithDenom=True)
+//   X(T)[abc] = 8 T[abc] - 4 T[bac] - 4 T[acb] - 4 T[cba] + 2 T[cab] + 2 T[bca]            (ccwfn.py:754-755)
+//   A1 = M - M[cba]                 A2 = 2 M - M[acb] - M[cba]         (:758-760, 766)
+//   B1 = 2 (M - M[bac])             Z3 = 2 (M - M[acb]) - (M[bac] - M[bca])               (:775, 769)
+//   P  = 2 X(M) + X(N)              Q  = X(M) + X(N)                   (:771-772, 777-778; :763, 790)
+// D^{ijk}_{abc} is invariant under permutations of (a, b, c).  Any output pointer may be null.
+template <typename T>
+struct T3DensityOut { T *M, *A1, *A2, *B1, *Z3, *P, *Q; };
+
+template <typename T>
+__global__ void t3_density_combine_kernel(const T* __restrict__ W, const T* __restrict__ Dd, int nk, int k0, int i, int j,
+                                          const T* __restrict__ eps, int no, int nv,
+                                          const __grid_constant__ T3DensityOut<T> o) {
+    const long long v2 = (long long)nv * nv, v3 = v2 * nv, total = v3 * nk;
+    for (long long idx = (long long)blockIdx.x * blockDim.x + threadIdx.x; idx < total;
+         idx += (long long)gridDim.x * blockDim.x) {
+        const int kk = (int)(idx / v3);
+        const long long r = idx - (long long)kk * v3;
+        const int a = (int)(r / v2), b = (int)((r / nv) % nv), c = (int)(r % nv);
+        const T* Wk = W + (long long)kk * v3;
+        const T* Dk = Dd + (long long)kk * v3;
+        const double d = (double)eps[i] + (double)eps[j] + (double)eps[k0 + kk] - (double)eps[no + a] -
+                         (double)eps[no + b] - (double)eps[no + c];
+        auto at = [&](const T* X, int x, int y, int z) { return (double)X[x * v2 + (long long)y * nv + z] / d; };
+        const double mabc = at(Wk, a, b, c), mbac = at(Wk, b, a, c), macb = at(Wk, a, c, b), mcba = at(Wk, c, b, a),
+                     mcab = at(Wk, c, a, b), mbca = at(Wk, b, c, a);
+        const double xm = 8.0 * mabc - 4.0 * mbac - 4.0 * macb - 4.0 * mcba + 2.0 * mcab + 2.0 * mbca;
+        const double xn = 8.0 * at(Dk, a, b, c) - 4.0 * at(Dk, b, a, c) - 4.0 * at(Dk, a, c, b) - 4.0 * at(Dk, c, b, a) +
+                          2.0 * at(Dk, c, a, b) + 2.0 * at(Dk, b, c, a);
+        if (o.M) o.M[idx] = (T)mabc;
+        if (o.A1) o.A1[idx] = (T)(mabc - mcba);
+        if (o.A2) o.A2[idx] = (T)(2.0 * mabc - macb - mcba);
+        if (o.B1) o.B1[idx] = (T)(2.0 * (mabc - mbac));
+        if (o.Z3) o.Z3[idx] = (T)(2.0 * (mabc - macb) - (mbac - mbca));
+        if (o.P) o.P[idx] = (T)(2.0 * xm + xn);
+        if (o.Q) o.Q[idx] = (T)(xm + xn);
+    }
+}
+
 template <typename T>
 int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_dev, int ntrip, const void* t1,
                      const void* t2, const void* g, const void* fov, int64_t ld_fov, const void* eps, int64_t no,
@@ -296,5 +337,30 @@ extern "C" int pccb_t3_combine(pccb_ctx* ctx, int dtype, const void* w_dev, int 
     else
         PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
     PCCB_CHECK_LAUNCH(ctx, "t3_combine_kernel");
+    return PCCB_OK;
+}
+
+extern "C" int pccb_t3_density_combine(pccb_ctx* ctx, int dtype, const void* w_dev, const void* dd_dev, int nk, int k0, int i,
+                                       int j, const void* eps_dev, int64_t no, int64_t nv, void* const* out7_dev_hostarray) {
+    if (!ctx) return PCCB_ERR_ARG;
+    PCCB_REQUIRE(ctx, w_dev && dd_dev && eps_dev && out7_dev_hostarray && nk >= 1 && no > 0 && nv > 0 && i >= 0 && j >= 0 &&
+                          k0 >= 0 && k0 + nk <= no && i < no && j < no,
+                 "pccb_t3_density_combine: bad arguments");
+    const long long total = (long long)nk * nv * nv * nv;
+    long long blocks = (total + 255) / 256;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    void* const* q = out7_dev_hostarray;
+    if (dtype == PCCB_F64) {
+        T3DensityOut<double> o{(double*)q[0], (double*)q[1], (double*)q[2], (double*)q[3], (double*)q[4], (double*)q[5], (double*)q[6]};
+        t3_density_combine_kernel<double><<<(unsigned)blocks, 256, 0, ctx->stream>>>(
+            (const double*)w_dev, (const double*)dd_dev, nk, k0, i, j, (const double*)eps_dev, (int)no, (int)nv, o);
+    } else if (dtype == PCCB_F32) {
+        T3DensityOut<float> o{(float*)q[0], (float*)q[1], (float*)q[2], (float*)q[3], (float*)q[4], (float*)q[5], (float*)q[6]};
+        t3_density_combine_kernel<float><<<(unsigned)blocks, 256, 0, ctx->stream>>>(
+            (const float*)w_dev, (const float*)dd_dev, nk, k0, i, j, (const float*)eps_dev, (int)no, (int)nv, o);
+    } else {
+        PCCB_FAIL(ctx, PCCB_ERR_ARG, "unknown dtype %d", dtype);
+    }
+    PCCB_CHECK_LAUNCH(ctx, "t3_density_combine_kernel");
     return PCCB_OK;
 }

@@ -304,6 +304,7 @@ class LambdaEngine(object):
                     L.is_ladder = "HvT[" in s
                     self.plans[name].append(L)
         self.ladder_events = None
+        self.t3_source = None        # (S1, S2) for model CCSD(T), set by cclambda
 
     def guess(self):
         """l1 = 2 t1, l2 = 2 (2 t2 - t2^T) (cclambda.py:57-58)."""
@@ -340,6 +341,14 @@ class LambdaEngine(object):
             self.eng.comm.allreduce_(self.r1)
         elif name == "r_L2":
             self.eng.comm.allreduce_(self.r2)
+        # CCSD(T): the (T) source terms of ccwfn.t3_density (cclambda.py:474-475, 519-520), added before the pair
+        # symmetrisation of r2 exactly as the reference does (S2 is symmetric: 1/2 S2 + 1/2 S2^T = S2)
+        src = getattr(self, "t3_source", None)
+        if src is not None:
+            if name == "r_L1":
+                self.be.axpby(self.r1, 1.0, self.r1, 1.0, src[0])
+            elif name == "r_L2":
+                self.be.axpby(self.r2, 1.0, self.r2, 0.5, src[1])
 
     def residuals(self, symmetrize=True):
         """r1, r2 for the amplitudes in self.l1 / self.l2 (the loop body of cclambda.py:146-151)."""

@@ -191,6 +191,22 @@ class InterpBackend(object):
     def register_lo_plane(self, x, lo):
         pass          # the interpreter contracts the full FP32 values
 
+    def t3_density_combine(self, W, Dd, nk, k0, i, j, eps, no, nv, outs):
+        e = eps.double()
+        ev = e[no:]
+        X = lambda T: 8 * T - 4 * T.permute(1, 0, 2) - 4 * T.permute(0, 2, 1) - 4 * T.permute(2, 1, 0) \
+            + 2 * T.permute(2, 0, 1) + 2 * T.permute(1, 2, 0)
+        for kk in range(nk):
+            d = e[i] + e[j] + e[k0 + kk] - (ev[:, None, None] + ev[None, :, None] + ev[None, None, :])
+            M, N = W[kk].double() / d, Dd[kk].double() / d
+            val = dict(M=M, A1=M - M.permute(2, 1, 0), A2=2 * M - M.permute(0, 2, 1) - M.permute(2, 1, 0),
+                       B1=2 * (M - M.permute(1, 0, 2)),
+                       Z3=2 * (M - M.permute(0, 2, 1)) - (M.permute(1, 0, 2) - M.permute(2, 0, 1)),    # permute(2,0,1)[a,b,c] = M[b,c,a]
+                       P=2 * X(M) + X(N), Q=X(M) + X(N))
+            for k, out in outs.items():
+                if out is not None:
+                    out[kk].copy_(val[k].to(out.dtype))
+
     def t3_combine(self, W, nk, k0, i, j, eps, no, nv, A1, A2):
         e = eps.double()
         ev = e[no:]

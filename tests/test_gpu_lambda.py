@@ -65,3 +65,14 @@ def test_lambda_linearity_mid_size():
         w.backend.use_naive_contract(False)
     for k in range(2):
         assert (rn[k] - rx[k]).abs().max().item() < 1e-11
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8", "o6v13"])
+def test_t3_density_and_ccsd_t_lambda(name):
+    """ccwfn.t3_density (S1, S2, Dvv, Doo, Dov, Goovv, Gooov, Gvvvo, E(T)) and the CCSD(T) Lambda equations on the
+    device (pycc/ccwfn.py:721-855, pycc/cclambda.py:474-475, 519-520) against the reference's own vectors."""
+    from pycc_b200.backend import CudaBackend
+    from tests import t3density_checks as tc
+    be = CudaBackend()
+    tc.check_t3_density(name, be)
+    tc.check_lambda_t(name, be)
