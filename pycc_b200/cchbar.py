@@ -15,8 +15,8 @@ import torch
 class cchbar(object):
     def __init__(self, ccwfn):
         time_init = time.time()
-        if ccwfn.model not in ('CCD', 'CC2', 'CCSD', 'CCSD(T)'):
-            raise Exception("HBAR in the B200 engine: models CCD, CC2, CCSD and CCSD(T) (got %s)." % (ccwfn.model))
+        if ccwfn.model not in ('CCD', 'CC2', 'CCSD', 'CCSD(T)', 'CC3'):
+            raise Exception("HBAR in the B200 engine: models CCD, CC2, CCSD, CCSD(T) and CC3 (got %s)." % (ccwfn.model))
         from .hbar_engine import HbarEngine
         self.ccwfn = ccwfn
         self.contract = ccwfn.contract

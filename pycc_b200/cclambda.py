@@ -1,6 +1,6 @@
 """
 cclambda.py: Lambda-amplitude solver, API-compatible with ``pycc/cclambda.py`` (class cclambda
-:16-581) for the models CCD, CC2, CCSD and CCSD(T), executing on the B200 engine
+:16-581) for the models CCD, CC2, CCSD, CCSD(T) and CC3, executing on the B200 engine
 (``hbar_engine.LambdaEngine``).
 
     hbar = pycc_b200.cchbar(cc)
@@ -31,6 +31,10 @@ class cclambda(object):
             if ccwfn.comm.world > 1:
                 raise Exception("CCSD(T) Lambda runs on one GPU for now.")
             self.engine.t3_source = (ccwfn.S1, ccwfn.S2)
+        if ccwfn.model == 'CC3':
+            # triples contributions Y1 / Y2 of the loops in solve_lambda (cclambda.py:118-139, 160-235)
+            from .cc3_lambda_engine import CC3LambdaEngine
+            self.engine.cc3 = CC3LambdaEngine(self.engine)
         self.engine.guess()                       # l1 = 2 t1, l2 = 2 (2 t2 - t2^T)  (cclambda.py:57-58)
         self.l1, self.l2 = self.engine.l1, self.engine.l2
 
@@ -81,6 +85,10 @@ class cclambda(object):
         if any(_is_complex(x) for x in (F, t1, t2, l1, l2)):
             # rtcc.f (pycc/rt/rtcc.py:132): complex amplitudes, HBAR rebuilt from them
             return self.ccwfn._complex().lambda_residuals(F, t1, t2, l1, l2)
+        if self.ccwfn.model == 'CC3':
+            # the reference's CC3 branch of residuals() (cclambda.py:323-440) repeats the solve_lambda loops for
+            # other (F, t1, t2): not built - only solve_lambda carries the CC3 triples terms
+            raise NotImplementedError("cclambda.residuals with model CC3 is outside the B200 engine (use solve_lambda)")
         w, eng, le = self.ccwfn, self.ccwfn.engine, self.engine
         own_t = t1 is eng.t1 and t2 is eng.t2
         own_l = l1 is le.l1 and l2 is le.l2

@@ -138,8 +138,8 @@ class HbarEngine(object):
     def __init__(self, eng):
         if eng.ovvv_full is None:
             raise ValueError("HBAR needs the full <mb|ef> block on every rank (ccwfn(..., full_ovvv=True))")
-        if eng.model not in ('CCD', 'CC2', 'CCSD'):
-            raise ValueError("HBAR / Lambda: models CCD, CC2, CCSD (got %r)" % (eng.model,))
+        if eng.model not in ('CCD', 'CC2', 'CCSD', 'CC3'):      # CC3 uses the CCSD HBAR (pycc/cchbar.py has no CC3 branch)
+            raise ValueError("HBAR / Lambda: models CCD, CC2, CCSD, CCSD(T), CC3 (got %r)" % (eng.model,))
         self.eng, self.be = eng, eng.be
         o, v, vl, dt = eng.no, eng.nv, eng.vl, eng.dtype
         E = lambda *s: self.be.zeros(s, dt)
@@ -305,6 +305,7 @@ class LambdaEngine(object):
                     self.plans[name].append(L)
         self.ladder_events = None
         self.t3_source = None        # (S1, S2) for model CCSD(T), set by cclambda
+        self.cc3 = None              # cc3_lambda_engine.CC3LambdaEngine for model CC3, set by cclambda
 
     def guess(self):
         """l1 = 2 t1, l2 = 2 (2 t2 - t2^T) (cclambda.py:57-58)."""
@@ -354,6 +355,8 @@ class LambdaEngine(object):
         """r1, r2 for the amplitudes in self.l1 / self.l2 (the loop body of cclambda.py:146-151)."""
         for name in ("G", "r_L1", "r_L2"):
             self.run(name)
+        if getattr(self, "cc3", None) is not None:
+            self.cc3.contribute()        # Y1, Y2 of the CC3 triples (cclambda.py:160-235), before r2 + r2^T
         if symmetrize:
             self.be.pair_symmetrize(self.r2, self.eng.no, self.eng.nv)     # :542
         return self.r1, self.r2

@@ -68,6 +68,50 @@ def _set(desc, f, val):
         setattr(desc, name, val)
 
 
+class TripletBatch(object):
+    """Statements written for ONE occupied triplet (i, j, k) over slices of stored tensors, launched for a pair
+    (i, j) with k as the batch index of the launch: every operand address is affine in (i, j, k), so each
+    statement is planned once at (0, 0, 0), the pointer derivatives come from the plans at the three unit steps,
+    and a launch only patches base pointers and batch strides.  ``tensors_fn(i, j, k) -> {name: tensor}``."""
+
+    def __init__(self, no, dcode, statements, tensors_fn, backend, prefer_flat=None):
+        self.be = backend
+        step = 1 if no > 1 else 0
+        mk = lambda i, j, k: {n: TRef.of(t, n) for n, t in tensors_fn(i, j, k).items()}
+        base = [plan(s, mk(0, 0, 0), dcode, prefer_flat=prefer_flat) for s in statements]
+        for L in base:
+            if len(L) != 1 or L[0].desc.batch != 1:
+                raise RuntimeError("unexpected triplet-batch plan structure")
+        shifted = [[plan(s, mk(*unit), dcode, prefer_flat=prefer_flat)[0].desc for s in statements]
+                   for unit in ((step, 0, 0), (0, step, 0), (0, 0, step))]
+        self.templates = []
+        for n, L in enumerate(base):
+            d0 = L[0].desc
+            fields = _ptr_fields(d0)
+            deriv = {f[0]: tuple((_get(shifted[ax][n], f) - _get(d0, f)) if step else 0 for ax in range(3))
+                     for f in fields}
+            self.templates.append((L[0], fields, deriv))
+        self._keep = base
+        self.itemsize = tensors_fn(0, 0, 0)[next(iter(tensors_fn(0, 0, 0)))].element_size()
+
+    def launch_pair(self, i, j, nk):
+        for (L, fields, deriv) in self.templates:
+            d = _lib.Contraction()
+            C.memmove(C.byref(d), C.byref(L.desc), C.sizeof(d))
+            for f in fields:
+                di, dj, dk = deriv[f[0]]
+                _set(d, f, _get(L.desc, f) + i * di + j * dj)
+                name, q, _ = f
+                if q is None:
+                    d.c_batch = dk // self.itemsize
+                elif name.endswith("A"):
+                    d.seg[q].a_batch = dk // self.itemsize
+                else:
+                    d.seg[q].b_batch = dk // self.itemsize
+            d.batch = nk
+            self.be.contract(d)
+
+
 class TriplesEngine(object):
     def __init__(self, ccsd_engine, V=None, O=None):
         """``V`` [i][x][y][e] = Wvvvo[x,y,e,i] and ``O`` [j][k][m][c] = Wovoo[m,c,j,k] default to the bare

@@ -76,3 +76,15 @@ def test_t3_density_and_ccsd_t_lambda(name):
     be = CudaBackend()
     tc.check_t3_density(name, be)
     tc.check_lambda_t(name, be)
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8", "o6v13"])
+def test_cc3_lambda(name):
+    """The CC3 Lambda equations on the device (pycc/cclambda.py:118-139, 160-235; cctriples.l3_ijk :219-277): one
+    iteration at perturbed unsymmetric amplitudes and the solve_cc -> cchbar -> solve_lambda chain, against the
+    reference's own vectors."""
+    from pycc_b200.backend import CudaBackend
+    from tests import lambda_cc3_checks as l3
+    be = CudaBackend()
+    l3.check_one_iteration(name, be)
+    l3.check_solve(name, be)
