@@ -12,7 +12,9 @@ integrals (``build_cc3_*``, :625-710), on the engine's kernels:
   * four contractions per pair, with k folded into the contracted index, add X1 / X2 (:395-398)
     straight into the unsymmetrised r1 / r2 (the final r2 + r2^T supplies X2^T, :401).
 
-No o^3 v^3 tensor exists at any time (three o v^3 buffers).  Single GPU only for now.
+No o^3 v^3 tensor exists at any time (three o v^3 buffers).  Several GPUs: the occupied pairs are dealt over the
+ranks, the v^4 term of the dressed <ab|ei> is formed from each rank's rows of <ab|ef> (one allreduce), and the
+partial X1 / X2 are summed by the iteration's allreduce of r1 / r2.
 """
 import torch
 
@@ -50,8 +52,6 @@ class CC3Engine(object):
     )
 
     def __init__(self, eng):
-        if eng.comm.world > 1:
-            raise ValueError("model='CC3' runs on one GPU for now (the dressed <ab|ei> needs every row of <ab|ef>)")
         if eng.ovvv_full is None:
             raise ValueError("model='CC3' needs the full <mb|ef> block")
         self.eng, self.be = eng, eng.be
@@ -69,8 +69,20 @@ class CC3Engine(object):
                  R=self.R, Q=self.Q, Qa=self.Qa, Wk=self.Wk, Wv=self.Wv)
         T = {k: TRef.of(t, k) for k, t in T.items()}
         self.launches = []
+        self.sharded = eng.comm.world > 1
         for s in self.STATEMENTS:
+            if self.sharded and "vvvv[" in s:
+                continue
             self.launches += plan(s, T, eng.dcode)
+        if self.sharded:
+            # several GPUs: a rank holds the rows a in [vlo, vhi) of <ab|ef>, so it forms those rows of the one
+            # v^4 term of Wabei in a zero-initialised buffer; one allreduce of the disjoint slices is the gather.
+            # Everything else is o-heavy and replicated; the occupied pairs of contribute() are dealt round-robin
+            # and the partial X1 / X2 ride on the iteration's allreduce of r1 / r2 (engine.residuals).
+            self.Wvv = E(o, v, v, v)
+            Tl = dict(WvA=self.Wvv.narrow(1, eng.vlo, eng.vl), t1=eng.t1, vvvvA=eng.vvvv_loc)
+            Tl = {k: TRef.of(t, k) for k, t in Tl.items()}
+            self.launch_vvvv = plan("WvA[iabe] = t1[if]*vvvvA[abef]", Tl, eng.dcode)
         self.tri = TriplesEngine(eng, V=self.Wv, O=self.Wo)
         self._pair_plans = {}
 
@@ -87,6 +99,17 @@ class CC3Engine(object):
         be.permute4(self.Wv, eng.ovvv_full.permute(0, 3, 2, 1))        # <ei|ab> = ovvv[i,e,b,a]
         for L in self.launches:
             be.contract(L.desc)
+        if self.sharded:
+            self.Wvv.zero_()             # the other ranks' rows hold the previous call's gathered values
+            for L in self.launch_vvvv:
+                be.contract(L.desc)
+            eng.comm.allreduce_(self.Wvv)
+            be.axpby(self.Wv, 1.0, self.Wv, 1.0, self.Wvv)
+
+    def my_pairs(self):
+        """The occupied pairs (i, j) this rank evaluates: all o^2 of them dealt round-robin (equal work each)."""
+        o, c = self.eng.no, self.eng.comm
+        return [(i, j) for i in range(o) for j in range(o)][c.rank::c.world]
 
     def _plans_for(self, i, j):
         key = (i, j)
@@ -110,9 +133,8 @@ class CC3Engine(object):
         o, v = eng.no, eng.nv
         self.build_intermediates()
         self.tri.refresh_t2T()
-        for i in range(o):
-            for j in range(o):
-                self.tri._launch_pair(i, j, nk=o)
-                be.t3_combine(self.tri.W, o, 0, i, j, eng.eps, o, v, self.A1, self.A2)
-                for L in self._plans_for(i, j):
-                    be.contract(L.desc)
+        for (i, j) in self.my_pairs():
+            self.tri._launch_pair(i, j, nk=o)
+            be.t3_combine(self.tri.W, o, 0, i, j, eng.eps, o, v, self.A1, self.A2)
+            for L in self._plans_for(i, j):
+                be.contract(L.desc)

@@ -370,6 +370,8 @@ class CCSDEngine(object):
                 self.be.split_lo(self.Wr2, self._lo["Wr2"])
         self._launch(name)
         # the one exchange step of the iteration: sum the per-rank partial residuals
+        if getattr(self, "_defer_reduce", False):
+            return                   # CC3 on several GPUs: after the triples terms (residuals())
         if name == "r_T1":
             self.comm.allreduce_(self.r1)
         elif name == "r_T2":
@@ -429,6 +431,7 @@ class CCSDEngine(object):
         # the solver's iteration (symmetrize=False) may leave r2 scattered over the ranks; callers that want the
         # whole residual get the allreduce.  CC3 adds its triples terms after the builders: allreduce there.
         self._scatter_r2 = (not symmetrize) and self.comm.world > 1 and self.model != 'CC3'
+        self._defer_reduce = self.model == 'CC3' and self.comm.world > 1
         order = list(self.builder_order())
         if self.pre_plans:
             self._run_small([n for n in order if n in self.pre_plans])
@@ -440,6 +443,11 @@ class CCSDEngine(object):
                 from .cc3_engine import CC3Engine
                 self.cc3 = CC3Engine(self)
             self.cc3.contribute()
+            if self._defer_reduce:       # builders + this rank's pairs of the triples terms: one sum over the ranks
+                self.comm.allreduce_(self.r1)
+                self.comm.allreduce_(self.r2)
+                self.r2_scattered = False
+        self._defer_reduce = False
         self._scatter_r2 = False
         if symmetrize:
             self.be.pair_symmetrize(self.r2, self.no, self.nv)       # ccwfn.py:621

@@ -221,6 +221,66 @@ def test_two_ranks_gloo(name):
         assert d["diis_pool"] == d["diis_chunk"] and d["gathered"] > 0
 
 
+def _cc3_worker(rank, world, port, name, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.conftest import Golden, GOLDEN_DIR
+        from tests.interp_backend import InterpBackend
+        import pycc_b200
+        from pycc_b200.parallel import virtual_slice
+        g = Golden(name)
+        z = np.load(os.path.join(GOLDEN_DIR, "models", name + ".npz"))
+        lo, hi = virtual_slice(g.nv, rank, world)
+        blocks = dict(g.blocks)
+        blocks["vvvv"] = np.ascontiguousarray(blocks["vvvv"][lo:hi])      # every rank: only its rows of <ab|ef>
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model="CC3", group="world", _backend=InterpBackend())
+            r1, r2 = w.residuals(g.F, g["gen_t1"], g["gen_t2"])
+            c = w.engine.cc3
+            out = dict(rank=rank, npairs=len(c.my_pairs()),
+                       d_Wabei=float(np.abs(c.Wv.permute(1, 2, 3, 0).numpy() - z["cc3_Wabei"]).max()),
+                       d_r1=float(np.abs(r1.numpy() - z["cc3_r1"]).max()),
+                       d_r2=float(np.abs(r2.numpy() - z["cc3_r2"]).max()))
+            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model="CC3", group="world", _backend=InterpBackend())
+            e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+        out.update(niter=len(w.iteration_log), niter_ref=int(z["cc3_solve_niter"]),
+                   d_e=abs(e - float(z["cc3_solve_ecc"])), d_t2=float(np.abs(w.t2.numpy() - z["cc3_solve_t2"]).max()))
+        q.put(out)
+    except Exception:
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
+def test_two_ranks_gloo_cc3(name):
+    """CC3 on two ranks: each holds its rows of <ab|ef>, forms its slice of the dressed <ab|ei> (allreduce), and
+    evaluates half of the occupied pairs; the partial triples terms are summed with the residual."""
+    from tests.conftest import Golden
+    g = Golden(name)
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cc3_worker, args=(r, world, port, name, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for d in res:
+        assert "error" not in d, d.get("error")
+    assert sum(d["npairs"] for d in res) == g.no ** 2
+    for d in res:
+        assert d["d_Wabei"] < 1e-12 and d["d_r1"] < 1e-12 and d["d_r2"] < 1e-12
+        assert d["niter"] == d["niter_ref"] and d["d_e"] < 1e-11 and d["d_t2"] < 1e-10
+
+
 def test_partition_helpers():
     from pycc_b200.parallel import virtual_slice, deal_pairs
     for nv in (1, 7, 19, 150, 250, 400):
