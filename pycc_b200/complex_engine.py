@@ -14,7 +14,8 @@ into real statements over the planes, planned by the same ``dsl.plan`` onto the 
   * a real addend goes to the real plane; '=' statements zero the output first.
 
 The Fock matrix is treated as complex as well (rtcc adds a real field, but ``residuals`` takes
-whatever it is given).  One GPU only.
+whatever it is given).  The amplitude residuals shard over several GPUs like the real engine (virtual
+slice, one allreduce per residual); HBAR + Lambda with complex amplitudes run on one GPU.
 """
 import re
 
@@ -83,10 +84,18 @@ def expand(stmt, is_complex, z="z"):
 class PlaneSet(object):
     """Plane buffers for the complex tensors plus the real constants, and the planner over them."""
 
-    def __init__(self, be, dtype, dcode):
+    def __init__(self, be, dtype, dcode, vslice=None):
         self.be, self.dtype, self.dcode = be, dtype, dcode
         self.cplx = {}     # name -> tensor (2, ...)
         self.real = {}     # name -> tensor
+        self.vslice = vslice   # (vlo, vl) on several GPUs: ``X_sK`` = X narrowed to the rank's virtual slice along dim K
+        self.local = {}        # names that ARE the rank's rows already (vvvv_s0, ovvv_s1)
+
+    @staticmethod
+    def _split(name):
+        """'t2_s3' -> ('t2', 3); 't2' -> ('t2', None)."""
+        m = re.match(r"^(.*)_s([0-9])$", name)
+        return (m.group(1), int(m.group(2))) if m else (name, None)
 
     def add_complex(self, name, shape=None, view=None):
         self.cplx[name] = view if view is not None else self.be.zeros((2,) + tuple(shape), self.dtype)
@@ -96,20 +105,33 @@ class PlaneSet(object):
         self.real[name] = t
 
     def is_complex(self, name):
-        if name in self.cplx:
+        if name in self.local:
+            return False
+        base, _ = self._split(name)
+        if base in self.cplx:
             return True
-        if name in self.real:
+        if base in self.real:
             return False
         raise dsl.PlanError("unknown tensor %r" % name)
 
     def _ref(self, name):
-        if name.endswith("__r") and name[:-3] in self.cplx:
-            return TRef.of(self.cplx[name[:-3]][0], name)
-        if name.endswith("__i") and name[:-3] in self.cplx:
-            return TRef.of(self.cplx[name[:-3]][1], name)
-        if name in self.cplx:
-            return TRef.of(self.cplx[name], name)
-        return TRef.of(self.real[name], name)
+        if name in self.local:
+            return TRef.of(self.local[name], name)
+        plane = None
+        full = name
+        if name.endswith("__r") or name.endswith("__i"):
+            plane, name = (0 if name.endswith("__r") else 1), name[:-3]
+        base, dim = self._split(name)
+        if base in self.cplx:
+            t = self.cplx[base]
+            off = 1                      # the plane index leads
+            if plane is not None:
+                t, off = t[plane], 0
+        else:
+            t, off = self.real[base], 0
+        if dim is not None and self.vslice is not None:
+            t = t.narrow(dim + off, self.vslice[0], self.vslice[1])
+        return TRef.of(t, full)
 
     def compile(self, stmts, rename=lambda n: n):
         """Statements -> list of ('zero', tensor) / ('launch', Launch).  ``rename`` maps the
@@ -164,14 +186,21 @@ class ComplexResiduals(object):
             "tauW[ijab] = 0.5*t2[ijab] + t1[ia]*t1[jb]"]
 
     def __init__(self, eng):
-        if eng.comm.world > 1:
-            raise ValueError("complex-amplitude residuals run on one GPU")
+        self.sharded = eng.comm.world > 1
+        if self.sharded and eng.model == 'CC2':
+            raise ValueError("complex-amplitude CC2 residuals run on one GPU")
         if eng.model not in ('CCD', 'CC2', 'CCSD'):
             raise ValueError("complex-amplitude residuals: models CCD, CC2, CCSD (got %r)" % (eng.model,))
         self.eng, self.be = eng, eng.be
         o, v = eng.no, eng.nv
         n = o + v
-        P = self.P = PlaneSet(eng.be, eng.dtype, eng.dcode)
+        # several GPUs: the statements keep their sliced form (engine.STATEMENTS: upper-case A / B = the rank's slice
+        # of the virtual index, X_sK = X narrowed along K), every rank accumulates partial r1 / r2 planes and one
+        # allreduce per residual sums them - the real engine's scheme, plane index included
+        P = self.P = PlaneSet(eng.be, eng.dtype, eng.dcode, (eng.vlo, eng.vl) if self.sharded else None)
+        if self.sharded:
+            P.local["vvvv_s0"] = eng.vvvv_loc
+            P.local["ovvv_s1"] = eng.ovvv_loc
         b = eng.blk
         for k in ("oooo", "ooov", "oovv", "ovov"):
             P.add_real(k, b[k])
@@ -183,17 +212,19 @@ class ComplexResiduals(object):
         P.add_complex("Foo", view=Fc[:, :o, :o])
         P.add_complex("Fov", view=Fc[:, :o, o:])
         P.add_complex("Fvv", view=Fc[:, o:, o:])
+        vl = eng.vl       # intermediates carrying the sliced index are local-sized, as in the real engine
         shapes = dict(t1=(o, v), t2=(o, o, v, v), tau=(o, o, v, v), tauh=(o, o, v, v), tauW=(o, o, v, v),
-                      t2s=(o, o, v, v), Fae=(v, v), Fmi=(o, o), Fme=(o, v), Fae2=(v, v), Fmi2=(o, o),
-                      Wmnij=(o, o, o, o), Wr1=(o, v, o, v), Wr2=(o, v, o, v), Zr=(o, o, o, v),
-                      Y1=(o, o, o, v), Y2=(o, o, v, o), r1=(o, v), r2=(o, o, v, v))
+                      t2s=(o, o, v, v), Fae=(vl, v), Fmi=(o, o), Fme=(o, v), Fae2=(vl, v), Fmi2=(o, o),
+                      Wmnij=(o, o, o, o), Wr1=(o, vl, o, v), Wr2=(o, vl, o, v), Zr=(o, o, o, vl),
+                      Y1=(o, o, o, vl), Y2=(o, o, vl, o), r1=(o, v), r2=(o, o, v, v))
         if eng.model == 'CC2':
             shapes.update(T11=(o, o, v, v), Yw=(o, o, o, v), Xv=(v, v, o, v))
         for k, s in shapes.items():
             P.add_complex(k, s)
         st = eng._statements(plain=False)
         self.prep = P.compile(self.PREP + (["T11[ijab] = t1[ia]*t1[jb]"] if eng.model == 'CC2' else []))
-        self.progs = {name: P.compile(st[name], _strip) for name in eng.builder_order()}
+        self.progs = {name: P.compile(st[name], (lambda n_: n_) if self.sharded else _strip)
+                      for name in eng.builder_order()}
         self._lam = None
 
     # ---- CCSD ---------------------------------------------------------------------------------
@@ -222,6 +253,9 @@ class ComplexResiduals(object):
         P.cplx["r2"].zero_()
         for name in eng.builder_order():
             P.run(self.progs[name])
+        if self.sharded:
+            eng.comm.allreduce_(P.cplx["r1"])
+            eng.comm.allreduce_(P.cplx["r2"])
         for z in range(2):
             be.pair_symmetrize(P.cplx["r2"][z], eng.no, eng.nv)
         return P.fetch("r1"), P.fetch("r2")
@@ -267,6 +301,8 @@ class ComplexResiduals(object):
     def lambda_residuals(self, F, t1, t2, l1, l2):
         """Complex L1 / L2 residuals with HBAR rebuilt from (F, t1, t2) (pycc/cclambda.py:281-323)."""
         P, be, eng = self.P, self.be, self.eng
+        if self.sharded:
+            raise ValueError("complex-amplitude Lambda residuals run on one GPU")
         be.bind_stream()
         if self._lam is None:
             self._lambda_setup()

@@ -281,6 +281,60 @@ def test_two_ranks_gloo_cc3(name):
         assert d["niter"] == d["niter_ref"] and d["d_e"] < 1e-11 and d["d_t2"] < 1e-10
 
 
+def _complex_worker(rank, world, port, name, model, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.conftest import Golden, GOLDEN_DIR
+        from tests.interp_backend import InterpBackend
+        import pycc_b200
+        from pycc_b200.parallel import virtual_slice
+        g = Golden(name)
+        z = np.load(os.path.join(GOLDEN_DIR, "complex", name + ".npz"))
+        lo, hi = virtual_slice(g.nv, rank, world)
+        blocks = dict(g.blocks)
+        blocks["vvvv"] = np.ascontiguousarray(blocks["vvvv"][lo:hi])
+        tag = model.lower()
+        t1 = np.zeros_like(z["t1"]) if model == "CCD" else z["t1"]
+        out = dict(rank=rank)
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model=model, group="world", _backend=InterpBackend())
+            for ftag, F in (("field", z["F_field"]), ("complex", z["F_complex"])):
+                r1, r2 = w.residuals(F, t1, z["t2"], real_time=True)
+                out["d1_" + ftag] = float(np.abs(r1.numpy() - z["%s_%s_r1" % (tag, ftag)]).max())
+                out["d2_" + ftag] = float(np.abs(r2.numpy() - z["%s_%s_r2" % (tag, ftag)]).max())
+        q.put(out)
+    except Exception:
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("model", ["CCSD", "CCD"])
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
+def test_two_ranks_gloo_complex(name, model):
+    """Complex-amplitude residuals (the real-time propagator's call) on two ranks: the plane-expanded statements in
+    their sliced form, partial planes summed by one allreduce per residual."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_complex_worker, args=(r, world, port, name, model, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for d in res:
+        assert "error" not in d, d.get("error")
+        for k in ("d1_field", "d2_field", "d1_complex", "d2_complex"):
+            assert d[k] < 1e-12, (k, d[k])
+
+
 def test_partition_helpers():
     from pycc_b200.parallel import virtual_slice, deal_pairs
     for nv in (1, 7, 19, 150, 250, 400):
