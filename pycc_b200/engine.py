@@ -28,7 +28,7 @@ import torch
 
 from . import _lib
 from .dsl import TRef, plan
-from .parallel import Comm, virtual_slice
+from .parallel import Comm, virtual_slice, nvtx_range
 
 
 def _unregister_lo(be, ptrs):
@@ -368,7 +368,8 @@ class CCSDEngine(object):
             if self._lo is not None and self.sp_plain:      # the ring intermediates are operands now
                 self.be.split_lo(self.Wr1, self._lo["Wr1"])
                 self.be.split_lo(self.Wr2, self._lo["Wr2"])
-        self._launch(name)
+        with nvtx_range("ccsd/" + name):
+            self._launch(name)
         # the one exchange step of the iteration: sum the per-rank partial residuals
         if getattr(self, "_defer_reduce", False):
             return                   # CC3 on several GPUs: after the triples terms (residuals())

@@ -336,7 +336,9 @@ class LambdaEngine(object):
                 return               # cclambda.py:462-466
         elif name == "r_L2":
             self.r2.zero_()
-        self._launch(name)
+        from .parallel import nvtx_range
+        with nvtx_range("lambda/" + name):
+            self._launch(name)
         # the one exchange step: sum the per-rank partial residuals
         if name == "r_L1":
             self.eng.comm.allreduce_(self.r1)

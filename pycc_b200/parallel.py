@@ -137,3 +137,26 @@ class Comm(object):
         if self.world > 1:
             import torch.distributed as dist
             dist.barrier(group=self.group)
+
+
+class nvtx_range(object):
+    """NVTX range around one builder / phase (ranges per builder for ncu / nsys timelines).
+    Enabled with PCCB_NVTX=1 on a CUDA device; otherwise a no-op with no per-call cost beyond one attribute test."""
+    import os as _os
+    enabled = _os.environ.get("PCCB_NVTX", "0") == "1"
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        if nvtx_range.enabled and torch.cuda.is_available():
+            torch.cuda.nvtx.range_push(self.name)
+            self.pushed = True
+        else:
+            self.pushed = False
+        return self
+
+    def __exit__(self, *exc):
+        if self.pushed:
+            torch.cuda.nvtx.range_pop()
+        return False

@@ -242,9 +242,11 @@ class TriplesEngine(object):
         self.refresh()
         fov = eng.F[:o, o:]
         pos = 0
+        from .parallel import nvtx_range
         for (i, j) in pairs:
             n = j + 1
-            self._launch_pair(i, j)
+            with nvtx_range("(T)/W %d,%d" % (i, j)):
+                self._launch_pair(i, j)
             be.triples_energy(self.W, ijk[3 * pos:], n, eng.t1, eng.t2, eng.blk["oovv"], fov, eng.F.stride(0),
                               eng.eps, o, v, et[pos:])
             pos += n
