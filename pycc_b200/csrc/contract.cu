@@ -2137,6 +2137,25 @@ extern "C" int pccb_contract(pccb_ctx* ctx, const pccb_contraction* d) {
             if (eff > best + 1e-9) { best = eff; splits = (int)sK; }
         }
     }
+    else if (tiles < 24ll * ctx->sm_count && kt >= 256 && d->batch == 1 && ctx->ws) {
+        // A handful of waves of LONG tiles (the ladder of one rank out of eight: 1197 tiles of 48 x 128 x 62500 = 8.09
+        // waves, the ninth wave 9 % full): split K so that the tail wave is a fraction of a tile long.  Cost in
+        // full-K tile times: ceil(tiles s / SMs) / s plus the workspace traffic of the deterministic reduction.
+        static const bool tail_split = [] { const char* e = getenv("PCCB_TAIL_SPLIT"); return e ? atoi(e) != 0 : true; }();
+        const double t_tile = 2.0 * (double)bm * BN * (16.0 * kt) / (37.0e12 / ctx->sm_count);
+        const long long by_ws = (long long)(ctx->ws_bytes / ((size_t)total * sizeof(double)));
+        long long smax = kt / 64 < 8 ? kt / 64 : 8;
+        if (smax > by_ws) smax = by_ws;
+        double best = (double)((tiles + ctx->sm_count - 1) / ctx->sm_count);
+        const double whole = best;
+        int pick = 1;
+        for (long long sK = 2; tail_split && sK <= smax; ++sK) {
+            const long long waves = (tiles * sK + ctx->sm_count - 1) / ctx->sm_count;
+            const double cost = (double)waves / (double)sK + (2.0 * sK + 1.0) * (double)total * 8.0 / 5.0e12 / t_tile;
+            if (cost < best - 1e-9) { best = cost; pick = (int)sK; }
+        }
+        if (best < 0.98 * whole) splits = pick;
+    }
     PCCB_REQUIRE(ctx, (long long)d->batch * splits <= 65535, "pccb_contract: batch*splits=%lld exceeds grid.z",
                  (long long)d->batch * splits);
     p.splits = splits;

@@ -68,6 +68,10 @@ CASES = [
     # short K, M = v^2 with v = 250 rows (128-row tiles by padding): rerouted to the kernel with epilogue warps
     ("C[abc] = A[eab]*B[ce] - A3[mc]*B3[mab]",
      dict(A=(250, 250, 250), B=(250, 250), A3=(9, 250), B3=(9, 250, 250), C=(250, 250, 250))),
+    # a few waves of long tiles (6 x 52 = 312 tiles = 2.1 waves, K = 4200 with a ragged tail): tail-aware split-K
+    # (one rank's ladder out of eight) on the TMA-staged kernel, plain and row-contiguous operands
+    ("C[mn] = A[mk]*B[nk]", dict(A=(480, 4200), B=(6650, 4200), C=(480, 6650))),
+    ("C[mn] = A[km]*B[kn]", dict(A=(4200, 480), B=(4200, 6650), C=(480, 6650))),
 ]
 
 
