@@ -19,7 +19,7 @@ partial X1 / X2 are summed by the iteration's allreduce of r1 / r2.
 import torch
 
 from .dsl import TRef, plan
-from .triples_engine import TriplesEngine
+from .triples_engine import TriplesEngine, TripletBatch
 
 
 class CC3Engine(object):
@@ -85,6 +85,15 @@ class CC3Engine(object):
             self.launch_vvvv = plan("WvA[iabe] = t1[if]*vvvvA[abef]", Tl, eng.dcode)
         self.tri = TriplesEngine(eng, V=self.Wv, O=self.Wo)
         self._pair_plans = {}
+        # real-time propagation with a field-dressed (real) Fock matrix: t3 -= t3_pert_ijk (pycc/ccwfn.py:378-386,
+        # cctriples.py:547-562), i.e. one more term of W before the common denominator:
+        #   W[abc] -= (sum_d V[l,d] t2[i,j,a,d]) t2[k,l,c,b],  V = F - H.F
+        self.pert = False
+        self.Vov, self.Tp = E(o, v), E(o, o, v, o)
+        Tq = dict(Tp=self.Tp, t2=eng.t2, Vov=self.Vov)
+        self.pert_tmp = plan("Tp[ijal] = t2[ijad]*Vov[ld]", {k: TRef.of(t, k) for k, t in Tq.items()}, eng.dcode)
+        self.pert_w = TripletBatch(o, eng.dcode, ("W[abc] -= tmp[al]*t2k[lcb]",),
+                                   lambda i, j, k: dict(W=self.tri.W[k], tmp=self.Tp[i, j], t2k=eng.t2[k]), self.be)
 
     def build_intermediates(self):
         eng, be = self.eng, self.be
@@ -133,8 +142,14 @@ class CC3Engine(object):
         o, v = eng.no, eng.nv
         self.build_intermediates()
         self.tri.refresh_t2T()
+        if self.pert:
+            self.Vov.copy_(eng.F[:o, o:] - eng.F0[:o, o:])
+            for L in self.pert_tmp:
+                be.contract(L.desc)
         for (i, j) in self.my_pairs():
             self.tri._launch_pair(i, j, nk=o)
+            if self.pert:
+                self.pert_w.launch_pair(i, j, o)
             be.t3_combine(self.tri.W, o, 0, i, j, eng.eps, o, v, self.A1, self.A2)
             for L in self._plans_for(i, j):
                 be.contract(L.desc)

@@ -352,13 +352,22 @@ class ccwfn(object):
         if _is_complex(F) or _is_complex(t1) or _is_complex(t2):
             # complex amplitudes (real-time propagation, pycc/rt/rtcc.py:125): two real planes
             return self._complex().residuals(F, t1, t2)
-        if real_time and self.model == 'CC3':
-            # the reference adds t3_pert_ijk terms built from the field-dressed F (pycc/ccwfn.py:378-386)
-            raise NotImplementedError("real_time=True with model CC3 (t3_pert_ijk) is outside the B200 engine")
         eng = self.engine
+        # CC3 with real_time=True: the reference adds the t3_pert_ijk term built from V = F - H.F
+        # (pycc/ccwfn.py:378-386); complex CC3 amplitudes are outside the engine (_complex() raises)
+        pert = bool(real_time) and self.model == 'CC3'
+        if pert and eng.cc3 is None:
+            from .cc3_engine import CC3Engine
+            eng.cc3 = CC3Engine(eng)
         with self._Pure(self, t1, t2):   # pure: the object's amplitudes and H.F are put back afterwards
             self._load(F, t1, t2)
-            r1, r2 = eng.residuals(symmetrize=True)
+            if pert:
+                eng.cc3.pert = True
+            try:
+                r1, r2 = eng.residuals(symmetrize=True)
+            finally:
+                if pert:
+                    eng.cc3.pert = False
             r1, r2 = r1.clone(), r2.clone()
         return r1, r2
 

@@ -269,6 +269,24 @@ def test_cc3_model(name):
     assert np.abs(w.t2.cpu().numpy() - z["cc3_solve_t2"]).max() < T_TOL
 
 
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8", "o6v13"])
+def test_cc3_real_time_field(name):
+    """CC3 residuals with a field-dressed Fock matrix and real_time=True: the t3_pert_ijk term (pycc/ccwfn.py:378-386,
+    cctriples.py:547-562) against the reference's own vectors; the same call without real_time stays the plain CC3."""
+    import os
+    from tests.conftest import GOLDEN_DIR, Golden
+    g = Golden(name)
+    z = np.load(os.path.join(GOLDEN_DIR, "rtcc3", name + ".npz"))
+    w = _wfn(g.F, g.blocks, g.no, "CC3")
+    r1, r2 = w.residuals(z["F_field"], z["t1"], z["t2"], real_time=True)
+    assert np.abs(z["r2"] - z["r2_plain"]).max() > 1e-6
+    assert np.abs(r1.cpu().numpy() - z["r1"]).max() < 1e-12
+    assert np.abs(r2.cpu().numpy() - z["r2"]).max() < 1e-12
+    p1, p2 = w.residuals(z["F_field"], z["t1"], z["t2"])
+    assert np.abs(p1.cpu().numpy() - z["r1_plain"]).max() < 1e-12
+    assert np.abs(p2.cpu().numpy() - z["r2_plain"]).max() < 1e-12
+
+
 def test_amplitude_shard_roundtrip(golden):
     """Engine-only API used by bench.py's end-to-end leg: the amplitude vector goes to pinned host
     memory and back (one GPU: the shard is the whole vector) without changing a bit."""

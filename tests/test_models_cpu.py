@@ -75,3 +75,21 @@ def test_cc3_solve(name):
     assert len(w.iteration_log) == int(z["cc3_solve_niter"])
     assert abs(e - float(z["cc3_solve_ecc"])) < 1e-12
     assert np.abs(w.t2.numpy() - z["cc3_solve_t2"]).max() < 1e-11
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
+def test_cc3_real_time_field(name):
+    """CC3 residuals with a field-dressed Fock matrix and real_time=True (t3_pert_ijk, pycc/ccwfn.py:378-386)."""
+    import os
+    from tests.conftest import GOLDEN_DIR
+    g, _ = load(name)
+    z = np.load(os.path.join(GOLDEN_DIR, "rtcc3", name + ".npz"))
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CC3", _backend=InterpBackend())
+    r1, r2 = w.residuals(z["F_field"], z["t1"], z["t2"], real_time=True)
+    assert np.abs(z["r2"] - z["r2_plain"]).max() > 1e-6
+    assert np.abs(r1.numpy() - z["r1"]).max() < 1e-12 and np.abs(r2.numpy() - z["r2"]).max() < 1e-12
+    p1, p2 = w.residuals(z["F_field"], z["t1"], z["t2"])
+    assert np.abs(p1.numpy() - z["r1_plain"]).max() < 1e-12 and np.abs(p2.numpy() - z["r2_plain"]).max() < 1e-12
+    # the object's own Fock matrix and amplitudes are untouched
+    assert np.abs(w.H.F.numpy() - g.F).max() == 0.0
