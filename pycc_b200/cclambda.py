@@ -28,8 +28,6 @@ class cclambda(object):
             if not hasattr(ccwfn, "S1") or not hasattr(ccwfn, "S2"):
                 raise Exception("CCSD(T) Lambda needs the (T) source terms: construct ccwfn with make_t3_density=True "
                                 "or call ccwfn.t3_density() first.")
-            if ccwfn.comm.world > 1:
-                raise Exception("CCSD(T) Lambda runs on one GPU for now.")
             self.engine.t3_source = (ccwfn.S1, ccwfn.S2)
         if ccwfn.model == 'CC3':
             # triples contributions Y1 / Y2 of the loops in solve_lambda (cclambda.py:118-139, 160-235)

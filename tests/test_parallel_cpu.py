@@ -335,6 +335,66 @@ def test_two_ranks_gloo_complex(name, model):
             assert d[k] < 1e-12, (k, d[k])
 
 
+def _t3density_worker(rank, world, port, name, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.interp_backend import InterpBackend
+        from tests import t3density_checks as tc
+        import pycc_b200
+        g, z = tc.load(name)
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CCSD(T)", group="world", full_ovvv=True,
+                                            _backend=InterpBackend())
+            w._load(None, g["sym_t1"], g["sym_t2"])
+            et = w.t3_density()
+            out = dict(rank=rank, d_et=abs(et - float(z["sym_ET"])))
+            for f in tc.FIELDS:
+                out["d_" + f] = float(np.abs(getattr(w, f).numpy() - z["sym_" + f]).max())
+            # the chain solve_cc(make_t3_density) -> cchbar -> solve_lambda on two ranks
+            w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CCSD(T)", group="world", full_ovvv=True,
+                                            make_t3_density=True, _backend=InterpBackend())
+            ecc = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+            lecc = lam.solve_lambda(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+        out.update(d_ecc=abs(ecc - float(z["solve_ecc_total"])), d_lecc=abs(lecc - float(z["solve_lecc"])),
+                   niter=len(lam.iteration_log), niter_ref=int(z["solve_niter"]),
+                   d_l2=float(np.abs(lam.l2.numpy() - z["solve_l2"]).max()))
+        q.put(out)
+    except Exception:
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
+def test_two_ranks_gloo_t3_density(name):
+    """ccwfn.t3_density with the occupied pairs dealt over two ranks (one allreduce per accumulator), and the
+    CCSD(T) Lambda chain on top of the sharded HBAR / Lambda engines."""
+    from tests import t3density_checks as tc
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_t3density_worker, args=(r, world, port, name, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for d in res:
+        assert "error" not in d, d.get("error")
+        assert d["d_et"] < 1e-12
+        for f in tc.FIELDS:
+            assert d["d_" + f] < 1e-12, (f, d["d_" + f])
+        assert d["d_ecc"] < 1e-10 and d["d_lecc"] < 1e-10 and d["niter"] == d["niter_ref"] and d["d_l2"] < 1e-9
+
+
 def test_partition_helpers():
     from pycc_b200.parallel import virtual_slice, deal_pairs
     for nv in (1, 7, 19, 150, 250, 400):
