@@ -17,7 +17,7 @@ outer products) and eight consumer einsums.  Here ONE loop over the o^2 occupied
   * the T-only intermediates Zmndi, Zmdfa and the three extra dressed integrals (Wmbje, Wmbej, Wabef,
     cclambda.py:546-577) once per solve.
 
-No o^3 v^3 tensor exists.  One GPU.  The amplitudes t1, t2 are those held by the CCSD engine (converged T).
+No o^3 v^3 tensor exists.  Several GPUs: pairs dealt over the ranks, see __init__.  The amplitudes t1, t2 are those held by the CCSD engine (converged T).
 """
 import torch
 
@@ -51,8 +51,8 @@ _L3_CONSUMERS = (
     "Zbi[bde] += t2j[kbc]*X[kcde]",           # :208 Zbide[:,i]  (= Zblad_1; Zblad_2 is its transpose)
     "Zmaij[xa] += t2[xkbc]*P1[kbca]",         # :211 Zjlma[:,i,j]  (= Zjlid_2, :213)
     "Zd1ij[xd] += t2[xkbc]*P2[kbcd]",         # :212 Zjlid_1[:,i,j]
-    "r2ij[ab] += Wv[keda]*P2[kedb]",          # :215 Y2[i,j] += l3[deb] Wvvvo[e,d,a,k]
-    "r2i[lab] -= Woj[kld]*X[kdab]",           # :216 Y2[i]  -= l3[dab] Wovoo[l,d,j,k]
+    "Y2ij[ab] += Wv[keda]*P2[kedb]",          # :215 Y2[i,j] += l3[deb] Wvvvo[e,d,a,k]
+    "Y2i[lab] -= Woj[kld]*X[kdab]",           # :216 Y2[i]  -= l3[dab] Wovoo[l,d,j,k]
 )
 
 # once per solve, per pair (l, m) with n folded / batched; T[n][def] = t3_lmn (with denominator)
@@ -68,7 +68,7 @@ _Y1 = (
     "r1[ia] += l2[imdf]*Zmd[mdfa]",           # :197
     "r1[ia] += Loovv[imaf]*Znf[mf]",          # :198
     "r1[ia] += l2[mnad]*Zmn[mndi]",           # :200
-    "r1[ia] += Zb[ibde]*Wab[deab]",           # :218 Zbide . Wvvvv
+    "Y1w[ia] += ZbD[ibde]*Wab[deab]",         # :218 Zbide . Wvvvv (the rank's rows d of the dressed <de|ab>)
     "r1[ia] += Woooo[ijlm]*Zma[lmja]",        # :219-222
     "r1[ia] -= Zd1[lijd]*WA[ljda]",           # :225 Zjlid_1[j,l] . Wovov[j,:,l,:]
     "r1[ia] -= Zma[lijd]*WC[ljda]",           # :226 Zjlid_2[j,l] . Wovvo[j,:,:,l]
@@ -89,9 +89,9 @@ _DRESSED = (
     "Xej[mbej] -= ooov[nmje]*t1[nb]",         # <mn|ej> = <nm|je>
     "Q3[jmne] = t1[jf]*oovv[mnef]",
     "Xej[mbej] -= Q3[jmne]*t1[nb]",
-    "Wab[abef] -= t1[ma]*ovvv[mbef]",
-    "Wab[abef] -= ovvv[mafe]*t1[mb]",
-    "Wab[abef] += T11[mnab]*oovv[mnef]",
+    "Wab[abef] -= t1A[ma]*ovvv[mbef]",        # rows a of this rank's virtual slice (all of them on one GPU)
+    "Wab[abef] -= ovvvA[mafe]*t1[mb]",
+    "Wab[abef] += T11A[mnab]*oovv[mnef]",
 )
 
 
@@ -100,8 +100,6 @@ class CC3LambdaEngine(object):
         """``lam``: hbar_engine.LambdaEngine of a CC3 wave function."""
         self.lam, self.eng, self.be = lam, lam.eng, lam.be
         eng = self.eng
-        if eng.comm.world > 1:
-            raise ValueError("CC3 Lambda runs on one GPU for now")
         if eng.cc3 is None:
             from .cc3_engine import CC3Engine
             eng.cc3 = CC3Engine(eng)
@@ -117,15 +115,22 @@ class CC3LambdaEngine(object):
         self.Xje, self.Xej = E(o, v, o, v), E(o, v, v, o)
         self.Q2, self.Q3 = E(o, o, o, v), E(o, o, o, v)
         self.WA, self.WB, self.WC, self.WD = E(o, o, v, v), E(o, o, v, v), E(o, o, v, v), E(o, o, v, v)
-        self.Wab = E(v, v, v, v)
+        # several GPUs: the dressed <ab|ef> holds the rank's rows a only (like <ab|ef> itself); the occupied pairs of
+        # both loops are dealt round-robin; every Z intermediate and Y2 is a sum over pairs (one allreduce each), and
+        # the one term that reads the dressed <ab|ef> gives a partial Y1 (allreduce).  One GPU: the same code path.
+        vlo, vl = eng.vlo, eng.vl
+        self.Wab = E(vl, v, v, v)
+        self.Y1w, self.Y2 = E(o, v), E(o, o, v, v)
         b = eng.blk
         self._b = b
         T = dict(ovvv=eng.ovvv_full, ooov=b["ooov"], oovv=b["oovv"], t1=eng.t1, T11=cc3.T11, Xje=self.Xje, Xej=self.Xej,
-                 Q2=self.Q2, Q3=self.Q3, Wab=self.Wab)
+                 Q2=self.Q2, Q3=self.Q3, Wab=self.Wab, t1A=eng.t1.narrow(1, vlo, vl),
+                 ovvvA=eng.ovvv_full.narrow(1, vlo, vl), T11A=cc3.T11.narrow(2, vlo, vl))
         T = {k: TRef.of(t, k) for k, t in T.items()}
         self.dressed = [L for s in _DRESSED for L in plan(s, T, eng.dcode)]
         self.l3 = TripletBatch(o, eng.dcode, _L3, self._l3_tensors, self.be)
         T = dict(r1=lam.r1, l2=lam.l2, Zmd=self.Zmd, Loovv=eng.Loovv, Znf=self.Znf, Zmn=self.Zmn, Zb=self.Zb, Wab=self.Wab,
+                 Y1w=self.Y1w, ZbD=self.Zb.narrow(2, vlo, vl),
                  Woooo=cc3.Wmnij3, Zma=self.Zma, Zd1=self.Zd1, WA=self.WA, WB=self.WB, WC=self.WC, WD=self.WD)
         T = {k: TRef.of(t, k) for k, t in T.items()}
         self.y1 = [L for s in _Y1 for L in plan(s, T, eng.dcode)]
@@ -183,13 +188,19 @@ class CC3LambdaEngine(object):
         self.Zmd.zero_()
         cc3.tri.refresh()
         outs = dict(M=cc3.A2)
-        for l in range(o):
-            for m in range(o):
-                cc3.tri._launch_pair(l, m, nk=o)
-                be.t3_density_combine(cc3.tri.W, cc3.tri.W, o, 0, l, m, e.eps, o, v, outs)
-                for L in self._setup_for(l, m):
-                    be.contract(L.desc)
+        for (l, m) in self.my_pairs():
+            cc3.tri._launch_pair(l, m, nk=o)
+            be.t3_density_combine(cc3.tri.W, cc3.tri.W, o, 0, l, m, e.eps, o, v, outs)
+            for L in self._setup_for(l, m):
+                be.contract(L.desc)
+        if e.comm.world > 1:
+            e.comm.allreduce_(self.Zmn)
+            e.comm.allreduce_(self.Zmd)
         self.ready = True
+
+    def my_pairs(self):
+        o, c = self.eng.no, self.eng.comm
+        return [(i, j) for i in range(o) for j in range(o)][c.rank::c.world]
 
     def _setup_for(self, l, m):
         key = (l, m)
@@ -206,7 +217,7 @@ class CC3LambdaEngine(object):
         if key not in self._pair:
             e, lam, cc3 = self.eng, self.lam, self.cc3
             T = dict(X=self.X, P1=self.P1, P2=self.P2, t2=e.t2, t2j=e.t2[j], Zbi=self.Zb[i], Zmaij=self.Zma[i, j],
-                     Zd1ij=self.Zd1[i, j], r2ij=lam.r2[i, j], r2i=lam.r2[i], Wv=cc3.Wv, Woj=cc3.Wo[j],
+                     Zd1ij=self.Zd1[i, j], Y2ij=self.Y2[i, j], Y2i=self.Y2[i], Wv=cc3.Wv, Woj=cc3.Wo[j],
                      A1=cc3.A1, l2ij=lam.l2[i, j], Znf=self.Znf)
             T = {k: TRef.of(t, k) for k, t in T.items()}
             con = [L for s in _L3_CONSUMERS for L in plan(s, T, e.dcode)]
@@ -222,23 +233,30 @@ class CC3LambdaEngine(object):
         e, be, cc3, lam = self.eng, self.be, self.cc3, self.lam
         o, v = e.no, e.nv
         be.bind_stream()
-        for z in (self.Znf, self.Zb, self.Zma, self.Zd1):
+        acc = (self.Znf, self.Zb, self.Zma, self.Zd1, self.Y2)
+        for z in acc + (self.Y1w,):
             z.zero_()
         t_out, x_out = dict(A1=cc3.A1), dict(M=self.X)
-        for i in range(o):
-            for j in range(o):
-                con, znf = self._pair_plans(i, j)
-                # t3 of (l, m, n) = (i, j, batch): Znf
-                cc3.tri._launch_pair(i, j, nk=o)
-                be.t3_density_combine(cc3.tri.W, cc3.tri.W, o, 0, i, j, e.eps, o, v, t_out)
-                for L in znf:
-                    be.contract(L.desc)
-                # l3 of (k, i, j), k = batch
-                self.l3.launch_pair(i, j, o)
-                be.t3_density_combine(self.L3, self.L3, o, 0, i, j, e.eps, o, v, x_out)
-                be.permute4(self.P1, self.X.permute(0, 3, 1, 2))       # P1[k][b][c][a] = X[k][c][a][b]
-                be.permute4(self.P2, self.X.permute(0, 2, 1, 3))       # P2[k][b][a][c] = X[k][a][b][c]
-                for L in con:
-                    be.contract(L.desc)
+        for (i, j) in self.my_pairs():
+            con, znf = self._pair_plans(i, j)
+            # t3 of (l, m, n) = (i, j, batch): Znf
+            cc3.tri._launch_pair(i, j, nk=o)
+            be.t3_density_combine(cc3.tri.W, cc3.tri.W, o, 0, i, j, e.eps, o, v, t_out)
+            for L in znf:
+                be.contract(L.desc)
+            # l3 of (k, i, j), k = batch
+            self.l3.launch_pair(i, j, o)
+            be.t3_density_combine(self.L3, self.L3, o, 0, i, j, e.eps, o, v, x_out)
+            be.permute4(self.P1, self.X.permute(0, 3, 1, 2))       # P1[k][b][c][a] = X[k][c][a][b]
+            be.permute4(self.P2, self.X.permute(0, 2, 1, 3))       # P2[k][b][a][c] = X[k][a][b][c]
+            for L in con:
+                be.contract(L.desc)
+        if e.comm.world > 1:
+            for z in acc:
+                e.comm.allreduce_(z)
         for L in self.y1:
             be.contract(L.desc)
+        if e.comm.world > 1:
+            e.comm.allreduce_(self.Y1w)
+        be.axpby(lam.r1, 1.0, lam.r1, 1.0, self.Y1w)
+        be.axpby(lam.r2, 1.0, lam.r2, 1.0, self.Y2)

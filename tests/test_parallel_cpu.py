@@ -395,6 +395,70 @@ def test_two_ranks_gloo_t3_density(name):
         assert d["d_ecc"] < 1e-10 and d["d_lecc"] < 1e-10 and d["niter"] == d["niter_ref"] and d["d_l2"] < 1e-9
 
 
+def _cc3_lambda_worker(rank, world, port, name, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.interp_backend import InterpBackend
+        from tests import lambda_cc3_checks as l3
+        import pycc_b200
+        from pycc_b200.parallel import virtual_slice
+        g, z = l3.load(name)
+        lo, hi = virtual_slice(g.nv, rank, world)
+        blocks = dict(g.blocks)
+        blocks["vvvv"] = np.ascontiguousarray(blocks["vvvv"][lo:hi])
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model="CC3", group="world", _backend=InterpBackend())
+            w._load(None, z["t1"], z["t2"])
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+            lam._load(z["l1"], z["l2"])
+            r1, r2 = lam.engine.residuals(symmetrize=True)
+            out = dict(rank=rank, d_r1=float(np.abs(r1.numpy() - z["r1"]).max()),
+                       d_r2=float(np.abs(r2.numpy() - z["r2"]).max()), rows=int(lam.engine.cc3.Wab.shape[0]))
+            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model="CC3", group="world", _backend=InterpBackend())
+            ecc = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+            lecc = lam.solve_lambda(e_conv=1e-12, r_conv=1e-12, maxiter=100)
+        out.update(d_ecc=abs(ecc - float(z["solve_ecc"])), d_lecc=abs(lecc - float(z["solve_lecc"])),
+                   niter=len(lam.iteration_log), niter_ref=int(z["solve_niter"]),
+                   d_l2=float(np.abs(lam.l2.numpy() - z["solve_l2"]).max()))
+        q.put(out)
+    except Exception:
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
+def test_two_ranks_gloo_cc3_lambda(name):
+    """The CC3 Lambda equations on two ranks: pairs of the t3 / l3 loops dealt over the ranks, the dressed <ab|ef> held
+    by rows, Z intermediates and Y2 completed by allreduces."""
+    from tests.conftest import Golden
+    g = Golden(name)
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_cc3_lambda_worker, args=(r, world, port, name, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=900) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for d in res:
+        assert "error" not in d, d.get("error")
+    assert sum(d["rows"] for d in res) == g.nv
+    for d in res:
+        assert d["d_r1"] < 1e-11 and d["d_r2"] < 1e-11
+        assert d["d_ecc"] < 1e-10 and d["d_lecc"] < 1e-10 and d["niter"] == d["niter_ref"] and d["d_l2"] < 1e-9
+
+
 def test_partition_helpers():
     from pycc_b200.parallel import virtual_slice, deal_pairs
     for nv in (1, 7, 19, 150, 250, 400):
