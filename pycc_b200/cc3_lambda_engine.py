@@ -137,6 +137,7 @@ class CC3LambdaEngine(object):
         self._pair = {}
         self._setup_plans = {}
         self.ready = False
+        self.pert = False            # set by cclambda.residuals when ccwfn.real_time is on and F carries a field
 
     # ---- tensors of one triplet for the l3 statements -------------------------------------------------------
     def _l3_tensors(self, i, j, k):
@@ -161,8 +162,7 @@ class CC3LambdaEngine(object):
         e, be, cc3 = self.eng, self.be, self.cc3
         o, v = e.no, e.nv
         be.bind_stream()
-        e.set_fock(e.F0)
-        e.run_builder("Fme")                       # Fov = build_Fme(t1)
+        e.run_builder("Fme")                       # Fov = build_Fme(F, t1) for the Fock matrix the engine holds
         cc3.build_intermediates()                  # Wmnij, Wmbij, Wmnie, Wamef, Wabei at the converged t1
         b = self._b
         # Wvovv[e,m,x,y] = Wamef[e,m,x,y] = Wk[m][e][x][y]
@@ -188,8 +188,14 @@ class CC3LambdaEngine(object):
         self.Zmd.zero_()
         cc3.tri.refresh()
         outs = dict(M=cc3.A2)
+        if self.pert:                              # ccwfn.real_time: t3 -= t3_pert_ijk (cclambda.py:350-356, 396-402)
+            cc3.Vov.copy_(e.F[:o, o:] - e.F0[:o, o:])
+            for L in cc3.pert_tmp:
+                be.contract(L.desc)
         for (l, m) in self.my_pairs():
             cc3.tri._launch_pair(l, m, nk=o)
+            if self.pert:
+                cc3.pert_w.launch_pair(l, m, o)
             be.t3_density_combine(cc3.tri.W, cc3.tri.W, o, 0, l, m, e.eps, o, v, outs)
             for L in self._setup_for(l, m):
                 be.contract(L.desc)
@@ -241,6 +247,8 @@ class CC3LambdaEngine(object):
             con, znf = self._pair_plans(i, j)
             # t3 of (l, m, n) = (i, j, batch): Znf
             cc3.tri._launch_pair(i, j, nk=o)
+            if self.pert:
+                cc3.pert_w.launch_pair(i, j, o)
             be.t3_density_combine(cc3.tri.W, cc3.tri.W, o, 0, i, j, e.eps, o, v, t_out)
             for L in znf:
                 be.contract(L.desc)

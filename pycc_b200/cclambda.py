@@ -83,11 +83,13 @@ class cclambda(object):
         if any(_is_complex(x) for x in (F, t1, t2, l1, l2)):
             # rtcc.f (pycc/rt/rtcc.py:132): complex amplitudes, HBAR rebuilt from them
             return self.ccwfn._complex().lambda_residuals(F, t1, t2, l1, l2)
-        if self.ccwfn.model == 'CC3':
-            # the reference's CC3 branch of residuals() (cclambda.py:323-440) repeats the solve_lambda loops for
-            # other (F, t1, t2): not built - only solve_lambda carries the CC3 triples terms
-            raise NotImplementedError("cclambda.residuals with model CC3 is outside the B200 engine (use solve_lambda)")
         w, eng, le = self.ccwfn, self.ccwfn.engine, self.engine
+        cc3 = getattr(le, "cc3", None)
+        if cc3 is not None:
+            # the CC3 branch (cclambda.py:323-440) repeats the solve_lambda loops for THESE (F, t1, t2): the T-only
+            # intermediates are rebuilt from them, with the t3_pert_ijk term when the wave function is a real-time one
+            cc3.ready = False
+            cc3.pert = bool(getattr(w, "real_time", False))
         own_t = t1 is eng.t1 and t2 is eng.t2
         own_l = l1 is le.l1 and l2 is le.l2
         self.hbar.engine.snapshot()
@@ -100,6 +102,8 @@ class cclambda(object):
         self._load(l1, l2)
         r1, r2 = le.residuals(symmetrize=True)
         r1, r2 = r1.clone(), r2.clone()
+        if cc3 is not None:
+            cc3.ready, cc3.pert = False, False     # the next solve_lambda rebuilds them from the object's own amplitudes
         if not own_t:
             eng.t1.copy_(kt1)
             eng.t2.copy_(kt2)

@@ -57,3 +57,21 @@ def check_solve(name, backend):
     assert abs(lecc - float(z["solve_lecc"])) < 1e-10
     assert np.abs(lam.l1.cpu().numpy() - z["solve_l1"]).max() < 1e-9
     assert np.abs(lam.l2.cpu().numpy() - z["solve_l2"]).max() < 1e-9
+
+
+def check_residuals_entry(name, backend, tol=1e-11):
+    """cclambda.residuals(F, t1, t2, l1, l2) for CC3 (the real-time entry, pycc/cclambda.py:276-447) with a
+    field-dressed Fock matrix, for a plain and a real_time wave function (t3_pert_ijk inside the t3 loops); the call is
+    pure: a solve_lambda afterwards reproduces the reference's chain."""
+    import pycc_b200
+    from tests.conftest import GOLDEN_DIR
+    g, zs = load(name)
+    z = np.load(os.path.join(GOLDEN_DIR, "rtcc3", name + "_lambda.npz"))
+    assert np.abs(z["rt_r1"] - z["plain_r1"]).max() > 1e-7
+    for tag, rt in (("plain", False), ("rt", True)):
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CC3", real_time=rt, _backend=backend)
+            lam = pycc_b200.cclambda(w, pycc_b200.cchbar(w))
+        r1, r2 = lam.residuals(z["F_field"], z["t1"], z["t2"], z["l1"], z["l2"])
+        assert np.abs(r1.cpu().numpy() - z[tag + "_r1"]).max() < tol
+        assert np.abs(r2.cpu().numpy() - z[tag + "_r2"]).max() < tol
