@@ -81,6 +81,25 @@ def test_golden_builder_api_and_operator(golden):
     assert np.abs(Dd.cpu().numpy() - ot.v_disconnected(F, Blocks(g.blocks), t1, t2, g.no - 1, 1, 0) / den).max() < 1e-11
 
 
+@pytest.mark.parametrize("no,nv", [(1, 1), (1, 3), (2, 1), (3, 2), (1, 17), (17, 2)])
+def test_degenerate_shapes_vs_oracle(no, nv):
+    """Edge cases: a single occupied or virtual orbital, more occupied than virtual orbitals - every tile ragged, every
+    index group of extent one somewhere.  Converged CCSD(T) against the oracle."""
+    import pycc_b200
+    from pycc_b200.synthetic import SyntheticSystem
+    from oracle import ccsd_oracle as oc, triples_oracle as ot
+    s = SyntheticSystem(no, nv, seed=3 * no + nv, fock_offdiag=True)
+    w = _wfn(s.F, s.blocks, no)
+    with contextlib.redirect_stdout(io.StringIO()):
+        e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=200)
+    eo, t1, t2, niter = oc.solve_cc(s.F, s.blocks, 1e-12, 1e-12, maxiter=200)
+    if no * nv + (no * nv) ** 2 > 16:        # fewer unknowns than DIIS vectors: the singular DIIS system amplifies rounding
+        assert len(w.iteration_log) == niter
+    assert abs(e - eo) < E_TOL
+    assert np.abs(w.t2.cpu().numpy() - t2).max() < T_TOL
+    assert abs(pycc_b200.t_tjl(w) - ot.t_tjl(s.F, s.blocks, t1, t2)) < 1e-12
+
+
 @pytest.mark.parametrize("no,nv,offdiag", [(8, 30, True), (10, 44, False), (7, 51, True)])
 def test_seeded_systems_vs_oracle(no, nv, offdiag):
     """Sizes the reference itself would need minutes for; the oracle (pinned) does them in seconds."""

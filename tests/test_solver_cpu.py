@@ -152,3 +152,26 @@ def test_integral_front_end_host_logic():
     from tests import frontend_checks as fc
     fc.check_factor_blocks(InterpBackend())
     fc.check_ao_transform(InterpBackend())
+
+
+@pytest.mark.parametrize("no,nv", [(1, 1), (1, 3), (2, 1), (3, 2), (1, 17), (9, 2)])
+def test_degenerate_shapes_vs_oracle(no, nv):
+    """Edge cases of the host logic (planner, DIIS, triplet batching): a single occupied or virtual orbital, more
+    occupied than virtual orbitals.  Converged CCSD(T) through the interpreter back end against the oracle."""
+    import contextlib, io
+    import numpy as np
+    import pycc_b200
+    from pycc_b200.synthetic import SyntheticSystem
+    from tests.interp_backend import InterpBackend
+    from oracle import ccsd_oracle as oc, triples_oracle as ot
+    s = SyntheticSystem(no, nv, seed=3 * no + nv, fock_offdiag=True)
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(s.F, s.blocks, no, model="CCSD(T)", _backend=InterpBackend())
+        e = w.solve_cc(e_conv=1e-12, r_conv=1e-12, maxiter=200)
+    eo, t1, t2, niter = oc.solve_cc(s.F, s.blocks, 1e-12, 1e-12, maxiter=200)
+    if no * nv + (no * nv) ** 2 > 16:        # fewer unknowns than DIIS vectors: the singular DIIS system amplifies rounding
+        assert len(w.iteration_log) == niter
+    et = ot.t_tjl(s.F, s.blocks, t1, t2)
+    assert abs(e - (eo + et)) < 1e-11                 # model CCSD(T): solve_cc returns E(CCSD) + E(T)
+    assert np.abs(w.t2.numpy() - t2).max() < 1e-10
+    assert abs(pycc_b200.t_tjl(w) - et) < 1e-12
