@@ -41,6 +41,16 @@ class CudaBackend(object):
         self._stream = None
         self.bind_stream()
 
+    def ensure_workspace(self, nbytes):
+        """Grow the split-K workspace to at least ``nbytes`` (the engine sizes it for the tail-aware split of a
+        rank's largest output, pccb_contract in contract.cu).  Launches already queued keep the old buffer alive
+        until they finish (stream-ordered free of the caching allocator)."""
+        nbytes = int(nbytes)
+        if nbytes > self._ws.numel():
+            self.synchronize()
+            self._ws = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+            self._check(self.lib.pccb_set_workspace(self.h, self._ws.data_ptr(), nbytes))
+
     # -- plumbing ------------------------------------------------------------------------------
     def _check(self, rc):
         if rc != 0:

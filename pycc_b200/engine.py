@@ -90,6 +90,10 @@ class CCSDEngine(object):
         self.Looov = be.empty((o, o, o, v), dtype)
         be.permute4(self.Looov, self.blk["ooov"], 2.0, 0.0)
         be.permute4(self.Looov, self.blk["ooov"].permute(1, 0, 2, 3), -1.0, 1.0)
+        # several GPUs: a rank's largest outputs (o^2 x vl v) are a few waves of long tiles; the tail-aware split-K of
+        # pccb_contract needs up to 4 partial copies of one in the workspace (256 MB by default)
+        if self.comm.world > 1 and hasattr(be, "ensure_workspace"):
+            be.ensure_workspace(min(2 << 30, 4 * o * o * vl * v * (8 if dtype == torch.float64 else 4)))
         # amplitudes and per-iteration buffers (intermediates carrying the sliced index are local-sized)
         E = lambda *s: be.zeros(s, dtype)
         # Several GPUs: the amplitude update is split over the ranks by (i,j) blocks of t2 - rank g owns the

@@ -32,6 +32,9 @@ class InterpBackend(object):
         self.n_contract = 0
         self.log = []
 
+    def ensure_workspace(self, nbytes):
+        pass
+
     def bind_stream(self):
         pass
 
