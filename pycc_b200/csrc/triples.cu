@@ -269,12 +269,26 @@ __global__ void t3_density_combine_kernel(const T* __restrict__ W, const T* __re
         const T* Dk = Dd + (long long)kk * v3;
         const double d = (double)eps[i] + (double)eps[j] + (double)eps[k0 + kk] - (double)eps[no + a] -
                          (double)eps[no + b] - (double)eps[no + c];
-        auto at = [&](const T* X, int x, int y, int z) { return (double)X[x * v2 + (long long)y * nv + z] / d; };
-        const double mabc = at(Wk, a, b, c), mbac = at(Wk, b, a, c), macb = at(Wk, a, c, b), mcba = at(Wk, c, b, a),
-                     mcab = at(Wk, c, a, b), mbca = at(Wk, b, c, a);
+        const double rd = 1.0 / d;      // one division per element; the twelve permuted values are scaled by it
+        auto at = [&](const T* X, int x, int y, int z) { return (double)X[x * v2 + (long long)y * nv + z] * rd; };
+        // only the permutations the requested outputs consume are read (the transposed ones are strided accesses:
+        // a caller that wants M alone - the CC3 Lambda engine - pays one coalesced read); with P / Q requested all
+        // twelve loads are issued unconditionally, back to back
+        double mabc, mbac, macb, mcba, mcab, mbca, xn = 0.0;
+        if (o.P || o.Q) {
+            mabc = at(Wk, a, b, c); mbac = at(Wk, b, a, c); macb = at(Wk, a, c, b); mcba = at(Wk, c, b, a);
+            mcab = at(Wk, c, a, b); mbca = at(Wk, b, c, a);
+            xn = 8.0 * at(Dk, a, b, c) - 4.0 * at(Dk, b, a, c) - 4.0 * at(Dk, a, c, b) - 4.0 * at(Dk, c, b, a) +
+                 2.0 * at(Dk, c, a, b) + 2.0 * at(Dk, b, c, a);
+        } else {
+            mabc = at(Wk, a, b, c);
+            mbac = (o.B1 || o.Z3) ? at(Wk, b, a, c) : 0.0;
+            macb = (o.A2 || o.Z3) ? at(Wk, a, c, b) : 0.0;
+            mcba = (o.A1 || o.A2) ? at(Wk, c, b, a) : 0.0;
+            mbca = o.Z3 ? at(Wk, b, c, a) : 0.0;
+            mcab = 0.0;
+        }
         const double xm = 8.0 * mabc - 4.0 * mbac - 4.0 * macb - 4.0 * mcba + 2.0 * mcab + 2.0 * mbca;
-        const double xn = 8.0 * at(Dk, a, b, c) - 4.0 * at(Dk, b, a, c) - 4.0 * at(Dk, a, c, b) - 4.0 * at(Dk, c, b, a) +
-                          2.0 * at(Dk, c, a, b) + 2.0 * at(Dk, b, c, a);
         if (o.M) o.M[idx] = (T)mabc;
         if (o.A1) o.A1[idx] = (T)(mabc - mcba);
         if (o.A2) o.A2[idx] = (T)(2.0 * mabc - macb - mcba);

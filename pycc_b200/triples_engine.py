@@ -92,9 +92,17 @@ class TripletBatch(object):
                      for f in fields}
             self.templates.append((L[0], fields, deriv))
         self._keep = base
+        self._cache = {}
         self.itemsize = tensors_fn(0, 0, 0)[next(iter(tensors_fn(0, 0, 0)))].element_size()
 
     def launch_pair(self, i, j, nk):
+        key = (i, j, nk)
+        cached = self._cache.get(key)
+        if cached is not None:           # the patched descriptors of a pair are reused by every later iteration
+            for d in cached:
+                self.be.contract(d)
+            return
+        made = []
         for (L, fields, deriv) in self.templates:
             d = _lib.Contraction()
             C.memmove(C.byref(d), C.byref(L.desc), C.sizeof(d))
@@ -110,6 +118,9 @@ class TripletBatch(object):
                     d.seg[q].b_batch = dk // self.itemsize
             d.batch = nk
             self.be.contract(d)
+            made.append(d)
+        if len(self._cache) < 4096:
+            self._cache[key] = made
 
 
 class TriplesEngine(object):
@@ -195,6 +206,14 @@ class TriplesEngine(object):
 
     def _launch_pair(self, i, j, nk=None):
         """W[k] for k = 0..nk-1 (default: 0..j) of the pair (i, j): three batched contractions."""
+        key = (i, j, nk)
+        cache = self.__dict__.setdefault("_desc_cache", {})
+        cached = cache.get(key)
+        if cached is not None:
+            for d in cached:
+                self.be.contract(d)
+            return
+        made = []
         for (L, fields, deriv) in self.templates:
             d = _lib.Contraction()
             C.memmove(C.byref(d), C.byref(L.desc), C.sizeof(d))
@@ -210,6 +229,9 @@ class TriplesEngine(object):
                     d.seg[q].b_batch = dk // self.itemsize
             d.batch = (j + 1) if nk is None else nk
             self.be.contract(d)
+            made.append(d)
+        if len(cache) < 4096:
+            cache[key] = made
 
     def pairs(self):
         """All occupied pairs (i >= j)."""
