@@ -90,3 +90,27 @@ def test_cc3_lambda(name):
     l3.check_solve(name, be)
     if name != "o6v13":
         l3.check_residuals_entry(name, be)
+
+
+def test_sp_mode_round2_engines():
+    """precision='SP' through the round-2 engines (t3_density, CC3 Lambda): FP32 storage and contractions, FP64 scalars;
+    against the reference's FP64 vectors at single-precision tolerance."""
+    import contextlib, io
+    import numpy as np
+    from tests import lambda_cc3_checks as l3, t3density_checks as tc
+    g, z = l3.load("o4v8")
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CC3", precision="SP")
+        w._load(None, z["t1"], z["t2"])
+        lam = pycc_b200.cclambda(w, pycc_b200.cchbar(w))
+    lam._load(z["l1"], z["l2"])
+    r1, r2 = lam.engine.residuals(symmetrize=True)
+    assert str(r2.dtype) == "torch.float32"
+    assert np.abs(r1.double().cpu().numpy() - z["r1"]).max() < 3e-5 and np.abs(r2.double().cpu().numpy() - z["r2"]).max() < 3e-5    # |r| ~ 1.5: FP32 rounding of the stored blocks
+    g, z = tc.load("o4v8")
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, model="CCSD(T)", precision="SP")
+        w._load(None, g["sym_t1"], g["sym_t2"])
+        et = w.t3_density()
+    assert abs(et - float(z["sym_ET"])) < 1e-7
+    assert np.abs(w.S2.double().cpu().numpy() - z["sym_S2"]).max() < 1e-6
