@@ -212,7 +212,9 @@ int pccb_t3_combine(pccb_ctx* ctx, int dtype, const void* w_dev, int nk, int k0,
  * combinations the density / Lambda contractions consume, out7 = {M, A1, A2, B1, Z3, P, Q} (any may be NULL):
  *   M = W/D, N = Dd/D, X(T) = 8T - 4T[bac] - 4T[acb] - 4T[cba] + 2T[cab] + 2T[bca],
  *   A1 = M - M[cba], A2 = 2M - M[acb] - M[cba], B1 = 2(M - M[bac]), Z3 = 2(M - M[acb]) - (M[bac] - M[bca]),
- *   P = 2X(M) + X(N), Q = X(M) + X(N).  Asynchronous. */
+ *   P = 2X(M) + X(N), Q = X(M) + X(N).  Only the permutations the non-NULL outputs consume are read (dd_dev is read
+ * for P / Q only and may alias w_dev otherwise: the CC3 Lambda engine asks for M or A1 alone, pycc/cclambda.py:133,
+ * 193, 206).  Asynchronous. */
 int pccb_t3_density_combine(pccb_ctx* ctx, int dtype, const void* w_dev, const void* dd_dev, int nk, int k0, int i, int j,
                             const void* eps_dev, int64_t no, int64_t nv, void* const* out7_dev_hostarray);
 
