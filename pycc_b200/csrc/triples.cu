@@ -9,6 +9,7 @@
 // Reductions are fixed-order: warp shuffle -> block -> one partial per CTA -> one block per
 // triplet.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -299,6 +300,87 @@ __global__ void t3_density_combine_kernel(const T* __restrict__ W, const T* __re
     }
 }
 
+// Brick form of the two combine kernels (the default): one CTA per 8x8x8 brick (TA, TB, TC) of one k.  The permuted
+// values M[bac], M[acb], ... of the CTA's elements live in the bricks (TB,TA,TC), (TA,TC,TB), ...: each is fetched with
+// coalesced 64-byte runs and transposed through the XOR-swizzled shared-memory layout of the energy kernel, instead
+// of the element-wise kernels' strided 8-byte reads (one useful double per 32-byte sector).  Outputs are written at the
+// element's own position, coalesced.  Only the bricks the requested outputs consume are fetched.
+template <typename T>
+__global__ void __launch_bounds__(512) t3_combine_brick_kernel(const T* __restrict__ W, const T* __restrict__ Dd, int k0,
+                                                               int i, int j, const T* __restrict__ eps, int no, int nv,
+                                                               int nb, const __grid_constant__ T3DensityOut<T> o) {
+    __shared__ double sW[5][BRICK];
+    const int tid = threadIdx.x;
+    const int lc = tid & 7, lb = (tid >> 3) & 7, la = tid >> 6;
+    const int bx = blockIdx.x, kk = blockIdx.y;
+    const int TC = bx % nb, TB = (bx / nb) % nb, TA = bx / (nb * nb);
+    const int A0 = TA * TB_, B0 = TB * TB_, C0 = TC * TB_;
+    const int a = A0 + la, b = B0 + lb, c = C0 + lc;
+    const long long v2 = (long long)nv * nv, v3 = v2 * nv;
+    const T* Wk = W + (long long)kk * v3;
+    const bool need_x = o.P || o.Q;
+    const bool n_bac = need_x || o.B1 || o.Z3, n_acb = need_x || o.A2 || o.Z3, n_cba = need_x || o.A1 || o.A2,
+               n_bca = need_x || o.Z3;
+    // this thread's element of the permuted bricks (brick-local position (la, lb, lc) of each)
+    auto gather = [&](const T* X, double& xabc, double& xacb, double& xbac, double& xbca, double& xcab, double& xcba) {
+        xabc = fetch_brick(X, nv, A0, B0, C0, tid);
+        const double r1 = n_acb ? fetch_brick(X, nv, A0, C0, B0, tid) : 0.0;     // [a][c][b]
+        const double r2 = n_bac ? fetch_brick(X, nv, B0, A0, C0, tid) : 0.0;     // [b][a][c]
+        const double r3 = n_bca ? fetch_brick(X, nv, B0, C0, A0, tid) : 0.0;     // [b][c][a]
+        const double r4 = need_x ? fetch_brick(X, nv, C0, A0, B0, tid) : 0.0;    // [c][a][b]
+        const double r5 = n_cba ? fetch_brick(X, nv, C0, B0, A0, tid) : 0.0;     // [c][b][a]
+        __syncthreads();
+        store_brick(sW[0], r1, tid); store_brick(sW[1], r2, tid); store_brick(sW[2], r3, tid);
+        store_brick(sW[3], r4, tid); store_brick(sW[4], r5, tid);
+        __syncthreads();
+        xacb = brick_at(sW[0], la, lc, lb);
+        xbac = brick_at(sW[1], lb, la, lc);
+        xbca = brick_at(sW[2], lb, lc, la);
+        xcab = brick_at(sW[3], lc, la, lb);
+        xcba = brick_at(sW[4], lc, lb, la);
+    };
+    double mabc, macb, mbac, mbca, mcab, mcba;
+    gather(Wk, mabc, macb, mbac, mbca, mcab, mcba);
+    double xn = 0.0;
+    if (need_x) {
+        double nabc, nacb, nbac, nbca, ncab, ncba;
+        gather(Dd + (long long)kk * v3, nabc, nacb, nbac, nbca, ncab, ncba);
+        xn = 8.0 * nabc - 4.0 * nbac - 4.0 * nacb - 4.0 * ncba + 2.0 * ncab + 2.0 * nbca;
+    }
+    if (a >= nv || b >= nv || c >= nv) return;
+    const double d = (double)eps[i] + (double)eps[j] + (double)eps[k0 + kk] - (double)eps[no + a] - (double)eps[no + b] -
+                     (double)eps[no + c];
+    const double rd = 1.0 / d;
+    mabc *= rd; macb *= rd; mbac *= rd; mbca *= rd; mcab *= rd; mcba *= rd; xn *= rd;
+    const double xm = 8.0 * mabc - 4.0 * mbac - 4.0 * macb - 4.0 * mcba + 2.0 * mcab + 2.0 * mbca;
+    const long long idx = (long long)kk * v3 + a * v2 + (long long)b * nv + c;
+    if (o.M) o.M[idx] = (T)mabc;
+    if (o.A1) o.A1[idx] = (T)(mabc - mcba);
+    if (o.A2) o.A2[idx] = (T)(2.0 * mabc - macb - mcba);
+    if (o.B1) o.B1[idx] = (T)(2.0 * (mabc - mbac));
+    if (o.Z3) o.Z3[idx] = (T)(2.0 * (mabc - macb) - (mbac - mbca));
+    if (o.P) o.P[idx] = (T)(2.0 * xm + xn);
+    if (o.Q) o.Q[idx] = (T)(xm + xn);
+}
+
+template <typename T>
+int launch_combine_brick(pccb_ctx* ctx, const void* w_dev, const void* dd_dev, int nk, int k0, int i, int j,
+                         const void* eps_dev, int64_t no, int64_t nv, void* const* q) {
+    const int nb = (int)((nv + TB_ - 1) / TB_);
+    T3DensityOut<T> o{(T*)q[0], (T*)q[1], (T*)q[2], (T*)q[3], (T*)q[4], (T*)q[5], (T*)q[6]};
+    dim3 grid((unsigned)(nb * nb * nb), (unsigned)nk);
+    t3_combine_brick_kernel<T><<<grid, 512, 0, ctx->stream>>>((const T*)w_dev, (const T*)dd_dev, k0, i, j, (const T*)eps_dev,
+                                                              (int)no, (int)nv, nb, o);
+    PCCB_CHECK_LAUNCH(ctx, "t3_combine_brick_kernel");
+    return PCCB_OK;
+}
+
+// PCCB_COMBINE_BRICK=0 restores the element-wise kernels (kept as the cross-check of the brick form)
+bool use_combine_brick(int64_t nv) {
+    static const bool on = [] { const char* e = getenv("PCCB_COMBINE_BRICK"); return !(e && e[0] == '0'); }();
+    return on && nv <= 1290;        // nb^3 bricks in grid.x
+}
+
 template <typename T>
 int triples_energy_t(pccb_ctx* ctx, const void* w_dev, const int32_t* ijk_dev, int ntrip, const void* t1,
                      const void* t2, const void* g, const void* fov, int64_t ld_fov, const void* eps, int64_t no,
@@ -370,10 +452,15 @@ extern "C" int pccb_t3_density_combine(pccb_ctx* ctx, int dtype, const void* w_d
     PCCB_REQUIRE(ctx, w_dev && dd_dev && eps_dev && out7_dev_hostarray && nk >= 1 && no > 0 && nv > 0 && i >= 0 && j >= 0 &&
                           k0 >= 0 && k0 + nk <= no && i < no && j < no,
                  "pccb_t3_density_combine: bad arguments");
+    void* const* q = out7_dev_hostarray;
+    // all six permutations of W and Dd (P / Q requested: ccwfn.t3_density): the brick form, 1.36 -> 1.27 s at (16,120);
+    // with one to three permutations (CC3: A1 / A2, M alone) the element-wise kernel is as fast or faster
+    if ((q[5] || q[6]) && use_combine_brick(nv) && nk <= 65535 && (dtype == PCCB_F64 || dtype == PCCB_F32))
+        return dtype == PCCB_F64 ? launch_combine_brick<double>(ctx, w_dev, dd_dev, nk, k0, i, j, eps_dev, no, nv, q)
+                                 : launch_combine_brick<float>(ctx, w_dev, dd_dev, nk, k0, i, j, eps_dev, no, nv, q);
     const long long total = (long long)nk * nv * nv * nv;
     long long blocks = (total + 255) / 256;
     if (blocks > 148 * 16) blocks = 148 * 16;
-    void* const* q = out7_dev_hostarray;
     if (dtype == PCCB_F64) {
         T3DensityOut<double> o{(double*)q[0], (double*)q[1], (double*)q[2], (double*)q[3], (double*)q[4], (double*)q[5], (double*)q[6]};
         t3_density_combine_kernel<double><<<(unsigned)blocks, 256, 0, ctx->stream>>>(
