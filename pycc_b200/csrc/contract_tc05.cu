@@ -33,7 +33,10 @@
 
 namespace {
 
-constexpr int BM = 128, BN = 256, BKF = 32;            // 32 floats = one 128-byte swizzle row
+#ifndef PCCB_TC05_BKF
+#define PCCB_TC05_BKF 32
+#endif
+constexpr int BM = 128, BN = 256, BKF = PCCB_TC05_BKF;   // 32 floats = one 128-byte swizzle row (16: 64-byte swizzle, twice the stages)
 constexpr int A_BYTES = BM * BKF * 4, B_BYTES = BN * BKF * 4;
 constexpr int NTHREADS = 192;
 constexpr int TMEM_COLS = 256;
@@ -62,9 +65,9 @@ __device__ __forceinline__ uint64_t smem_desc(unsigned addr) {
     uint64_t d = 0;
     d |= (uint64_t)((addr & 0x3FFFF) >> 4);
     d |= (uint64_t)1 << 16;
-    d |= (uint64_t)(1024 >> 4) << 32;
+    d |= (uint64_t)((8 * BKF * 4) >> 4) << 32;
     d |= (uint64_t)1 << 46;
-    d |= (uint64_t)2 << 61;
+    d |= (uint64_t)(BKF == 32 ? 2 : 4) << 61;      // SWIZZLE_128B / SWIZZLE_64B
     return d;
 }
 __device__ __forceinline__ void umma_tf32(unsigned tmem_d, uint64_t adesc, uint64_t bdesc, unsigned idesc, unsigned accumulate) {
@@ -74,13 +77,36 @@ __device__ __forceinline__ void umma_tf32(unsigned tmem_d, uint64_t adesc, uint6
 __device__ __forceinline__ void umma_commit(unsigned bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
 }
+// the same arrive on the barrier at this offset in every CTA of the cluster named by the mask
+__device__ __forceinline__ void umma_commit_multicast(unsigned bar, unsigned short mask) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+                 ::"r"(bar), "h"(mask) : "memory");
+}
+// TMA load delivered to the same shared-memory offset (and signalled on the same barrier offset) of every CTA in the mask
+__device__ __forceinline__ void tma_load_2d_multicast(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar,
+                                                      unsigned short mask) {
+    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
+                 " [%0], [%1, {%2, %3}], [%4], %5;\n"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ unsigned cluster_ctarank() {
+    unsigned r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
 
 struct alignas(64) TcMaps {
     CUtensorMap a[MAXSEG], alo[MAXSEG], b[MAXSEG], blo[MAXSEG];
+    CUtensorMap bh[MAXSEG], blh[MAXSEG];      // B with a 128-row box: the half each CTA of a pair loads and multicasts
 };
 
 struct TcParams {
     unsigned M, N;
+    unsigned m_tile0;         // first m-tile of this launch (the odd last tile column runs without a cluster)
     int nseg;
     int nkb[MAXSEG];          // k-blocks (of 32) per segment
     float* C;
@@ -93,10 +119,13 @@ struct TcParams {
 // FUSED = false: three K-concatenated passes (A,B), (A_lo,B), (A,B_lo), 4 stages of 48 KB.
 // FUSED = true : each stage holds A, A_lo, B, B_lo of one k-block (96 KB, 2 stages) and feeds all three
 //                products, so every operand byte crosses L2 -> shared memory once instead of 1.5 times.
-template <bool FUSED>
-__global__ void __launch_bounds__(NTHREADS, 1)
-contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
-    constexpr int STAGES = FUSED ? 2 : 4;
+// CL = 2: the two CTAs of a cluster own adjacent m-tiles of the same n-tile.  They need the same B tile: each loads
+// half of it (128 rows, both planes) and multicasts it into both shared memories, so a stage costs 64 KB instead of
+// 96 KB of L2 -> SM traffic per CTA - the resource that bounds this kernel.  A stage may be
+// refilled once BOTH CTAs have consumed it: the MMA warps commit to the "empty" barrier of both CTAs (count 2).
+template <bool FUSED, int CL>
+__device__ __forceinline__ void tc05_body(const TcParams& p, const TcMaps& maps) {
+    constexpr int STAGES = FUSED ? (BKF == 32 ? 2 : 4) : 4;
     constexpr int STAGE_BYTES = FUSED ? 2 * (A_BYTES + B_BYTES) : (A_BYTES + B_BYTES);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     const unsigned raw_s = (unsigned)__cvta_generic_to_shared(smem_raw);
@@ -107,12 +136,13 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
     volatile unsigned* slot = reinterpret_cast<volatile unsigned*>(smem_raw + pad + STAGES * STAGE_BYTES + 16 * STAGES + 8);
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const unsigned m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+    const unsigned m0 = (p.m_tile0 + blockIdx.x) * BM, n0 = blockIdx.y * BN;
+    const unsigned rank = CL > 1 ? cluster_ctarank() : 0u;
     int total_kb = 0;
     for (int s = 0; s < p.nseg; ++s) total_kb += (FUSED ? 1 : 3) * p.nkb[s];
 
     if (tid == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(full_s + 8 * s, 1); mbar_init(empty_s + 8 * s, 1); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_s + 8 * s, 1); mbar_init(empty_s + 8 * s, CL); }
         mbar_init(tfull_s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
@@ -125,6 +155,7 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
     const unsigned tmem = *slot;
+    if (CL > 1) cluster_sync_all();          // the partner's barriers exist before anything is multicast to them
 
     if (warp == 0) {
         if (lane == 0) {
@@ -139,10 +170,19 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
                         const unsigned bar = full_s + 8 * st, base = ring_s + st * STAGE_BYTES;
                         mbar_expect_tx(bar, STAGE_BYTES);
                         tma_load_2d(base, ma, kb * BKF, (int)m0, bar);
-                        tma_load_2d(base + A_BYTES, mb, kb * BKF, (int)n0, bar);
-                        if (FUSED) {
+                        if (CL > 1 && FUSED) {
+                            const unsigned half = rank * (B_BYTES / 2);
+                            const int nrow = (int)(n0 + rank * (BN / 2));
+                            tma_load_2d_multicast(base + A_BYTES + half, &maps.bh[s], kb * BKF, nrow, bar, (unsigned short)3);
                             tma_load_2d(base + A_BYTES + B_BYTES, &maps.alo[s], kb * BKF, (int)m0, bar);
-                            tma_load_2d(base + 2 * A_BYTES + B_BYTES, &maps.blo[s], kb * BKF, (int)n0, bar);
+                            tma_load_2d_multicast(base + 2 * A_BYTES + B_BYTES + half, &maps.blh[s], kb * BKF, nrow, bar,
+                                                  (unsigned short)3);
+                        } else {
+                            tma_load_2d(base + A_BYTES, mb, kb * BKF, (int)n0, bar);
+                            if (FUSED) {
+                                tma_load_2d(base + A_BYTES + B_BYTES, &maps.alo[s], kb * BKF, (int)m0, bar);
+                                tma_load_2d(base + 2 * A_BYTES + B_BYTES, &maps.blo[s], kb * BKF, (int)n0, bar);
+                            }
                         }
                     }
                 }
@@ -166,7 +206,8 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
                         umma_tf32(tmem, ad + 2 * k, bl + 2 * k, idesc, 1u);
                     }
                 }
-                umma_commit(empty_s + 8 * st);
+                if (CL > 1) umma_commit_multicast(empty_s + 8 * st, (unsigned short)3);
+                else umma_commit(empty_s + 8 * st);
             }
             umma_commit(tfull_s);
         }
@@ -212,6 +253,18 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
     asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
     __syncthreads();
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
+    if (CL > 1) cluster_sync_all();          // my shared memory and barriers stay valid until the partner is done too
+}
+
+template <bool FUSED>
+__global__ void __launch_bounds__(NTHREADS, 1)
+contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
+    tc05_body<FUSED, 1>(p, maps);
+}
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
+contract_tf32x3_tc05_pair_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
+    tc05_body<true, 2>(p, maps);
 }
 
 // lo[i] = x[i] - trunc_tf32(x[i])   (exact in FP32; what the tensor core drops from an FP32 word)
@@ -246,7 +299,7 @@ bool make_map(CUtensorMap* m, const float* base, long long rows, long long K, lo
     const cuuint32_t box[2] = {(cuuint32_t)BKF, (cuuint32_t)box_rows};
     const cuuint32_t estr[2] = {1, 1};
     return enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr,
-               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+               CU_TENSOR_MAP_INTERLEAVE_NONE, BKF == 32 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
@@ -311,12 +364,13 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
     }
     const long long gm = (d->M + BM - 1) / BM, gn = (d->N + BN - 1) / BN;
     if (gn > 65535) return 0;
-    constexpr size_t SMEM = 4 * (A_BYTES + B_BYTES) + 16 * 4 + 16 + 1024;       // both variants: 192 KB of ring
+    constexpr size_t SMEM = (BKF == 32 ? 4 : 8) * (A_BYTES + B_BYTES) + 16 * 4 + 16 + 1024;       // both variants: 192 KB of ring
     static const bool fused = [] { const char* e = getenv("PCCB_TC05_FUSED"); return e ? atoi(e) != 0 : true; }();
     static bool attr_set = false;
     if (!attr_set) {
         PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
         PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
+        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
         attr_set = true;
     }
     const long long Ktot = segs[0]->K;
@@ -336,7 +390,8 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
             const float* blo = lo_of(ctx, g.B_dev) + koff;
             const long long ars = row_stride_of(g.am, d->M), brs = row_stride_of(g.bn, d->N);
             if (!make_map(&maps.a[s], a, d->M, Kp, ars, BM) || !make_map(&maps.alo[s], alo, d->M, Kp, ars, BM) ||
-                !make_map(&maps.b[s], b, d->N, Kp, brs, BN) || !make_map(&maps.blo[s], blo, d->N, Kp, brs, BN)) {
+                !make_map(&maps.b[s], b, d->N, Kp, brs, BN) || !make_map(&maps.blo[s], blo, d->N, Kp, brs, BN) ||
+                !make_map(&maps.bh[s], b, d->N, Kp, brs, BN / 2) || !make_map(&maps.blh[s], blo, d->N, Kp, brs, BN / 2)) {
                 if (k0 == 0) return 0;
                 PCCB_FAIL(ctx, PCCB_ERR_ARG, "pccb_contract (tcgen05): tensor map of K panel %lld failed", (long long)k0);
             }
@@ -358,11 +413,25 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
         } else {
             p.beta = 1.f;
         }
-        if (fused)
-            contract_tf32x3_tc05_kernel<true><<<dim3((unsigned)gm, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
-        else
-            contract_tf32x3_tc05_kernel<false><<<dim3((unsigned)gm, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
-        PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_kernel");
+        // Pairs of adjacent m-tiles share their B tile through TMA multicast (2-CTA clusters).  Measured at (40,300)
+        // (tools/time_sp_ladder.py): ring product M = N = K = 12000 15.64 -> 14.86 ms (221 -> 233 TFLOP/s); the ladder
+        // (13 m-tiles: six pairs + a separate launch for the odd column) 137.5 -> 138.1 ms, so an odd tile count keeps
+        // the unpaired kernel (PCCB_TC05_PAIRS=2 pairs it anyway, =0 never pairs).
+        static const int pairs = [] { const char* e = getenv("PCCB_TC05_PAIRS"); return e ? atoi(e) : 1; }();
+        const long long gm2 = (fused && pairs > 0 && gm >= 2 && (pairs >= 2 || (gm & 1) == 0)) ? (gm & ~1ll) : 0;
+        if (gm2 > 0) {
+            p.m_tile0 = 0;
+            contract_tf32x3_tc05_pair_kernel<<<dim3((unsigned)gm2, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
+            PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_pair_kernel");
+        }
+        if (gm2 < gm) {
+            p.m_tile0 = (unsigned)gm2;
+            if (fused)
+                contract_tf32x3_tc05_kernel<true><<<dim3((unsigned)(gm - gm2), (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
+            else
+                contract_tf32x3_tc05_kernel<false><<<dim3((unsigned)(gm - gm2), (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
+            PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_kernel");
+        }
     }
     return 1;
 }

@@ -306,7 +306,9 @@ def test_contract_f32_tcgen05_vs_einsum(be, case):
     assert ((got1 - ref).abs() <= tol).all()
     assert ((got2 - (ref + C0.double())).abs() <= tol).all()
     assert ((got1 - got_sync).abs() <= tol).all()
-    assert be.launch_count() - n0 == 2          # one launch each: no split-K reduction, i.e. not the mma.sync path
+    # one launch each (two when the number of m-tiles is odd: the paired-CTA kernel + the last tile column): no split-K
+    # reduction, i.e. not the mma.sync path
+    assert be.launch_count() - n0 in (2, 4)
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
