@@ -331,7 +331,7 @@ def run_ours(args):
     lad_flops = 2.0 * o * o * vl * v**3
     lad_ms = sum(ladder_ms) / max(len(ladder_ms), 1)
     lad_tf = lad_flops / (lad_ms * 1e-3) / 1e12 if lad_ms > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "%s (ladder r2 += 1/2 tau <ab|ef>)" % ("contract_tf32x3_tc05_kernel" if sp else "contract_f64_tma_kernel"),
+    roofline = {"bound": "tensor", "kernel": "%s (ladder r2 += 1/2 tau <ab|ef>)" % ("contract_tf32x3_tc05_2sm_kernel (+ contract_tf32x3_tc05_kernel for an odd tile column)" if sp else "contract_f64_tma_kernel"),
                 "achieved": round(lad_tf, 3), "peak": peak, "unit": "TFLOP/s", "frac": round(lad_tf / peak, 4),
                 "traffic": None, "launch_ms": round(lad_ms, 4), "flops_per_launch": lad_flops,
                 "peak_source": peak_src + (" (cuBLAS SGEMM on the same box: 63.9 TFLOP/s; the mma.sync 3xTF32 kernel this replaced: 66.7)" if sp else

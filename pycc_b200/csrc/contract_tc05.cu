@@ -24,6 +24,10 @@
 //   warps 2-5        : epilogue - tcgen05.ld 32 lanes x 16 columns at a time, alpha / beta / gamma D
 //                      and the compound output strides of the descriptor, thread = output row.
 // Edges: TMA zero-fills rows >= M / N and k >= K; the epilogue masks rows and columns.
+//
+// Round 2: contract_tf32x3_tc05_2sm_kernel - CTA pairs (2-CTA clusters), tcgen05.mma.cta_group::2 with M = 256 over the
+// two SMs, each CTA staging its 128 rows of A and half of the B tile (64 KB stages, three of them) - runs the even part
+// of the m-tiles; the kernel described above keeps an odd last tile column (and PCCB_TC05_2SM=0).
 #include <cuda.h>
 
 #include <cstdlib>
@@ -77,18 +81,6 @@ __device__ __forceinline__ void umma_tf32(unsigned tmem_d, uint64_t adesc, uint6
 __device__ __forceinline__ void umma_commit(unsigned bar) {
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(bar) : "memory");
 }
-// the same arrive on the barrier at this offset in every CTA of the cluster named by the mask
-__device__ __forceinline__ void umma_commit_multicast(unsigned bar, unsigned short mask) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
-                 ::"r"(bar), "h"(mask) : "memory");
-}
-// TMA load delivered to the same shared-memory offset (and signalled on the same barrier offset) of every CTA in the mask
-__device__ __forceinline__ void tma_load_2d_multicast(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar,
-                                                      unsigned short mask) {
-    asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster"
-                 " [%0], [%1, {%2, %3}], [%4], %5;\n"
-                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar), "h"(mask) : "memory");
-}
 __device__ __forceinline__ unsigned cluster_ctarank() {
     unsigned r;
     asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
@@ -99,9 +91,27 @@ __device__ __forceinline__ void cluster_sync_all() {
     asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
 }
 
+// ---- cta_group::2 forms (one MMA over the two SMs of a CTA pair; cute/arch/{copy_sm100_tma,mma_sm100_umma}.hpp) ----
+// executed by both CTAs of the pair: data into the issuing CTA's shared memory, bytes counted on the LEADER's barrier
+// (the shared::cluster address of the same barrier with the CTA-rank bit cleared)
+__device__ __forceinline__ void tma_load_2d_2sm(unsigned dst, const CUtensorMap* map, int c0, int c1, unsigned bar) {
+    asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];\n"
+                 ::"r"(dst), "l"(map), "r"(c0), "r"(c1), "r"(bar & 0xFEFFFFFFu) : "memory");
+}
+__device__ __forceinline__ void umma_tf32_2sm(unsigned tmem_d, uint64_t adesc, uint64_t bdesc, unsigned idesc, unsigned accumulate) {
+    const unsigned z = 0;
+    asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\n"
+                 "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, {%5, %5, %5, %5, %5, %5, %5, %5}, p;\n}\n"
+                 ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate), "r"(z) : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(unsigned bar, unsigned short mask) {
+    asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;\n"
+                 ::"r"(bar), "h"(mask) : "memory");
+}
+
 struct alignas(64) TcMaps {
     CUtensorMap a[MAXSEG], alo[MAXSEG], b[MAXSEG], blo[MAXSEG];
-    CUtensorMap bh[MAXSEG], blh[MAXSEG];      // B with a 128-row box: the half each CTA of a pair loads and multicasts
+    CUtensorMap bh[MAXSEG], blh[MAXSEG];      // B with a 128-row box: the half of the tile each CTA of a pair stages
 };
 
 struct TcParams {
@@ -119,12 +129,9 @@ struct TcParams {
 // FUSED = false: three K-concatenated passes (A,B), (A_lo,B), (A,B_lo), 4 stages of 48 KB.
 // FUSED = true : each stage holds A, A_lo, B, B_lo of one k-block (96 KB, 2 stages) and feeds all three
 //                products, so every operand byte crosses L2 -> shared memory once instead of 1.5 times.
-// CL = 2: the two CTAs of a cluster own adjacent m-tiles of the same n-tile.  They need the same B tile: each loads
-// half of it (128 rows, both planes) and multicasts it into both shared memories, so a stage costs 64 KB instead of
-// 96 KB of L2 -> SM traffic per CTA - the resource that bounds this kernel.  A stage may be
-// refilled once BOTH CTAs have consumed it: the MMA warps commit to the "empty" barrier of both CTAs (count 2).
-template <bool FUSED, int CL>
-__device__ __forceinline__ void tc05_body(const TcParams& p, const TcMaps& maps) {
+template <bool FUSED>
+__global__ void __launch_bounds__(NTHREADS, 1)
+contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
     constexpr int STAGES = FUSED ? (BKF == 32 ? 2 : 4) : 4;
     constexpr int STAGE_BYTES = FUSED ? 2 * (A_BYTES + B_BYTES) : (A_BYTES + B_BYTES);
     extern __shared__ __align__(1024) unsigned char smem_raw[];
@@ -137,12 +144,11 @@ __device__ __forceinline__ void tc05_body(const TcParams& p, const TcMaps& maps)
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const unsigned m0 = (p.m_tile0 + blockIdx.x) * BM, n0 = blockIdx.y * BN;
-    const unsigned rank = CL > 1 ? cluster_ctarank() : 0u;
     int total_kb = 0;
     for (int s = 0; s < p.nseg; ++s) total_kb += (FUSED ? 1 : 3) * p.nkb[s];
 
     if (tid == 0) {
-        for (int s = 0; s < STAGES; ++s) { mbar_init(full_s + 8 * s, 1); mbar_init(empty_s + 8 * s, CL); }
+        for (int s = 0; s < STAGES; ++s) { mbar_init(full_s + 8 * s, 1); mbar_init(empty_s + 8 * s, 1); }
         mbar_init(tfull_s, 1);
         asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
@@ -155,7 +161,6 @@ __device__ __forceinline__ void tc05_body(const TcParams& p, const TcMaps& maps)
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
     const unsigned tmem = *slot;
-    if (CL > 1) cluster_sync_all();          // the partner's barriers exist before anything is multicast to them
 
     if (warp == 0) {
         if (lane == 0) {
@@ -170,19 +175,10 @@ __device__ __forceinline__ void tc05_body(const TcParams& p, const TcMaps& maps)
                         const unsigned bar = full_s + 8 * st, base = ring_s + st * STAGE_BYTES;
                         mbar_expect_tx(bar, STAGE_BYTES);
                         tma_load_2d(base, ma, kb * BKF, (int)m0, bar);
-                        if (CL > 1 && FUSED) {
-                            const unsigned half = rank * (B_BYTES / 2);
-                            const int nrow = (int)(n0 + rank * (BN / 2));
-                            tma_load_2d_multicast(base + A_BYTES + half, &maps.bh[s], kb * BKF, nrow, bar, (unsigned short)3);
+                        tma_load_2d(base + A_BYTES, mb, kb * BKF, (int)n0, bar);
+                        if (FUSED) {
                             tma_load_2d(base + A_BYTES + B_BYTES, &maps.alo[s], kb * BKF, (int)m0, bar);
-                            tma_load_2d_multicast(base + 2 * A_BYTES + B_BYTES + half, &maps.blh[s], kb * BKF, nrow, bar,
-                                                  (unsigned short)3);
-                        } else {
-                            tma_load_2d(base + A_BYTES, mb, kb * BKF, (int)n0, bar);
-                            if (FUSED) {
-                                tma_load_2d(base + A_BYTES + B_BYTES, &maps.alo[s], kb * BKF, (int)m0, bar);
-                                tma_load_2d(base + 2 * A_BYTES + B_BYTES, &maps.blo[s], kb * BKF, (int)n0, bar);
-                            }
+                            tma_load_2d(base + 2 * A_BYTES + B_BYTES, &maps.blo[s], kb * BKF, (int)n0, bar);
                         }
                     }
                 }
@@ -206,8 +202,7 @@ __device__ __forceinline__ void tc05_body(const TcParams& p, const TcMaps& maps)
                         umma_tf32(tmem, ad + 2 * k, bl + 2 * k, idesc, 1u);
                     }
                 }
-                if (CL > 1) umma_commit_multicast(empty_s + 8 * st, (unsigned short)3);
-                else umma_commit(empty_s + 8 * st);
+                umma_commit(empty_s + 8 * st);
             }
             umma_commit(tfull_s);
         }
@@ -253,19 +248,132 @@ __device__ __forceinline__ void tc05_body(const TcParams& p, const TcMaps& maps)
     asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
     __syncthreads();
     if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
-    if (CL > 1) cluster_sync_all();          // my shared memory and barriers stay valid until the partner is done too
 }
 
-template <bool FUSED>
-__global__ void __launch_bounds__(NTHREADS, 1)
-contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
-    tc05_body<FUSED, 1>(p, maps);
-}
+// ---- cta_group::2 kernel: one 256 x 256 output tile per CTA PAIR ------------------------------------------------
+// Each CTA stages its own 128 rows of A and HALF of the B tile (128 of the 256 n-rows), both planes: 64 KB per stage,
+// three stages.  The leader CTA (rank 0) issues tcgen05.mma.cta_group::2 (M = 256, N = 256, K = 8): the tensor cores of
+// both SMs read A from their own shared memory and each half of B once - half the B reads per SM of the single-CTA
+// kernel, whose limiter is shared-memory bandwidth.  Both producers count their bytes on the
+// leader's "full" barrier; the leader's commits arrive on the "empty" / "accumulator full" barriers of both CTAs;
+// each CTA's epilogue warps drain its own 128 TMEM lanes.
+constexpr int STAGES_2SM = 3;
+constexpr int STAGE_2SM_BYTES = 2 * A_BYTES + B_BYTES;        // A, A_lo, B half, B_lo half
 
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(NTHREADS, 1)
-contract_tf32x3_tc05_pair_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
-    tc05_body<true, 2>(p, maps);
+contract_tf32x3_tc05_2sm_kernel(const __grid_constant__ TcParams p, const __grid_constant__ TcMaps maps) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    const unsigned raw_s = (unsigned)__cvta_generic_to_shared(smem_raw);
+    const unsigned pad = (1024u - (raw_s & 1023u)) & 1023u;
+    const unsigned ring_s = raw_s + pad;
+    const unsigned full_s = ring_s + STAGES_2SM * STAGE_2SM_BYTES, empty_s = full_s + 8 * STAGES_2SM,
+                   tfull_s = empty_s + 8 * STAGES_2SM, slot_s = tfull_s + 8;
+    volatile unsigned* slot = reinterpret_cast<volatile unsigned*>(smem_raw + pad + STAGES_2SM * STAGE_2SM_BYTES +
+                                                                   16 * STAGES_2SM + 8);
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const unsigned rank = cluster_ctarank();
+    const bool leader = rank == 0;
+    const unsigned m0 = (p.m_tile0 + blockIdx.x) * BM, n0 = blockIdx.y * BN;
+    int total_kb = 0;
+    for (int s = 0; s < p.nseg; ++s) total_kb += p.nkb[s];
+
+    if (tid == 0) {
+        for (int s = 0; s < STAGES_2SM; ++s) { mbar_init(full_s + 8 * s, 1); mbar_init(empty_s + 8 * s, 1); }
+        mbar_init(tfull_s, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    }
+    if (warp == 1) {
+        asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(slot_s), "r"(TMEM_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+    const unsigned tmem = *slot;
+    cluster_sync_all();
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int g = 0;
+            const int nrow = (int)(n0 + rank * (BN / 2));
+            for (int s = 0; s < p.nseg; ++s)
+                for (int kb = 0; kb < p.nkb[s]; ++kb, ++g) {
+                    const int st = g % STAGES_2SM;
+                    if (g >= STAGES_2SM) mbar_wait(empty_s + 8 * st, ((g / STAGES_2SM) - 1) & 1);
+                    const unsigned bar = full_s + 8 * st, base = ring_s + st * STAGE_2SM_BYTES;
+                    if (leader) mbar_expect_tx(bar, 2 * STAGE_2SM_BYTES);          // both CTAs' bytes
+                    tma_load_2d_2sm(base, &maps.a[s], kb * BKF, (int)m0, bar);
+                    tma_load_2d_2sm(base + A_BYTES, &maps.alo[s], kb * BKF, (int)m0, bar);
+                    tma_load_2d_2sm(base + 2 * A_BYTES, &maps.bh[s], kb * BKF, nrow, bar);
+                    tma_load_2d_2sm(base + 2 * A_BYTES + B_BYTES / 2, &maps.blh[s], kb * BKF, nrow, bar);
+                }
+        }
+    } else if (warp == 1) {
+        if (lane == 0 && leader) {
+            // instruction descriptor: D = F32, A = B = TF32, both K-major, N = 256, M = 256 (over the pair)
+            const unsigned idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((unsigned)(BN >> 3) << 17) | ((unsigned)((2 * BM) >> 4) << 24);
+            for (int g = 0; g < total_kb; ++g) {
+                const int st = g % STAGES_2SM;
+                mbar_wait(full_s + 8 * st, (g / STAGES_2SM) & 1);
+                asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+                const unsigned base = ring_s + st * STAGE_2SM_BYTES;
+                const uint64_t ad = smem_desc(base), al = smem_desc(base + A_BYTES), bd = smem_desc(base + 2 * A_BYTES),
+                               bl = smem_desc(base + 2 * A_BYTES + B_BYTES / 2);
+#pragma unroll
+                for (int k = 0; k < BKF / 8; ++k) {
+                    umma_tf32_2sm(tmem, ad + 2 * k, bd + 2 * k, idesc, (g > 0 || k > 0) ? 1u : 0u);
+                    umma_tf32_2sm(tmem, al + 2 * k, bd + 2 * k, idesc, 1u);
+                    umma_tf32_2sm(tmem, ad + 2 * k, bl + 2 * k, idesc, 1u);
+                }
+                umma_commit_2sm(empty_s + 8 * st, (unsigned short)3);
+            }
+            umma_commit_2sm(tfull_s, (unsigned short)3);
+        }
+    } else {
+        mbar_wait(tfull_s, 0);
+        asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+        const unsigned lane_base = (warp & 3) * 32;
+        const unsigned row = m0 + lane_base + lane;
+        const bool row_ok = row < p.M;
+        const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
+        float* crow = p.C + (row_ok ? didx_off(p.cm, row) : 0);
+        const float* drow = use_d ? p.D + (row_ok ? didx_off(p.dm, row) : 0) : nullptr;
+        const bool c_flat = p.cn.flat && p.cn.s_lo == 1, d_flat = !use_d || (p.dn.flat && p.dn.s_lo == 1);
+#pragma unroll 1
+        for (unsigned c = 0; c < BN; c += 16) {
+            unsigned v[16];
+            const unsigned taddr = tmem + (lane_base << 16) + c;
+            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                         : "r"(taddr));
+            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+            if (!row_ok || n0 + c >= p.N) continue;
+            float add[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const unsigned col = n0 + c + q;
+                float x = 0.f;
+                if (col < p.N) {
+                    if (use_beta) x = p.beta * crow[c_flat ? (long long)col : didx_off(p.cn, col)];
+                    if (use_d) x += p.gamma * drow[d_flat ? (long long)col : didx_off(p.dn, col)];
+                }
+                add[q] = x;
+            }
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const unsigned col = n0 + c + q;
+                if (col < p.N) crow[c_flat ? (long long)col : didx_off(p.cn, col)] = p.alpha * __uint_as_float(v[q]) + add[q];
+            }
+        }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+    __syncthreads();
+    cluster_sync_all();                      // both epilogues are done with the pair's tensor memory
+    if (warp == 1) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem), "r"(TMEM_COLS) : "memory");
 }
+
 
 // lo[i] = x[i] - trunc_tf32(x[i])   (exact in FP32; what the tensor core drops from an FP32 word)
 __global__ void split_lo_kernel(const float* __restrict__ x, float* __restrict__ lo, long long n) {
@@ -370,7 +478,6 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
     if (!attr_set) {
         PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
         PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
-        PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_pair_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM));
         attr_set = true;
     }
     const long long Ktot = segs[0]->K;
@@ -413,16 +520,21 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
         } else {
             p.beta = 1.f;
         }
-        // Pairs of adjacent m-tiles share their B tile through TMA multicast (2-CTA clusters).  Measured at (40,300)
-        // (tools/time_sp_ladder.py): ring product M = N = K = 12000 15.64 -> 14.86 ms (221 -> 233 TFLOP/s); the ladder
-        // (13 m-tiles: six pairs + a separate launch for the odd column) 137.5 -> 138.1 ms, so an odd tile count keeps
-        // the unpaired kernel (PCCB_TC05_PAIRS=2 pairs it anyway, =0 never pairs).
-        static const int pairs = [] { const char* e = getenv("PCCB_TC05_PAIRS"); return e ? atoi(e) : 1; }();
-        const long long gm2 = (fused && pairs > 0 && gm >= 2 && (pairs >= 2 || (gm & 1) == 0)) ? (gm & ~1ll) : 0;
+        // CTA pairs (cta_group::2, 256 x 256 tiles) for the even part of the m-tiles, the single-CTA kernel for an odd last
+        // tile column.  Measured at (40,300) (tools/time_sp_ladder.py): ring product M = N = K = 12000 15.64 -> 14.48 ms
+        // (221 -> 239 TFLOP/s), ladder (13 m-tiles = 6 pairs + 1) 137.5 -> 128.5 ms (188 -> 202).  PCCB_TC05_2SM=0 disables.
+        static const int two_sm = [] { const char* e = getenv("PCCB_TC05_2SM"); return e ? atoi(e) : 1; }();
+        const long long gm2 = (fused && two_sm > 0 && gm >= 2) ? (gm & ~1ll) : 0;
         if (gm2 > 0) {
             p.m_tile0 = 0;
-            contract_tf32x3_tc05_pair_kernel<<<dim3((unsigned)gm2, (unsigned)gn), NTHREADS, SMEM, ctx->stream>>>(p, maps);
-            PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_pair_kernel");
+            constexpr size_t SMEM2 = (size_t)STAGES_2SM * STAGE_2SM_BYTES + 16 * 4 + 16 + 1024;
+            static bool attr2 = false;
+            if (!attr2) {
+                PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM2));
+                attr2 = true;
+            }
+            contract_tf32x3_tc05_2sm_kernel<<<dim3((unsigned)gm2, (unsigned)gn), NTHREADS, SMEM2, ctx->stream>>>(p, maps);
+            PCCB_CHECK_LAUNCH(ctx, "contract_tf32x3_tc05_2sm_kernel");
         }
         if (gm2 < gm) {
             p.m_tile0 = (unsigned)gm2;
