@@ -524,7 +524,10 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
         // tile column.  Measured at (40,300) (tools/time_sp_ladder.py): ring product M = N = K = 12000 15.64 -> 14.48 ms
         // (221 -> 239 TFLOP/s), ladder (13 m-tiles = 6 pairs + 1) 137.5 -> 128.5 ms (188 -> 202).  PCCB_TC05_2SM=0 disables.
         static const int two_sm = [] { const char* e = getenv("PCCB_TC05_2SM"); return e ? atoi(e) : 1; }();
-        const long long gm2 = (fused && two_sm > 0 && gm >= 2) ? (gm & ~1ll) : 0;
+        // (an odd tile count costs a second launch: worth it only when the pair part runs many waves - one rank's ladder
+        //  out of eight, 12 x 45 + 45 tiles, went 14.4 -> 15.4 ms with the split)
+        const bool many_waves = (gm & ~1ll) * gn >= 8ll * ctx->sm_count;
+        const long long gm2 = (fused && two_sm > 0 && gm >= 2 && ((gm & 1) == 0 || many_waves || two_sm >= 2)) ? (gm & ~1ll) : 0;
         if (gm2 > 0) {
             p.m_tile0 = 0;
             constexpr size_t SMEM2 = (size_t)STAGES_2SM * STAGE_2SM_BYTES + 16 * 4 + 16 + 1024;
