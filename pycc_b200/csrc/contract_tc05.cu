@@ -124,7 +124,119 @@ struct TcParams {
     const float* D;
     DIdx dm, dn;
     float alpha, beta, gamma;
+    int c_tr;                 // epilogue leaves through shared memory, lane = column (set by the host: n contiguous in C)
 };
+
+// ---- epilogue (warps 2-5 of either kernel): TMEM -> alpha * acc + beta * C + gamma * D -> C -------------------------
+// Warp w may touch TMEM lanes 32 (w % 4) .. +31, one output ROW per thread.  Written straight from that mapping a warp
+// store touches 32 rows: fine when the m index has unit stride in C (Zr[mijB], rows (m,B)), 32 separate sectors per
+// instruction when it is the n index that runs contiguously (r2[ijAb], Wr1[jBme], ...).  Those outputs go through a
+// 32 x 33 shared-memory tile per warp and leave with lane = COLUMN: one 128-byte line per store.  D is added in
+// whichever of the two mappings reads it along its own unit stride.
+constexpr int EPI_PITCH = 33;
+constexpr int EPI_BYTES = 4 * 32 * EPI_PITCH * 4;
+
+__device__ __forceinline__ void tmem_ld16(unsigned taddr, unsigned* v) {
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
+                 : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                   "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+                 : "r"(taddr));
+}
+
+__device__ __forceinline__ void epilogue_rows(const TcParams& p, unsigned tmem, unsigned m0, unsigned n0, int warp, int lane,
+                                              float* stage) {
+    const unsigned lane_base = (warp & 3) * 32;
+    const unsigned row = m0 + lane_base + lane;
+    const bool row_ok = row < p.M;
+    const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
+    const long long coff_row = row_ok ? didx_off(p.cm, row) : -1;
+    const float* drow = use_d ? p.D + (row_ok ? didx_off(p.dm, row) : 0) : nullptr;
+    if (!p.c_tr) {
+        float* crow = p.C + (row_ok ? coff_row : 0);
+        const bool c_flat = p.cn.flat && p.cn.s_lo == 1, d_flat = !use_d || (p.dn.flat && p.dn.s_lo == 1);
+#pragma unroll 1
+        for (unsigned c = 0; c < BN; c += 16) {
+            unsigned v[16];
+            tmem_ld16(tmem + (lane_base << 16) + c, v);
+            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+            if (!row_ok || n0 + c >= p.N) continue;
+            // raw loads first, arithmetic after (a value consumed next to its load serialises the round trips)
+            float cv[16], dv[16];
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const unsigned col = n0 + c + q;
+                cv[q] = (use_beta && col < p.N) ? crow[c_flat ? (long long)col : didx_off(p.cn, col)] : 0.f;
+            }
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const unsigned col = n0 + c + q;
+                dv[q] = (use_d && col < p.N) ? drow[d_flat ? (long long)col : didx_off(p.dn, col)] : 0.f;
+            }
+#pragma unroll
+            for (int q = 0; q < 16; ++q) {
+                const unsigned col = n0 + c + q;
+                if (col < p.N)
+                    crow[c_flat ? (long long)col : didx_off(p.cn, col)] =
+                        p.alpha * __uint_as_float(v[q]) + (p.beta * cv[q] + p.gamma * dv[q]);
+            }
+        }
+        return;
+    }
+    // lane = column on the way out
+    const bool d_tr = use_d && p.dn.s_lo == 1 && p.dm.s_lo != 1;
+    const long long doff_row = (use_d && row_ok) ? didx_off(p.dm, row) : -1;
+    float* tile = stage + (warp & 3) * 32 * EPI_PITCH;
+#pragma unroll 1
+    for (unsigned c = 0; c < BN; c += 32) {
+        if (n0 + c >= p.N) break;                       // uniform over the CTA
+        unsigned v[32];
+        tmem_ld16(tmem + (lane_base << 16) + c, v);
+        tmem_ld16(tmem + (lane_base << 16) + c + 16, v + 16);
+        asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+        // (every batch of global loads is issued before its first value is used: a warp issues in order, and a load
+        //  consumed right away costs one DRAM round trip per element - 4 warps per SM cannot hide that)
+        float dd[32];
+        if (use_d && !d_tr) {
+#pragma unroll
+            for (int q = 0; q < 32; ++q) {
+                const unsigned col = n0 + c + q;
+                dd[q] = (row_ok && col < p.N) ? drow[didx_off(p.dn, col)] : 0.f;
+            }
+        }
+#pragma unroll
+        for (int q = 0; q < 32; ++q) {
+            float x = p.alpha * __uint_as_float(v[q]);
+            if (use_d && !d_tr) x += p.gamma * dd[q];
+            tile[lane * EPI_PITCH + q] = x;
+        }
+        __syncwarp();
+        const unsigned col = n0 + c + lane;
+        const bool col_ok = col < p.N;
+        const long long coff_col = col_ok ? didx_off(p.cn, col) : 0;
+        const long long doff_col = (d_tr && col_ok) ? didx_off(p.dn, col) : 0;
+        float cx[32];
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+            const long long ro = __shfl_sync(0xffffffffu, coff_row, r);
+            cx[r] = (use_beta && ro >= 0 && col_ok) ? p.C[ro + coff_col] : 0.f;
+        }
+        if (d_tr) {
+#pragma unroll
+            for (int r = 0; r < 32; ++r) {
+                const long long dro = __shfl_sync(0xffffffffu, doff_row, r);
+                dd[r] = (dro >= 0 && col_ok) ? p.D[dro + doff_col] : 0.f;
+            }
+        }
+#pragma unroll
+        for (int r = 0; r < 32; ++r) {
+            const long long ro = __shfl_sync(0xffffffffu, coff_row, r);
+            float x = tile[r * EPI_PITCH + lane] + p.beta * cx[r];
+            if (d_tr) x += p.gamma * dd[r];
+            if (ro >= 0 && col_ok) p.C[ro + coff_col] = x;
+        }
+        __syncwarp();
+    }
+}
 
 // FUSED = false: three K-concatenated passes (A,B), (A_lo,B), (A,B_lo), 4 stages of 48 KB.
 // FUSED = true : each stage holds A, A_lo, B, B_lo of one k-block (96 KB, 2 stages) and feeds all three
@@ -207,43 +319,9 @@ contract_tf32x3_tc05_kernel(const __grid_constant__ TcParams p, const __grid_con
             umma_commit(tfull_s);
         }
     } else {
-        // epilogue: warp w may touch TMEM lanes 32 (w % 4) .. +31; thread = one output row
         mbar_wait(tfull_s, 0);
         asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
-        const unsigned lane_base = (warp & 3) * 32;
-        const unsigned row = m0 + lane_base + lane;
-        const bool row_ok = row < p.M;
-        const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
-        float* crow = p.C + (row_ok ? didx_off(p.cm, row) : 0);
-        const float* drow = use_d ? p.D + (row_ok ? didx_off(p.dm, row) : 0) : nullptr;
-        const bool c_flat = p.cn.flat && p.cn.s_lo == 1, d_flat = !use_d || (p.dn.flat && p.dn.s_lo == 1);
-#pragma unroll 1
-        for (unsigned c = 0; c < BN; c += 16) {
-            unsigned v[16];
-            const unsigned taddr = tmem + (lane_base << 16) + c;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
-                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                         : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
-            if (!row_ok || n0 + c >= p.N) continue;
-            float add[16];
-#pragma unroll
-            for (int q = 0; q < 16; ++q) {
-                const unsigned col = n0 + c + q;
-                float x = 0.f;
-                if (col < p.N) {
-                    if (use_beta) x = p.beta * crow[c_flat ? (long long)col : didx_off(p.cn, col)];
-                    if (use_d) x += p.gamma * drow[d_flat ? (long long)col : didx_off(p.dn, col)];
-                }
-                add[q] = x;
-            }
-#pragma unroll
-            for (int q = 0; q < 16; ++q) {
-                const unsigned col = n0 + c + q;
-                if (col < p.N) crow[c_flat ? (long long)col : didx_off(p.cn, col)] = p.alpha * __uint_as_float(v[q]) + add[q];
-            }
-        }
+        epilogue_rows(p, tmem, m0, n0, warp, lane, reinterpret_cast<float*>(smem_raw + pad + STAGES * STAGE_BYTES + 128));
     }
     asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
     __syncthreads();
@@ -333,40 +411,7 @@ contract_tf32x3_tc05_2sm_kernel(const __grid_constant__ TcParams p, const __grid
     } else {
         mbar_wait(tfull_s, 0);
         asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
-        const unsigned lane_base = (warp & 3) * 32;
-        const unsigned row = m0 + lane_base + lane;
-        const bool row_ok = row < p.M;
-        const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
-        float* crow = p.C + (row_ok ? didx_off(p.cm, row) : 0);
-        const float* drow = use_d ? p.D + (row_ok ? didx_off(p.dm, row) : 0) : nullptr;
-        const bool c_flat = p.cn.flat && p.cn.s_lo == 1, d_flat = !use_d || (p.dn.flat && p.dn.s_lo == 1);
-#pragma unroll 1
-        for (unsigned c = 0; c < BN; c += 16) {
-            unsigned v[16];
-            const unsigned taddr = tmem + (lane_base << 16) + c;
-            asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];\n"
-                         : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                           "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
-                         : "r"(taddr));
-            asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
-            if (!row_ok || n0 + c >= p.N) continue;
-            float add[16];
-#pragma unroll
-            for (int q = 0; q < 16; ++q) {
-                const unsigned col = n0 + c + q;
-                float x = 0.f;
-                if (col < p.N) {
-                    if (use_beta) x = p.beta * crow[c_flat ? (long long)col : didx_off(p.cn, col)];
-                    if (use_d) x += p.gamma * drow[d_flat ? (long long)col : didx_off(p.dn, col)];
-                }
-                add[q] = x;
-            }
-#pragma unroll
-            for (int q = 0; q < 16; ++q) {
-                const unsigned col = n0 + c + q;
-                if (col < p.N) crow[c_flat ? (long long)col : didx_off(p.cn, col)] = p.alpha * __uint_as_float(v[q]) + add[q];
-            }
-        }
+        epilogue_rows(p, tmem, m0, n0, warp, lane, reinterpret_cast<float*>(smem_raw + pad + STAGES_2SM * STAGE_2SM_BYTES + 128));
     }
     asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
     __syncthreads();
@@ -437,7 +482,9 @@ const float* lo_of(pccb_ctx* ctx, const void* ptr) {
 // returns 1 when the tcgen05 kernel was launched, 0 when the contraction is not eligible, < 0 on error
 int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
     static const bool enabled = [] { const char* e = getenv("PCCB_TC05"); return e ? atoi(e) != 0 : true; }();
-    if (!enabled || ctx->lo_planes.empty() || d->batch != 1 || d->M < BM || d->N < BN) return 0;
+    // (a short M - t1[ie] <ja|be>, M = o - still pays: a quarter-filled 128-row tile at the tcgen05 rate beats the
+    //  mma.sync kernel's short-K pipeline, 4.5 -> 1.x ms at (40,300))
+    if (!enabled || ctx->lo_planes.empty() || d->batch != 1 || d->M < BM / 4 || d->N < BN) return 0;
     int ns = 0;
     const pccb_segment* segs[MAXSEG];
     for (int s = 0; s < d->nseg; ++s) {
@@ -464,15 +511,16 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
             if (kpanel < 512) kpanel = 512;
         }
     }
+    const long long min_k = [] { const char* e = getenv("PCCB_TC05_MIN_K"); return e ? atoll(e) : 256ll; }();
     for (int s = 0; s < ns; ++s) {
         const pccb_segment& g = *segs[s];
-        if (g.scale != segs[0]->scale || g.K < 256) return 0;
+        if (g.scale != segs[0]->scale || g.K < min_k) return 0;
         if (!operand_ok(g.A_dev, g.am, g.ak, d->M, g.K) || !operand_ok(g.B_dev, g.bn, g.bk, d->N, g.K)) return 0;
         if (!lo_of(ctx, g.A_dev) || !lo_of(ctx, g.B_dev)) return 0;
     }
     const long long gm = (d->M + BM - 1) / BM, gn = (d->N + BN - 1) / BN;
     if (gn > 65535) return 0;
-    constexpr size_t SMEM = (BKF == 32 ? 4 : 8) * (A_BYTES + B_BYTES) + 16 * 4 + 16 + 1024;       // both variants: 192 KB of ring
+    constexpr size_t SMEM = (BKF == 32 ? 4 : 8) * (A_BYTES + B_BYTES) + 128 + EPI_BYTES + 1024;       // both variants: 192 KB of ring
     static const bool fused = [] { const char* e = getenv("PCCB_TC05_FUSED"); return e ? atoi(e) != 0 : true; }();
     static bool attr_set = false;
     if (!attr_set) {
@@ -511,6 +559,10 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
         p.cm = to_didx(d->cm, d->M);
         p.cn = to_didx(d->cn, d->N);
         p.alpha = (float)(d->alpha * segs[0]->scale);
+        {
+            const char* e = getenv("PCCB_TC05_EPI");        // 0: thread = row stores for every output
+            p.c_tr = (p.cn.s_lo == 1 && p.cm.s_lo != 1 && !(e && atoi(e) == 0)) ? 1 : 0;
+        }
         if (k0 == 0) {
             p.D = static_cast<const float*>(d->D_dev);
             p.dm = to_didx(d->dm, d->M);
@@ -530,7 +582,7 @@ int pccb_contract_f32_tc05(pccb_ctx* ctx, const pccb_contraction* d) {
         const long long gm2 = (fused && two_sm > 0 && gm >= 2 && ((gm & 1) == 0 || many_waves || two_sm >= 2)) ? (gm & ~1ll) : 0;
         if (gm2 > 0) {
             p.m_tile0 = 0;
-            constexpr size_t SMEM2 = (size_t)STAGES_2SM * STAGE_2SM_BYTES + 16 * 4 + 16 + 1024;
+            constexpr size_t SMEM2 = (size_t)STAGES_2SM * STAGE_2SM_BYTES + 128 + EPI_BYTES + 1024;
             static bool attr2 = false;
             if (!attr2) {
                 PCCB_CUDA(ctx, cudaFuncSetAttribute(contract_tf32x3_tc05_2sm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM2));

@@ -141,6 +141,13 @@ class CCSDEngine(object):
             be.permute4(self.LoovvP, self.Loovv.permute(0, 2, 1, 3))
             self.t2sP, self.t2P, self.t2Q = E(o, v, o, v), E(o, v, o, v), E(o, v, o, v)            # [i,a,m,e]
             self.tauWPn, self.t2Rh = E(o, vl, o, v), E(o, vl, o, v)                                # [j,B,n,f]
+        # tcgen05 mode only: K-contiguous copies for the o^4 v^2 term of r_T2, tauT[Abmn] = tau[mnAb] and
+        # WmnijT[ijmn] = Wmnij[mnij] (12.1 -> 2.x ms at (40,300)); t1, t2 and Fae2 get residual planes so that
+        # t1[ie] <ja|be> and t2[ijae] Fae2[be] run there as well
+        self.sp_tc = self.sp_plain and dtype == torch.float32 and hasattr(be, "split_lo") and \
+            os.environ.get("PCCB_SP_TC_EXTRA", "1") != "0"
+        if self.sp_tc:
+            self.tauT, self.WmnijT = E(vl, v, o, o), E(o, o, o, o)
         if dtype == torch.float32 and hasattr(be, "split_lo"):
             self._lo = {}
             const = [("vvvv", self.vvvv_loc), ("ovvv", self.blk["ovvv"]), ("oovv", self.blk["oovv"])]
@@ -152,6 +159,8 @@ class CCSDEngine(object):
                 be.register_lo_plane(x, lo)
                 self._lo[name] = lo
             varying = ["tau"] + (["t2sP", "t2P", "t2Q", "tauWPn", "t2Rh", "Wr1", "Wr2"] if self.sp_plain else [])
+            if self.sp_tc:
+                varying += ["tauT", "WmnijT", "t1", "t2", "Fae2"]
             for name in varying:
                 x = getattr(self, name)
                 self._lo[name] = be.empty(tuple(x.shape), dtype)
@@ -184,6 +193,8 @@ class CCSDEngine(object):
         if self.sp_plain:
             d.update(oovvP=self.oovvP, oovvX=self.oovvX, LoovvP=self.LoovvP, t2sP=self.t2sP, t2P=self.t2P, t2Q=self.t2Q,
                      tauWPn=self.tauWPn, t2Rh=self.t2Rh)
+        if getattr(self, "sp_tc", False):
+            d.update(tauT=self.tauT, WmnijT=self.WmnijT)
         out = {}
         for nm in names:
             if nm == "vvvv_s0":
@@ -306,6 +317,7 @@ class CCSDEngine(object):
     }
     R_T2_SP = {"r2_s3[ijaB] += t2s[imae]*Wr1[jBme] + t2[imae]*Wr2[jBme]": "r2_s3[ijaB] += t2sP[iame]*Wr1[jBme] + t2P[iame]*Wr2[jBme]",
                "r2_s3[ijaB] += t2[mjae]*Wr2[iBme]": "r2_s3[ijaB] += t2Q[jame]*Wr2[iBme]"}
+    R_T2_TC = {"r2_s2[ijAb] += 0.5*Wmnij[mnij]*tau_s2[mnAb]": "r2_s2[ijAb] += 0.5*WmnijT[ijmn]*tauT[Abmn]"}
 
     def builder_order(self):
         """Builders run by residuals(), in the reference's order (pycc/ccwfn.py:357-366).
@@ -319,6 +331,7 @@ class CCSDEngine(object):
 
     def _statements(self, plain=None):
         """``plain=False``: the layout-independent statement set (complex_engine expands that one)."""
+        own = plain is None
         plain = self.sp_plain if plain is None else plain
         st = dict(self.STATEMENTS)
         if self.model == 'CC2':
@@ -327,6 +340,8 @@ class CCSDEngine(object):
         elif plain:
             st.update(self.STATEMENTS_SP)
             st["r_T2"] = [self.R_T2_SP.get(x, x) for x in st["r_T2"]]
+            if getattr(self, "sp_tc", False) and own:
+                st["r_T2"] = [self.R_T2_TC.get(x, x) for x in st["r_T2"]]
         return st
 
     def _plan_list(self, stmts):
@@ -334,9 +349,13 @@ class CCSDEngine(object):
         launches = []
         for s in stmts:
             T = self._tensors(set(re.findall(r"([A-Za-z_][A-Za-z_0-9]*)\[", s)))
-            for L in plan(s, T, self.dcode, prefer_flat=True if self.sp_plain else None):
+            mine = plan(s, T, self.dcode, prefer_flat=True if self.sp_plain else None)
+            for L in mine:
                 L.is_ladder = "vvvv_s0" in s
+                L.post = None
                 launches.append(L)
+            if getattr(self, "sp_tc", False) and s.startswith("Fae2[") and mine:
+                mine[-1].post = "Fae2"          # _launch: refresh its residual plane right after
         return launches
 
     def _build_plans(self):
@@ -372,6 +391,9 @@ class CCSDEngine(object):
             if self._lo is not None and self.sp_plain:      # the ring intermediates are operands now
                 self.be.split_lo(self.Wr1, self._lo["Wr1"])
                 self.be.split_lo(self.Wr2, self._lo["Wr2"])
+            if getattr(self, "sp_tc", False):
+                self.be.permute4(self.WmnijT, self.Wmnij.permute(2, 3, 0, 1))
+                self.be.split_lo(self.WmnijT, self._lo["WmnijT"])
         with nvtx_range("ccsd/" + name):
             self._launch(name)
         # the one exchange step of the iteration: sum the per-rank partial residuals
@@ -401,6 +423,8 @@ class CCSDEngine(object):
                 self.ladder_events.append((e0, e1))
             else:
                 self.be.contract(L.desc)
+            if L.post is not None:
+                self.be.split_lo(getattr(self, L.post), self._lo[L.post])
 
     # ---- amplitude-dependent element-wise preparations ---------------------------------------
     def prepare(self):
@@ -414,7 +438,10 @@ class CCSDEngine(object):
             outs.update(t2sP=self.t2sP, t2P=self.t2P, t2Q=self.t2Q, tauWPn=self.tauWPn, t2Rh=self.t2Rh)
         be.prepare_amplitudes(self.t1, self.t2, o, v, self.vlo, self.vl, **outs)
         if self._lo is not None:
-            for name in ["tau"] + (["t2sP", "t2P", "t2Q", "tauWPn", "t2Rh"] if self.sp_plain else []):
+            if self.sp_tc:
+                be.permute4(self.tauT, self.tau.narrow(2, self.vlo, self.vl).permute(2, 3, 0, 1))
+            for name in ["tau"] + (["t2sP", "t2P", "t2Q", "tauWPn", "t2Rh"] if self.sp_plain else []) + \
+                    (["tauT", "t1", "t2"] if self.sp_tc else []):
                 be.split_lo(getattr(self, name), self._lo[name])
 
     def set_amplitudes(self, t1, t2):

@@ -223,6 +223,12 @@ TC05_CASES = [
     ("C[mn] = A[mk]*B[nk]", dict(A=(300, 1000), B=(520, 1000), C=(300, 520))),
     ("C[nm] = A[mk]*B[nk]", dict(A=(260, 512), B=(300, 512), C=(300, 260))),                                # strided output
     ("C[mn] = A[mk]*B[nk] + A2[mk]*B2[nk]", dict(A=(256, 260), B=(256, 260), A2=(256, 260), B2=(256, 260), C=(256, 256))),
+    # the epilogue that leaves through shared memory with lane = column (n contiguous in C): D read along n as well,
+    ("C[iajb] = D[ijab] + A[iak]*B[jbk]", dict(A=(12, 12, 260), B=(20, 16, 260), D=(12, 20, 12, 16), C=(12, 12, 20, 16))),
+    # compound m and n of the output (r2[ijaB] of the ring terms) with D read along m (thread = row mapping),
+    ("C[ijab] = 2.0*D[jbia] + A[iak]*B[jbk]", dict(A=(11, 13, 300), B=(19, 17, 300), D=(19, 17, 11, 13), C=(11, 19, 13, 17))),
+    # and a short M (t1[ie] <ja|be>: M = o rows in a 128-row tile)
+    ("C[mn] = A[mk]*B[nk]", dict(A=(40, 300), B=(1000, 300), C=(40, 1000))),
 ]
 
 

@@ -217,12 +217,13 @@ def test_mixed_precision_mode(golden):
     assert np.abs(w.t2.cpu().numpy().astype(np.float64) - g["solve_t2"]).max() < 1e-5
 
 
-def test_mixed_precision_seeded():
+@pytest.mark.parametrize("no,nv,seed", [(8, 36, 11), (16, 24, 12)])
+def test_mixed_precision_seeded(no, nv, seed):
+    """(16,24): o^2 = 256 makes the K-contiguous o^4 v^2 term WmnijT[ijmn] tauT[abmn] eligible for the tcgen05 kernel."""
     import pycc_b200
     from pycc_b200.synthetic import SyntheticSystem
     from oracle import ccsd_oracle as oc
-    no, nv = 8, 36
-    s = SyntheticSystem(no, nv, seed=11, fock_offdiag=True)
+    s = SyntheticSystem(no, nv, seed=seed, fock_offdiag=True)
     with contextlib.redirect_stdout(io.StringIO()):
         w = pycc_b200.ccwfn.from_arrays(s.F, s.blocks, no, precision="SP")
         e = w.solve_cc(e_conv=1e-7, r_conv=1e-7, maxiter=100)
