@@ -200,6 +200,71 @@ __device__ __forceinline__ void load_tile_mnmajor(unsigned tile_s, const double*
     }
 }
 
+// Epilogue of the DMMA kernels: C = alpha * acc + beta * C + gamma * D over the thread's fragment (rows roff[i], columns
+// colbase + 8 j + {c0, c1}), JG column groups at a time.  Every load of a block is issued - unconditionally, from C[0] /
+// D[0] for masked elements - before the first value is used: with `if (ok) v = beta * C[..]` each element was its own
+// basic block (LDG, DMUL, BRA in the SASS) and the warp paid one round trip per element.
+template <int MI, int JG>
+__device__ __forceinline__ void store_tile_f64(const DParams& p, double (&acc)[MI][4][2], double alpha, const long long (&roff)[MI],
+                                               const long long (&droff)[MI], unsigned colbase, unsigned c0, unsigned c1) {
+    const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
+#pragma unroll
+    for (int j0 = 0; j0 < 4; j0 += JG) {
+        long long co[JG][2];
+        bool cok[JG][2];
+        double add[JG][2][MI];
+#pragma unroll
+        for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const unsigned col = colbase + (j0 + jj) * 8 + (e ? c1 : c0);
+                cok[jj][e] = col < p.N;
+                co[jj][e] = cok[jj][e] ? didx_off(p.cn, col) : 0;
+#pragma unroll
+                for (int i = 0; i < MI; ++i) add[jj][e][i] = 0.0;
+            }
+        if (use_beta) {
+#pragma unroll
+            for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+#pragma unroll
+                    for (int i = 0; i < MI; ++i) add[jj][e][i] = p.C[(cok[jj][e] && roff[i] >= 0) ? roff[i] + co[jj][e] : 0];
+        }
+#pragma unroll
+        for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int i = 0; i < MI; ++i) acc[i][j0 + jj][e] = alpha * acc[i][j0 + jj][e] + p.beta * add[jj][e][i];
+        if (use_d) {
+#pragma unroll
+            for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const unsigned col = colbase + (j0 + jj) * 8 + (e ? c1 : c0);
+                    const long long dco = cok[jj][e] ? didx_off(p.dn, col) : 0;
+#pragma unroll
+                    for (int i = 0; i < MI; ++i) add[jj][e][i] = p.D[(cok[jj][e] && roff[i] >= 0) ? droff[i] + dco : 0];
+                }
+#pragma unroll
+            for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+#pragma unroll
+                    for (int i = 0; i < MI; ++i) acc[i][j0 + jj][e] += p.gamma * add[jj][e][i];
+        }
+#pragma unroll
+        for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int i = 0; i < MI; ++i)
+                    if (cok[jj][e] && roff[i] >= 0) p.C[roff[i] + co[jj][e]] = acc[i][j0 + jj][e];
+    }
+}
+
+
 template <int VEC, int MI>
 __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kernel(const __grid_constant__ DParams p) {
     constexpr int BM = 16 * MI;
@@ -421,37 +486,7 @@ __global__ void __launch_bounds__(NTHREADS, (MI <= 2) ? 2 : 1) contract_f64_kern
         roff[i] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
         droff[i] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
     }
-    // Two-phase per column group: all loads of C / D for the group are issued before the first
-    // store, so their latencies overlap (a store to C may alias the next load of C as far as the
-    // compiler knows; interleaving them serialises ~8*MI round trips to L2/HBM per thread).
-    const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        long long co[2], dco[2];
-        bool cok[2];
-        double add[2][MI];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const unsigned col = colbase + j * 8 + e;
-            cok[e] = col < p.N;
-            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
-            dco[e] = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
-#pragma unroll
-            for (int i = 0; i < MI; ++i) {
-                double v = 0.0;
-                if (cok[e] && roff[i] >= 0) {
-                    if (use_beta) v = p.beta * p.C[roff[i] + co[e]];
-                    if (use_d) v += p.gamma * p.D[droff[i] + dco[e]];
-                }
-                add[e][i] = v;
-            }
-        }
-#pragma unroll
-        for (int e = 0; e < 2; ++e)
-#pragma unroll
-            for (int i = 0; i < MI; ++i)
-                if (cok[e] && roff[i] >= 0) p.C[roff[i] + co[e]] = alpha * acc[i][j][e] + add[e][i];
-    }
+    store_tile_f64<MI, 1>(p, acc, alpha, roff, droff, colbase, 0u, 1u);
 }
 
 // ---- warp-specialised variant ------------------------------------------------------------------
@@ -683,46 +718,8 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f64_ws_kernel(const _
         roff[i] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
         droff[i] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
     }
-    // Two-phase per column group: all loads of C / D for the group are issued before the first
-    // store, so their latencies overlap (a store to C may alias the next load of C as far as the
-    // compiler knows; interleaving them serialises ~8*MI round trips to L2/HBM per thread).
-    const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
-    // column groups of JG*8 columns: every load of C / D of a group is issued before its first store
-    // (the consumers own 216 registers, so up to MI = 4 the whole tile is one group, MI = 5, 6 two groups: fewer L2/HBM round
-    // trips per tile)
-    constexpr int JG = (MI <= 4) ? 4 : ((MI <= 5) ? 2 : 1);
-#pragma unroll
-    for (int j0 = 0; j0 < 4; j0 += JG) {
-        long long co[JG][2];
-        bool cok[JG][2];
-        double add[JG][2][MI];
-#pragma unroll
-        for (int jj = 0; jj < JG; ++jj)
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const unsigned col = colbase + (j0 + jj) * 8 + e;
-                cok[jj][e] = col < p.N;
-                co[jj][e] = cok[jj][e] ? didx_off(p.cn, col) : 0;
-                const long long dco = (cok[jj][e] && use_d) ? didx_off(p.dn, col) : 0;
-#pragma unroll
-                for (int i = 0; i < MI; ++i) {
-                    double v = 0.0;
-                    if (cok[jj][e] && roff[i] >= 0) {
-                        if (use_beta) v = p.beta * p.C[roff[i] + co[jj][e]];
-                        if (use_d) v += p.gamma * p.D[droff[i] + dco];
-                    }
-                    add[jj][e][i] = v;
-                }
-            }
-#pragma unroll
-        for (int jj = 0; jj < JG; ++jj)
-#pragma unroll
-            for (int e = 0; e < 2; ++e)
-#pragma unroll
-                for (int i = 0; i < MI; ++i)
-                    if (cok[jj][e] && roff[i] >= 0)
-                        p.C[roff[i] + co[jj][e]] = alpha * acc[i][j0 + jj][e] + add[jj][e][i];
-    }
+    // (the consumers own 216 registers: up to MI = 4 the whole tile is one block of loads, MI = 5 two, MI = 6 four)
+    store_tile_f64<MI, (MI <= 4) ? 4 : ((MI <= 5) ? 2 : 1)>(p, acc, alpha, roff, droff, colbase, 0u, 1u);
     }   // tile loop
 }
 
@@ -1304,34 +1301,7 @@ contract_f64_tma_kernel(const __grid_constant__ DParams p, const __grid_constant
         roff[i] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
         droff[i] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
     }
-    const bool use_beta = p.beta != 0.0, use_d = p.D != nullptr;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        long long co[2];
-        bool cok[2];
-        double add[2][MI];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const unsigned col = colbase + j * 8 + (e ? pc1 : pc0);
-            cok[e] = col < p.N;
-            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
-            const long long dco = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
-#pragma unroll
-            for (int i = 0; i < MI; ++i) {
-                double v = 0.0;
-                if (cok[e] && roff[i] >= 0) {
-                    if (use_beta) v = p.beta * p.C[roff[i] + co[e]];
-                    if (use_d) v += p.gamma * p.D[droff[i] + dco];
-                }
-                add[e][i] = v;
-            }
-        }
-#pragma unroll
-        for (int e = 0; e < 2; ++e)
-#pragma unroll
-            for (int i = 0; i < MI; ++i)
-                if (cok[e] && roff[i] >= 0) p.C[roff[i] + co[e]] = alpha * acc[i][j][e] + add[e][i];
-    }
+    store_tile_f64<MI, 1>(p, acc, alpha, roff, droff, colbase, (unsigned)pc0, (unsigned)pc1);
     }   // tile loop
 }
 

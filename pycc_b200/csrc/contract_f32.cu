@@ -177,6 +177,90 @@ __device__ __forceinline__ void load_tile_mnmajor(unsigned tile_s, const float* 
     }
 }
 
+// Epilogue of the mma.sync kernels: C = alpha * acc + beta * C + gamma * D over the thread's fragment (rows roff[i][h],
+// columns colbase + 8 j + e).  The loads of a block of column groups are issued as plain predicated loads, all of them
+// before the first value is used: written as `if (ok) v = beta * C[..]` every element became its own basic block
+// (LDG, FMUL, BRA in the SASS) and a warp - which issues in order - paid one L2 / HBM round trip per element; the
+// K = o launches of r_T2 (epilogue-bound) ran at 0.7 TB/s.
+template <int MJ>
+__device__ __forceinline__ void store_tile_f32(const FParams& p, float (&acc)[MJ][4][4], float alpha, const long long (&roff)[MJ][2],
+                                               const long long (&droff)[MJ][2], unsigned colbase) {
+    const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
+    constexpr int JG = MJ <= 2 ? 4 : 2;
+#pragma unroll
+    for (int j0 = 0; j0 < 4; j0 += JG) {
+        long long co[JG][2];
+        bool cok[JG][2];
+        float add[JG][2][MJ][2];
+#pragma unroll
+        for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const unsigned col = colbase + (j0 + jj) * 8 + e;
+                cok[jj][e] = col < p.N;
+                co[jj][e] = cok[jj][e] ? didx_off(p.cn, col) : 0;
+#pragma unroll
+                for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+                        add[jj][e][i][h] = 0.f;
+            }
+        // (masked elements read C[0] / D[0] - always mapped - instead of branching around the load; their result is never stored)
+        if (use_beta) {
+#pragma unroll
+            for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+#pragma unroll
+                    for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+                            add[jj][e][i][h] = p.C[(cok[jj][e] && roff[i][h] >= 0) ? roff[i][h] + co[jj][e] : 0];
+        }
+#pragma unroll
+        for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+                        acc[i][j0 + jj][2 * h + e] = alpha * acc[i][j0 + jj][2 * h + e] + p.beta * add[jj][e][i][h];
+        if (use_d) {
+#pragma unroll
+            for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e) {
+                    const unsigned col = colbase + (j0 + jj) * 8 + e;
+                    const long long dco = cok[jj][e] ? didx_off(p.dn, col) : 0;
+#pragma unroll
+                    for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h)
+                            add[jj][e][i][h] = p.D[(cok[jj][e] && roff[i][h] >= 0) ? droff[i][h] + dco : 0];
+                }
+#pragma unroll
+            for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+#pragma unroll
+                    for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                        for (int h = 0; h < 2; ++h) acc[i][j0 + jj][2 * h + e] += p.gamma * add[jj][e][i][h];
+        }
+#pragma unroll
+        for (int jj = 0; jj < JG; ++jj)
+#pragma unroll
+            for (int e = 0; e < 2; ++e)
+#pragma unroll
+                for (int i = 0; i < MJ; ++i)
+#pragma unroll
+                    for (int h = 0; h < 2; ++h)
+                        if (cok[jj][e] && roff[i][h] >= 0) p.C[roff[i][h] + co[jj][e]] = acc[i][j0 + jj][2 * h + e];
+    }
+}
+
+
 template <int VEC, int MJ>
 __global__ void __launch_bounds__(NTHREADS, 1) contract_f32_kernel(const __grid_constant__ FParams p) {
     constexpr int BM = 32 * MJ;
@@ -360,39 +444,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) contract_f32_kernel(const __grid_
             roff[i][h] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
             droff[i][h] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
         }
-    const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        long long co[2], dco[2];
-        bool cok[2];
-        float add[2][MJ][2];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const unsigned col = colbase + j * 8 + e;
-            cok[e] = col < p.N;
-            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
-            dco[e] = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
-#pragma unroll
-            for (int i = 0; i < MJ; ++i)
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    float v = 0.f;
-                    if (cok[e] && roff[i][h] >= 0) {
-                        if (use_beta) v = p.beta * p.C[roff[i][h] + co[e]];
-                        if (use_d) v += p.gamma * p.D[droff[i][h] + dco[e]];
-                    }
-                    add[e][i][h] = v;
-                }
-        }
-#pragma unroll
-        for (int e = 0; e < 2; ++e)
-#pragma unroll
-            for (int i = 0; i < MJ; ++i)
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-                    if (cok[e] && roff[i][h] >= 0)
-                        p.C[roff[i][h] + co[e]] = alpha * acc[i][j][2 * h + e] + add[e][i][h];
-    }
+    store_tile_f32<MJ>(p, acc, alpha, roff, droff, colbase);
 }
 
 // ---- warp-specialised, persistent variant (see contract.cu): 4 producer warps stage the tiles,
@@ -624,39 +676,7 @@ __global__ void __launch_bounds__(NTHREADS_WS, 1) contract_f32_ws_kernel(const _
             roff[i][h] = (row < p.M) ? didx_off(p.cm, row) + (long long)batch * p.c_batch : -1;
             droff[i][h] = (row < p.M && p.D) ? didx_off(p.dm, row) + (long long)batch * p.d_batch : 0;
         }
-    const bool use_beta = p.beta != 0.f, use_d = p.D != nullptr;
-#pragma unroll
-    for (int j = 0; j < 4; ++j) {
-        long long co[2], dco[2];
-        bool cok[2];
-        float add[2][MJ][2];
-#pragma unroll
-        for (int e = 0; e < 2; ++e) {
-            const unsigned col = colbase + j * 8 + e;
-            cok[e] = col < p.N;
-            co[e] = cok[e] ? didx_off(p.cn, col) : 0;
-            dco[e] = (cok[e] && use_d) ? didx_off(p.dn, col) : 0;
-#pragma unroll
-            for (int i = 0; i < MJ; ++i)
-#pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    float v = 0.f;
-                    if (cok[e] && roff[i][h] >= 0) {
-                        if (use_beta) v = p.beta * p.C[roff[i][h] + co[e]];
-                        if (use_d) v += p.gamma * p.D[droff[i][h] + dco[e]];
-                    }
-                    add[e][i][h] = v;
-                }
-        }
-#pragma unroll
-        for (int e = 0; e < 2; ++e)
-#pragma unroll
-            for (int i = 0; i < MJ; ++i)
-#pragma unroll
-                for (int h = 0; h < 2; ++h)
-                    if (cok[e] && roff[i][h] >= 0)
-                        p.C[roff[i][h] + co[e]] = alpha * acc[i][j][2 * h + e] + add[e][i][h];
-    }
+    store_tile_f32<MJ>(p, acc, alpha, roff, droff, colbase);
     }   // tile loop
 }
 
