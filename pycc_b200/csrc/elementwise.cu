@@ -49,33 +49,47 @@ __global__ void final_sum_kernel(const double* __restrict__ partials, int n, int
 }
 
 // ---- pair_combine: out[ijab] = c0 X[ijab] + c1 X[ijba] + c2 u[ia] w[jb] -----------------------
-// One CTA per 32x32 (a,b) tile of one (i,j) pair; the transposed read goes through shared memory
-// so both global reads are coalesced.
+// One CTA (256 threads, 32 x 8) per 64 x 64 (a,b) tile of one (i,j) pair; the transposed read goes through shared
+// memory so both global reads are coalesced.  Every thread has its 16 elements of each stream in flight before the
+// barrier: with 32 x 32 tiles (4 per thread) these kernels were latency-bound at 0.54 - 0.63 of the HBM roofline.
+constexpr int PT = 64;                    // pair-kernel tile edge
+#define PAIR_K_R(k) (ty + 8 * ((k) >> 1))
+#define PAIR_K_C(k) (tx + 32 * ((k) & 1))
+
 template <typename T>
-__global__ void pair_combine_kernel(T* __restrict__ out, const T* __restrict__ X, double c0, double c1,
-                                    const T* __restrict__ u, const T* __restrict__ w, double c2, int no, int nv,
-                                    int tiles_per_dim) {
-    __shared__ T tile[32][33];
+__global__ void __launch_bounds__(256) pair_combine_kernel(T* __restrict__ out, const T* __restrict__ X, double c0, double c1,
+                                                           const T* __restrict__ u, const T* __restrict__ w, double c2, int no,
+                                                           int nv, int tiles_per_dim) {
+    __shared__ T tile[PT][PT + 1];
     const long long ij = blockIdx.y;
     const int ta = blockIdx.x / tiles_per_dim, tb = blockIdx.x % tiles_per_dim;
     const int i = (int)(ij / no), j = (int)(ij % no);
     const T* Xij = X + ij * (long long)nv * nv;
     T* Oij = out + ij * (long long)nv * nv;
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;   // 32 x 8
-    if (c1 != 0.0) {
-        // tile[r][c] = X[b0 + r][a0 + c]  (rows are b, columns a)
-        for (int r = ty; r < 32; r += 8) {
-            const int b = tb * 32 + r, a = ta * 32 + tx;
-            tile[r][tx] = (a < nv && b < nv) ? Xij[(long long)b * nv + a] : T(0);
-        }
-        __syncthreads();
+    T xt[16], xd[16];
+    const bool want_t = c1 != 0.0, want_d = c0 != 0.0;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {        // tile[r][c] = X[b0 + r][a0 + c]  (rows are b, columns a)
+        const int b = tb * PT + PAIR_K_R(k), a = ta * PT + PAIR_K_C(k);
+        xt[k] = (want_t && a < nv && b < nv) ? Xij[(long long)b * nv + a] : T(0);
     }
-    for (int r = ty; r < 32; r += 8) {
-        const int a = ta * 32 + r, b = tb * 32 + tx;
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int a = ta * PT + PAIR_K_R(k), b = tb * PT + PAIR_K_C(k);
+        xd[k] = (want_d && a < nv && b < nv) ? Xij[(long long)a * nv + b] : T(0);
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) tile[PAIR_K_R(k)][PAIR_K_C(k)] = xt[k];
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int r = PAIR_K_R(k), c = PAIR_K_C(k);
+        const int a = ta * PT + r, b = tb * PT + c;
         if (a < nv && b < nv) {
             double v = 0.0;
-            if (c0 != 0.0) v += c0 * (double)Xij[(long long)a * nv + b];
-            if (c1 != 0.0) v += c1 * (double)tile[tx][r];
+            if (want_d) v += c0 * (double)xd[k];
+            if (want_t) v += c1 * (double)tile[c][r];
             if (u != nullptr) v += c2 * (double)u[(long long)i * nv + a] * (double)w[(long long)j * nv + b];
             Oij[(long long)a * nv + b] = (T)v;
         }
@@ -85,8 +99,8 @@ __global__ void pair_combine_kernel(T* __restrict__ out, const T* __restrict__ X
 // ---- pair_symmetrize: r2[ijab] += r2[jiba] in place --------------------------------------------
 // CTA handles the tile pair {(i,j; A,B), (j,i; B,A)}; only canonical pairs do work.
 template <typename T>
-__global__ void pair_symmetrize_kernel(T* __restrict__ r2, int no, int nv, int tiles_per_dim) {
-    __shared__ T tile[32][33];
+__global__ void __launch_bounds__(256) pair_symmetrize_kernel(T* __restrict__ r2, int no, int nv, int tiles_per_dim) {
+    __shared__ T tile[PT][PT + 1];
     const long long ij = blockIdx.y;
     const int i = (int)(ij / no), j = (int)(ij % no);
     const int ta = blockIdx.x / tiles_per_dim, tb = blockIdx.x % tiles_per_dim;
@@ -96,35 +110,38 @@ __global__ void pair_symmetrize_kernel(T* __restrict__ r2, int no, int nv, int t
     T* P = r2 + ((long long)i * no + j) * nv * nv;   // [a][b]
     T* Q = r2 + ((long long)j * no + i) * nv * nv;   // partner, element [b][a]
     const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
-    // tile[r][c] = Q[b0 + r][a0 + c]
-    for (int r = ty; r < 32; r += 8) {
-        const int b = tb * 32 + r, a = ta * 32 + tx;
-        tile[r][tx] = (a < nv && b < nv) ? Q[(long long)b * nv + a] : T(0);
+    T q[16], s[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {        // tile[r][c] = Q[b0 + r][a0 + c]
+        const int b = tb * PT + PAIR_K_R(k), a = ta * PT + PAIR_K_C(k);
+        q[k] = (a < nv && b < nv) ? Q[(long long)b * nv + a] : T(0);
     }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int a = ta * PT + PAIR_K_R(k), b = tb * PT + PAIR_K_C(k);
+        s[k] = (a < nv && b < nv) ? P[(long long)a * nv + b] : T(0);
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) tile[PAIR_K_R(k)][PAIR_K_C(k)] = q[k];
     __syncthreads();
     // s[a][b] = P[a][b] + Q[b][a]; write P now, stage s for the partner write
-    T s_reg[4];
-    int cnt = 0;
-    for (int r = ty; r < 32; r += 8, ++cnt) {
-        const int a = ta * 32 + r, b = tb * 32 + tx;
-        T s = T(0);
-        if (a < nv && b < nv) {
-            s = P[(long long)a * nv + b] + tile[tx][r];
-        }
-        s_reg[cnt] = s;
-    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) s[k] += tile[PAIR_K_C(k)][PAIR_K_R(k)];
     __syncthreads();
-    cnt = 0;
-    for (int r = ty; r < 32; r += 8, ++cnt) {
-        const int a = ta * 32 + r, b = tb * 32 + tx;
-        if (a < nv && b < nv) P[(long long)a * nv + b] = s_reg[cnt];
-        tile[r][tx] = s_reg[cnt];        // tile[a_local][b_local] = s
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int r = PAIR_K_R(k), c = PAIR_K_C(k);
+        const int a = ta * PT + r, b = tb * PT + c;
+        if (a < nv && b < nv) P[(long long)a * nv + b] = s[k];
+        tile[r][c] = s[k];        // tile[a_local][b_local] = s
     }
     __syncthreads();
     if (self) return;
-    for (int r = ty; r < 32; r += 8) {
-        const int b = tb * 32 + r, a = ta * 32 + tx;
-        if (a < nv && b < nv) Q[(long long)b * nv + a] = tile[tx][r];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const int r = PAIR_K_R(k), c = PAIR_K_C(k);
+        const int b = tb * PT + r, a = ta * PT + c;
+        if (a < nv && b < nv) Q[(long long)b * nv + a] = tile[c][r];
     }
 }
 
@@ -144,6 +161,79 @@ __global__ void permute4_kernel(T* __restrict__ out, const T* __restrict__ in, l
         double v = alpha * (double)in[i0 * s0 + i1 * s1 + i2 * s2 + i3 * s3];
         if (beta != 0.0) v += beta * (double)out[idx];
         out[idx] = (T)v;
+    }
+}
+
+// Two faster forms of the same operation (pccb_permute4 picks one; the kernel above keeps the shapes they do not take):
+//  * rows: the input's contiguous index is also the output's last one.  One warp per output row, lanes along it; the
+//    row index is decomposed once per row instead of four 64-bit divisions per element (the generic kernel ran at
+//    0.46 of the HBM roofline on [i,a,m,e] <- [i,m,a,e] although both sides are coalesced).
+//  * tiles: the input's contiguous index q is another output index.  64 x 64 tiles over (q, last) through shared
+//    memory, read with lanes along q and written with lanes along the last index; 16 loads per thread are in flight
+//    before the barrier (a 32 x 32 tile leaves 4 per thread: latency-bound).
+template <typename T>
+__global__ void __launch_bounds__(256) permute4_rows_kernel(T* __restrict__ out, const T* __restrict__ in, unsigned n1, unsigned n2,
+                                                            unsigned n3, long long s0, long long s1, long long s2, long long s3,
+                                                            unsigned rows, double alpha, double beta) {
+    const unsigned lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (unsigned row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
+        const unsigned i2 = row % n2, r = row / n2, i1 = r % n1, i0 = r / n1;
+        const T* src = in + i0 * s0 + i1 * s1 + i2 * s2;
+        T* dst = out + (long long)row * n3;
+        for (unsigned c = lane; c < n3; c += 128) {
+            T x[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) x[u] = (c + 32 * u < n3) ? src[(long long)(c + 32 * u) * s3] : T(0);
+            if (beta != 0.0) {
+                T y[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) y[u] = (c + 32 * u < n3) ? dst[c + 32 * u] : T(0);
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (c + 32 * u < n3) dst[c + 32 * u] = (T)(alpha * (double)x[u] + beta * (double)y[u]);
+            } else {
+#pragma unroll
+                for (int u = 0; u < 4; ++u)
+                    if (c + 32 * u < n3) dst[c + 32 * u] = (T)(alpha * (double)x[u]);
+            }
+        }
+    }
+}
+
+// q: the output dimension (0..2) along which the input is contiguous; u, w: the two remaining output dimensions (grid y, z)
+template <typename T>
+__global__ void __launch_bounds__(256) permute4_tiles_kernel(T* __restrict__ out, const T* __restrict__ in, unsigned nq, unsigned n3,
+                                                             unsigned tq, long long sq, long long s3, long long su, long long sw,
+                                                             long long oq, long long ou, long long ow, double alpha, double beta) {
+    __shared__ T tile[64][65];
+    const unsigned tx = threadIdx.x & 31, ty = threadIdx.x >> 5;          // 32 x 8
+    const unsigned q0 = (blockIdx.x % tq) * 64, c0 = (blockIdx.x / tq) * 64;
+    const T* src = in + blockIdx.y * su + blockIdx.z * sw;
+    T* dst = out + blockIdx.y * ou + blockIdx.z * ow;
+    T x[16];
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {            // row r of the tile = last index, columns = q
+        const unsigned r = ty + 8 * (k >> 1), iq = q0 + tx + 32 * (k & 1), i3 = c0 + r;
+        x[k] = (iq < nq && i3 < n3) ? src[(long long)iq * sq + (long long)i3 * s3] : T(0);
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) tile[ty + 8 * (k >> 1)][tx + 32 * (k & 1)] = x[k];
+    __syncthreads();
+    if (beta != 0.0) {
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+            const unsigned r = ty + 8 * (k >> 1), iq = q0 + r, i3 = c0 + tx + 32 * (k & 1);
+            x[k] = (iq < nq && i3 < n3) ? dst[(long long)iq * oq + i3] : T(0);
+        }
+    }
+#pragma unroll
+    for (int k = 0; k < 16; ++k) {
+        const unsigned r = ty + 8 * (k >> 1), iq = q0 + r, i3 = c0 + tx + 32 * (k & 1);
+        if (iq < nq && i3 < n3) {
+            double v = alpha * (double)tile[tx + 32 * (k & 1)][r];
+            if (beta != 0.0) v += beta * (double)x[k];
+            dst[(long long)iq * oq + i3] = (T)v;
+        }
     }
 }
 
@@ -554,7 +644,7 @@ int finish_reduction(pccb_ctx* ctx, int n, int nout, double* host_out) {
 template <typename T>
 int pair_combine_t(pccb_ctx* ctx, void* out, const void* X, double c0, double c1, const void* u, const void* w,
                    double c2, int64_t no, int64_t nv) {
-    const int tpd = (int)((nv + 31) / 32);
+    const int tpd = (int)((nv + PT - 1) / PT);
     dim3 grid(tpd * tpd, (unsigned)(no * no));
     pair_combine_kernel<T><<<grid, 256, 0, ctx->stream>>>((T*)out, (const T*)X, c0, c1, (const T*)u, (const T*)w, c2,
                                                           (int)no, (int)nv, tpd);
@@ -646,7 +736,7 @@ extern "C" int pccb_pair_combine(pccb_ctx* ctx, int dtype, void* out_dev, const 
 extern "C" int pccb_pair_symmetrize(pccb_ctx* ctx, int dtype, void* r2_dev, int64_t no, int64_t nv) {
     if (!ctx) return PCCB_ERR_ARG;
     PCCB_REQUIRE(ctx, r2_dev && no > 0 && nv > 0 && no * no <= 65535, "pccb_pair_symmetrize: bad arguments");
-    const int tpd = (int)((nv + 31) / 32);
+    const int tpd = (int)((nv + PT - 1) / PT);
     dim3 grid(tpd * tpd, (unsigned)(no * no));
     if (dtype == PCCB_F64)
         pair_symmetrize_kernel<double><<<grid, 256, 0, ctx->stream>>>((double*)r2_dev, (int)no, (int)nv, tpd);
@@ -664,6 +754,46 @@ extern "C" int pccb_permute4(pccb_ctx* ctx, int dtype, void* out_dev, const void
     PCCB_REQUIRE(ctx, out_dev && in_dev && shape && in_strides, "pccb_permute4: null argument");
     const long long total = shape[0] * shape[1] * shape[2] * shape[3];
     PCCB_REQUIRE(ctx, total > 0, "pccb_permute4: empty shape");
+    PCCB_REQUIRE(ctx, dtype == PCCB_F64 || dtype == PCCB_F32, "pccb_permute4: unknown dtype");
+    // the input's contiguous index: smallest stride among the indices of extent > 1
+    int q = -1;
+    for (int d = 0; d < 4; ++d)
+        if (shape[d] > 1 && in_strides[d] > 0 && (q < 0 || in_strides[d] < in_strides[q])) q = d;
+    static const bool fast = [] { const char* e = getenv("PCCB_PERMUTE_FAST"); return e ? atoi(e) != 0 : true; }();
+    const long long rows = shape[0] * shape[1] * shape[2];
+    if (fast && q == 3 && rows < (1ll << 31) && shape[3] < (1ll << 31)) {
+        const int gr = (int)((rows + 7) / 8 < 148 * 32 ? (rows + 7) / 8 : 148 * 32);
+        if (dtype == PCCB_F64)
+            permute4_rows_kernel<double><<<gr, 256, 0, ctx->stream>>>((double*)out_dev, (const double*)in_dev, (unsigned)shape[1],
+                                                                      (unsigned)shape[2], (unsigned)shape[3], in_strides[0], in_strides[1],
+                                                                      in_strides[2], in_strides[3], (unsigned)rows, alpha, beta);
+        else
+            permute4_rows_kernel<float><<<gr, 256, 0, ctx->stream>>>((float*)out_dev, (const float*)in_dev, (unsigned)shape[1],
+                                                                     (unsigned)shape[2], (unsigned)shape[3], in_strides[0], in_strides[1],
+                                                                     in_strides[2], in_strides[3], (unsigned)rows, alpha, beta);
+        PCCB_CHECK_LAUNCH(ctx, "permute4_rows_kernel");
+        return PCCB_OK;
+    }
+    if (fast && q >= 0 && q < 3) {
+        int uw[2], k = 0;
+        for (int d = 0; d < 3; ++d)
+            if (d != q) uw[k++] = d;
+        const long long ostr[4] = {shape[1] * shape[2] * shape[3], shape[2] * shape[3], shape[3], 1};
+        const long long tq = (shape[q] + 63) / 64, t3 = (shape[3] + 63) / 64;
+        if (shape[uw[0]] <= 65535 && shape[uw[1]] <= 65535 && tq * t3 < (1ll << 31)) {
+            const dim3 grid((unsigned)(tq * t3), (unsigned)shape[uw[0]], (unsigned)shape[uw[1]]);
+            if (dtype == PCCB_F64)
+                permute4_tiles_kernel<double><<<grid, 256, 0, ctx->stream>>>(
+                    (double*)out_dev, (const double*)in_dev, (unsigned)shape[q], (unsigned)shape[3], (unsigned)tq, in_strides[q],
+                    in_strides[3], in_strides[uw[0]], in_strides[uw[1]], ostr[q], ostr[uw[0]], ostr[uw[1]], alpha, beta);
+            else
+                permute4_tiles_kernel<float><<<grid, 256, 0, ctx->stream>>>(
+                    (float*)out_dev, (const float*)in_dev, (unsigned)shape[q], (unsigned)shape[3], (unsigned)tq, in_strides[q],
+                    in_strides[3], in_strides[uw[0]], in_strides[uw[1]], ostr[q], ostr[uw[0]], ostr[uw[1]], alpha, beta);
+            PCCB_CHECK_LAUNCH(ctx, "permute4_tiles_kernel");
+            return PCCB_OK;
+        }
+    }
     const int g = grid_for(total, 256, 148 * 16);
     if (dtype == PCCB_F64)
         permute4_kernel<double><<<g, 256, 0, ctx->stream>>>((double*)out_dev, (const double*)in_dev, shape[0],

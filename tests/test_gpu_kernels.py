@@ -318,6 +318,27 @@ def test_contract_f32_tcgen05_vs_einsum(be, case):
 
 
 @pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
+def test_permute4_forms(be, dtype):
+    """pccb_permute4 picks one of three kernels: rows (the input's contiguous index stays last), 64 x 64 tiles (it becomes
+    output index 0, 1 or 2) and the generic gather.  Every permutation of a ragged 4-index tensor, a narrowed (strided)
+    source, and the accumulate form; exact (a permutation times a power of two)."""
+    import itertools
+    g = torch.Generator(device="cpu").manual_seed(21)
+    X = torch.randn(5, 70, 9, 67, generator=g, dtype=torch.float64).to(dtype).to(be.device)
+    for perm in itertools.permutations(range(4)):
+        src = X.permute(*perm)
+        out = torch.full(tuple(src.shape), float("nan"), dtype=dtype, device=be.device)
+        be.permute4(out, src, 2.0, 0.0)
+        assert torch.equal(out, 2.0 * src), perm
+    for perm, dim in (((0, 3, 1, 2), 1), ((0, 1, 2, 3), 3), ((2, 3, 0, 1), 2)):
+        src = X.permute(*perm).narrow(dim, 1, X.permute(*perm).shape[dim] - 2)
+        out = torch.randn(tuple(src.shape), generator=g, dtype=torch.float64).to(dtype).to(be.device)
+        want = 0.5 * src + 2.0 * out
+        be.permute4(out, src, 0.5, 2.0)
+        assert torch.equal(out, want), (perm, dim)
+
+
+@pytest.mark.parametrize("dtype", [torch.float64, torch.float32])
 def test_dot_many_vs_dot(be, dtype):
     """pccb_dot_many (one pass, one synchronisation: the new DIIS Gram row) against pccb_dot entry by entry and
     an FP64 torch dot; odd length (scalar tail) and an unaligned view (VEC = 1 path)."""

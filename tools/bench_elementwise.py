@@ -71,7 +71,9 @@ row("pair_symmetrize_kernel (r2 += r2^T in place)", "ccwfn.py:621", 2 * w * N2, 
 row("dot_vec_kernel (DIIS Gram entry)", "utils.py:108-112", 2 * w * N2, lambda: be.dot(x, y))
 row("axpby_vec_kernel (DIIS error vector)", "utils.py:26-46", 3 * w * N2, lambda: be.axpby(z, 1.0, x, -1.0, y))
 row("lincomb_vec_kernel, 8 vectors (DIIS extrapolation)", "utils.py:129-133", 9 * w * N2, lambda: be.lincomb(z, vecs, [0.125] * 8))
-row("permute4_kernel [i,a,m,e] <- [i,m,a,e] (set-up only)", "set-up", 2 * w * N2, lambda: be.permute4(perm["t2P"], t2.permute(0, 2, 1, 3)))
+row("permute4_rows_kernel [i,a,m,e] <- [i,m,a,e] (set-up only)", "set-up", 2 * w * N2, lambda: be.permute4(perm["t2P"], t2.permute(0, 2, 1, 3)))
+tauT = torch.empty(v, v, o, o, dtype=t2.dtype, device=t2.device)
+row("permute4_tiles_kernel [a,b,m,n] <- [m,n,a,b] (tauT, FP32 mode)", "layout", 2 * w * N2, lambda: be.permute4(tauT, t2.permute(2, 3, 0, 1)))
 
 print("# element-wise kernels of libpyccb200.so at o=%d v=%d FP64 (o^2 v^2 tensor = %.2f GB), B200, CUDA events" % (o, v, w * N2 / 1e9))
 print("# peak = %.1f GB/s (%s: copy bandwidth, read + write bytes)" % (peak, src))
