@@ -31,7 +31,7 @@ for line in sass.splitlines():
         cur = re.sub(r"\(.*$", "", cur)                  # drop the parameter list
         kern[cur] = collections.Counter()
         continue
-    m = re.match(r"\s+/\*[0-9a-f]{4}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
+    m = re.match(r"\s+/\*[0-9a-f]{4,6}\*/\s+(?:@!?U?P\d+\s+)?([A-Z0-9_.]+)", line)
     if m and cur is not None:
         op = m.group(1)
         kern[cur]["_total"] += 1
