@@ -142,8 +142,27 @@ def test_sp_mode_plain_matrix_ring_terms(golden, model):
         r1, r2 = w.residuals(g.F, t1, g["gen_t2"])
         d1, d2 = wd.residuals(g.F, t1, g["gen_t2"])
     assert w.engine.sp_plain and any("t2sP" in L.text for L in w.engine.plans["r_T2"])
+    # the K-contiguous copies of the o^4 v^2 term and the residual plane of Fae2 refreshed right after its launch
+    assert w.engine.sp_tc and any("WmnijT[ijmn]*tauT[Abmn]" in L.text for L in w.engine.plans["r_T2"])
+    assert [L.post for L in w.engine.plans["r_T2"] if L.post] == ["Fae2"]
     assert np.abs(r2.double().numpy() - d2.numpy()).max() < 2e-6 * max(1.0, np.abs(d2.numpy()).max())
     assert np.abs(r1.double().numpy() - d1.numpy()).max() < 2e-6
+
+
+def test_sp_mode_without_extra_layouts(golden, monkeypatch):
+    """PCCB_SP_TC_EXTRA=0: the mixed-precision engine without tauT / WmnijT and the extra residual planes - the
+    statement set of the first round-2 bench - gives the same residual to FP32 rounding."""
+    g = golden
+    with contextlib.redirect_stdout(io.StringIO()):
+        w1 = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, precision="SP", _backend=InterpBackend())
+        a1, a2 = w1.residuals(g.F, g["gen_t1"], g["gen_t2"])
+        a1, a2 = a1.clone(), a2.clone()
+        monkeypatch.setenv("PCCB_SP_TC_EXTRA", "0")
+        w0 = pycc_b200.ccwfn.from_arrays(g.F, g.blocks, g.no, precision="SP", _backend=InterpBackend())
+        b1, b2 = w0.residuals(g.F, g["gen_t1"], g["gen_t2"])
+    assert not w0.engine.sp_tc and not any("WmnijT" in L.text for L in w0.engine.plans["r_T2"])
+    assert all(L.post is None for L in w0.engine.plans["r_T2"])
+    assert (a2 - b2).abs().max().item() < 2e-6 and (a1 - b1).abs().max().item() < 2e-6
 
 
 def test_integral_front_end_host_logic():
