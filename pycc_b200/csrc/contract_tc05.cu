@@ -21,8 +21,11 @@
 //                      from shared-memory matrix descriptors, tcgen05.commit -> the stage's "empty"
 //                      barrier, and after the last k-block -> the "accumulator full" barrier;
 //                      warp 1 also owns the 256-column TMEM allocation;
-//   warps 2-5        : epilogue - tcgen05.ld 32 lanes x 16 columns at a time, alpha / beta / gamma D
-//                      and the compound output strides of the descriptor, thread = output row.
+//   warps 2-5        : epilogue (epilogue_rows) - tcgen05.ld 32 lanes x 16 / 32 columns at a time, alpha / beta /
+//                      gamma D and the compound output strides of the descriptor; thread = output row out of TMEM,
+//                      and either stored that way (C contiguous along m) or through a 32 x 33 shared-memory tile
+//                      per warp with lane = column (C contiguous along n); every block of C / D loads is issued
+//                      before its first use.
 // Edges: TMA zero-fills rows >= M / N and k >= K; the epilogue masks rows and columns.
 //
 // Round 2: contract_tf32x3_tc05_2sm_kernel - CTA pairs (2-CTA clusters), tcgen05.mma.cta_group::2 with M = 256 over the
