@@ -77,3 +77,22 @@ def test_no_device_is_an_error_not_a_fallback():
     with pytest.raises(_lib.EngineError, match="no CPU fallback"):
         pycc_b200.ccwfn.from_arrays(s.F, s.blocks, 2)
     assert np.isfinite(s.F).all()
+
+
+def test_product_never_imports_the_oracle():
+    """oracle/ is the checker (tests, smoke(), bench.py's cpu_baseline / --impl reference legs): nothing under
+    pycc_b200/ may import, load or execute it, and no module there falls back to NumPy einsum for a contraction."""
+    pkg = os.path.join(ROOT, "pycc_b200")
+    bad = []
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if not f.endswith(".py"):
+                continue
+            text = open(os.path.join(dirpath, f)).read()
+            for n, line in enumerate(text.splitlines(), 1):
+                code = line.split("#", 1)[0]
+                if re.search(r"^\s*(from|import)\s+oracle\b|import_module\(\s*[\"']oracle|[\"']oracle[./]", code):
+                    bad.append("%s:%d: %s" % (f, n, line.strip()))
+                if re.search(r"\b(np|numpy|torch)\.einsum\(", code) and f not in ("synthetic.py",):
+                    bad.append("%s:%d: %s" % (f, n, line.strip()))
+    assert not bad, "\n".join(bad)
