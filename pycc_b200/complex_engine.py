@@ -14,8 +14,8 @@ into real statements over the planes, planned by the same ``dsl.plan`` onto the 
   * a real addend goes to the real plane; '=' statements zero the output first.
 
 The Fock matrix is treated as complex as well (rtcc adds a real field, but ``residuals`` takes
-whatever it is given).  The amplitude residuals shard over several GPUs like the real engine (virtual
-slice, one allreduce per residual); HBAR + Lambda with complex amplitudes run on one GPU.
+whatever it is given).  Both residual calls shard over several GPUs like the real engines (virtual
+slice, HvT / Hs by rows, one allreduce per residual); CC2 with complex amplitudes runs on one GPU.
 """
 import re
 
@@ -264,17 +264,20 @@ class ComplexResiduals(object):
     def _lambda_setup(self):
         from .hbar_engine import HbarEngine, LambdaEngine
         P, eng = self.P, self.eng
-        o, v = eng.no, eng.nv
-        shapes = dict(Hov=(o, v), Hvv=(v, v), Hoo=(o, o), Hoooo=(o, o, o, o), HvT=(v, v, v, v), Hvovv=(v, o, v, v),
-                      Hooov=(o, o, o, v), Hovvo=(o, v, v, o), Hovov=(o, v, o, v), Hs=(v, o, v, v), Hovoo=(o, v, o, o),
+        o, v, vl = eng.no, eng.nv, eng.vl
+        # several GPUs: as in hbar_engine, HvT[A,b,e,f] and Hs[E,i,a,b] (and the transposed integral copies ovA / ovB)
+        # hold this rank's rows only, everything else is replicated; the statements keep their sliced form, every
+        # rank accumulates its part of the rl1 / rl2 planes and one allreduce per residual sums them
+        shapes = dict(Hov=(o, v), Hvv=(v, v), Hoo=(o, o), Hoooo=(o, o, o, o), HvT=(vl, v, v, v), Hvovv=(v, o, v, v),
+                      Hooov=(o, o, o, v), Hovvo=(o, v, v, o), Hovov=(o, v, o, v), Hs=(vl, o, v, v), Hovoo=(o, v, o, o),
                       Xa=(o, v, o, v), Xb=(v, o, o, v), t2x=(o, o, v, v),
                       l1=(o, v), l2=(o, o, v, v), rl1=(o, v), rl2=(o, o, v, v), Goo=(o, o), Gvv=(v, v),
                       Ya=(o, v), Yb=(o, v), Fa=(v, v), Fi=(o, o))
         for k, s in shapes.items():
             P.add_complex(k, s)
-        ovA, ovB = self.be.empty((o, v, v, v), eng.dtype), self.be.empty((o, v, v, v), eng.dtype)
-        self.be.permute4(ovA, eng.ovvv_full.permute(0, 3, 2, 1))
-        self.be.permute4(ovB, eng.ovvv_full.permute(0, 2, 3, 1))
+        ovA, ovB = self.be.empty((o, vl, v, v), eng.dtype), self.be.empty((o, vl, v, v), eng.dtype)
+        self.be.permute4(ovA, eng.ovvv_full.permute(0, 3, 2, 1).narrow(1, eng.vlo, vl))
+        self.be.permute4(ovB, eng.ovvv_full.permute(0, 2, 3, 1).narrow(1, eng.vlo, vl))
         P.add_real("ovA", ovA)
         P.add_real("ovB", ovB)
         if eng.model == 'CC2':
@@ -293,16 +296,22 @@ class ComplexResiduals(object):
         if eng.model == 'CC2':
             hs.update(HbarEngine.STATEMENTS_CC2)
             ls.update(LambdaEngine.STATEMENTS_CC2)
-        ren = lambda n_: {"r1": "rl1", "r2": "rl2"}.get(_strip(n_), _strip(n_))
-        self.hbar_prog = [P.compile(hs[name], _strip) for name in HbarEngine.ORDER]
+        if self.sharded:          # keep the X_sK suffixes: r1_s1 -> rl1_s1
+            ren = lambda n_: re.sub(r"^r([12])(_s[0-9])?$", r"rl\1\2", n_)
+            keep = lambda n_: n_
+        else:
+            ren = lambda n_: {"r1": "rl1", "r2": "rl2"}.get(_strip(n_), _strip(n_))
+            keep = _strip
+        self.hbar_prog = [P.compile(hs[name], keep) for name in HbarEngine.ORDER]
         self.lam_prog = {name: P.compile(ls[name], ren) for name in ("G", "r_L1", "r_L2")}
         self._lam = True
 
     def lambda_residuals(self, F, t1, t2, l1, l2):
         """Complex L1 / L2 residuals with HBAR rebuilt from (F, t1, t2) (pycc/cclambda.py:281-323)."""
         P, be, eng = self.P, self.be, self.eng
-        if self.sharded:
-            raise ValueError("complex-amplitude Lambda residuals run on one GPU")
+        if self.sharded and eng.ovvv_full is None:
+            raise ValueError("complex-amplitude Lambda residuals need the full <mb|ef> block on every rank "
+                             "(ccwfn(..., full_ovvv=True))")
         be.bind_stream()
         if self._lam is None:
             self._lambda_setup()
@@ -326,6 +335,9 @@ class ComplexResiduals(object):
         if eng.model != 'CCD':
             P.run(self.lam_prog["r_L1"])
         P.run(self.lam_prog["r_L2"])
+        if self.sharded:
+            eng.comm.allreduce_(P.cplx["rl1"])
+            eng.comm.allreduce_(P.cplx["rl2"])
         for z in range(2):
             be.pair_symmetrize(P.cplx["rl2"][z], eng.no, eng.nv)
         return P.fetch("rl1"), P.fetch("rl2")

@@ -301,11 +301,21 @@ def _complex_worker(rank, world, port, name, model, q):
         t1 = np.zeros_like(z["t1"]) if model == "CCD" else z["t1"]
         out = dict(rank=rank)
         with contextlib.redirect_stdout(io.StringIO()):
-            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model=model, group="world", _backend=InterpBackend())
+            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model=model, group="world", full_ovvv=True,
+                                            _backend=InterpBackend())
+            w._load(None, 0 * g["gen_t1"] if model == "CCD" else g["gen_t1"], g["gen_t2"])     # the object's own amplitudes
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+            l1 = np.zeros_like(z["l1"]) if model == "CCD" else z["l1"]
             for ftag, F in (("field", z["F_field"]), ("complex", z["F_complex"])):
                 r1, r2 = w.residuals(F, t1, z["t2"], real_time=True)
                 out["d1_" + ftag] = float(np.abs(r1.numpy() - z["%s_%s_r1" % (tag, ftag)]).max())
                 out["d2_" + ftag] = float(np.abs(r2.numpy() - z["%s_%s_r2" % (tag, ftag)]).max())
+                # the Lambda residuals of the same call (rtcc.f, pycc/rt/rtcc.py:132): HBAR rebuilt from the complex
+                # amplitudes with HvT / Hs sharded by rows, one allreduce per residual
+                q1, q2 = lam.residuals(F, t1, z["t2"], l1, z["l2"])
+                out["dl1_" + ftag] = float(np.abs(q1.numpy() - z["%s_%s_rl1" % (tag, ftag)]).max())
+                out["dl2_" + ftag] = float(np.abs(q2.numpy() - z["%s_%s_rl2" % (tag, ftag)]).max())
         q.put(out)
     except Exception:
         import traceback
@@ -317,8 +327,8 @@ def _complex_worker(rank, world, port, name, model, q):
 @pytest.mark.parametrize("model", ["CCSD", "CCD"])
 @pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
 def test_two_ranks_gloo_complex(name, model):
-    """Complex-amplitude residuals (the real-time propagator's call) on two ranks: the plane-expanded statements in
-    their sliced form, partial planes summed by one allreduce per residual."""
+    """Complex-amplitude residuals and Lambda residuals (the real-time propagator's two calls) on two ranks: the
+    plane-expanded statements in their sliced form, partial planes summed by one allreduce per residual."""
     world = 2
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
@@ -331,7 +341,7 @@ def test_two_ranks_gloo_complex(name, model):
         p.join(timeout=60)
     for d in res:
         assert "error" not in d, d.get("error")
-        for k in ("d1_field", "d2_field", "d1_complex", "d2_complex"):
+        for k in ("d1_field", "d2_field", "d1_complex", "d2_complex", "dl1_field", "dl2_field", "dl1_complex", "dl2_complex"):
             assert d[k] < 1e-12, (k, d[k])
 
 
