@@ -27,7 +27,7 @@ the CCSD engine - HvT[A,b,e,f] and Hs[E,i,a,b] hold a, e in [vlo, vhi) only - ev
 replicated; an upper-case A / B / E in a statement is the sliced index and ``X_sK`` the matching
 view of X (as in ``engine.STATEMENTS``).  Every Lambda term then produces the rows a (or columns
 b) of r1 / r2 that belong to the slice, and one allreduce per residual sums the partial results -
-the same exchange step as the CCSD iteration.  CCSD and CCD; CC2 runs on one GPU.
+the same exchange step as the CCSD iteration.  CCSD, CCD and CC2.
 """
 import re
 
@@ -264,18 +264,21 @@ class LambdaEngine(object):
     # As in the reference these terms read the OBJECT's Fock matrix and amplitudes (self.ccwfn.H.F,
     # self.ccwfn.t1 / .t2): F0.., t1_0, t2_0, tau_0 - identical to the arguments inside solve_lambda,
     # different when cclambda.residuals is called with other amplitudes (real-time propagation).
+    # Sliced like STATEMENTS (upper-case A / B = this rank's part of the virtual index); the small intermediates
+    # Ya / Yb / Fa / Fi are formed in full on every rank.
     STATEMENTS_CC2 = {
-        "r_L1": ["r1[ia] += 2.0*Hov[ia] + l1[ie]*Hvv[ea] - l1[ma]*Hoo[im] + l2[imef]*Hs[amef] - l2[mnae]*Hovoo[iemn]",
-                 "r1[ia] += 2.0*l1[me]*Hovvo[ieam] - l1[me]*Hovov[iema]",
+        "r_L1": ["r1_s1[iA] += 2.0*Hov_s1[iA] + l1[ie]*Hvv_s1[eA] - l1_s1[mA]*Hoo[im] + l2[imef]*Hs[Amef]"
+                 " - l2_s2[mnAe]*Hovoo[iemn]",
+                 "r1_s1[iA] += 2.0*l1[me]*Hovvo_s2[ieAm] - l1[me]*Hovov_s3[iemA]",
                  "Ya[nf] = l1[me]*t2_0[nmfe]",
                  "Yb[nf] = l1[me]*tau_0[mnfe]",
-                 "r1[ia] += 2.0*Ya[nf]*Loovv[inaf] - 2.0*Yb[nf]*oovv[inaf] + Yb[nf]*oovv[infa]"],
-        "r_L2": ["r2[ijab] += Loovv[ijab] + 2.0*l1[ia]*Hov[jb] - l1[ja]*Hov[ib]",
-                 "r2[ijab] += 2.0*l1[ie]*Hvovv[ejab] - l1[ie]*Hvovv[ejba]",
-                 "r2[ijab] += l1[mb]*Hooov[ijma] - 2.0*l1[mb]*Hooov[jima]",
+                 "r1_s1[iA] += 2.0*Ya[nf]*Loovv_s2[inAf] - 2.0*Yb[nf]*oovv_s2[inAf] + Yb[nf]*oovv_s3[infA]"],
+        "r_L2": ["r2_s2[ijAb] += Loovv_s2[ijAb] + 2.0*l1_s1[iA]*Hov[jb] - l1_s1[jA]*Hov[ib]",
+                 "r2_s2[ijAb] += 2.0*l1[ie]*Hvovv_s2[ejAb] - l1[ie]*Hvovv_s3[ejbA]",
+                 "r2_s3[ijaB] += l1_s1[mB]*Hooov[ijma] - 2.0*l1_s1[mB]*Hooov[jima]",
                  "Fa[ea] = F0vv[ea] - F0ov[ma]*t1_0[me]",      # (F_vv - F_ov^T t1)[e,a], index order as the reference uses it
                  "Fi[im] = F0oo[im] + t1_0[me]*F0ov[ie]",
-                 "r2[ijab] += l2[ijeb]*Fa[ea] - l2[mjab]*Fi[im]"],
+                 "r2_s2[ijAb] += l2[ijeb]*Fa_s1[eA] - l2_s2[mjAb]*Fi[im]"],
     }
 
     def __init__(self, hbar):
@@ -290,8 +293,6 @@ class LambdaEngine(object):
         st = dict(self.STATEMENTS)
         if eng.model == 'CC2':
             st.update(self.STATEMENTS_CC2)
-        if eng.model == 'CC2' and eng.comm.world > 1:
-            raise ValueError("CC2 Lambda runs on one GPU")
         T = hbar.tensors()
         for k in ("l1", "l2", "r1", "r2", "Goo", "Gvv", "Ya", "Yb", "Fa", "Fi"):
             T[k] = getattr(self, k)

@@ -163,7 +163,8 @@ def _lambda_worker(rank, world, port, name, model, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("name,model", [("o4v8", "CCSD"), ("o3v5_offdiag", "CCSD"), ("o4v8", "CCD")])
+@pytest.mark.parametrize("name,model", [("o4v8", "CCSD"), ("o3v5_offdiag", "CCSD"), ("o4v8", "CCD"), ("o4v8", "CC2"),
+                                        ("o3v5_offdiag", "CC2")])
 def test_two_ranks_gloo_lambda(name, model):
     from tests.conftest import Golden
     g = Golden(name)
