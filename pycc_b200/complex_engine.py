@@ -15,7 +15,7 @@ into real statements over the planes, planned by the same ``dsl.plan`` onto the 
 
 The Fock matrix is treated as complex as well (rtcc adds a real field, but ``residuals`` takes
 whatever it is given).  Both residual calls shard over several GPUs like the real engines (virtual
-slice, HvT / Hs by rows, one allreduce per residual); CC2 with complex amplitudes runs on one GPU.
+slice, HvT / Hs by rows, one allreduce per residual).
 """
 import re
 
@@ -187,8 +187,6 @@ class ComplexResiduals(object):
 
     def __init__(self, eng):
         self.sharded = eng.comm.world > 1
-        if self.sharded and eng.model == 'CC2':
-            raise ValueError("complex-amplitude CC2 residuals run on one GPU")
         if eng.model not in ('CCD', 'CC2', 'CCSD'):
             raise ValueError("complex-amplitude residuals: models CCD, CC2, CCSD (got %r)" % (eng.model,))
         self.eng, self.be = eng, eng.be
@@ -218,7 +216,7 @@ class ComplexResiduals(object):
                       Wmnij=(o, o, o, o), Wr1=(o, vl, o, v), Wr2=(o, vl, o, v), Zr=(o, o, o, vl),
                       Y1=(o, o, o, vl), Y2=(o, o, vl, o), r1=(o, v), r2=(o, o, v, v))
         if eng.model == 'CC2':
-            shapes.update(T11=(o, o, v, v), Yw=(o, o, o, v), Xv=(v, v, o, v))
+            shapes.update(T11=(o, o, v, v), Yw=(o, o, o, vl), Xv=(vl, v, o, v))
         for k, s in shapes.items():
             P.add_complex(k, s)
         st = eng._statements(plain=False)

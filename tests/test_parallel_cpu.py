@@ -325,7 +325,7 @@ def _complex_worker(rank, world, port, name, model, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("model", ["CCSD", "CCD"])
+@pytest.mark.parametrize("model", ["CCSD", "CCD", "CC2"])
 @pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
 def test_two_ranks_gloo_complex(name, model):
     """Complex-amplitude residuals and Lambda residuals (the real-time propagator's two calls) on two ranks: the
