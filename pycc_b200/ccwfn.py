@@ -351,7 +351,7 @@ class ccwfn(object):
         inputs give complex results."""
         if _is_complex(F) or _is_complex(t1) or _is_complex(t2):
             # complex amplitudes (real-time propagation, pycc/rt/rtcc.py:125): two real planes
-            return self._complex().residuals(F, t1, t2)
+            return self._complex().residuals(F, t1, t2, real_time=bool(real_time))
         eng = self.engine
         # CC3 with real_time=True: the reference adds the t3_pert_ijk term built from V = F - H.F
         # (pycc/ccwfn.py:378-386); complex CC3 amplitudes are outside the engine (_complex() raises)

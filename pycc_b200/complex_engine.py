@@ -187,8 +187,11 @@ class ComplexResiduals(object):
 
     def __init__(self, eng):
         self.sharded = eng.comm.world > 1
-        if eng.model not in ('CCD', 'CC2', 'CCSD'):
-            raise ValueError("complex-amplitude residuals: models CCD, CC2, CCSD (got %r)" % (eng.model,))
+        if eng.model not in ('CCD', 'CC2', 'CCSD', 'CC3'):
+            raise ValueError("complex-amplitude residuals: models CCD, CC2, CCSD, CC3 (got %r)" % (eng.model,))
+        if self.sharded and eng.model == 'CC3':
+            raise ValueError("complex-amplitude CC3 residuals run on one GPU")
+        self.cc3 = None
         self.eng, self.be = eng, eng.be
         o, v = eng.no, eng.nv
         n = o + v
@@ -241,7 +244,7 @@ class ComplexResiduals(object):
             P.load("t1", t1)
         P.load("t2", t2)
 
-    def residuals(self, F, t1, t2):
+    def residuals(self, F, t1, t2, real_time=False):
         """Complex r1, r2 (pycc/ccwfn.py:331-406 evaluated with complex amplitudes)."""
         P, be, eng = self.P, self.be, self.eng
         be.bind_stream()
@@ -251,6 +254,11 @@ class ComplexResiduals(object):
         P.cplx["r2"].zero_()
         for name in eng.builder_order():
             P.run(self.progs[name])
+        if eng.model == 'CC3':       # triples contributions X1, X2 (:371-401) before r2 + r2^T
+            if self.cc3 is None:
+                from .complex_cc3 import ComplexCC3
+                self.cc3 = ComplexCC3(self)
+            self.cc3.contribute(real_time)
         if self.sharded:
             eng.comm.allreduce_(P.cplx["r1"])
             eng.comm.allreduce_(P.cplx["r2"])
@@ -307,6 +315,8 @@ class ComplexResiduals(object):
     def lambda_residuals(self, F, t1, t2, l1, l2):
         """Complex L1 / L2 residuals with HBAR rebuilt from (F, t1, t2) (pycc/cclambda.py:281-323)."""
         P, be, eng = self.P, self.be, self.eng
+        if eng.model == 'CC3':
+            raise ValueError("complex-amplitude Lambda residuals: models CCD, CC2, CCSD (the CC3 Lambda equations take real amplitudes)")
         if self.sharded and eng.ovvv_full is None:
             raise ValueError("complex-amplitude Lambda residuals need the full <mb|ef> block on every rank "
                              "(ccwfn(..., full_ovvv=True))")

@@ -78,19 +78,23 @@ class TripletBatch(object):
         self.be = backend
         step = 1 if no > 1 else 0
         mk = lambda i, j, k: {n: TRef.of(t, n) for n, t in tensors_fn(i, j, k).items()}
-        base = [plan(s, mk(0, 0, 0), dcode, prefer_flat=prefer_flat) for s in statements]
+        # a statement may plan into several launches (more than four product terms: the plane-expanded complex
+        # statements of complex_cc3.py); the launch list has the same structure at every (i, j, k)
+        base = [L for s in statements for L in plan(s, mk(0, 0, 0), dcode, prefer_flat=prefer_flat)]
         for L in base:
-            if len(L) != 1 or L[0].desc.batch != 1:
+            if L.desc.batch != 1:
                 raise RuntimeError("unexpected triplet-batch plan structure")
-        shifted = [[plan(s, mk(*unit), dcode, prefer_flat=prefer_flat)[0].desc for s in statements]
+        shifted = [[L.desc for s in statements for L in plan(s, mk(*unit), dcode, prefer_flat=prefer_flat)]
                    for unit in ((step, 0, 0), (0, step, 0), (0, 0, step))]
+        if any(len(x) != len(base) or any(a.nseg != b.desc.nseg for a, b in zip(x, base)) for x in shifted):
+            raise RuntimeError("triplet-batch plans differ between triplets")
         self.templates = []
         for n, L in enumerate(base):
-            d0 = L[0].desc
+            d0 = L.desc
             fields = _ptr_fields(d0)
             deriv = {f[0]: tuple((_get(shifted[ax][n], f) - _get(d0, f)) if step else 0 for ax in range(3))
                      for f in fields}
-            self.templates.append((L[0], fields, deriv))
+            self.templates.append((L, fields, deriv))
         self._keep = base
         self._cache = {}
         self.itemsize = tensors_fn(0, 0, 0)[next(iter(tensors_fn(0, 0, 0)))].element_size()

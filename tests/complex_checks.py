@@ -47,3 +47,41 @@ def check_complex_residuals(make_wfn, name, model, tol=1e-12):
                          g["gen_t2"].astype(complex))
     assert np.abs(host(c2).imag).max() == 0.0
     assert np.abs(host(c2).real - host(r2)).max() < tol and np.abs(host(c1).real - host(r1)).max() < tol
+
+
+CC3_CASES = ["o3v5_offdiag", "o4v8"]
+
+
+def check_complex_cc3_residuals(make_wfn, name, tol=1e-12):
+    """Model CC3 with complex amplitudes (the real-time propagator's call) against the reference's own vectors
+    (tests/golden/make_golden_rtcc3_complex.py): a real field-dressed and a complex Fock matrix with a real
+    diagonal, with and without the t3_pert_ijk term of real_time=True."""
+    g = Golden(name)
+    z = np.load(os.path.join(GOLDEN_DIR, "rtcc3_complex", name + ".npz"))
+    with contextlib.redirect_stdout(io.StringIO()):
+        w = make_wfn(g, "CC3")
+    for tag in ("field", "mixed"):
+        for rt, suf in ((True, ""), (False, "_plain")):
+            r1, r2 = w.residuals(z["F_" + tag], z["t1"], z["t2"], real_time=rt)
+            assert r1.is_complex() and r2.is_complex()
+            assert np.abs(host(r1) - z[tag + "_r1" + suf]).max() < tol, (tag, rt)
+            assert np.abs(host(r2) - z[tag + "_r2" + suf]).max() < tol, (tag, rt)
+    # the perturbation term is there: the two calls differ
+    assert np.abs(z["field_r2"] - z["field_r2_plain"]).max() > 1e-7
+    # a complex diagonal of F has no real triples denominator: refused, not approximated
+    Fc = z["F_mixed"].copy()
+    Fc[0, 0] += 0.25j
+    try:
+        w.residuals(Fc, z["t1"], z["t2"])
+    except ValueError as err:
+        assert "diagonal of F must be real" in str(err)
+    else:
+        raise AssertionError("a complex Fock diagonal was accepted")
+    # the object's own state is untouched, and real inputs still take the real CC3 path
+    assert np.abs(host(w.H.F) - g.F).max() == 0.0
+    q1, q2 = w.residuals(g.F, g["gen_t1"], g["gen_t2"])
+    assert not q2.is_complex()
+    # complex inputs with zero imaginary parts reproduce the real path
+    c1, c2 = w.residuals(g.F.astype(complex), g["gen_t1"].astype(complex), g["gen_t2"].astype(complex))
+    assert np.abs(host(c2).imag).max() == 0.0 and np.abs(host(c2).real - host(q2)).max() < tol
+    assert np.abs(host(c1).real - host(q1)).max() < tol
