@@ -13,7 +13,7 @@ kernels as the real path (cc3_engine.py), with every complex tensor held as two 
     ``pccb_t3_combine`` - linear in W - is applied to each plane;
   * the four consumer contractions per pair add X1 / X2 (:395-398) into the planes of r1 / r2.
 
-One GPU (the occupied pairs are not dealt over ranks here).
+Several GPUs: the occupied pairs are dealt over the ranks as in cc3_engine.py.
 """
 import torch
 
@@ -65,8 +65,6 @@ class ComplexCC3(object):
         """``cr``: the ComplexResiduals of a CC3 engine (its plane set holds t1, t2, Fme, r1, r2, F)."""
         self.cr, self.eng, self.be, self.P = cr, cr.eng, cr.be, cr.P
         eng, P = self.eng, self.P
-        if cr.sharded:
-            raise ValueError("complex-amplitude CC3 residuals run on one GPU")
         if eng.ovvv_full is None:
             raise ValueError("model='CC3' needs the full <mb|ef> block")
         o, v = eng.no, eng.nv
@@ -76,7 +74,17 @@ class ComplexCC3(object):
         for k, s in shapes.items():
             P.add_complex(k, s)
         c = P.cplx
-        self.inter = P.compile(["T11[ijab] = t1[ia]*t1[jb]"] + list(CC3Engine.STATEMENTS))
+        stm = ["T11[ijab] = t1[ia]*t1[jb]"] + list(CC3Engine.STATEMENTS)
+        self.sharded = cr.sharded
+        if self.sharded:
+            # several GPUs, as in cc3_engine: a rank holds the rows a in [vlo, vhi) of <ab|ef>, so it forms those rows of
+            # the one v^4 term of Wabei in a zero-initialised buffer and one allreduce of the disjoint slices gathers
+            # them; the occupied pairs are dealt over the ranks and the partial X1 / X2 ride on the allreduce of the
+            # r1 / r2 planes in ComplexResiduals.residuals
+            stm = [x for x in stm if "vvvv[" not in x]
+            P.add_complex("WvG", (o, v, v, v))
+            self.gather = P.compile(["WvG_s1[iAbe] += t1[if]*vvvv_s0[Abef]"])
+        self.inter = P.compile(stm)
         self.pert_tmp = P.compile(["Tp[ijal] = t2[ijad]*Vov[ld]"])
         every = lambda name: True
         t2, V, O, W = c["t2"], c["Wv"], c["Wo"], c["W3"]
@@ -135,18 +143,23 @@ class ComplexCC3(object):
         self._bare("R", b["oovv"].permute(1, 0, 3, 2))
         self._bare("Wv", eng.ovvv_full.permute(0, 3, 2, 1))
         P.run(self.inter)
+        if self.sharded:
+            c["WvG"].zero_()             # the other ranks' rows hold the previous call's gathered values
+            P.run(self.gather)
+            eng.comm.allreduce_(c["WvG"])
+            c["Wv"].add_(c["WvG"])
         if real_time:
             c["Vov"].copy_(c["F"][:, :o, o:])
             c["Vov"][0].sub_(eng.F0[:o, o:])
             P.run(self.pert_tmp)
         W, A1, A2 = c["W3"], c["A1"], c["A2"]
-        for i in range(o):
-            for j in range(o):
-                W.zero_()
-                self.w_batch.launch_pair(i, j, o)
-                if real_time:
-                    self.pert_batch.launch_pair(i, j, o)
-                for z in range(2):
-                    be.t3_combine(W[z], o, 0, i, j, eps, o, v, A1[z], A2[z])
-                for L in self._consumers(i, j):
-                    be.contract(L.desc)
+        pairs = [(i, j) for i in range(o) for j in range(o)][eng.comm.rank::eng.comm.world]
+        for (i, j) in pairs:
+            W.zero_()
+            self.w_batch.launch_pair(i, j, o)
+            if real_time:
+                self.pert_batch.launch_pair(i, j, o)
+            for z in range(2):
+                be.t3_combine(W[z], o, 0, i, j, eps, o, v, A1[z], A2[z])
+            for L in self._consumers(i, j):
+                be.contract(L.desc)

@@ -189,8 +189,6 @@ class ComplexResiduals(object):
         self.sharded = eng.comm.world > 1
         if eng.model not in ('CCD', 'CC2', 'CCSD', 'CC3'):
             raise ValueError("complex-amplitude residuals: models CCD, CC2, CCSD, CC3 (got %r)" % (eng.model,))
-        if self.sharded and eng.model == 'CC3':
-            raise ValueError("complex-amplitude CC3 residuals run on one GPU")
         self.cc3 = None
         self.eng, self.be = eng, eng.be
         o, v = eng.no, eng.nv

@@ -346,6 +346,59 @@ def test_two_ranks_gloo_complex(name, model):
             assert d[k] < 1e-12, (k, d[k])
 
 
+def _complex_cc3_worker(rank, world, port, name, q):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    import torch.distributed as dist
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        from tests.conftest import Golden, GOLDEN_DIR
+        from tests.interp_backend import InterpBackend
+        import pycc_b200
+        from pycc_b200.parallel import virtual_slice
+        g = Golden(name)
+        z = np.load(os.path.join(GOLDEN_DIR, "rtcc3_complex", name + ".npz"))
+        lo, hi = virtual_slice(g.nv, rank, world)
+        blocks = dict(g.blocks)
+        blocks["vvvv"] = np.ascontiguousarray(blocks["vvvv"][lo:hi])
+        out = dict(rank=rank)
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = pycc_b200.ccwfn.from_arrays(g.F, blocks, g.no, model="CC3", group="world", _backend=InterpBackend())
+            for call in range(2):            # twice: the gathered rows of the first call must not leak into the second
+                for tag in ("field", "mixed"):
+                    r1, r2 = w.residuals(z["F_" + tag], z["t1"], z["t2"], real_time=True)
+                    out["d1_%s_%d" % (tag, call)] = float(np.abs(r1.numpy() - z[tag + "_r1"]).max())
+                    out["d2_%s_%d" % (tag, call)] = float(np.abs(r2.numpy() - z[tag + "_r2"]).max())
+        q.put(out)
+    except Exception:
+        import traceback
+        q.put(dict(rank=rank, error=traceback.format_exc()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("name", ["o3v5_offdiag", "o4v8"])
+def test_two_ranks_gloo_complex_cc3(name):
+    """CC3 residuals with complex amplitudes on two ranks: occupied pairs dealt over the ranks, the v^4 term of the
+    dressed <ab|ei> from each rank's rows of <ab|ef> (one allreduce), partial planes summed with the builders'."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_complex_cc3_worker, args=(r, world, port, name, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=600) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    for d in res:
+        assert "error" not in d, d.get("error")
+        for k, val in d.items():
+            if k.startswith("d"):
+                assert val < 1e-12, (k, val)
+
+
 def _t3density_worker(rank, world, port, name, q):
     sys.path.insert(0, ROOT)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
