@@ -6,7 +6,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .dsl import TRef, plan
+from .dsl import PlanError, TRef, plan
 
 
 class helper_diis(object):
@@ -209,6 +209,28 @@ class cc_contract(object):
             self.device1 = self.be.device
         return self.be
 
+    def _complex_call(self, spec, ins, out_idx, ops):
+        """Complex operands (the real-time code of the reference contracts complex amplitudes through the same
+        operator, pycc/rt/rtcc.py): the real and imaginary planes go through the real kernels,
+        (Ar + i Ai)(Br + i Bi) = (Ar Br - Ai Bi) + i (Ar Bi + Ai Br); a real operand has no imaginary plane."""
+        if len(ops) == 1:
+            perm = [ins[0].index(c) for c in out_idx]
+            if len(perm) != len(ins[0]):
+                raise ValueError("cc_contract: single-operand reductions are not supported: %r" % spec)
+            return ops[0].permute(perm).contiguous()
+        parts = [(x.real.contiguous(), x.imag.contiguous()) if x.is_complex() else (x, None) for x in ops]
+        (ar, ai), (br, bi) = parts
+        re = self(spec, ar, br)
+        if ai is not None and bi is not None:
+            re = re - self(spec, ai, bi)
+        im = None
+        if bi is not None:
+            im = self(spec, ar, bi)
+        if ai is not None:
+            x = self(spec, ai, br)
+            im = x if im is None else im + x
+        return torch.complex(re, im)
+
     def __call__(self, subscripts, *operands):
         be = self._backend()
         spec = subscripts.replace(" ", "")
@@ -225,11 +247,14 @@ class cc_contract(object):
             if x.device != be.device:
                 x = x.to(be.device)
             ops.append(x)
-        dtype = ops[0].dtype
-        if dtype not in (torch.float64, torch.float32):
-            raise ValueError("cc_contract: float64 / float32 operands only (got %s)" % dtype)
-        ops = [x if x.dtype == dtype else x.to(dtype) for x in ops]
-        dcode = _lib.F64 if dtype == torch.float64 else _lib.F32
+        if any(x.is_complex() for x in ops) and len(ops) <= 2:
+            return self._complex_call(spec, ins, out_idx, ops)
+        dtype = next((x.dtype for x in ops if x.is_complex()), ops[0].dtype)
+        if dtype not in (torch.float64, torch.float32, torch.complex128, torch.complex64):
+            raise ValueError("cc_contract: float64 / float32 (or complex128 / complex64) operands only (got %s)" % dtype)
+        if not dtype.is_complex:
+            ops = [x if x.dtype == dtype else x.to(dtype) for x in ops]
+        dcode = _lib.F64 if dtype in (torch.float64, torch.complex128) else _lib.F32
         if len(ops) == 1:
             perm = [ins[0].index(c) for c in out_idx]
             if len(perm) != len(ins[0]):
@@ -268,6 +293,22 @@ class cc_contract(object):
         else:
             T = {"C": out, "A": ops[0], "B": ops[1]}
         be.bind_stream()
-        for L in plan("C[%s] = A[%s]*B[%s]" % (out_idx, ins[0], ins[1]), T, dcode):
+        try:
+            launches = plan("C[%s] = A[%s]*B[%s]" % (out_idx, ins[0], ins[1]), T, dcode)
+        except PlanError:
+            # an index group that does not fit the descriptor's two stride levels (e.g. 'iajb,ijab->'): contract
+            # contiguous copies in the canonical orders [batch, M, K] x [batch, N, K] -> [batch, M, N] instead
+            Bt = [c for c in ins[0] if c in ins[1] and c in out_idx]
+            K = [c for c in ins[0] if c in ins[1] and c not in out_idx]
+            M = [c for c in ins[0] if c not in ins[1]]
+            N = [c for c in ins[1] if c not in ins[0]]
+            a_idx, b_idx, c_idx = "".join(Bt + M + K), "".join(Bt + N + K), "".join(Bt + M + N)
+            a = ops[0].permute([ins[0].index(c) for c in a_idx]).contiguous()
+            b = ops[1].permute([ins[1].index(c) for c in b_idx]).contiguous()
+            if (a_idx, b_idx, c_idx) == (ins[0], ins[1], out_idx):
+                raise
+            res = self("%s,%s->%s" % (a_idx, b_idx, c_idx), a, b)
+            return res if c_idx == out_idx else res.permute([c_idx.index(c) for c in out_idx]).contiguous()
+        for L in launches:
             be.contract(L.desc)
         return out.reshape(()) if out_idx == "" else out

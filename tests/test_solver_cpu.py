@@ -118,6 +118,30 @@ def test_contract_operator_and_triples_builders(golden):
     assert abs(pycc_b200.t_vikings(w) - float(g["sym_et_tjl"])) < 1e-12
 
 
+def test_contract_operator_complex_and_awkward_layouts():
+    """cc_contract beyond the strings of the CCSD path: complex operands (the reference's real-time code contracts
+    complex amplitudes through the same operator), three operands, and index groups that do not fit the descriptor's
+    two stride levels (retried on contiguous copies in canonical order) - numpy.einsum semantics (pycc/utils.py:162-187)."""
+    from pycc_b200.utils import cc_contract
+    c = cc_contract(backend=InterpBackend())
+    rng = np.random.default_rng(3)
+    rz = lambda *s: rng.standard_normal(s)
+    cz = lambda *s: rz(*s) + 1j * rz(*s)
+    A, B, R = cz(3, 4, 5, 6), cz(7, 2, 5, 6), rz(7, 2, 5, 6)
+    cases = (("ijef,abef->ijab", (A, B)), ("ijef,abef->abij", (A, R)), ("abef,ijef->ijab", (R, A)), ("ijef,ijef->", (A, A)),
+             ("ijef->jife", (A,)), ("ia,jb,ijab->", (cz(3, 5), cz(4, 6), cz(3, 4, 5, 6))), ("ia,jb->ijab", (cz(3, 5), rz(4, 6))),
+             ("ia,jb,ijab->", (rz(3, 5), rz(4, 6), rz(3, 4, 5, 6))), ("iajb,ijab->", (rz(3, 5, 4, 6), rz(3, 4, 5, 6))),
+             ("iajb,jbia->ab", (rz(3, 5, 4, 6), rz(4, 6, 3, 5))), ("abc,dbc->ad", (cz(5, 5, 5), rz(6, 5, 5))))
+    for spec, ops in cases:
+        got = c(spec, *ops)
+        ref = np.einsum(spec, *ops)
+        assert got.is_complex() == np.iscomplexobj(ref), spec
+        assert np.abs(got.numpy() - ref).max() < 1e-12, spec
+    got = c("ijef,abef->ijab", A.astype(np.complex64), B.astype(np.complex64))
+    assert got.dtype == torch.complex64
+    assert np.abs(got.numpy() - np.einsum("ijef,abef->ijab", A, B)).max() < 1e-4
+
+
 def test_sp_mode_host_logic(golden):
     """precision='SP' through the interpreter back end: FP32 storage, FP64 energy/norm/DIIS."""
     g = golden
