@@ -164,7 +164,11 @@ class CCSDEngine(object):
             for name in varying:
                 x = getattr(self, name)
                 self._lo[name] = be.empty(tuple(x.shape), dtype)
-                be.register_lo_plane(x, self._lo[name])
+                # t1 / t2 are also written OUTSIDE prepare() (update, DIIS, set_amplitudes), after which their planes
+                # are stale until the next prepare(): they are registered only while r_T2 runs (_run), so that no
+                # other engine's launch over t1 / t2 (HBAR, (T), CC3, Lambda) can pick up a stale plane
+                if name not in ("t1", "t2"):
+                    be.register_lo_plane(x, self._lo[name])
         if self._lo is not None:
             # the registry maps raw address ranges to lo planes: drop this engine's ranges when it dies, so
             # that memory the caching allocator recycles can never match a stale entry
@@ -394,8 +398,17 @@ class CCSDEngine(object):
             if getattr(self, "sp_tc", False):
                 self.be.permute4(self.WmnijT, self.Wmnij.permute(2, 3, 0, 1))
                 self.be.split_lo(self.WmnijT, self._lo["WmnijT"])
-        with nvtx_range("ccsd/" + name):
-            self._launch(name)
+        amp_planes = name == "r_T2" and getattr(self, "sp_tc", False)
+        if amp_planes:                # fresh since this call's prepare()
+            self.be.register_lo_plane(self.t1, self._lo["t1"])
+            self.be.register_lo_plane(self.t2, self._lo["t2"])
+        try:
+            with nvtx_range("ccsd/" + name):
+                self._launch(name)
+        finally:
+            if amp_planes:
+                self.be.unregister_lo_plane(self.t1.data_ptr())
+                self.be.unregister_lo_plane(self.t2.data_ptr())
         # the one exchange step of the iteration: sum the per-rank partial residuals
         if getattr(self, "_defer_reduce", False):
             return                   # CC3 on several GPUs: after the triples terms (residuals())

@@ -192,7 +192,11 @@ class InterpBackend(object):
         lo.copy_(x - hi)
 
     def register_lo_plane(self, x, lo):
-        pass          # the interpreter contracts the full FP32 values
+        # the interpreter contracts the full FP32 values; the registry is kept so that tests can check the protocol
+        self.__dict__.setdefault("lo_registry", {})[x.data_ptr()] = lo
+
+    def unregister_lo_plane(self, x_ptr):
+        self.__dict__.setdefault("lo_registry", {}).pop(x_ptr, None)
 
     def t3_density_combine(self, W, Dd, nk, k0, i, j, eps, no, nv, outs):
         e = eps.double()

@@ -169,6 +169,17 @@ def test_sp_mode_plain_matrix_ring_terms(golden, model):
     # the K-contiguous copies of the o^4 v^2 term and the residual plane of Fae2 refreshed right after its launch
     assert w.engine.sp_tc and any("WmnijT[ijmn]*tauT[Abmn]" in L.text for L in w.engine.plans["r_T2"])
     assert [L.post for L in w.engine.plans["r_T2"] if L.post] == ["Fae2"]
+    # t1 / t2 change outside prepare() (update, DIIS): their residual planes are registered only while r_T2 runs
+    eng, reg = w.engine, w.engine.be.lo_registry
+    assert eng.t1.data_ptr() not in reg and eng.t2.data_ptr() not in reg and eng.tau.data_ptr() in reg
+    seen = []
+    launch = eng._launch
+    eng._launch = lambda name: (seen.append((name, eng.t1.data_ptr() in reg, eng.t2.data_ptr() in reg)), launch(name))[1]
+    with contextlib.redirect_stdout(io.StringIO()):
+        w.residuals(g.F, t1, g["gen_t2"])
+    eng._launch = launch
+    assert ("r_T2", True, True) in seen and all(a == b == (n == "r_T2") for n, a, b in seen)
+    assert eng.t1.data_ptr() not in reg and eng.t2.data_ptr() not in reg
     assert np.abs(r2.double().numpy() - d2.numpy()).max() < 2e-6 * max(1.0, np.abs(d2.numpy()).max())
     assert np.abs(r1.double().numpy() - d1.numpy()).max() < 2e-6
 
