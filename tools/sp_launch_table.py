@@ -19,6 +19,9 @@ d = w.make_diis(8)
 for n in (1, 2):
     w._iteration(d, n, 1)
 eng = w.engine
+if getattr(eng, "sp_tc", False):       # the engine registers these two planes only while r_T2 runs; here launches run alone
+    eng.be.register_lo_plane(eng.t1, eng._lo["t1"])
+    eng.be.register_lo_plane(eng.t2, eng._lo["t2"])
 VARIANTS = [("mma.sync", {"PCCB_TC05_MIN_K": "2000000000"}), ("tc05 row-epi", {"PCCB_TC05_EPI": "0"}), ("tc05", {})]
 rows = []
 plans = dict(eng.plans)
