@@ -82,7 +82,8 @@ class cclambda(object):
         from .ccwfn import _is_complex
         if any(_is_complex(x) for x in (F, t1, t2, l1, l2)):
             # rtcc.f (pycc/rt/rtcc.py:132): complex amplitudes, HBAR rebuilt from them
-            return self.ccwfn._complex().lambda_residuals(F, t1, t2, l1, l2)
+            return self.ccwfn._complex().lambda_residuals(F, t1, t2, l1, l2,
+                                                          real_time=bool(getattr(self.ccwfn, "real_time", False)))
         w, eng, le = self.ccwfn, self.ccwfn.engine, self.engine
         cc3 = getattr(le, "cc3", None)
         if cc3 is not None:

@@ -126,8 +126,9 @@ class ComplexCC3(object):
         self.be.permute4(p[0], view)
         p[1].zero_()
 
-    def contribute(self, real_time=False):
-        """r1 += X1, r2 (unsymmetrised) += X2 in the planes of the ComplexResiduals; Fme must be current."""
+    def build_intermediates(self, real_time=False):
+        """T1-dressed integrals (and the field term's Tp) for the amplitudes in the planes; returns the real
+        orbital energies of the triples denominators."""
         eng, be, P = self.eng, self.be, self.P
         c = P.cplx
         o, v = eng.no, eng.nv
@@ -152,14 +153,205 @@ class ComplexCC3(object):
             c["Vov"].copy_(c["F"][:, :o, o:])
             c["Vov"][0].sub_(eng.F0[:o, o:])
             P.run(self.pert_tmp)
+        return eps
+
+    def launch_w(self, i, j, real_time=False):
+        """W planes of the triplets (i, j, k), k = 0 .. o-1 (no denominator)."""
+        self.P.cplx["W3"].zero_()
+        self.w_batch.launch_pair(i, j, self.eng.no)
+        if real_time:
+            self.pert_batch.launch_pair(i, j, self.eng.no)
+
+    def contribute(self, real_time=False):
+        """r1 += X1, r2 (unsymmetrised) += X2 in the planes of the ComplexResiduals; Fme must be current."""
+        eng, be, c = self.eng, self.be, self.P.cplx
+        o, v = eng.no, eng.nv
+        eps = self.build_intermediates(real_time)
         W, A1, A2 = c["W3"], c["A1"], c["A2"]
         pairs = [(i, j) for i in range(o) for j in range(o)][eng.comm.rank::eng.comm.world]
         for (i, j) in pairs:
-            W.zero_()
-            self.w_batch.launch_pair(i, j, o)
-            if real_time:
-                self.pert_batch.launch_pair(i, j, o)
+            self.launch_w(i, j, real_time)
             for z in range(2):
                 be.t3_combine(W[z], o, 0, i, j, eps, o, v, A1[z], A2[z])
             for L in self._consumers(i, j):
                 be.contract(L.desc)
+
+
+# ---- CC3 terms of the Lambda residuals with complex amplitudes ------------------------------------------------------
+def compile_planes(statements, tensors, real, dcode):
+    """Statements over named tensors -> [('zero', tensor) | ('launch', Launch)]: complex tensors are (2, ...) plane
+    pairs, the names in ``real`` are real tensors; the plane expansion of complex_engine.expand, planned at once."""
+    prog = []
+    for s in statements:
+        for kind, arg in expand(s, lambda n: n not in real):
+            if kind == "zero":
+                prog.append(("zero", tensors[arg]))
+            else:
+                prog += [("launch", L) for L in plan(arg, _plane_refs(arg, tensors, real), dcode)]
+    return prog
+
+
+def run_planes(prog, be):
+    for kind, x in prog:
+        if kind == "zero":
+            x.zero_()
+        else:
+            be.contract(x.desc)
+
+
+class ComplexCC3Lambda(object):
+    """Y1 / Y2 of the CC3 triples in ``cclambda.residuals`` (pycc/cclambda.py:323-440: the t3 and l3 loops of the
+    Lambda equations rebuilt for the call's own amplitudes) with complex t and l: the statements of
+    cc3_lambda_engine.py plane by plane; ``pccb_t3_density_combine`` (linear, real denominators) per plane.
+    One GPU."""
+
+    def __init__(self, cr):
+        from . import cc3_lambda_engine as rl
+        self.rl = rl
+        self.cr, self.eng, self.be, self.P = cr, cr.eng, cr.be, cr.P
+        eng, P = self.eng, self.P
+        if cr.sharded:
+            raise ValueError("complex-amplitude CC3 Lambda residuals run on one GPU")
+        if cr.cc3 is None:
+            cr.cc3 = ComplexCC3(cr)
+        self.cc3 = cr.cc3
+        o, v = eng.no, eng.nv
+        E = lambda *s: self.be.zeros((2,) + s, eng.dtype)
+        self.WK, self.LwK, self.Lo = E(o, v, v, v), E(o, v, v, v), E(o, o, o, v)
+        self.L3, self.X, self.P1, self.P2 = E(o, v, v, v), E(o, v, v, v), E(o, v, v, v), E(o, v, v, v)
+        self.l2T = E(o, o, v, v)
+        self.Zb, self.Zmd = E(o, v, v, v), E(o, v, v, v)
+        self.Zma, self.Zd1, self.Zmn = E(o, o, o, v), E(o, o, o, v), E(o, o, v, o)
+        self.Znf = E(o, v)
+        self.Xje, self.Xej = E(o, v, o, v), E(o, v, v, o)
+        self.Q2, self.Q3 = E(o, o, o, v), E(o, o, o, v)
+        self.WA, self.WB, self.WC, self.WD = E(o, o, v, v), E(o, o, v, v), E(o, o, v, v), E(o, o, v, v)
+        self.Wab = E(v, v, v, v)
+        self.Y1w, self.Y2 = E(o, v), E(o, o, v, v)
+        c, b = P.cplx, eng.blk
+        T = dict(ovvv=eng.ovvv_full, ooov=b["ooov"], oovv=b["oovv"], t1=c["t1"], T11=c["T11"], Xje=self.Xje, Xej=self.Xej,
+                 Q2=self.Q2, Q3=self.Q3, Wab=self.Wab, t1A=c["t1"], ovvvA=eng.ovvv_full, T11A=c["T11"])
+        self.dressed = compile_planes(rl._DRESSED, T, ("ovvv", "ooov", "oovv", "ovvvA"), eng.dcode)
+        T = dict(r1=c["rl1"], l2=c["l2"], Zmd=self.Zmd, Loovv=eng.Loovv, Znf=self.Znf, Zmn=self.Zmn, Zb=self.Zb,
+                 Wab=self.Wab, Y1w=self.Y1w, ZbD=self.Zb, Woooo=c["Wmnij3"], Zma=self.Zma, Zd1=self.Zd1,
+                 WA=self.WA, WB=self.WB, WC=self.WC, WD=self.WD)
+        self.y1 = compile_planes(rl._Y1, T, ("Loovv",), eng.dcode)
+        # l3 of one triplet: the spin-adapted integrals L[x,y] are the only real operands
+        import re
+        is_real = lambda n: re.match(r"^L[ijk][ijk]$", n) is not None
+        texts = []
+        for s in rl._L3:
+            for kind, arg in expand(s.replace(" = ", " += ", 1), lambda n: not is_real(n)):
+                texts.append(arg)
+        self.l3 = TripletBatch(o, eng.dcode, texts, self._l3_tensors, self.be)
+        self._pair, self._setup_plans = {}, {}
+
+    def _l3_tensors(self, i, j, k):
+        e, c = self.eng, self.P.cplx
+        l1, l2, L, f, Wo3 = c["l1"], c["l2"], e.Loovv, c["Fme"], c["Wmnie3"]
+        d = dict(W=self.L3[:, k])
+        ix = dict(i=i, j=j, k=k)
+        for x in "ijk":
+            d["LwK" + x], d["WK" + x] = self.LwK[:, ix[x]], self.WK[:, ix[x]]
+            d["l2" + x], d["l1" + x], d["f" + x] = l2[:, ix[x]], l1[:, ix[x]], f[:, ix[x]]
+            d["l2T" + x] = self.l2T[:, ix[x]]
+            for y in "ijk":
+                if x != y:
+                    d["l2" + x + y] = l2[:, ix[x], ix[y]]
+                    d["l2T" + x + y] = self.l2T[:, ix[x], ix[y]]
+                    d["Lo" + x + y] = self.Lo[:, ix[x], ix[y]]
+                    d["Wo" + x + y] = Wo3[:, ix[x], ix[y]]
+        out = {}
+        for n, t in d.items():            # both planes under the plain name, one plane under __r / __i
+            out[n], out[n + "__r"], out[n + "__i"] = t, t[0], t[1]
+        for x in "ijk":
+            for y in "ijk":
+                if x != y:
+                    out["L" + x + y] = L[ix[x], ix[y]]
+        return out
+
+    def _planes(self, fn, *args):
+        for z in range(2):
+            fn(z, *args)
+
+    def setup(self, real_time):
+        """Everything that depends on the T amplitudes only (cclambda.py:118-139), for the planes' (F, t1, t2);
+        the Fme planes must be current."""
+        e, be, cc3, c = self.eng, self.be, self.cc3, self.P.cplx
+        o, v = e.no, e.nv
+        b = e.blk
+        eps = self.eps = cc3.build_intermediates(real_time)
+        for z in range(2):
+            be.permute4(self.WK[z], c["Wk"][z].permute(0, 2, 3, 1))
+            be.permute4(self.LwK[z], self.WK[z].permute(0, 2, 1, 3))
+            be.axpby(self.LwK[z], 2.0, self.WK[z], -1.0, self.LwK[z])
+            be.permute4(self.Lo[z], c["Wmnie3"][z].permute(1, 0, 2, 3))
+            be.axpby(self.Lo[z], 2.0, c["Wmnie3"][z], -1.0, self.Lo[z])
+        self.Wab[0].copy_(e.vvvv_loc)
+        self.Wab[1].zero_()
+        run_planes(self.dressed, be)
+        self.Xje[0].add_(b["ovov"])                                               # <mb|je>
+        self.Xej[0].add_(b["oovv"].permute(0, 3, 2, 1))                           # <mb|ej> = <mj|eb>
+        for z in range(2):
+            be.permute4(self.WA[z], self.Xje[z].permute(2, 0, 1, 3))
+            be.permute4(self.WB[z], self.Xje[z].permute(0, 2, 3, 1))
+            be.permute4(self.WC[z], self.Xej[z].permute(3, 0, 1, 2))
+            be.permute4(self.WD[z], self.Xej[z].permute(0, 3, 2, 1))
+        self.Zmn.zero_()
+        self.Zmd.zero_()
+        W, A2 = c["W3"], c["A2"]
+        for l in range(o):
+            for m in range(o):
+                cc3.launch_w(l, m, real_time)
+                for z in range(2):
+                    be.t3_density_combine(W[z], W[z], o, 0, l, m, eps, o, v, dict(M=A2[z]))
+                run_planes(self._setup_for(l, m), be)
+
+    def _setup_for(self, l, m):
+        key = (l, m)
+        if key not in self._setup_plans:
+            e = self.eng
+            T = dict(T=self.P.cplx["A2"], gl=e.blk["oovv"][:, l], Ll=e.Loovv[:, l], Zmn_m=self.Zmn[:, m], Zmd_m=self.Zmd[:, m])
+            self._setup_plans[key] = compile_planes(self.rl._T3_SETUP, T, ("gl", "Ll"), e.dcode)
+        return self._setup_plans[key]
+
+    def _pair_plans(self, i, j):
+        key = (i, j)
+        if key not in self._pair:
+            e, c = self.eng, self.P.cplx
+            T = dict(X=self.X, P1=self.P1, P2=self.P2, t2=c["t2"], t2j=c["t2"][:, j], Zbi=self.Zb[:, i], Zmaij=self.Zma[:, i, j],
+                     Zd1ij=self.Zd1[:, i, j], Y2ij=self.Y2[:, i, j], Y2i=self.Y2[:, i], Wv=c["Wv"], Woj=c["Wo"][:, j],
+                     A1=c["A1"], l2ij=c["l2"][:, i, j], Znf=self.Znf)
+            con = compile_planes(self.rl._L3_CONSUMERS, T, (), e.dcode)
+            znf = compile_planes(("Znf[nf] += A1[ndef]*l2ij[de]",), T, (), e.dcode)
+            self._pair[key] = (con, znf)
+        return self._pair[key]
+
+    def contribute(self, real_time=False):
+        """rl1 += Y1, rl2 (unsymmetrised) += Y2 for the l1 / l2 planes (cclambda.py:160-235)."""
+        e, be, cc3, c = self.eng, self.be, self.cc3, self.P.cplx
+        o, v = e.no, e.nv
+        self.setup(real_time)
+        eps = self.eps
+        for z in range(2):
+            be.permute4(self.l2T[z], c["l2"][z].permute(0, 1, 3, 2))
+        for t in (self.Znf, self.Zb, self.Zma, self.Zd1, self.Y2, self.Y1w):
+            t.zero_()
+        W, A1 = c["W3"], c["A1"]
+        for i in range(o):
+            for j in range(o):
+                con, znf = self._pair_plans(i, j)
+                cc3.launch_w(i, j, real_time)                   # t3 of (l, m, n) = (i, j, batch): Znf
+                for z in range(2):
+                    be.t3_density_combine(W[z], W[z], o, 0, i, j, eps, o, v, dict(A1=A1[z]))
+                run_planes(znf, be)
+                self.L3.zero_()                                 # l3 of (k, i, j), k = batch
+                self.l3.launch_pair(i, j, o)
+                for z in range(2):
+                    be.t3_density_combine(self.L3[z], self.L3[z], o, 0, i, j, eps, o, v, dict(M=self.X[z]))
+                    be.permute4(self.P1[z], self.X[z].permute(0, 3, 1, 2))
+                    be.permute4(self.P2[z], self.X[z].permute(0, 2, 1, 3))
+                run_planes(con, be)
+        run_planes(self.y1, be)
+        c["rl1"].add_(self.Y1w)
+        c["rl2"].add_(self.Y2)

@@ -310,11 +310,11 @@ class ComplexResiduals(object):
         self.lam_prog = {name: P.compile(ls[name], ren) for name in ("G", "r_L1", "r_L2")}
         self._lam = True
 
-    def lambda_residuals(self, F, t1, t2, l1, l2):
+    def lambda_residuals(self, F, t1, t2, l1, l2, real_time=False):
         """Complex L1 / L2 residuals with HBAR rebuilt from (F, t1, t2) (pycc/cclambda.py:281-323)."""
         P, be, eng = self.P, self.be, self.eng
-        if eng.model == 'CC3':
-            raise ValueError("complex-amplitude Lambda residuals: models CCD, CC2, CCSD (the CC3 Lambda equations take real amplitudes)")
+        if eng.model == 'CC3' and self.sharded:
+            raise ValueError("complex-amplitude CC3 Lambda residuals run on one GPU")
         if self.sharded and eng.ovvv_full is None:
             raise ValueError("complex-amplitude Lambda residuals need the full <mb|ef> block on every rank "
                              "(ccwfn(..., full_ovvv=True))")
@@ -341,6 +341,12 @@ class ComplexResiduals(object):
         if eng.model != 'CCD':
             P.run(self.lam_prog["r_L1"])
         P.run(self.lam_prog["r_L2"])
+        if eng.model == 'CC3':       # Y1, Y2 of the triples (cclambda.py:323-440), before rl2 + rl2^T
+            if getattr(self, "cc3lam", None) is None:
+                from .complex_cc3 import ComplexCC3Lambda
+                self.cc3lam = ComplexCC3Lambda(self)
+            P.run(self.progs["Fme"])         # Fov = build_Fme(F, t1) of this call
+            self.cc3lam.contribute(real_time)
         if self.sharded:
             eng.comm.allreduce_(P.cplx["rl1"])
             eng.comm.allreduce_(P.cplx["rl2"])

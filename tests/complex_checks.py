@@ -85,3 +85,23 @@ def check_complex_cc3_residuals(make_wfn, name, tol=1e-12):
     c1, c2 = w.residuals(g.F.astype(complex), g["gen_t1"].astype(complex), g["gen_t2"].astype(complex))
     assert np.abs(host(c2).imag).max() == 0.0 and np.abs(host(c2).real - host(q2)).max() < tol
     assert np.abs(host(c1).real - host(q1)).max() < tol
+
+
+def check_complex_cc3_lambda_residuals(make_wfn, name, tol=1e-12):
+    """cclambda.residuals for model CC3 with complex t and l (the propagator's second call, pycc/rt/rtcc.py:132)
+    against the reference's own vectors (tests/golden/make_golden_rtcc3_complex_lambda.py), for a plain and a
+    real_time wave function (the latter subtracts t3_pert_ijk inside the t3 loops), two Fock matrices each."""
+    g = Golden(name)
+    z = np.load(os.path.join(GOLDEN_DIR, "rtcc3_complex", name + "_lambda.npz"))
+    for tag, rt in (("plain", False), ("rt", True)):
+        with contextlib.redirect_stdout(io.StringIO()):
+            w = make_wfn(g, "CC3")
+            w.real_time = rt
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+        for ftag in ("field", "mixed"):
+            r1, r2 = lam.residuals(z["F_" + ftag], z["t1"], z["t2"], z["l1"], z["l2"])
+            assert r1.is_complex() and r2.is_complex()
+            assert np.abs(host(r1) - z["%s_%s_r1" % (ftag, tag)]).max() < tol, (tag, ftag)
+            assert np.abs(host(r2) - z["%s_%s_r2" % (ftag, tag)]).max() < tol, (tag, ftag)
+    assert np.abs(z["field_rt_r1"] - z["field_plain_r1"]).max() > 1e-7          # the field term is there

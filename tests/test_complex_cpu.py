@@ -23,6 +23,11 @@ def test_complex_cc3_residuals(name):
     cc.check_complex_cc3_residuals(make_wfn, name)
 
 
+@pytest.mark.parametrize("name", cc.CC3_CASES)
+def test_complex_cc3_lambda_residuals(name):
+    cc.check_complex_cc3_lambda_residuals(make_wfn, name)
+
+
 def test_expand_rules():
     cplx = lambda n: n in ("C", "A", "B", "D")
     acts = expand("C[ij] = D[ij] + 0.5*A[ik]*R[jk] - A[ik]*B[jk] + S[ij]", cplx)
