@@ -202,16 +202,13 @@ def run_planes(prog, be):
 class ComplexCC3Lambda(object):
     """Y1 / Y2 of the CC3 triples in ``cclambda.residuals`` (pycc/cclambda.py:323-440: the t3 and l3 loops of the
     Lambda equations rebuilt for the call's own amplitudes) with complex t and l: the statements of
-    cc3_lambda_engine.py plane by plane; ``pccb_t3_density_combine`` (linear, real denominators) per plane.
-    One GPU."""
+    cc3_lambda_engine.py plane by plane; ``pccb_t3_density_combine`` (linear, real denominators) per plane."""
 
     def __init__(self, cr):
         from . import cc3_lambda_engine as rl
         self.rl = rl
         self.cr, self.eng, self.be, self.P = cr, cr.eng, cr.be, cr.P
         eng, P = self.eng, self.P
-        if cr.sharded:
-            raise ValueError("complex-amplitude CC3 Lambda residuals run on one GPU")
         if cr.cc3 is None:
             cr.cc3 = ComplexCC3(cr)
         self.cc3 = cr.cc3
@@ -226,14 +223,19 @@ class ComplexCC3Lambda(object):
         self.Xje, self.Xej = E(o, v, o, v), E(o, v, v, o)
         self.Q2, self.Q3 = E(o, o, o, v), E(o, o, o, v)
         self.WA, self.WB, self.WC, self.WD = E(o, o, v, v), E(o, o, v, v), E(o, o, v, v), E(o, o, v, v)
-        self.Wab = E(v, v, v, v)
+        # several GPUs, as in cc3_lambda_engine: the dressed <ab|ef> holds the rank's rows a only; the occupied pairs of
+        # both loops are dealt round-robin; every Z intermediate and Y2 is a sum over pairs (one allreduce each), and the
+        # one term that reads the dressed <ab|ef> gives a partial Y1 (allreduce).  One GPU: the same code path.
+        vlo, vl = eng.vlo, eng.vl
+        self.Wab = E(vl, v, v, v)
         self.Y1w, self.Y2 = E(o, v), E(o, o, v, v)
         c, b = P.cplx, eng.blk
         T = dict(ovvv=eng.ovvv_full, ooov=b["ooov"], oovv=b["oovv"], t1=c["t1"], T11=c["T11"], Xje=self.Xje, Xej=self.Xej,
-                 Q2=self.Q2, Q3=self.Q3, Wab=self.Wab, t1A=c["t1"], ovvvA=eng.ovvv_full, T11A=c["T11"])
+                 Q2=self.Q2, Q3=self.Q3, Wab=self.Wab, t1A=c["t1"].narrow(2, vlo, vl),
+                 ovvvA=eng.ovvv_full.narrow(1, vlo, vl), T11A=c["T11"].narrow(3, vlo, vl))
         self.dressed = compile_planes(rl._DRESSED, T, ("ovvv", "ooov", "oovv", "ovvvA"), eng.dcode)
         T = dict(r1=c["rl1"], l2=c["l2"], Zmd=self.Zmd, Loovv=eng.Loovv, Znf=self.Znf, Zmn=self.Zmn, Zb=self.Zb,
-                 Wab=self.Wab, Y1w=self.Y1w, ZbD=self.Zb, Woooo=c["Wmnij3"], Zma=self.Zma, Zd1=self.Zd1,
+                 Wab=self.Wab, Y1w=self.Y1w, ZbD=self.Zb.narrow(3, vlo, vl), Woooo=c["Wmnij3"], Zma=self.Zma, Zd1=self.Zd1,
                  WA=self.WA, WB=self.WB, WC=self.WC, WD=self.WD)
         self.y1 = compile_planes(rl._Y1, T, ("Loovv",), eng.dcode)
         # l3 of one triplet: the spin-adapted integrals L[x,y] are the only real operands
@@ -300,12 +302,18 @@ class ComplexCC3Lambda(object):
         self.Zmn.zero_()
         self.Zmd.zero_()
         W, A2 = c["W3"], c["A2"]
-        for l in range(o):
-            for m in range(o):
-                cc3.launch_w(l, m, real_time)
-                for z in range(2):
-                    be.t3_density_combine(W[z], W[z], o, 0, l, m, eps, o, v, dict(M=A2[z]))
-                run_planes(self._setup_for(l, m), be)
+        for (l, m) in self.my_pairs():
+            cc3.launch_w(l, m, real_time)
+            for z in range(2):
+                be.t3_density_combine(W[z], W[z], o, 0, l, m, eps, o, v, dict(M=A2[z]))
+            run_planes(self._setup_for(l, m), be)
+        if e.comm.world > 1:
+            e.comm.allreduce_(self.Zmn)
+            e.comm.allreduce_(self.Zmd)
+
+    def my_pairs(self):
+        o, cm = self.eng.no, self.eng.comm
+        return [(i, j) for i in range(o) for j in range(o)][cm.rank::cm.world]
 
     def _setup_for(self, l, m):
         key = (l, m)
@@ -338,20 +346,24 @@ class ComplexCC3Lambda(object):
         for t in (self.Znf, self.Zb, self.Zma, self.Zd1, self.Y2, self.Y1w):
             t.zero_()
         W, A1 = c["W3"], c["A1"]
-        for i in range(o):
-            for j in range(o):
-                con, znf = self._pair_plans(i, j)
-                cc3.launch_w(i, j, real_time)                   # t3 of (l, m, n) = (i, j, batch): Znf
-                for z in range(2):
-                    be.t3_density_combine(W[z], W[z], o, 0, i, j, eps, o, v, dict(A1=A1[z]))
-                run_planes(znf, be)
-                self.L3.zero_()                                 # l3 of (k, i, j), k = batch
-                self.l3.launch_pair(i, j, o)
-                for z in range(2):
-                    be.t3_density_combine(self.L3[z], self.L3[z], o, 0, i, j, eps, o, v, dict(M=self.X[z]))
-                    be.permute4(self.P1[z], self.X[z].permute(0, 3, 1, 2))
-                    be.permute4(self.P2[z], self.X[z].permute(0, 2, 1, 3))
-                run_planes(con, be)
-        run_planes(self.y1, be)
+        for (i, j) in self.my_pairs():
+            con, znf = self._pair_plans(i, j)
+            cc3.launch_w(i, j, real_time)                   # t3 of (l, m, n) = (i, j, batch): Znf
+            for z in range(2):
+                be.t3_density_combine(W[z], W[z], o, 0, i, j, eps, o, v, dict(A1=A1[z]))
+            run_planes(znf, be)
+            self.L3.zero_()                                 # l3 of (k, i, j), k = batch
+            self.l3.launch_pair(i, j, o)
+            for z in range(2):
+                be.t3_density_combine(self.L3[z], self.L3[z], o, 0, i, j, eps, o, v, dict(M=self.X[z]))
+                be.permute4(self.P1[z], self.X[z].permute(0, 3, 1, 2))
+                be.permute4(self.P2[z], self.X[z].permute(0, 2, 1, 3))
+            run_planes(con, be)
+        if e.comm.world > 1:
+            for t in (self.Znf, self.Zb, self.Zma, self.Zd1, self.Y2):
+                e.comm.allreduce_(t)
+        run_planes(self.y1, be)          # (rl1 holds the summed builders' part by now: complex_engine.lambda_residuals)
+        if e.comm.world > 1:
+            e.comm.allreduce_(self.Y1w)
         c["rl1"].add_(self.Y1w)
         c["rl2"].add_(self.Y2)

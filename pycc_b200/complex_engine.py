@@ -313,8 +313,6 @@ class ComplexResiduals(object):
     def lambda_residuals(self, F, t1, t2, l1, l2, real_time=False):
         """Complex L1 / L2 residuals with HBAR rebuilt from (F, t1, t2) (pycc/cclambda.py:281-323)."""
         P, be, eng = self.P, self.be, self.eng
-        if eng.model == 'CC3' and self.sharded:
-            raise ValueError("complex-amplitude CC3 Lambda residuals run on one GPU")
         if self.sharded and eng.ovvv_full is None:
             raise ValueError("complex-amplitude Lambda residuals need the full <mb|ef> block on every rank "
                              "(ccwfn(..., full_ovvv=True))")
@@ -346,8 +344,11 @@ class ComplexResiduals(object):
                 from .complex_cc3 import ComplexCC3Lambda
                 self.cc3lam = ComplexCC3Lambda(self)
             P.run(self.progs["Fme"])         # Fov = build_Fme(F, t1) of this call
+            if self.sharded:                 # the builders' partial planes first: the triples terms are added in full
+                eng.comm.allreduce_(P.cplx["rl1"])
+                eng.comm.allreduce_(P.cplx["rl2"])
             self.cc3lam.contribute(real_time)
-        if self.sharded:
+        elif self.sharded:
             eng.comm.allreduce_(P.cplx["rl1"])
             eng.comm.allreduce_(P.cplx["rl2"])
         for z in range(2):

@@ -370,6 +370,17 @@ def _complex_cc3_worker(rank, world, port, name, q):
                     r1, r2 = w.residuals(z["F_" + tag], z["t1"], z["t2"], real_time=True)
                     out["d1_%s_%d" % (tag, call)] = float(np.abs(r1.numpy() - z[tag + "_r1"]).max())
                     out["d2_%s_%d" % (tag, call)] = float(np.abs(r2.numpy() - z[tag + "_r2"]).max())
+            # the Lambda residuals of a real-time wave function: pairs of both triples loops dealt over the ranks, the
+            # dressed <ab|ef> by rows
+            zl = np.load(os.path.join(GOLDEN_DIR, "rtcc3_complex", name + "_lambda.npz"))
+            w.real_time = True
+            hb = pycc_b200.cchbar(w)
+            lam = pycc_b200.cclambda(w, hb)
+            for call in range(2):
+                for tag in ("field", "mixed"):
+                    q1, q2 = lam.residuals(zl["F_" + tag], zl["t1"], zl["t2"], zl["l1"], zl["l2"])
+                    out["dl1_%s_%d" % (tag, call)] = float(np.abs(q1.numpy() - zl[tag + "_rt_r1"]).max())
+                    out["dl2_%s_%d" % (tag, call)] = float(np.abs(q2.numpy() - zl[tag + "_rt_r2"]).max())
         q.put(out)
     except Exception:
         import traceback
